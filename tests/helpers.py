@@ -1,0 +1,60 @@
+"""Shared test plumbing: fixture loading, spec construction, comparison with stated tolerances."""
+import os
+
+import numpy as np
+import torch
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+ENV_CASES = {"go2_n64": ("go2", 64, True), "go2_n64_signed": ("go2", 64, False), "h1_n40": ("h1", 40, False),
+             "g1_n64": ("g1", 64, True), "h1_2_n33": ("h1_2", 33, False)}
+
+# north_star tolerances: masks / indices bit-exact; obs, rewards, torques 1e-5 relative (fp32)
+RTOL = 1e-5
+ATOL = 2e-6     # absolute floor for values near zero (sums of O(1) terms in fp32)
+EXACT = {"reset_buf", "time_out_buf", "episode_length_buf", "last_contacts", "extras_time_outs"}
+
+
+def load_case(name):
+    z = np.load(os.path.join(GOLDEN, f"env_{name}.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def make_cfg(task, num_envs, only_positive):
+    from unitree_rl_gym_b200.legged_gym.envs import robot_configs as rc
+    cls = {"go2": rc.GO2RoughCfg, "h1": rc.H1RoughCfg, "g1": rc.G1RoughCfg, "h1_2": rc.H1_2RoughCfg}[task]
+    cfg = cls()
+    cfg.env.num_envs = num_envs
+    cfg.rewards.only_positive_rewards = only_positive
+    return cfg
+
+
+def make_spec(case):
+    from unitree_rl_gym_b200.envspec import build_env_spec
+    from unitree_rl_gym_b200.robots import ROBOTS
+    task, n, pos = ENV_CASES[case]
+    cfg = make_cfg(task, n, pos)
+    return build_env_spec(task, cfg, ROBOTS[task], cfg.sim.dt, seed=1)
+
+
+def frames_of(fx):
+    return {k.split("/", 1)[1]: torch.from_numpy(v) for k, v in fx.items() if k.startswith("frames/")}
+
+
+def compare(name, got, want, where=""):
+    got = np.asarray(got)
+    want = np.asarray(want)
+    assert got.shape == want.shape, f"{where}{name}: shape {got.shape} != {want.shape}"
+    if name in EXACT or want.dtype == np.bool_ or np.issubdtype(want.dtype, np.integer):
+        assert np.array_equal(got.astype(want.dtype), want), f"{where}{name}: mask/index mismatch at " \
+            f"{np.argwhere(got.astype(want.dtype) != want)[:5].tolist()}"
+    else:
+        err = np.abs(got.astype(np.float64) - want.astype(np.float64))
+        tol = ATOL + RTOL * np.abs(want.astype(np.float64))
+        bad = err > tol
+        assert not bad.any(), f"{where}{name}: {bad.sum()} of {bad.size} beyond rtol={RTOL} " \
+            f"(max err {err.max():.3e} at {np.unravel_index(err.argmax(), err.shape)}, want {want.flat[err.argmax()]})"
+
+
+def snapshot_keys(fx, prefix):
+    p = prefix + "/"
+    return [k[len(p):] for k in fx if k.startswith(p)]

@@ -1,0 +1,80 @@
+"""The oracle's env port (oracle/env_port.py) against fixtures produced by the unmodified
+reference classes (tests/golden/gen_golden.py).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+from oracle.env_port import EnvPort
+
+
+def port_snapshot(p):
+    out = {"obs_buf": p.obs_buf, "rew_buf": p.rew_buf, "reset_buf": p.reset_buf, "time_out_buf": p.time_out_buf,
+           "episode_length_buf": p.episode_length_buf, "torques": p.torques, "commands": p.commands,
+           "actions": p.actions, "last_actions": p.last_actions, "last_dof_vel": p.last_dof_vel,
+           "last_root_vel": p.last_root_vel, "feet_air_time": p.feet_air_time, "last_contacts": p.last_contacts,
+           "rpy": p.rpy, "base_lin_vel": p.base_lin_vel, "base_ang_vel": p.base_ang_vel,
+           "projected_gravity": p.projected_gravity, "root_states": p.root_states, "dof_state": p.dof_state}
+    if p.privileged_obs_buf is not None:
+        out["privileged_obs_buf"] = p.privileged_obs_buf
+    for k, v in p.episode_sums.items():
+        out["episode_sums/" + k] = v
+    for k, v in p.extras.get("episode", {}).items():
+        out["extras_episode/" + k] = v.reshape(1)
+    if "time_outs" in p.extras:
+        out["extras_time_outs"] = p.extras["time_outs"]
+    return {k: v.numpy() for k, v in out.items()}
+
+
+def run_port(case, fx):
+    spec = H.make_spec(case)
+    frames = H.frames_of(fx)
+    port = EnvPort(spec)
+    calls = {"n": 0}
+    P = frames["root"].shape[0]
+
+    def physics(sub):
+        if sub is not None:
+            calls["n"] += 1
+        f = ((calls["n"] - 1) // spec.decimation) % P
+        port.load_frame(frames, f, sub if sub is not None else None)
+    return spec, port, physics
+
+
+@pytest.mark.parametrize("case", list(H.ENV_CASES))
+def test_constants_match_reference(case):
+    fx = H.load_case(case)
+    s = H.make_spec(case)
+    np.testing.assert_array_equal(s.p_gains, fx["const/p_gains"])
+    np.testing.assert_array_equal(s.d_gains, fx["const/d_gains"])
+    np.testing.assert_array_equal(s.default_dof_pos.reshape(1, -1), fx["const/default_dof_pos"])
+    np.testing.assert_array_equal(s.torque_limits, fx["const/torque_limits"])
+    np.testing.assert_array_equal(s.dof_vel_limits, fx["const/dof_vel_limits"])
+    np.testing.assert_array_equal(s.dof_pos_limits, fx["const/dof_pos_limits"])
+    np.testing.assert_array_equal(s.noise_scale_vec, fx["const/noise_scale_vec"])
+    assert s.feet_idx == fx["const/feet_indices"].tolist()
+    assert s.pen_idx == fx["const/penalised_contact_indices"].tolist()
+    assert s.term_idx == fx["const/termination_contact_indices"].tolist()
+    np.testing.assert_array_equal(s.env_origins, fx["const/env_origins"])
+    np.testing.assert_array_equal(s.base_init_state, fx["const/base_init_state"])
+    assert s.reward_names == fx["const/reward_names"].tolist()
+    np.testing.assert_array_equal(np.array(s.reward_scales), fx["const/reward_scales"])
+    dt, max_len, push, resample = fx["const/scalars"][:4]
+    assert (s.dt, s.max_episode_length, s.push_interval, s.resample_steps) == (dt, max_len, int(push), int(resample))
+
+
+@pytest.mark.parametrize("case", list(H.ENV_CASES))
+def test_env_port_matches_reference_fixture(case):
+    fx = H.load_case(case)
+    spec, port, physics = run_port(case, fx)
+    port.reset(physics)
+    snap = port_snapshot(port)
+    for k in H.snapshot_keys(fx, "reset"):
+        H.compare(k, snap[k], fx["reset/" + k], "reset/")
+    port.episode_length_buf = torch.from_numpy(fx["planted_episode_length"]).clone()
+    steps = int(fx["const/scalars"][4])
+    for t in range(steps):
+        port.step(torch.from_numpy(fx[f"actions/{t}"]), physics)
+        snap = port_snapshot(port)
+        for k in H.snapshot_keys(fx, f"step{t}"):
+            H.compare(k, snap[k], fx[f"step{t}/{k}"], f"step{t}/")
