@@ -1,0 +1,158 @@
+/* urlg_b200.h — C ABI of the B200-native hot path of unitree-rl-gym.
+ *
+ * The reference has no FFI: its seams are Python duck-typed APIs above (LeggedRobot /
+ * OnPolicyRunner / PPO / ActorCritic[Recurrent] / RolloutStorage) and the Isaac Gym tensor
+ * API below.  This ABI sits between them; each entry point cites the reference code
+ * (file:line under /root/reference, or [UPSTREAM rsl_rl v1.0.2] where the submodule is
+ * absent) that it replaces.  The reference-side binding is the ctypes stub shown in
+ * INTEGRATION.md.
+ *
+ * Conventions
+ *  - plain C types only; every large buffer is BORROWED device memory (allocated by the
+ *    caller, e.g. PyTorch); the library owns only its handle structs and small scratch.
+ *  - every call enqueues on the given cudaStream_t (passed as void*), never synchronises,
+ *    never reads device memory on the host: a whole rollout is CUDA-graph capturable.
+ *  - return 0 on success, negative urlg_status otherwise; urlg_last_error() has the text.
+ *  - "step" arguments come as (const int64_t* base_dev, int64_t offset): the effective
+ *    value is (*base_dev if non-NULL else 0) + offset, so a captured graph can advance.
+ *  - bool tensors are uint8 0/1 (torch.bool layout); quaternions are xyzw.
+ */
+#ifndef URLG_B200_H
+#define URLG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define URLG_ABI_VERSION 1
+#define URLG_MAX_DOF 16
+#define URLG_MAX_IDX 16
+#define URLG_MAX_TERMS 32
+#define URLG_MAX_OBS 128
+
+typedef enum {
+  URLG_OK = 0,
+  URLG_EINVAL = -1,   /* bad argument / unsupported shape */
+  URLG_ECUDA = -2,    /* a CUDA runtime call failed */
+  URLG_ENOMEM = -3
+} urlg_status;
+
+/* Reward-term ids: alphabetical = the reference's execution order (helpers.py:15 dir()). */
+typedef enum {
+  URLG_T_ACTION_RATE = 0, URLG_T_ALIVE, URLG_T_ANG_VEL_XY, URLG_T_BASE_HEIGHT, URLG_T_COLLISION,
+  URLG_T_CONTACT, URLG_T_CONTACT_NO_VEL, URLG_T_DOF_ACC, URLG_T_DOF_POS_LIMITS, URLG_T_DOF_VEL,
+  URLG_T_DOF_VEL_LIMITS, URLG_T_FEET_AIR_TIME, URLG_T_FEET_CONTACT_FORCES, URLG_T_FEET_SWING_HEIGHT,
+  URLG_T_HIP_POS, URLG_T_LIN_VEL_Z, URLG_T_ORIENTATION, URLG_T_STAND_STILL, URLG_T_STUMBLE,
+  URLG_T_TORQUE_LIMITS, URLG_T_TORQUES, URLG_T_TRACKING_ANG_VEL, URLG_T_TRACKING_LIN_VEL,
+  URLG_T_COUNT
+} urlg_reward_term;
+
+/* Init-time constants of one env instance: what LeggedRobot._parse_cfg / _init_buffers /
+ * _process_dof_props / _prepare_reward_function / _get_noise_scale_vec compute once
+ * (legged_robot.py:52-67, 69-186, 442-470, 817-840, 188-219; h1_env.py:10-32). */
+typedef struct urlg_env_desc {
+  int32_t family;            /* 0 = LeggedRobot obs layout, 1 = H1-family (gait phase + privileged obs) */
+  int32_t num_envs, num_dof, num_bodies, num_obs, num_priv;
+  int32_t num_feet, num_pen, num_term_bodies, num_hip;
+  int32_t decimation, control_type;          /* control_type: 'P','V','T' as ASCII */
+  int32_t resample_steps, push_interval;
+  int32_t push_robots, heading_command, add_noise, only_positive, has_termination, send_timeouts;
+  int32_t num_terms;                          /* active terms, in order */
+  int32_t num_sums;                           /* episode_sums rows (num_terms [+1 for termination]) */
+  int32_t termination_sum_row;                /* row of 'termination' in episode_sums, or -1 */
+  int32_t term_ids[URLG_MAX_TERMS];
+  int32_t term_sum_row[URLG_MAX_TERMS];       /* episode_sums row of each active term */
+  float term_scales[URLG_MAX_TERMS];          /* scale * dt */
+  float termination_scale;
+  float dt, sim_dt, max_episode_length, max_episode_length_s, max_push_vel;
+  float action_scale, clip_actions, clip_obs;
+  float tracking_sigma, base_height_target, soft_dof_vel_limit, soft_torque_limit, max_contact_force;
+  float obs_scale_lin_vel, obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel;
+  float cmd_x[2], cmd_y[2], cmd_yaw[2], cmd_heading[2];
+  float p_gains[URLG_MAX_DOF], d_gains[URLG_MAX_DOF], default_dof_pos[URLG_MAX_DOF];
+  float torque_limits[URLG_MAX_DOF], dof_vel_limits[URLG_MAX_DOF];
+  float dof_pos_lo[URLG_MAX_DOF], dof_pos_hi[URLG_MAX_DOF];
+  int32_t feet_idx[URLG_MAX_IDX], pen_idx[URLG_MAX_IDX], term_idx[URLG_MAX_IDX], hip_idx[URLG_MAX_IDX];
+  float noise_scale_vec[URLG_MAX_OBS];
+  float base_init_state[13];
+  uint32_t seed_lo, seed_hi;
+  int64_t env_offset;                         /* global id of local env 0 (multi-GPU shard) */
+} urlg_env_desc;
+
+/* Device pointers of every public tensor of the env (legged_robot.py:104-186, base_task.py:41-49,
+ * h1_env.py:37-42).  All float32 unless noted; shapes in comments; N = num_envs. */
+typedef struct urlg_env_buffers {
+  float* root_states;              /* [N,13]   physics seam */
+  float* dof_state;                /* [N*A,2]  physics seam, interleaved (pos,vel) */
+  const float* contact_forces;     /* [N,B,3]  physics seam */
+  const float* rigid_body_states;  /* [N,B,13] physics seam, H1 family only (else NULL) */
+  float* obs_buf[2];               /* [N,num_obs] ping-pong (reference re-binds obs_buf every step) */
+  float* priv_obs_buf[2];          /* [N,num_priv] or NULL */
+  float* rew_buf;                  /* [N] */
+  uint8_t* reset_buf;              /* [N] bool */
+  uint8_t* time_out_buf;           /* [N] bool */
+  int64_t* episode_length_buf;     /* [N] int64 */
+  float* torques;                  /* [N,A] */
+  float* actions;                  /* [N,A] */
+  float* last_actions;             /* [N,A] */
+  float* last_dof_vel;             /* [N,A] */
+  float* last_root_vel;            /* [N,6] */
+  float* commands;                 /* [N,4] */
+  float* feet_air_time;            /* [N,F] */
+  uint8_t* last_contacts;          /* [N,F] bool */
+  float* rpy;                      /* [N,3] */
+  float* base_lin_vel;             /* [N,3] */
+  float* base_ang_vel;             /* [N,3] */
+  float* projected_gravity;        /* [N,3] */
+  float* phase;                    /* [N]   H1 family (else NULL) */
+  float* leg_phase;                /* [N,2] H1 family (else NULL) */
+  float* episode_sums;             /* [num_sums,N] one row per dict entry of episode_sums */
+  const float* env_origins;        /* [N,3] */
+  float* extras_episode;           /* [num_sums] extras["episode"]["rew_*"], refreshed only when >=1 env reset */
+  uint8_t* extras_time_outs;       /* [N] bool, extras["time_outs"], same staleness rule (legged_robot.py:742,767) */
+  int32_t* reset_ids;              /* [N] compacted ids of envs reset this step (for set_*_tensor_indexed), may be NULL */
+  int32_t* reset_count;            /* [1] */
+  const float* rng_override;       /* optional [N,num_rng_slots] uniforms replacing Philox (debug), else NULL */
+} urlg_env_buffers;
+
+typedef struct urlg_env urlg_env;
+
+int urlg_version(void);
+const char* urlg_last_error(void);
+
+/* ---- env half: replaces LeggedRobot.step minus PhysX (legged_robot.py:615-811) ---- */
+int urlg_env_create(const urlg_env_desc* desc, urlg_env** out);
+int urlg_env_bind(urlg_env* env, const urlg_env_buffers* bufs);
+void urlg_env_destroy(urlg_env* env);
+int urlg_env_num_rng_slots(const urlg_env* env);
+
+/* K1: _compute_torques (legged_robot.py:649-671).  If raw_actions != NULL this is the first
+ * substep: actions = clip(raw_actions, +-clip_actions) is stored first (legged_robot.py:623-624). */
+int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream);
+
+/* K2 (+finalize): post_physics_step (legged_robot.py:673-709) + the obs clips of step()
+ * (:643-646).  step = common_step_counter AFTER the increment at :682.  obs_slot selects the
+ * ping-pong buffer written. */
+int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot, void* stream);
+
+/* reset_idx(env_ids) called from outside step() (base_task.py:82-86, legged_robot.py:723-768).
+ * env_ids: device int64 [n], or NULL for "all envs". */
+int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const int64_t* step_base,
+                       int64_t step_offset, void* stream);
+
+/* ---- synthetic physics stand-in for the Isaac Gym tensor seam (bench / tests) ---- */
+/* dst[i] = pool[frame * elems + i], frame = ((*base + offset) / divisor) % num_frames * frames_per + ((*base+offset) % divisor) * sub
+ * i.e. refresh_*_tensor (legged_robot.py:639,678-679; h1_env.py:49) served from a device-resident pool. */
+int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num_frames, int64_t substeps,
+                       int per_substep, const int64_t* calls_base, int64_t calls_offset, void* stream);
+
+/* Philox4x32-10 uniforms exactly as the kernels draw them (for tests): out[N,num_slots]. */
+int urlg_philox_uniform(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
+                        uint32_t stream_id, int64_t env_offset, int64_t step, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* URLG_B200_H */

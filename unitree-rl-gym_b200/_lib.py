@@ -1,0 +1,135 @@
+"""ctypes binding of liburlg_b200.so (C ABI in include/urlg_b200.h).
+
+No CPU fallback: `lib()` raises if the shared library is missing, and every compute call needs
+CUDA tensors.  `build()` compiles the library in-tree with nvcc for sm_100a.
+"""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "liburlg_b200.so")
+
+MAX_DOF, MAX_IDX, MAX_TERMS, MAX_OBS = 16, 16, 32, 128
+
+
+class EnvDesc(C.Structure):
+    _fields_ = [
+        ("family", C.c_int32), ("num_envs", C.c_int32), ("num_dof", C.c_int32), ("num_bodies", C.c_int32),
+        ("num_obs", C.c_int32), ("num_priv", C.c_int32),
+        ("num_feet", C.c_int32), ("num_pen", C.c_int32), ("num_term_bodies", C.c_int32), ("num_hip", C.c_int32),
+        ("decimation", C.c_int32), ("control_type", C.c_int32),
+        ("resample_steps", C.c_int32), ("push_interval", C.c_int32),
+        ("push_robots", C.c_int32), ("heading_command", C.c_int32), ("add_noise", C.c_int32),
+        ("only_positive", C.c_int32), ("has_termination", C.c_int32), ("send_timeouts", C.c_int32),
+        ("num_terms", C.c_int32), ("num_sums", C.c_int32), ("termination_sum_row", C.c_int32),
+        ("term_ids", C.c_int32 * MAX_TERMS), ("term_sum_row", C.c_int32 * MAX_TERMS),
+        ("term_scales", C.c_float * MAX_TERMS), ("termination_scale", C.c_float),
+        ("dt", C.c_float), ("sim_dt", C.c_float), ("max_episode_length", C.c_float),
+        ("max_episode_length_s", C.c_float), ("max_push_vel", C.c_float),
+        ("action_scale", C.c_float), ("clip_actions", C.c_float), ("clip_obs", C.c_float),
+        ("tracking_sigma", C.c_float), ("base_height_target", C.c_float), ("soft_dof_vel_limit", C.c_float),
+        ("soft_torque_limit", C.c_float), ("max_contact_force", C.c_float),
+        ("obs_scale_lin_vel", C.c_float), ("obs_scale_ang_vel", C.c_float), ("obs_scale_dof_pos", C.c_float),
+        ("obs_scale_dof_vel", C.c_float),
+        ("cmd_x", C.c_float * 2), ("cmd_y", C.c_float * 2), ("cmd_yaw", C.c_float * 2), ("cmd_heading", C.c_float * 2),
+        ("p_gains", C.c_float * MAX_DOF), ("d_gains", C.c_float * MAX_DOF), ("default_dof_pos", C.c_float * MAX_DOF),
+        ("torque_limits", C.c_float * MAX_DOF), ("dof_vel_limits", C.c_float * MAX_DOF),
+        ("dof_pos_lo", C.c_float * MAX_DOF), ("dof_pos_hi", C.c_float * MAX_DOF),
+        ("feet_idx", C.c_int32 * MAX_IDX), ("pen_idx", C.c_int32 * MAX_IDX), ("term_idx", C.c_int32 * MAX_IDX),
+        ("hip_idx", C.c_int32 * MAX_IDX),
+        ("noise_scale_vec", C.c_float * MAX_OBS), ("base_init_state", C.c_float * 13),
+        ("seed_lo", C.c_uint32), ("seed_hi", C.c_uint32), ("env_offset", C.c_int64),
+    ]
+
+
+_P = C.c_void_p
+
+
+class EnvBuffers(C.Structure):
+    _fields_ = [
+        ("root_states", _P), ("dof_state", _P), ("contact_forces", _P), ("rigid_body_states", _P),
+        ("obs_buf", _P * 2), ("priv_obs_buf", _P * 2),
+        ("rew_buf", _P), ("reset_buf", _P), ("time_out_buf", _P), ("episode_length_buf", _P),
+        ("torques", _P), ("actions", _P), ("last_actions", _P), ("last_dof_vel", _P), ("last_root_vel", _P),
+        ("commands", _P), ("feet_air_time", _P), ("last_contacts", _P),
+        ("rpy", _P), ("base_lin_vel", _P), ("base_ang_vel", _P), ("projected_gravity", _P),
+        ("phase", _P), ("leg_phase", _P), ("episode_sums", _P), ("env_origins", _P),
+        ("extras_episode", _P), ("extras_time_outs", _P), ("reset_ids", _P), ("reset_count", _P),
+        ("rng_override", _P),
+    ]
+
+
+_lib = None
+
+# symbol -> (restype, argtypes); every symbol declared in include/urlg_b200.h appears here
+_I64P = C.c_void_p
+SIGNATURES = {
+    "urlg_version": (C.c_int, []),
+    "urlg_last_error": (C.c_char_p, []),
+    "urlg_env_create": (C.c_int, [C.POINTER(EnvDesc), C.POINTER(C.c_void_p)]),
+    "urlg_env_bind": (C.c_int, [C.c_void_p, C.POINTER(EnvBuffers)]),
+    "urlg_env_destroy": (None, [C.c_void_p]),
+    "urlg_env_num_rng_slots": (C.c_int, [C.c_void_p]),
+    "urlg_pd_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "urlg_post_physics": (C.c_int, [C.c_void_p, _I64P, C.c_int64, C.c_int, C.c_void_p]),
+    "urlg_env_reset_idx": (C.c_int, [C.c_void_p, _I64P, C.c_int64, _I64P, C.c_int64, C.c_void_p]),
+    "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
+                                     C.c_int64, C.c_void_p]),
+    "urlg_philox_uniform": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32, C.c_uint32,
+                                      C.c_int64, C.c_int64, C.c_void_p]),
+}
+
+
+def build(verbose=False):
+    """Compile csrc/*.cu -> csrc/liburlg_b200.so (nvcc, -gencode arch=compute_100a,code=sm_100a -lineinfo)."""
+    out = subprocess.run(["bash", os.path.join(CSRC, "build.sh")], capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("liburlg_b200 build failed:\n" + out.stdout + out.stderr)
+    if verbose:
+        print(out.stdout)
+    global _lib
+    _lib = None
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback for the hot path)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        if L.urlg_version() != 1:
+            raise RuntimeError("liburlg_b200 ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def check(code):
+    if code != 0:
+        msg = lib().urlg_last_error().decode()
+        if code == -1:
+            if msg.startswith("Unknown controller type"):
+                raise NameError(msg)       # same exception type as legged_robot.py:670
+            raise ValueError(msg)
+        raise RuntimeError(f"urlg error {code}: {msg}")
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (or None)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("urlg_b200: the hot path runs on CUDA tensors only (no CPU fallback)")
+    return C.c_void_p(t.data_ptr())
+
+
+def cur_stream():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,15 @@
+#!/bin/bash
+# Builds liburlg_b200.so in-tree for sm_100a (nvcc cross-compiles without a GPU).
+set -e
+cd "$(dirname "$0")"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+ARCH="-gencode arch=compute_100a,code=sm_100a"
+COMMON="-O3 -std=c++17 -lineinfo -Xcompiler -fPIC $ARCH"
+mkdir -p build
+# env kernels: no FMA contraction (expressions evaluate as written, like the reference's eager ops)
+$NVCC $COMMON -fmad=false -c env_kernels.cu -o build/env_kernels.o "$@"
+for f in storage_kernels policy_kernels; do
+  if [ -f $f.cu ]; then $NVCC $COMMON -c $f.cu -o build/$f.o "$@"; fi
+done
+$NVCC -shared $ARCH -o liburlg_b200.so build/*.o -lcudart
+echo "built $(pwd)/liburlg_b200.so"

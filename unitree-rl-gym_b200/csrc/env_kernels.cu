@@ -1,0 +1,737 @@
+// Env half of the hot path: LeggedRobot.step minus the PhysX call, as three kernels.
+//   K1  pd_torques_kernel      _compute_torques                 legged_robot.py:649-671 (+ :623-624)
+//   K2  post_physics_kernel    post_physics_step + obs clips    legged_robot.py:673-709, 643-646; h1_env.py:55-123
+//   K2b finalize_step_kernel   _push_robots' all-env rewrite, last_root_vel, extras publication
+//                                                               legged_robot.py:540-555, 709, 742-768
+// Data layout: one warp owns 32 consecutive envs.  Row tensors ([N,13] root, [N,2A] dof_state,
+// [N,3B] contacts, [N,A] action-like) are staged through shared memory with coalesced loads and
+// odd row strides (bank-conflict-free thread-per-env access); [N] and [N,<=4] tensors are accessed
+// directly (already coalesced).  Compiled with -fmad=false: expressions evaluate as written.
+#include "common.cuh"
+#include "philox.cuh"
+#include <new>
+
+namespace urlg {
+
+thread_local char g_err[512] = "";
+
+constexpr int kWarp = 32;
+constexpr int kMaxFeet = 8;
+constexpr float kPi = 3.14159274101257324f;      // float32(np.pi)
+constexpr float kTwoPi = 6.28318548202636719f;   // float32(2*np.pi)
+constexpr float kHalfPi = 1.57079637050628662f;  // float32(np.pi/2)
+
+struct StepScratch {   // library-owned device scratch (zeroed at create)
+  float ep_acc[3][URLG_MAX_TERMS + 1];   // [slot][row] sums over reset envs, [slot][URLG_MAX_TERMS] = count
+  int push_flag[3];
+  int reset_cnt[3];
+};
+
+}  // namespace urlg
+
+struct urlg_env {
+  urlg_env_desc desc;
+  urlg_env_buffers bufs;
+  urlg::StepScratch* scratch;
+  int bound;
+  int smem_bytes;
+};
+
+namespace urlg {
+
+// ---------------------------------------------------------------- shared-memory layout
+struct Layout {
+  int sRoot, sDof, sCon, sA, sRb, sObs, sPriv;
+  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, total;
+};
+
+__host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
+  Layout L;
+  const int A = c.num_dof;
+  L.sRoot = 13;
+  L.sDof = 2 * A + 1;
+  L.sCon = (3 * c.num_bodies) | 1;
+  L.sA = A | 1;
+  L.sRb = c.family == 1 ? ((c.num_feet * 13) | 1) : 0;
+  L.sObs = c.num_obs | 1;
+  L.sPriv = c.num_priv ? (c.num_priv | 1) : 0;
+  int o = 0;
+  L.oRoot = o; o += kWarp * L.sRoot;
+  L.oDof = o; o += kWarp * L.sDof;
+  L.oCon = o; o += kWarp * L.sCon;
+  L.oAct = o; o += kWarp * L.sA;
+  L.oLact = o; o += kWarp * L.sA;
+  L.oLdv = o; o += kWarp * L.sA;
+  L.oTq = o; o += kWarp * L.sA;
+  L.oRb = o; o += kWarp * L.sRb;
+  L.oObs = o; o += kWarp * L.sObs;
+  L.oPriv = o; o += kWarp * L.sPriv;
+  L.total = o;
+  return L;
+}
+
+// Coalesced copy of `nrows` contiguous rows of `w` words into padded shared rows.
+__device__ __forceinline__ void stage_in(float* __restrict__ s, const float* __restrict__ g, int w, int stride,
+                                         int nrows, int lane) {
+  const int total = nrows * w;
+  int r = 0, col = lane;
+  while (col >= w) { col -= w; ++r; }
+  for (int i = lane; i < total; i += kWarp) {
+    s[r * stride + col] = g[i];
+    col += kWarp;
+    while (col >= w) { col -= w; ++r; }
+  }
+}
+
+__device__ __forceinline__ void stage_out(float* __restrict__ g, const float* __restrict__ s, int w, int stride,
+                                          int nrows, int lane) {
+  const int total = nrows * w;
+  int r = 0, col = lane;
+  while (col >= w) { col -= w; ++r; }
+  for (int i = lane; i < total; i += kWarp) {
+    g[i] = s[r * stride + col];
+    col += kWarp;
+    while (col >= w) { col -= w; ++r; }
+  }
+}
+
+// torch.remainder for floats: fmod then fix the sign (ATen BinaryOpsKernel remainder_kernel).
+__device__ __forceinline__ float py_remainder(float a, float b) {
+  float m = fmodf(a, b);
+  if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m += b;
+  return m;
+}
+
+__device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
+
+// [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw
+__device__ __forceinline__ void rot_inv(float qx, float qy, float qz, float qw, float vx, float vy, float vz,
+                                        float& ox, float& oy, float& oz) {
+  const float s = 2.0f * (qw * qw) - 1.0f;
+  const float cx = qy * vz - qz * vy, cy = qz * vx - qx * vz, cz = qx * vy - qy * vx;
+  const float d = qx * vx + qy * vy + qz * vz;
+  ox = vx * s - cx * qw * 2.0f + qx * d * 2.0f;
+  oy = vy * s - cy * qw * 2.0f + qy * d * 2.0f;
+  oz = vz * s - cz * qw * 2.0f + qz * d * 2.0f;
+}
+
+// ---------------------------------------------------------------- K1: PD torques
+// One thread per (env, dof); actions / torques coalesced, dof_state read as float2.
+__global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__ urlg_env_desc c,
+                                                         const __grid_constant__ urlg_env_buffers b,
+                                                         const float* __restrict__ raw_actions) {
+  const int64_t total = (int64_t)c.num_envs * c.num_dof;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i % c.num_dof);
+    float a;
+    if (raw_actions) {
+      a = fminf(fmaxf(raw_actions[i], -c.clip_actions), c.clip_actions);
+      b.actions[i] = a;
+    } else {
+      a = b.actions[i];
+    }
+    const float2 pv = reinterpret_cast<const float2*>(b.dof_state)[i];
+    const float as = a * c.action_scale;
+    float tq;
+    if (c.control_type == 'P') {
+      tq = c.p_gains[j] * (as + c.default_dof_pos[j] - pv.x) - c.d_gains[j] * pv.y;
+    } else if (c.control_type == 'V') {
+      tq = c.p_gains[j] * (as - pv.y) - c.d_gains[j] * (pv.y - b.last_dof_vel[i]) / c.sim_dt;
+    } else {
+      tq = as;
+    }
+    const float lim = c.torque_limits[j];
+    b.torques[i] = fminf(fmaxf(tq, -lim), lim);
+  }
+}
+
+// ---------------------------------------------------------------- command resampling (E6)
+__device__ __forceinline__ void resample_commands(const urlg_env_desc& c, SlotRng& rng, int slot, float* cmd) {
+  cmd[0] = (c.cmd_x[1] - c.cmd_x[0]) * rng.uniform(slot) + c.cmd_x[0];
+  cmd[1] = (c.cmd_y[1] - c.cmd_y[0]) * rng.uniform(slot + 1) + c.cmd_y[0];
+  if (c.heading_command)
+    cmd[3] = (c.cmd_heading[1] - c.cmd_heading[0]) * rng.uniform(slot + 2) + c.cmd_heading[0];
+  else
+    cmd[2] = (c.cmd_yaw[1] - c.cmd_yaw[0]) * rng.uniform(slot + 2) + c.cmd_yaw[0];
+  const float keep = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) > 0.2f ? 1.0f : 0.0f;
+  cmd[0] *= keep;
+  cmd[1] *= keep;
+}
+
+}  // namespace urlg
+
+namespace urlg {
+
+// ---------------------------------------------------------------- K2: fused post-physics step
+__global__ void __launch_bounds__(kWarp) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+                                                             const __grid_constant__ urlg_env_buffers b,
+                                                             StepScratch* __restrict__ scratch,
+                                                             const int64_t* __restrict__ step_base, int64_t step_off,
+                                                             int obs_slot, int num_slots) {
+  extern __shared__ float sm[];
+  const Layout L = make_layout(c);
+  const int lane = threadIdx.x;
+  const int env0 = blockIdx.x * kWarp;
+  const int nrows = min(kWarp, c.num_envs - env0);
+  const int A = c.num_dof, B = c.num_bodies, F = c.num_feet, N = c.num_envs;
+  const int64_t step = eff_step(step_base, step_off);
+  const int acc = (int)(step & 1);
+
+  // ---- stage the row tensors of this warp's 32 envs (coalesced) ----
+  stage_in(sm + L.oRoot, b.root_states + (size_t)env0 * 13, 13, L.sRoot, nrows, lane);
+  stage_in(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, 2 * A, L.sDof, nrows, lane);
+  stage_in(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, 3 * B, L.sCon, nrows, lane);
+  stage_in(sm + L.oAct, b.actions + (size_t)env0 * A, A, L.sA, nrows, lane);
+  stage_in(sm + L.oLact, b.last_actions + (size_t)env0 * A, A, L.sA, nrows, lane);
+  stage_in(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, A, L.sA, nrows, lane);
+  stage_in(sm + L.oTq, b.torques + (size_t)env0 * A, A, L.sA, nrows, lane);
+  if (c.family == 1) {   // only the feet rows of rigid_body_states (h1_env.py:51-53)
+    const int w = F * 13;
+    for (int i = lane; i < nrows * w; i += kWarp) {
+      const int r = i / w, rem = i - r * w, f = rem / 13, k = rem - f * 13;
+      sm[L.oRb + r * L.sRb + rem] = b.rigid_body_states[((size_t)(env0 + r) * B + c.feet_idx[f]) * 13 + k];
+    }
+  }
+  __syncwarp();
+
+  bool push_due = false;
+  if (lane < nrows) {
+    const int e = env0 + lane;
+    float* root = sm + L.oRoot + lane * L.sRoot;
+    float* dof = sm + L.oDof + lane * L.sDof;
+    const float* con = sm + L.oCon + lane * L.sCon;
+    float* act = sm + L.oAct + lane * L.sA;
+    float* lact = sm + L.oLact + lane * L.sA;
+    float* ldv = sm + L.oLdv + lane * L.sA;
+    const float* tq = sm + L.oTq + lane * L.sA;
+    const float* rb = sm + L.oRb + lane * L.sRb;
+    float* obs = sm + L.oObs + lane * L.sObs;
+    float* priv = sm + L.oPriv + lane * L.sPriv;
+
+    SlotRng rng;
+    rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
+             b.rng_override ? b.rng_override + (size_t)e * num_slots : nullptr);
+
+    int64_t len = b.episode_length_buf[e] + 1;                       // :681
+    const float flen = (float)len;
+
+    // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
+    const float qx = root[3], qy = root[4], qz = root[5], qw = root[6];
+    const float roll = atan2f(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
+    const float sinp = 2.0f * (qw * qy - qz * qx);
+    const float pitch = fabsf(sinp) >= 1.0f ? copysignf(kHalfPi, sinp) : asinf(sinp);
+    const float yaw = atan2f(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
+    float lvx, lvy, lvz, avx, avy, avz, gx, gy, gz;
+    rot_inv(qx, qy, qz, qw, root[7], root[8], root[9], lvx, lvy, lvz);
+    rot_inv(qx, qy, qz, qw, root[10], root[11], root[12], avx, avy, avz);
+    rot_inv(qx, qy, qz, qw, 0.0f, 0.0f, -1.0f, gx, gy, gz);
+
+    // ---- E5 callback: gait phase (h1_env.py:58-63), resample (:511-512), heading (:513-516) ----
+    float phase = 0.0f, leg_phase[2] = {0.0f, 0.0f};
+    if (c.family == 1) {
+      phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
+      leg_phase[0] = phase;
+      leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
+    }
+    float cmd[4];
+    {
+      const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
+      cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
+    }
+    if (len % c.resample_steps == 0) resample_commands(c, rng, 0, cmd);
+    if (c.heading_command) {
+      // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
+      const float ty = qz * 2.0f, tz = -qy * 2.0f;
+      const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
+      const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
+      const float heading = atan2f(fy, fx);
+      float a = py_remainder(cmd[3] - heading, kTwoPi);
+      a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
+      cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
+    }
+
+    // ---- E7 termination :715-721 ----
+    bool reset = false;
+    for (int k = 0; k < c.num_term_bodies; ++k) {
+      const float* f3 = con + 3 * c.term_idx[k];
+      reset |= norm3(f3[0], f3[1], f3[2]) > 1.0f;
+    }
+    reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
+    const bool time_out = flen > c.max_episode_length;
+    reset |= time_out;
+
+    // ---- E8/E9 rewards, alphabetical, :775-787 ----
+    float air[kMaxFeet];
+    uint8_t lastc[kMaxFeet];
+    for (int f = 0; f < F; ++f) {
+      air[f] = b.feet_air_time[(size_t)e * F + f];
+      lastc[f] = b.last_contacts[(size_t)e * F + f];
+    }
+    float rew = 0.0f;
+    for (int t = 0; t < c.num_terms; ++t) {
+      float r = 0.0f;
+      switch (c.term_ids[t]) {
+        case URLG_T_ACTION_RATE:
+          for (int j = 0; j < A; ++j) { const float d = lact[j] - act[j]; r += d * d; }
+          break;
+        case URLG_T_ALIVE: r = 1.0f; break;
+        case URLG_T_ANG_VEL_XY: r = avx * avx + avy * avy; break;
+        case URLG_T_BASE_HEIGHT: { const float d = root[2] - c.base_height_target; r = d * d; } break;
+        case URLG_T_COLLISION:
+          for (int k = 0; k < c.num_pen; ++k) {
+            const float* f3 = con + 3 * c.pen_idx[k];
+            r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
+          }
+          break;
+        case URLG_T_CONTACT:
+          for (int f = 0; f < F && f < 2; ++f) {
+            const bool stance = leg_phase[f] < 0.55f;
+            const bool contact = con[3 * c.feet_idx[f] + 2] > 1.0f;
+            r += (contact != stance) ? 0.0f : 1.0f;
+          }
+          break;
+        case URLG_T_CONTACT_NO_VEL:
+          for (int f = 0; f < F; ++f) {
+            const float* f3 = con + 3 * c.feet_idx[f];
+            const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
+            for (int k = 0; k < 3; ++k) { const float v = rb[f * 13 + 7 + k] * m; r += v * v; }
+          }
+          break;
+        case URLG_T_DOF_ACC:
+          for (int j = 0; j < A; ++j) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
+          break;
+        case URLG_T_DOF_POS_LIMITS:
+          for (int j = 0; j < A; ++j) {
+            const float q = dof[2 * j];
+            r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
+          }
+          break;
+        case URLG_T_DOF_VEL:
+          for (int j = 0; j < A; ++j) { const float v = dof[2 * j + 1]; r += v * v; }
+          break;
+        case URLG_T_DOF_VEL_LIMITS:
+          for (int j = 0; j < A; ++j)
+            r += fminf(fmaxf(fabsf(dof[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
+          break;
+        case URLG_T_FEET_AIR_TIME: {   // stateful, :912-923
+          for (int f = 0; f < F; ++f) {
+            const bool contact = con[3 * c.feet_idx[f] + 2] > 1.0f;
+            const bool filt = contact || lastc[f];
+            lastc[f] = contact;
+            const float first = (air[f] > 0.0f && filt) ? 1.0f : 0.0f;
+            air[f] += c.dt;
+            r += (air[f] - 0.5f) * first;
+            air[f] *= filt ? 0.0f : 1.0f;
+          }
+          r *= sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) > 0.1f ? 1.0f : 0.0f;
+        } break;
+        case URLG_T_FEET_CONTACT_FORCES:
+          for (int f = 0; f < F; ++f) {
+            const float* f3 = con + 3 * c.feet_idx[f];
+            r += fmaxf(norm3(f3[0], f3[1], f3[2]) - c.max_contact_force, 0.0f);
+          }
+          break;
+        case URLG_T_FEET_SWING_HEIGHT:
+          for (int f = 0; f < F; ++f) {
+            const float* f3 = con + 3 * c.feet_idx[f];
+            const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 0.0f : 1.0f;
+            const float d = rb[f * 13 + 2] - 0.08f;
+            r += d * d * m;
+          }
+          break;
+        case URLG_T_HIP_POS:
+          for (int k = 0; k < c.num_hip; ++k) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
+          break;
+        case URLG_T_LIN_VEL_Z: r = lvz * lvz; break;
+        case URLG_T_ORIENTATION: r = gx * gx + gy * gy; break;
+        case URLG_T_STAND_STILL:
+          for (int j = 0; j < A; ++j) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
+          r *= sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) < 0.1f ? 1.0f : 0.0f;
+          break;
+        case URLG_T_STUMBLE: {
+          bool any = false;
+          for (int f = 0; f < F; ++f) {
+            const float* f3 = con + 3 * c.feet_idx[f];
+            any |= sqrtf(f3[0] * f3[0] + f3[1] * f3[1]) > 5.0f * fabsf(f3[2]);
+          }
+          r = any ? 1.0f : 0.0f;
+        } break;
+        case URLG_T_TORQUE_LIMITS:
+          for (int j = 0; j < A; ++j) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
+          break;
+        case URLG_T_TORQUES:
+          for (int j = 0; j < A; ++j) r += tq[j] * tq[j];
+          break;
+        case URLG_T_TRACKING_ANG_VEL: { const float d = cmd[2] - avz; r = expf(-(d * d) / c.tracking_sigma); } break;
+        case URLG_T_TRACKING_LIN_VEL: {
+          const float dx = cmd[0] - lvx, dy = cmd[1] - lvy;
+          r = expf(-(dx * dx + dy * dy) / c.tracking_sigma);
+        } break;
+        default: break;
+      }
+      r *= c.term_scales[t];
+      rew += r;
+      b.episode_sums[(size_t)c.term_sum_row[t] * N + e] += r;
+    }
+    if (c.only_positive) rew = fmaxf(rew, 0.0f);
+    if (c.has_termination) {
+      const float r = ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale;
+      rew += r;
+      b.episode_sums[(size_t)c.termination_sum_row * N + e] += r;
+    }
+
+    // ---- E10 reset_idx for this env :723-768 ----
+    if (reset) {
+      for (int k = 0; k < c.num_sums; ++k) {
+        float* s = b.episode_sums + (size_t)k * N + e;
+        atomicAdd(&scratch->ep_acc[acc][k], *s);
+        *s = 0.0f;
+      }
+      atomicAdd(&scratch->ep_acc[acc][URLG_MAX_TERMS], 1.0f);
+      const int pos = atomicAdd(&scratch->reset_cnt[acc], 1);
+      if (b.reset_ids) b.reset_ids[pos] = e;
+      float* gdof = b.dof_state + (size_t)e * 2 * A;
+      for (int j = 0; j < A; ++j) {                                  // _reset_dofs :566-567
+        const float p = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
+        dof[2 * j] = p; dof[2 * j + 1] = 0.0f;
+        gdof[2 * j] = p; gdof[2 * j + 1] = 0.0f;
+      }
+      float* groot = b.root_states + (size_t)e * 13;                 // _reset_root_states :587-590
+      for (int k = 0; k < 13; ++k) root[k] = c.base_init_state[k];
+      for (int k = 0; k < 3; ++k) root[k] += b.env_origins[(size_t)e * 3 + k];
+      for (int k = 0; k < 6; ++k) root[7 + k] = (0.5f - (-0.5f)) * rng.uniform(3 + A + k) + (-0.5f);
+      for (int k = 0; k < 13; ++k) groot[k] = root[k];
+      resample_commands(c, rng, 9 + A, cmd);                         // :749
+      float* gact = b.actions + (size_t)e * A;
+      for (int j = 0; j < A; ++j) { act[j] = 0.0f; gact[j] = 0.0f; } // :752 (last_* follow from the tail copies)
+      for (int f = 0; f < F; ++f) air[f] = 0.0f;                     // :755
+      len = 0;                                                        // :756
+    }
+    push_due = c.push_robots && (len % c.push_interval == 0);        // :545, evaluated after the reset
+
+    // ---- E12 observations :789-811 / h1_env.py:68-95, then the clips of step() :643-646 ----
+    int o = 0;
+    float* dst = (c.family == 1) ? priv : obs;     // H1 family: privileged = [lin_vel] ++ obs
+    dst[o++] = lvx * c.obs_scale_lin_vel; dst[o++] = lvy * c.obs_scale_lin_vel; dst[o++] = lvz * c.obs_scale_lin_vel;
+    if (c.family == 1) { dst = obs; o = 0; }
+    dst[o++] = avx * c.obs_scale_ang_vel; dst[o++] = avy * c.obs_scale_ang_vel; dst[o++] = avz * c.obs_scale_ang_vel;
+    dst[o++] = gx; dst[o++] = gy; dst[o++] = gz;
+    dst[o++] = cmd[0] * c.obs_scale_lin_vel; dst[o++] = cmd[1] * c.obs_scale_lin_vel; dst[o++] = cmd[2] * c.obs_scale_ang_vel;
+    for (int j = 0; j < A; ++j) dst[o++] = (dof[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
+    for (int j = 0; j < A; ++j) dst[o++] = dof[2 * j + 1] * c.obs_scale_dof_vel;
+    for (int j = 0; j < A; ++j) dst[o++] = act[j];
+    if (c.family == 1) {
+      dst[o++] = sinf(kTwoPi * phase);
+      dst[o++] = cosf(kTwoPi * phase);
+      for (int i = 0; i < c.num_obs; ++i) priv[3 + i] = fminf(fmaxf(obs[i], -c.clip_obs), c.clip_obs);
+      for (int i = 0; i < 3; ++i) priv[i] = fminf(fmaxf(priv[i], -c.clip_obs), c.clip_obs);
+    }
+    for (int i = 0; i < c.num_obs; ++i) {
+      float v = obs[i];
+      const float ns = c.noise_scale_vec[i];
+      if (c.add_noise && ns != 0.0f) v += (2.0f * rng.uniform(14 + A + i) - 1.0f) * ns;
+      obs[i] = fminf(fmaxf(v, -c.clip_obs), c.clip_obs);
+    }
+
+    // ---- tail copies :707-708 (in shared; stored coalesced below) ----
+    for (int j = 0; j < A; ++j) { lact[j] = act[j]; ldv[j] = dof[2 * j + 1]; }
+
+    // ---- per-env scalars and short rows (already coalesced) ----
+    b.episode_length_buf[e] = len;
+    b.rew_buf[e] = rew;
+    b.reset_buf[e] = reset ? 1 : 0;
+    b.time_out_buf[e] = time_out ? 1 : 0;
+    reinterpret_cast<float4*>(b.commands)[e] = make_float4(cmd[0], cmd[1], cmd[2], cmd[3]);
+    for (int f = 0; f < F; ++f) {
+      b.feet_air_time[(size_t)e * F + f] = air[f];
+      b.last_contacts[(size_t)e * F + f] = lastc[f];
+    }
+    float* o3 = b.rpy + (size_t)e * 3; o3[0] = roll; o3[1] = pitch; o3[2] = yaw;
+    o3 = b.base_lin_vel + (size_t)e * 3; o3[0] = lvx; o3[1] = lvy; o3[2] = lvz;
+    o3 = b.base_ang_vel + (size_t)e * 3; o3[0] = avx; o3[1] = avy; o3[2] = avz;
+    o3 = b.projected_gravity + (size_t)e * 3; o3[0] = gx; o3[1] = gy; o3[2] = gz;
+    if (c.family == 1) {
+      b.phase[e] = phase;
+      b.leg_phase[(size_t)e * 2] = leg_phase[0];
+      b.leg_phase[(size_t)e * 2 + 1] = leg_phase[1];
+    }
+  }
+  if (__any_sync(0xffffffffu, push_due) && lane == 0) atomicOr(&scratch->push_flag[acc], 1);
+  __syncwarp();
+
+  // ---- coalesced stores of the row outputs ----
+  stage_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, c.num_obs, L.sObs, nrows, lane);
+  if (c.num_priv)
+    stage_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, c.num_priv, L.sPriv, nrows, lane);
+  stage_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, A, L.sA, nrows, lane);
+  stage_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, A, L.sA, nrows, lane);
+}
+
+// ---------------------------------------------------------------- K2b: finalize
+// Runs after K2 of the same step (stream order).  Reads this step's accumulators, applies the
+// all-env push (quirk: any due env => every env's xy velocity is redrawn, :544-550), copies
+// last_root_vel (:709), publishes extras only if >= 1 env reset (:742-743, 759-768), and clears the
+// other parity's accumulators for the next step.
+__global__ void __launch_bounds__(256) finalize_step_kernel(const __grid_constant__ urlg_env_desc c,
+                                                            const __grid_constant__ urlg_env_buffers b,
+                                                            StepScratch* __restrict__ scratch,
+                                                            const int64_t* __restrict__ step_base, int64_t step_off,
+                                                            int num_slots) {
+  const int64_t step = eff_step(step_base, step_off);
+  const int acc = (int)(step & 1);
+  const bool push = scratch->push_flag[acc] != 0;
+  const float cnt = scratch->ep_acc[acc][URLG_MAX_TERMS];
+  const int A = c.num_dof;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < c.num_envs; e += gridDim.x * blockDim.x) {
+    float* root = b.root_states + (size_t)e * 13;
+    if (push) {
+      SlotRng rng;
+      rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
+               b.rng_override ? b.rng_override + (size_t)e * num_slots : nullptr);
+      const float m = c.max_push_vel;
+      root[7] = (m - (-m)) * rng.uniform(12 + A) + (-m);
+      root[8] = (m - (-m)) * rng.uniform(13 + A) + (-m);
+    }
+    float* lrv = b.last_root_vel + (size_t)e * 6;
+    for (int k = 0; k < 6; ++k) lrv[k] = root[7 + k];
+    if (cnt > 0.0f && c.send_timeouts) b.extras_time_outs[e] = b.time_out_buf[e];
+  }
+  if (blockIdx.x == 0 && threadIdx.x < URLG_MAX_TERMS + 1) {
+    const int k = threadIdx.x;
+    if (cnt > 0.0f && k < c.num_sums) b.extras_episode[k] = scratch->ep_acc[acc][k] / cnt / c.max_episode_length_s;
+    if (k == 0 && b.reset_count) *b.reset_count = scratch->reset_cnt[acc];
+    // clear the other parity for step+1 (its last reader was finalize of step-1)
+    scratch->ep_acc[acc ^ 1][k] = 0.0f;
+    if (k == 0) { scratch->push_flag[acc ^ 1] = 0; scratch->reset_cnt[acc ^ 1] = 0; }
+  }
+}
+
+}  // namespace urlg
+
+namespace urlg {
+
+// ---------------------------------------------------------------- reset_idx(env_ids) outside step()
+// base_task.py:82-86 -> legged_robot.py:723-768.  One thread per listed env, straight to global memory
+// (construction-time path, not bandwidth critical).  Accumulator slot 2 is private to this path.
+__global__ void __launch_bounds__(128) reset_idx_kernel(const __grid_constant__ urlg_env_desc c,
+                                                        const __grid_constant__ urlg_env_buffers b,
+                                                        StepScratch* __restrict__ scratch,
+                                                        const int64_t* __restrict__ env_ids, int64_t n,
+                                                        const int64_t* __restrict__ step_base, int64_t step_off,
+                                                        int num_slots) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int e = env_ids ? (int)env_ids[i] : (int)i;
+  const int A = c.num_dof, F = c.num_feet, N = c.num_envs;
+  const int64_t step = eff_step(step_base, step_off);
+  SlotRng rng;
+  rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
+           b.rng_override ? b.rng_override + (size_t)e * num_slots : nullptr);
+  float* gdof = b.dof_state + (size_t)e * 2 * A;
+  for (int j = 0; j < A; ++j) {
+    gdof[2 * j] = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
+    gdof[2 * j + 1] = 0.0f;
+  }
+  float* groot = b.root_states + (size_t)e * 13;
+  for (int k = 0; k < 13; ++k) groot[k] = c.base_init_state[k] + (k < 3 ? b.env_origins[(size_t)e * 3 + k] : 0.0f);
+  for (int k = 0; k < 6; ++k) groot[7 + k] = (0.5f - (-0.5f)) * rng.uniform(3 + A + k) + (-0.5f);
+  float cmd[4];
+  for (int k = 0; k < 4; ++k) cmd[k] = b.commands[(size_t)e * 4 + k];
+  resample_commands(c, rng, 9 + A, cmd);
+  for (int k = 0; k < 4; ++k) b.commands[(size_t)e * 4 + k] = cmd[k];
+  for (int j = 0; j < A; ++j) {
+    b.actions[(size_t)e * A + j] = 0.0f;
+    b.last_actions[(size_t)e * A + j] = 0.0f;
+    b.last_dof_vel[(size_t)e * A + j] = 0.0f;
+  }
+  for (int f = 0; f < F; ++f) b.feet_air_time[(size_t)e * F + f] = 0.0f;
+  b.episode_length_buf[e] = 0;
+  b.reset_buf[e] = 1;
+  for (int k = 0; k < c.num_sums; ++k) {
+    float* s = b.episode_sums + (size_t)k * N + e;
+    atomicAdd(&scratch->ep_acc[2][k], *s);
+    *s = 0.0f;
+  }
+  atomicAdd(&scratch->ep_acc[2][URLG_MAX_TERMS], 1.0f);
+}
+
+__global__ void __launch_bounds__(256) finalize_reset_kernel(const __grid_constant__ urlg_env_desc c,
+                                                             const __grid_constant__ urlg_env_buffers b,
+                                                             StepScratch* __restrict__ scratch) {
+  // single block: publish, then clear slot 2
+  const float cnt = scratch->ep_acc[2][URLG_MAX_TERMS];
+  if (cnt > 0.0f) {
+    if (c.send_timeouts)
+      for (int e = threadIdx.x; e < c.num_envs; e += blockDim.x) b.extras_time_outs[e] = b.time_out_buf[e];
+    if (threadIdx.x < c.num_sums)
+      b.extras_episode[threadIdx.x] = scratch->ep_acc[2][threadIdx.x] / cnt / c.max_episode_length_s;
+  }
+  __syncthreads();
+  if (threadIdx.x < URLG_MAX_TERMS + 1) scratch->ep_acc[2][threadIdx.x] = 0.0f;
+}
+
+// ---------------------------------------------------------------- synthetic physics seam
+__global__ void __launch_bounds__(256) synth_refresh_kernel(float* __restrict__ dst, const float* __restrict__ pool,
+                                                            int64_t elems, int64_t num_frames, int64_t substeps,
+                                                            int per_substep, const int64_t* __restrict__ calls_base,
+                                                            int64_t calls_off) {
+  const int64_t calls = eff_step(calls_base, calls_off);
+  if (calls <= 0) return;
+  const int64_t cidx = calls - 1;
+  const int64_t frame = (cidx / substeps) % num_frames;
+  const int64_t sub = cidx % substeps;
+  const float* src = pool + (per_substep ? (frame * substeps + sub) : frame) * elems;
+  const int64_t n4 = elems >> 2;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+  if (((elems & 3) == 0) && ((((uintptr_t)src | (uintptr_t)dst) & 15) == 0)) {
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    for (int64_t i = tid; i < n4; i += nt) d4[i] = s4[i];
+  } else {
+    for (int64_t i = tid; i < elems; i += nt) dst[i] = src[i];
+  }
+}
+
+__global__ void philox_uniform_kernel(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
+                                      uint32_t stream_id, int64_t env_offset, int64_t step) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * num_slots) return;
+  const int64_t e = i / num_slots;
+  const int s = (int)(i - e * num_slots);
+  SlotRng rng;
+  rng.init(seed_lo, seed_hi, stream_id, env_offset + e, step, nullptr);
+  out[i] = rng.uniform(s);
+}
+
+static int grid_for(int64_t work, int block, int max_waves = 8) {
+  int64_t g = (work + block - 1) / block;
+  const int64_t cap = (int64_t)kNumSMs * max_waves;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace urlg
+
+// ================================================================= C ABI
+using namespace urlg;
+
+extern "C" int urlg_version(void) { return URLG_ABI_VERSION; }
+extern "C" const char* urlg_last_error(void) { return g_err; }
+
+extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
+  if (!d || !out) return fail(URLG_EINVAL, "urlg_env_create: null argument");
+  if (d->num_envs <= 0 || d->num_dof <= 0 || d->num_dof > URLG_MAX_DOF)
+    return fail(URLG_EINVAL, "urlg_env_create: num_envs=%d num_dof=%d out of range (max dof %d)", d->num_envs,
+                d->num_dof, URLG_MAX_DOF);
+  if (d->num_obs > URLG_MAX_OBS || d->num_priv > URLG_MAX_OBS || d->num_terms > URLG_MAX_TERMS ||
+      d->num_sums > URLG_MAX_TERMS || d->num_feet > kMaxFeet || d->num_pen > URLG_MAX_IDX ||
+      d->num_term_bodies > URLG_MAX_IDX || d->num_hip > URLG_MAX_IDX)
+    return fail(URLG_EINVAL, "urlg_env_create: a table exceeds its ABI bound");
+  if (d->control_type != 'P' && d->control_type != 'V' && d->control_type != 'T')
+    return fail(URLG_EINVAL, "Unknown controller type: %c", (char)d->control_type);   // NameError at legged_robot.py:670
+  const int expect_obs = d->family == 0 ? 12 + 3 * d->num_dof : 9 + 3 * d->num_dof + 2;
+  if (d->num_obs != expect_obs || (d->family == 1 && d->num_priv != d->num_obs + 3) || (d->family == 0 && d->num_priv != 0))
+    return fail(URLG_EINVAL, "urlg_env_create: num_obs=%d num_priv=%d inconsistent with family %d, num_dof %d",
+                d->num_obs, d->num_priv, d->family, d->num_dof);
+  if (d->resample_steps <= 0 || d->push_interval <= 0)
+    return fail(URLG_EINVAL, "urlg_env_create: resample_steps / push_interval must be positive");
+  urlg_env* e = new (std::nothrow) urlg_env();
+  if (!e) return fail(URLG_ENOMEM, "urlg_env_create: host allocation failed");
+  e->desc = *d;
+  e->bound = 0;
+  e->scratch = nullptr;
+  URLG_CUDA(cudaMalloc(&e->scratch, sizeof(StepScratch)));
+  URLG_CUDA(cudaMemset(e->scratch, 0, sizeof(StepScratch)));
+  e->smem_bytes = make_layout(e->desc).total * (int)sizeof(float);
+  if (e->smem_bytes > 48 * 1024)
+    URLG_CUDA(cudaFuncSetAttribute(post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes));
+  *out = e;
+  return URLG_OK;
+}
+
+extern "C" int urlg_env_bind(urlg_env* env, const urlg_env_buffers* b) {
+  if (!env || !b) return fail(URLG_EINVAL, "urlg_env_bind: null argument");
+  const void* need[] = {b->root_states, b->dof_state, b->contact_forces, b->obs_buf[0], b->obs_buf[1], b->rew_buf,
+                        b->reset_buf, b->time_out_buf, b->episode_length_buf, b->torques, b->actions, b->last_actions,
+                        b->last_dof_vel, b->last_root_vel, b->commands, b->feet_air_time, b->last_contacts, b->rpy,
+                        b->base_lin_vel, b->base_ang_vel, b->projected_gravity, b->episode_sums, b->env_origins,
+                        b->extras_episode, b->extras_time_outs};
+  for (size_t i = 0; i < sizeof(need) / sizeof(need[0]); ++i)
+    if (!need[i]) return fail(URLG_EINVAL, "urlg_env_bind: required buffer #%zu is NULL", i);
+  if (env->desc.family == 1 && (!b->rigid_body_states || !b->priv_obs_buf[0] || !b->priv_obs_buf[1] || !b->phase || !b->leg_phase))
+    return fail(URLG_EINVAL, "urlg_env_bind: H1-family env needs rigid_body_states, priv_obs_buf, phase, leg_phase");
+  if (((uintptr_t)b->commands & 15) || ((uintptr_t)b->dof_state & 7))
+    return fail(URLG_EINVAL, "urlg_env_bind: commands must be 16-byte and dof_state 8-byte aligned");
+  env->bufs = *b;
+  env->bound = 1;
+  return URLG_OK;
+}
+
+extern "C" void urlg_env_destroy(urlg_env* env) {
+  if (!env) return;
+  if (env->scratch) cudaFree(env->scratch);
+  delete env;
+}
+
+extern "C" int urlg_env_num_rng_slots(const urlg_env* env) {
+  return env ? 14 + env->desc.num_dof + env->desc.num_obs : 0;
+}
+
+extern "C" int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream) {
+  if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_pd_torques: env not bound");
+  const int64_t total = (int64_t)env->desc.num_envs * env->desc.num_dof;
+  pd_torques_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot,
+                                 void* stream) {
+  if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_post_physics: env not bound");
+  if (obs_slot != 0 && obs_slot != 1) return fail(URLG_EINVAL, "urlg_post_physics: obs_slot must be 0 or 1");
+  const int N = env->desc.num_envs;
+  const int slots = urlg_env_num_rng_slots(env);
+  cudaStream_t st = (cudaStream_t)stream;
+  post_physics_kernel<<<(N + kWarp - 1) / kWarp, kWarp, env->smem_bytes, st>>>(env->desc, env->bufs, env->scratch,
+                                                                             step_base, step_offset, obs_slot, slots);
+  URLG_LAUNCH_CHECK();
+  finalize_step_kernel<<<grid_for(N, 256), 256, 0, st>>>(env->desc, env->bufs, env->scratch, step_base, step_offset,
+                                                        slots);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const int64_t* step_base,
+                                  int64_t step_offset, void* stream) {
+  if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_env_reset_idx: env not bound");
+  if (!env_ids) n = env->desc.num_envs;
+  if (n <= 0) return URLG_OK;   // len(env_ids)==0 early-out, legged_robot.py:742-743
+  cudaStream_t st = (cudaStream_t)stream;
+  reset_idx_kernel<<<(int)((n + 127) / 128), 128, 0, st>>>(env->desc, env->bufs, env->scratch, env_ids, n, step_base,
+                                                          step_offset, urlg_env_num_rng_slots(env));
+  URLG_LAUNCH_CHECK();
+  finalize_reset_kernel<<<1, 256, 0, st>>>(env->desc, env->bufs, env->scratch);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num_frames, int64_t substeps,
+                                  int per_substep, const int64_t* calls_base, int64_t calls_offset, void* stream) {
+  if (!dst || !pool || elems <= 0 || num_frames <= 0 || substeps <= 0)
+    return fail(URLG_EINVAL, "urlg_synth_refresh: bad argument");
+  synth_refresh_kernel<<<grid_for((elems + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+      dst, pool, elems, num_frames, substeps, per_substep, calls_base, calls_offset);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_philox_uniform(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
+                                   uint32_t stream_id, int64_t env_offset, int64_t step, void* stream) {
+  if (!out || n <= 0 || num_slots <= 0) return fail(URLG_EINVAL, "urlg_philox_uniform: bad argument");
+  const int64_t total = n * num_slots;
+  philox_uniform_kernel<<<(int)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(out, n, num_slots, seed_lo,
+                                                                                      seed_hi, stream_id, env_offset, step);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
