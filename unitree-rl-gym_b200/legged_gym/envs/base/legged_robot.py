@@ -110,8 +110,8 @@ class LeggedRobot(BaseTask):
         self.gravity_vec = torch.tensor([0., 0., -1.], **f).repeat((N, 1))
         self.forward_vec = torch.tensor([1., 0., 0.], **f).repeat((N, 1))
         self.torques = torch.zeros(N, self.num_actions, **f)
-        self.p_gains = torch.as_tensor(s.p_gains, **f)
-        self.d_gains = torch.as_tensor(s.d_gains, **f)
+        self.p_gains = torch.tensor(s.p_gains, **f)
+        self.d_gains = torch.tensor(s.d_gains, **f)
         self.actions = torch.zeros(N, self.num_actions, **f)
         self.last_actions = torch.zeros(N, self.num_actions, **f)
         self.last_dof_vel = torch.zeros(N, A, **f)
@@ -125,7 +125,7 @@ class LeggedRobot(BaseTask):
         self.base_ang_vel = torch.zeros(N, 3, **f)
         self.projected_gravity = torch.zeros(N, 3, **f)
         self.projected_gravity[:, 2] = -1.0
-        self.default_dof_pos = torch.as_tensor(s.default_dof_pos, **f).unsqueeze(0)
+        self.default_dof_pos = torch.tensor(s.default_dof_pos, **f).unsqueeze(0)
 
     def _get_noise_scale_vec(self, cfg):
         self.add_noise = cfg.noise.add_noise
