@@ -152,6 +152,29 @@ int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num
 int urlg_philox_uniform(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
                         uint32_t stream_id, int64_t env_offset, int64_t step, void* stream);
 
+/* ---- tensor-core building block of the PPO half ----
+ * D[M,N] = sum_k A[m,k]*B[n,k] on tcgen05 (bf16 operands via TMA, fp32 accumulate in TMEM) with a fused
+ * epilogue.  Replaces the cuBLAS GEMMs behind nn.Linear forward/backward in ActorCritic
+ * ([UPSTREAM rsl_rl v1.0.2] modules/actor_critic.py; reference call sites task_registry.py:118-119).
+ * a_mn/b_mn = 0: operand is row-major [rows, K] (K-major); = 1: row-major [K, rows] (MN-major). */
+#define URLG_GEMM_ELU 1      /* out = ELU(acc + bias) */
+#define URLG_GEMM_ATOMIC 2   /* out_f32 += acc (split-K accumulation; caller zeroes out_f32) */
+typedef struct urlg_gemm_desc {
+  const void* A; int64_t lda;     /* bf16, ld in elements (row pitch must be a multiple of 16 bytes) */
+  const void* B; int64_t ldb;
+  int32_t a_mn, b_mn;
+  int32_t M, N, K;
+  int32_t block_n;                /* 0 = auto */
+  int32_t k_splits;               /* 0/1 = none */
+  float* out_f32; int32_t ld_f32; /* optional fp32 output [M,N] */
+  void* out_bf16; int32_t ld_bf16;/* optional bf16 output [M,N] */
+  const float* bias;              /* optional [N] */
+  const void* dact_ref; int32_t ld_ref;   /* optional bf16 [M,N]: out *= ELU'(y), y = post-activation */
+  float* colsum;                  /* optional [N]: += column sums of the stored values */
+  int32_t flags;
+} urlg_gemm_desc;
+int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

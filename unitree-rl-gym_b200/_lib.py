@@ -61,6 +61,18 @@ class EnvBuffers(C.Structure):
     ]
 
 
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("A", _P), ("lda", C.c_int64), ("B", _P), ("ldb", C.c_int64),
+        ("a_mn", C.c_int32), ("b_mn", C.c_int32), ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
+        ("block_n", C.c_int32), ("k_splits", C.c_int32),
+        ("out_f32", _P), ("ld_f32", C.c_int32), ("out_bf16", _P), ("ld_bf16", C.c_int32),
+        ("bias", _P), ("dact_ref", _P), ("ld_ref", C.c_int32), ("colsum", _P), ("flags", C.c_int32),
+    ]
+
+
+GEMM_ELU, GEMM_ATOMIC = 1, 2
+
 _lib = None
 
 # symbol -> (restype, argtypes); every symbol declared in include/urlg_b200.h appears here
@@ -77,6 +89,7 @@ SIGNATURES = {
     "urlg_env_reset_idx": (C.c_int, [C.c_void_p, _I64P, C.c_int64, _I64P, C.c_int64, C.c_void_p]),
     "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
                                      C.c_int64, C.c_void_p]),
+    "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
     "urlg_philox_uniform": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32, C.c_uint32,
                                       C.c_int64, C.c_int64, C.c_void_p]),
 }

@@ -8,7 +8,7 @@ COMMON="-O3 -std=c++17 -lineinfo -Xcompiler -fPIC $ARCH"
 mkdir -p build
 # env kernels: no FMA contraction (expressions evaluate as written, like the reference's eager ops)
 $NVCC $COMMON -fmad=false -c env_kernels.cu -o build/env_kernels.o "$@"
-for f in storage_kernels policy_kernels; do
+for f in tc_gemm storage_kernels policy_kernels ppo_kernels lstm_kernels; do
   if [ -f $f.cu ]; then $NVCC $COMMON -c $f.cu -o build/$f.o "$@"; fi
 done
 $NVCC -shared $ARCH -o liburlg_b200.so build/*.o -lcudart

@@ -1,0 +1,88 @@
+// Host side of the tcgen05 GEMM: tensor-map construction (driver entry point resolved at run time, so
+// the library still loads on a box without libcuda) and the launch.
+#include "common.cuh"
+#include "tc_gemm.cuh"
+#include <cudaTypedefs.h>
+
+namespace urlg {
+namespace tc {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 row-major matrix [outer, inner] with row pitch ld (elements); box {box_inner, box_outer}; zero OOB fill.
+int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  if (((uintptr_t)ptr & 15) || ((ld * 2) & 15))
+    return fail(URLG_EINVAL, "tensor map: base must be 16-byte aligned and row pitch a multiple of 16 bytes (ld=%lld)", (long long)ld);
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return URLG_OK;
+}
+
+int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
+  if (!d || !d->A || !d->B || d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(URLG_EINVAL, "urlg_tc_gemm: bad argument");
+  GemmArgs g;
+  g.M = d->M; g.N = d->N; g.K = d->K;
+  g.a_mn = d->a_mn ? 1 : 0; g.b_mn = d->b_mn ? 1 : 0;
+  int bn = d->block_n;
+  if (bn <= 0) bn = g.b_mn ? ((d->N + 63) / 64) * 64 : ((d->N + 15) / 16) * 16;
+  if (bn > 256) bn = 256;
+  if ((bn & 15) || (g.b_mn && (bn & 63))) return fail(URLG_EINVAL, "urlg_tc_gemm: block_n=%d invalid", bn);
+  g.block_n = bn;
+  int splits = d->k_splits > 0 ? d->k_splits : 1;
+  int kps = ((d->K + splits - 1) / splits + kBlockK - 1) / kBlockK * kBlockK;
+  splits = (d->K + kps - 1) / kps;
+  g.k_per_split = kps;
+  if (splits > 1 && !(d->flags & kFlagAtomic)) return fail(URLG_EINVAL, "urlg_tc_gemm: k_splits > 1 needs the atomic flag");
+  g.out_f32 = d->out_f32; g.ld_f32 = d->ld_f32;
+  g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(d->out_bf16); g.ld_bf16 = d->ld_bf16;
+  g.bias = d->bias;
+  g.dact_ref = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref); g.ld_ref = d->ld_ref;
+  g.colsum = d->colsum;
+  g.flags = d->flags;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!g.a_mn) rc = make_tmap_bf16(&ta, d->A, d->K, d->M, d->lda, kBlockK, kBlockM);
+  else rc = make_tmap_bf16(&ta, d->A, d->M, d->K, d->lda, 64, kBlockK);
+  if (rc) return rc;
+  if (!g.b_mn) rc = make_tmap_bf16(&tb, d->B, d->K, d->N, d->ldb, kBlockK, bn);
+  else rc = make_tmap_bf16(&tb, d->B, d->N, d->K, d->ldb, 64, kBlockK);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(256)));
+    attr_set = true;
+  }
+  dim3 grid((d->M + kBlockM - 1) / kBlockM, (d->N + bn - 1) / bn, splits);
+  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn), st>>>(ta, tb, g);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+}  // namespace tc
+}  // namespace urlg
+
+extern "C" int urlg_tc_gemm(const urlg_gemm_desc* d, void* stream) {
+  return urlg::tc::launch_gemm(d, (cudaStream_t)stream);
+}
