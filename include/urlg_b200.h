@@ -175,6 +175,114 @@ typedef struct urlg_gemm_desc {
 } urlg_gemm_desc;
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 
+/* ======================================================================================
+ * PPO half: rsl_rl v1.0.2 [UPSTREAM, submodule absent from /root/reference] — reference call
+ * sites legged_gym/utils/task_registry.py:8-9,118-126; scripts/train.py:14; play.py:34,39;
+ * utils/helpers.py:150-189; config keys envs/base/legged_robot_config.py:244-286.
+ * ====================================================================================== */
+#define URLG_MAX_LAYERS 8
+
+/* One MLP: Linear(dims[0],dims[1]) ELU ... Linear(dims[L-1],dims[L]) (no activation after the last).
+ * w_off/b_off: element offsets of weight [out,in] (row-major, nn.Linear layout) and bias [out]
+ * inside the flat fp32 parameter buffer (same offsets in the flat gradient / Adam buffers). */
+typedef struct urlg_mlp_desc {
+  int32_t num_layers;
+  int32_t dims[URLG_MAX_LAYERS + 1];
+  int64_t w_off[URLG_MAX_LAYERS], b_off[URLG_MAX_LAYERS];
+} urlg_mlp_desc;
+
+/* ActorCritic / ActorCriticRecurrent ([UPSTREAM] modules/actor_critic.py, actor_critic_recurrent.py;
+ * shapes from legged_robot_config.py:247-255, h1_config.py:103-115, g1_config.py:91-105). */
+typedef struct urlg_policy_desc {
+  int32_t recurrent;                 /* 0: MLP on obs; 1: LSTM(obs->rnn_hidden) then MLP on the LSTM output */
+  int32_t num_actor_obs, num_critic_obs, num_actions, rnn_hidden;
+  urlg_mlp_desc actor, critic;
+  int64_t std_off;
+  int64_t lstm_a_off[4], lstm_c_off[4];   /* weight_ih_l0 [4H,in], weight_hh_l0 [4H,H], bias_ih_l0, bias_hh_l0 */
+  int64_t num_params;
+  int32_t max_rows;                  /* largest row count of any call (rollout N or minibatch rows) */
+  int32_t max_seq;                   /* recurrent: largest T of an update call */
+  uint32_t seed_lo, seed_hi;         /* Philox key of the action-sampling stream */
+  int64_t env_offset;                /* global id of local env 0 */
+} urlg_policy_desc;
+
+/* RolloutStorage tensors ([UPSTREAM] storage/rollout_storage.py), time-major [T,N,...], fp32 unless noted. */
+typedef struct urlg_storage {
+  int32_t T, N, num_obs, num_priv, num_actions, rnn_hidden;
+  float* observations;               /* [T,N,num_obs] */
+  float* privileged_observations;    /* [T,N,num_priv] or NULL (critic then reads observations) */
+  float* actions; float* mu; float* sigma;          /* [T,N,A] */
+  float* rewards; float* values; float* returns; float* advantages; float* actions_log_prob;   /* [T,N,1] */
+  uint8_t* dones;                    /* [T,N,1] uint8 */
+  float* hid_a_h; float* hid_a_c; float* hid_c_h; float* hid_c_c;   /* saved hidden states [T,1,N,H] or NULL */
+} urlg_storage;
+
+typedef struct urlg_ppo_hparams {
+  float clip_param, value_loss_coef, entropy_coef, max_grad_norm, desired_kl;
+  float beta1, beta2, eps;
+  float lr_min, lr_max;
+  int32_t use_clipped_value_loss, adaptive_lr;
+  float grad_scale;                  /* 1/world_size: applied to the (all-reduced) gradient sum */
+  float kl_count_scale;              /* world_size: rows contributing to the all-reduced KL sum = rows * this */
+} urlg_ppo_hparams;
+
+/* Device-resident scalars of the update (float[URLG_STAT_COUNT]); nothing is read back per step. */
+enum {
+  URLG_STAT_LR = 0,        /* current learning rate (adaptive schedule runs on the device) */
+  URLG_STAT_STEP,          /* Adam step count */
+  URLG_STAT_KL_SUM,        /* this minibatch: sum over rows of KL */
+  URLG_STAT_SURR_SUM, URLG_STAT_VLOSS_SUM, URLG_STAT_ENT_SUM,   /* this minibatch: sums over rows */
+  URLG_STAT_GNORM_SQ,      /* this minibatch: squared gradient norm (after grad_scale) */
+  URLG_STAT_CLIP_COEF,
+  URLG_STAT_ACC_VLOSS, URLG_STAT_ACC_SURR, URLG_STAT_ACC_N,      /* accumulated minibatch means since last reset */
+  URLG_STAT_KL_MEAN,       /* last minibatch's KL mean (what the LR rule saw) */
+  URLG_STAT_BC1, URLG_STAT_BC2,   /* Adam bias corrections 1-beta^step of the current step */
+  URLG_STAT_COUNT = 16
+};
+
+typedef struct urlg_policy urlg_policy;
+
+/* The library borrows params/grads/exp_avg/exp_avg_sq (flat fp32 [num_params]), stats
+ * (float[URLG_STAT_COUNT]) and a workspace of urlg_policy_workspace_bytes() bytes. */
+int64_t urlg_policy_workspace_bytes(const urlg_policy_desc* desc);
+int urlg_policy_create(const urlg_policy_desc* desc, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                       float* stats, void* workspace, int64_t workspace_bytes, urlg_policy** out);
+void urlg_policy_destroy(urlg_policy* p);
+/* Refresh the bf16 operand images of the weights from the fp32 parameters (after load_state_dict etc.). */
+int urlg_policy_sync_weights(urlg_policy* p, void* stream);
+
+/* PPO.act ([UPSTREAM] algorithms/ppo.py act): actor forward, Normal(mu, std).sample() with Philox
+ * (or mu + std*noise when noise != NULL: parity injection), critic forward, log-prob; writes the transition
+ * straight into storage slabs [t] (observations, privileged_observations, actions, mu, sigma, values,
+ * actions_log_prob, and for a recurrent policy the pre-step hidden states) and actions_out [N,A]. */
+int urlg_policy_act(urlg_policy* p, const float* obs, const float* critic_obs, const urlg_storage* s, int t,
+                    float* hidden /* recurrent: [4,N,H] = a_h,a_c,c_h,c_c, updated in place */,
+                    const float* noise, float* actions_out, const int64_t* step_base, int64_t step_offset,
+                    void* stream);
+/* act_inference / evaluate on their own: out = actor(obs) [rows,A] (which=0) or critic(obs) [rows,1] (which=1). */
+int urlg_policy_forward(urlg_policy* p, int which, const float* x, int64_t rows, float* hidden_h, float* hidden_c,
+                        float* out, void* stream);
+
+/* PPO.process_env_step: rewards[t] = rew + gamma * values[t] * time_outs (if non-NULL), dones[t] = dones,
+ * recurrent: hidden[..., dones, :] = 0. */
+int urlg_process_env_step(const urlg_storage* s, int t, const float* rew, const uint8_t* dones,
+                          const uint8_t* time_outs, float gamma, float* hidden, void* stream);
+
+/* RolloutStorage.compute_returns: GAE reverse scan, advantages = returns - values, then
+ * (adv - mean) / (std_unbiased + 1e-8) over all T*N.  moments: double[3] device scratch (sum, sumsq, count);
+ * phase 1 = scan + local moments, phase 2 = normalise (an all-reduce of `moments` may go between), 3 = both. */
+int urlg_gae(const urlg_storage* s, const float* last_values, float gamma, float lam, double* moments, int phase,
+             void* stream);
+
+/* One PPO minibatch: gather rows `indices` (flattened t*N+env, device int64 [rows]), forward, loss,
+ * backward -> flat grads (+ KL / loss sums in stats).  Recurrent policies take an env slice instead:
+ * envs [env_begin, env_begin+env_count), all T steps, hidden state re-seeded from the saved states at
+ * trajectory starts (equivalent to split_and_pad_trajectories + masks). */
+int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, const int64_t* indices, int64_t rows,
+                             int32_t env_begin, int32_t env_count, const urlg_ppo_hparams* h, void* stream);
+/* Adaptive-KL learning-rate rule, clip_grad_norm_, Adam, refresh of the bf16 weight images. */
+int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -72,6 +72,43 @@ class GemmDesc(C.Structure):
 
 
 GEMM_ELU, GEMM_ATOMIC = 1, 2
+MAX_LAYERS = 8
+
+
+class MlpDesc(C.Structure):
+    _fields_ = [("num_layers", C.c_int32), ("dims", C.c_int32 * (MAX_LAYERS + 1)),
+                ("w_off", C.c_int64 * MAX_LAYERS), ("b_off", C.c_int64 * MAX_LAYERS)]
+
+
+class PolicyDesc(C.Structure):
+    _fields_ = [("recurrent", C.c_int32), ("num_actor_obs", C.c_int32), ("num_critic_obs", C.c_int32),
+                ("num_actions", C.c_int32), ("rnn_hidden", C.c_int32),
+                ("actor", MlpDesc), ("critic", MlpDesc), ("std_off", C.c_int64),
+                ("lstm_a_off", C.c_int64 * 4), ("lstm_c_off", C.c_int64 * 4), ("num_params", C.c_int64),
+                ("max_rows", C.c_int32), ("max_seq", C.c_int32), ("seed_lo", C.c_uint32), ("seed_hi", C.c_uint32),
+                ("env_offset", C.c_int64)]
+
+
+class Storage(C.Structure):
+    _fields_ = [("T", C.c_int32), ("N", C.c_int32), ("num_obs", C.c_int32), ("num_priv", C.c_int32),
+                ("num_actions", C.c_int32), ("rnn_hidden", C.c_int32),
+                ("observations", _P), ("privileged_observations", _P), ("actions", _P), ("mu", _P), ("sigma", _P),
+                ("rewards", _P), ("values", _P), ("returns", _P), ("advantages", _P), ("actions_log_prob", _P),
+                ("dones", _P), ("hid_a_h", _P), ("hid_a_c", _P), ("hid_c_h", _P), ("hid_c_c", _P)]
+
+
+class PpoHparams(C.Structure):
+    _fields_ = [("clip_param", C.c_float), ("value_loss_coef", C.c_float), ("entropy_coef", C.c_float),
+                ("max_grad_norm", C.c_float), ("desired_kl", C.c_float),
+                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+                ("lr_min", C.c_float), ("lr_max", C.c_float),
+                ("use_clipped_value_loss", C.c_int32), ("adaptive_lr", C.c_int32),
+                ("grad_scale", C.c_float), ("kl_count_scale", C.c_float)]
+
+
+(STAT_LR, STAT_STEP, STAT_KL_SUM, STAT_SURR_SUM, STAT_VLOSS_SUM, STAT_ENT_SUM, STAT_GNORM_SQ, STAT_CLIP_COEF,
+ STAT_ACC_VLOSS, STAT_ACC_SURR, STAT_ACC_N, STAT_KL_MEAN, STAT_BC1, STAT_BC2) = range(14)
+STAT_COUNT = 16
 
 _lib = None
 
@@ -90,6 +127,18 @@ SIGNATURES = {
     "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
                                      C.c_int64, C.c_void_p]),
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
+    "urlg_policy_workspace_bytes": (C.c_int64, [C.POINTER(PolicyDesc)]),
+    "urlg_policy_create": (C.c_int, [C.POINTER(PolicyDesc), _P, _P, _P, _P, _P, _P, C.c_int64, C.POINTER(C.c_void_p)]),
+    "urlg_policy_destroy": (None, [C.c_void_p]),
+    "urlg_policy_sync_weights": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "urlg_policy_act": (C.c_int, [C.c_void_p, _P, _P, C.POINTER(Storage), C.c_int, _P, _P, _P, _I64P, C.c_int64,
+                                  C.c_void_p]),
+    "urlg_policy_forward": (C.c_int, [C.c_void_p, C.c_int, _P, C.c_int64, _P, _P, _P, C.c_void_p]),
+    "urlg_process_env_step": (C.c_int, [C.POINTER(Storage), C.c_int, _P, _P, _P, C.c_float, _P, C.c_void_p]),
+    "urlg_gae": (C.c_int, [C.POINTER(Storage), _P, C.c_float, C.c_float, _P, C.c_int, C.c_void_p]),
+    "urlg_ppo_minibatch_grads": (C.c_int, [C.c_void_p, C.POINTER(Storage), _I64P, C.c_int64, C.c_int32, C.c_int32,
+                                           C.POINTER(PpoHparams), C.c_void_p]),
+    "urlg_ppo_apply": (C.c_int, [C.c_void_p, C.POINTER(PpoHparams), C.c_void_p]),
     "urlg_philox_uniform": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32, C.c_uint32,
                                       C.c_int64, C.c_int64, C.c_void_p]),
 }
@@ -128,6 +177,8 @@ def check(code):
     if code != 0:
         msg = lib().urlg_last_error().decode()
         if code == -1:
+            if msg == "Rollout buffer overflow":
+                raise AssertionError(msg)  # same as [UPSTREAM] RolloutStorage.add_transitions
             if msg.startswith("Unknown controller type"):
                 raise NameError(msg)       # same exception type as legged_robot.py:670
             raise ValueError(msg)

@@ -1,0 +1,60 @@
+// Internal layout of a urlg_policy: where the bf16 operand images and activation slabs live inside the
+// caller-provided workspace.  Shared by policy_kernels.cu (rollout forward), ppo_kernels.cu (update) and
+// lstm_kernels.cu (recurrent variants).
+#pragma once
+#include "common.cuh"
+#include <cuda_bf16.h>
+
+namespace urlg {
+
+typedef __nv_bfloat16 bf16;
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+struct NetWs {                       // one MLP (actor or critic)
+  urlg_mlp_desc d;
+  int kpad[URLG_MAX_LAYERS];         // padded input width of layer l (multiple of 8 -> 16-byte bf16 row pitch)
+  bf16* w[URLG_MAX_LAYERS];          // [dims[l+1], kpad[l]] image of weight l (pad columns zero)
+  bf16* x;                           // [R, kpad[0]] network input
+  bf16* h[URLG_MAX_LAYERS];          // h[l], l=1..L-1: [R, dims[l]] post-activation output of layer l-1
+  float* out;                        // [R, dims[L]] fp32 output of the last layer
+  bf16* dout;                        // [R, opad] gradient wrt the output (opad = round_up(dims[L], 8))
+  bf16* dz[URLG_MAX_LAYERS];         // dz[l], l=1..L-1: [R, dims[l]] gradient wrt the pre-activation of layer l-1
+  int opad;
+};
+
+struct LstmWs {                      // one Memory (nn.LSTM, 1 layer)
+  int in, in_pad, H, kcat;           // kcat = in_pad + H: gates = [x | h_prev] * [W_ih | W_hh]^T
+  int64_t off[4];                    // w_ih, w_hh, b_ih, b_hh offsets in the flat parameter buffer
+  bf16* w;                           // [4H, kcat] image
+  float* bias;                       // [4H] = b_ih + b_hh
+  bf16* xcat;                        // [T*R, kcat]   (rollout uses the first R rows)
+  float* gates;                      // [T*R, 4H] activated gates (i,f,g,o) kept for the backward pass
+  float* c;                          // [(T+1)*R, H] cell states (c[0] = initial)
+  float* h0;                         // [R, H] initial hidden of the sequence (update mode)
+  bf16* dgates;                      // [T*R, 4H]
+  float* dh;                         // [R, H] running dL/dh
+  float* dc;                         // [R, H] running dL/dc
+  float* dhrec;                      // [R, H] dgates * W_hh (fp32 out of the recurrent dgrad)
+  bf16* dx_head;                     // [T*R, H] dL/dh_t coming from the MLP head
+};
+
+}  // namespace urlg
+
+struct urlg_policy {
+  urlg_policy_desc desc;
+  float *params, *grads, *m, *v, *stats;
+  urlg::NetWs net[2];                // 0 = actor, 1 = critic
+  urlg::LstmWs lstm[2];
+  int R;                             // max rows
+  int T;                             // max sequence length (recurrent update)
+  float* red;                        // small fp32 scratch (head reductions)
+  int64_t last_rows;                 // rows of the pending minibatch gradient (set by minibatch_grads)
+};
+
+namespace urlg {
+int sync_weights(urlg_policy* p, cudaStream_t st);
+int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st);
+int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);
+int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int kpad, int ld, cudaStream_t st);
+}

@@ -1,0 +1,297 @@
+// ActorCritic rollout side ([UPSTREAM rsl_rl v1.0.2] modules/actor_critic.py, algorithms/ppo.py act;
+// SURVEY.md §8(a).6 R5/R7, kernels K3/K4): workspace carving, bf16 weight images, MLP forward on the
+// tcgen05 GEMM (bias+ELU fused in its epilogue), Gaussian sampling with counter-based Philox, and the
+// transition store fused into the prep / sample kernels (no separate add_transitions pass).
+#include "policy.cuh"
+#include "philox.cuh"
+#include <new>
+
+namespace urlg {
+namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
+
+// ---------------------------------------------------------------- workspace carving
+struct Carver {
+  uint8_t* base; int64_t off;
+  template <typename T> T* take(int64_t n) {
+    off = (off + 255) & ~int64_t(255);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * (int64_t)sizeof(T);
+    return p;
+  }
+};
+
+static int carve_net(Carver& c, NetWs& n, const urlg_mlp_desc& d, int R) {
+  n.d = d;
+  const int L = d.num_layers;
+  if (L < 1 || L > URLG_MAX_LAYERS) return fail(URLG_EINVAL, "mlp: num_layers=%d out of range", L);
+  for (int l = 0; l < L; ++l) {
+    if (d.dims[l] <= 0 || d.dims[l + 1] <= 0) return fail(URLG_EINVAL, "mlp: bad dims");
+    if (l > 0 && (d.dims[l] & 7)) return fail(URLG_EINVAL, "mlp: hidden width %d must be a multiple of 8", d.dims[l]);
+    n.kpad[l] = round_up(d.dims[l], 8);
+    n.w[l] = c.take<bf16>((int64_t)d.dims[l + 1] * n.kpad[l]);
+  }
+  n.x = c.take<bf16>((int64_t)R * n.kpad[0]);
+  for (int l = 1; l < L; ++l) {
+    n.h[l] = c.take<bf16>((int64_t)R * d.dims[l]);
+    n.dz[l] = c.take<bf16>((int64_t)R * d.dims[l]);
+  }
+  n.out = c.take<float>((int64_t)R * d.dims[L]);
+  n.opad = round_up(d.dims[L], 8);
+  n.dout = c.take<bf16>((int64_t)R * n.opad);
+  return URLG_OK;
+}
+
+static void carve_lstm(Carver& c, LstmWs& w, int in, int H, const int64_t* off, int R) {
+  w.in = in; w.in_pad = round_up(in, 8); w.H = H; w.kcat = w.in_pad + H;
+  for (int i = 0; i < 4; ++i) w.off[i] = off[i];
+  w.w = c.take<bf16>((int64_t)4 * H * w.kcat);
+  w.bias = c.take<float>(4 * H);
+  w.xcat = c.take<bf16>((int64_t)R * w.kcat);
+  w.gates = c.take<float>((int64_t)R * 4 * H);
+  w.c = c.take<float>((int64_t)2 * R * H);
+  w.h0 = c.take<float>((int64_t)R * H);
+  w.dgates = c.take<bf16>((int64_t)R * 4 * H);
+  w.dh = c.take<float>((int64_t)R * H);
+  w.dc = c.take<float>((int64_t)R * H);
+  w.dhrec = c.take<float>((int64_t)R * H);
+  w.dx_head = c.take<bf16>((int64_t)R * H);
+}
+
+static int carve(urlg_policy* p, uint8_t* base, int64_t* total) {
+  const urlg_policy_desc& d = p->desc;
+  if (d.max_rows <= 0) return fail(URLG_EINVAL, "policy: max_rows must be positive");
+  if (d.num_actions <= 0 || d.num_actions > 32) return fail(URLG_EINVAL, "policy: num_actions=%d unsupported (1..32)", d.num_actions);
+  Carver c{base, 0};
+  p->R = d.max_rows;
+  p->T = d.max_seq > 0 ? d.max_seq : 1;
+  if (int rc = carve_net(c, p->net[0], d.actor, p->R)) return rc;
+  if (int rc = carve_net(c, p->net[1], d.critic, p->R)) return rc;
+  if (d.actor.dims[d.actor.num_layers] != d.num_actions || d.critic.dims[d.critic.num_layers] != 1)
+    return fail(URLG_EINVAL, "policy: actor must end in num_actions, critic in 1");
+  if (d.recurrent) {
+    if (d.rnn_hidden <= 0 || (d.rnn_hidden & 15)) return fail(URLG_EINVAL, "policy: rnn_hidden must be a multiple of 16");
+    if (d.actor.dims[0] != d.rnn_hidden || d.critic.dims[0] != d.rnn_hidden)
+      return fail(URLG_EINVAL, "policy: recurrent heads take the LSTM output");
+    carve_lstm(c, p->lstm[0], d.num_actor_obs, d.rnn_hidden, d.lstm_a_off, p->R);
+    carve_lstm(c, p->lstm[1], d.num_critic_obs, d.rnn_hidden, d.lstm_c_off, p->R);
+  } else if (d.actor.dims[0] != d.num_actor_obs || d.critic.dims[0] != d.num_critic_obs) {
+    return fail(URLG_EINVAL, "policy: MLP input widths must equal the observation widths");
+  }
+  p->red = c.take<float>(256);
+  *total = (c.off + 255) & ~int64_t(255);
+  return URLG_OK;
+}
+
+// ---------------------------------------------------------------- bf16 weight images
+__global__ void __launch_bounds__(256)
+weight_image_kernel(bf16* __restrict__ dst, const float* __restrict__ src, int rows, int cols, int kpad, int dst_col0, int ld) {
+  const int64_t total = (int64_t)rows * kpad;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / kpad), c = (int)(i % kpad);
+    dst[(size_t)r * ld + dst_col0 + c] = __float2bfloat16(c < cols ? src[(size_t)r * cols + c] : 0.0f);
+  }
+}
+__global__ void bias_sum_kernel(float* __restrict__ dst, const float* __restrict__ a, const float* __restrict__ b, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = a[i] + b[i];
+}
+
+int sync_weights(urlg_policy* p, cudaStream_t st) {
+  for (int k = 0; k < 2; ++k) {
+    NetWs& n = p->net[k];
+    for (int l = 0; l < n.d.num_layers; ++l) {
+      const int rows = n.d.dims[l + 1], cols = n.d.dims[l];
+      const int64_t total = (int64_t)rows * n.kpad[l];
+      weight_image_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(n.w[l], p->params + n.d.w_off[l], rows, cols,
+                                                                      n.kpad[l], 0, n.kpad[l]);
+    }
+    if (p->desc.recurrent) {
+      LstmWs& w = p->lstm[k];
+      const int G = 4 * w.H;
+      weight_image_kernel<<<(G * w.in_pad + 255) / 256, 256, 0, st>>>(w.w, p->params + w.off[0], G, w.in, w.in_pad, 0, w.kcat);
+      weight_image_kernel<<<(G * w.H + 255) / 256, 256, 0, st>>>(w.w, p->params + w.off[1], G, w.H, w.H, w.in_pad, w.kcat);
+      bias_sum_kernel<<<(G + 255) / 256, 256, 0, st>>>(w.bias, p->params + w.off[2], p->params + w.off[3], G);
+    }
+  }
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+// ---------------------------------------------------------------- MLP forward (x already staged in n.x)
+// keep_hidden: activations stay in n.h[] (needed by the backward pass); the rollout reuses the same slabs.
+int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st) {
+  const int L = n.d.num_layers;
+  for (int l = 0; l < L; ++l) {
+    urlg_gemm_desc g = {};
+    g.A = l == 0 ? (const void*)n.x : (const void*)n.h[l];
+    g.lda = l == 0 ? n.kpad[0] : n.d.dims[l];
+    g.B = n.w[l]; g.ldb = n.kpad[l];
+    g.M = (int)rows; g.N = n.d.dims[l + 1]; g.K = n.kpad[l];
+    g.bias = p->params + n.d.b_off[l];
+    if (l + 1 < L) { g.out_bf16 = n.h[l + 1]; g.ld_bf16 = n.d.dims[l + 1]; g.flags = URLG_GEMM_ELU; }
+    else { g.out_f32 = n.out; g.ld_f32 = n.d.dims[L]; }
+    if (int rc = tc::launch_gemm(&g, st)) return rc;
+  }
+  return URLG_OK;
+}
+
+// ---------------------------------------------------------------- prep: obs -> storage slab + bf16 staging
+__global__ void __launch_bounds__(256)
+stage_obs_kernel(const float* __restrict__ src, int64_t rows, int cols, float* __restrict__ store, bf16* __restrict__ dst,
+                 int kpad, int ld) {
+  const int64_t total = rows * kpad;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / kpad;
+    const int c = (int)(i % kpad);
+    float v = 0.0f;
+    if (c < cols) {
+      v = src[r * cols + c];
+      if (store) store[r * cols + c] = v;
+    }
+    dst[r * ld + c] = __float2bfloat16(v);
+  }
+}
+
+int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int kpad, int ld, cudaStream_t st) {
+  const int64_t total = rows * kpad;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  stage_obs_kernel<<<blocks, 256, 0, st>>>(src, rows, cols, store, dst, kpad, ld);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+// ---------------------------------------------------------------- sample + log-prob + transition store
+// Normal(mu, std).sample(): eps from Philox (Box-Muller on slots 2j, 2j+1 of stream kStreamPolicy, counter
+// (global env, step)) or injected.  log_prob follows torch.distributions.Normal.log_prob term by term.
+__global__ void __launch_bounds__(128)
+sample_store_kernel(const float* __restrict__ mu_in, const float* __restrict__ val_in, const float* __restrict__ std_param,
+                    const float* __restrict__ noise, urlg_storage s, int t, float* __restrict__ actions_out, int A,
+                    uint32_t seed_lo, uint32_t seed_hi, int64_t env_offset, const int64_t* step_base, int64_t step_off) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.N) return;
+  SlotRng rng;
+  rng.init(seed_lo, seed_hi, kStreamPolicy, env_offset + i, eff_step(step_base, step_off), nullptr);
+  const size_t row = (size_t)t * s.N + i;
+  float lp = 0.0f;
+  for (int j = 0; j < A; ++j) {
+    const float mu = mu_in[(size_t)i * A + j];
+    const float sd = mu * 0.0f + std_param[j];
+    float eps;
+    if (noise) {
+      eps = noise[(size_t)i * A + j];
+    } else {
+      const float u1 = 1.0f - rng.uniform(2 * j), u2 = rng.uniform(2 * j + 1);   // u1 in (0,1]
+      eps = sqrtf(-2.0f * logf(u1)) * cosf(6.28318530717958647692f * u2);
+    }
+    const float a = mu + sd * eps;
+    const float d = a - mu;
+    lp += -(d * d) / (2.0f * (sd * sd)) - logf(sd) - 0.918938533204672741780f;
+    s.actions[row * A + j] = a;
+    s.mu[row * A + j] = mu;
+    s.sigma[row * A + j] = sd;
+    actions_out[(size_t)i * A + j] = a;
+  }
+  s.actions_log_prob[row] = lp;
+  s.values[row] = val_in[i];
+}
+
+}  // namespace urlg
+
+using namespace urlg;
+
+extern "C" int64_t urlg_policy_workspace_bytes(const urlg_policy_desc* desc) {
+  if (!desc) return fail(URLG_EINVAL, "urlg_policy_workspace_bytes: null desc");
+  urlg_policy tmp = {};
+  tmp.desc = *desc;
+  int64_t total = 0;
+  if (int rc = carve(&tmp, nullptr, &total)) return rc;
+  return total;
+}
+
+extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, float* grads, float* exp_avg,
+                                  float* exp_avg_sq, float* stats, void* workspace, int64_t workspace_bytes,
+                                  urlg_policy** out) {
+  if (!desc || !params || !grads || !exp_avg || !exp_avg_sq || !stats || !workspace || !out)
+    return fail(URLG_EINVAL, "urlg_policy_create: null argument");
+  if ((uintptr_t)workspace & 255) return fail(URLG_EINVAL, "urlg_policy_create: workspace must be 256-byte aligned");
+  urlg_policy* p = new (std::nothrow) urlg_policy();
+  if (!p) return fail(URLG_ENOMEM, "urlg_policy_create: out of host memory");
+  p->desc = *desc;
+  p->params = params; p->grads = grads; p->m = exp_avg; p->v = exp_avg_sq; p->stats = stats;
+  int64_t total = 0;
+  int rc = carve(p, static_cast<uint8_t*>(workspace), &total);
+  if (!rc && total > workspace_bytes) rc = fail(URLG_EINVAL, "urlg_policy_create: workspace too small (%lld < %lld)",
+                                                (long long)workspace_bytes, (long long)total);
+  if (rc) { delete p; return rc; }
+  *out = p;
+  return URLG_OK;
+}
+
+extern "C" void urlg_policy_destroy(urlg_policy* p) { delete p; }
+
+extern "C" int urlg_policy_sync_weights(urlg_policy* p, void* stream) {
+  if (!p) return fail(URLG_EINVAL, "urlg_policy_sync_weights: null policy");
+  return sync_weights(p, (cudaStream_t)stream);
+}
+
+namespace urlg {
+// lstm_kernels.cu: one rollout-mode LSTM step for Memory k (0 actor / 1 critic): saves the pre-step state
+// to (save_h, save_c) if given, h/c [rows,H] fp32 updated in place, bf16 h' staged as the head's input.
+int lstm_rollout_step(urlg_policy* p, int k, const float* x, int64_t rows, float* store_x, float* h, float* c,
+                      float* save_h, float* save_c, cudaStream_t st);
+}
+
+extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* critic_obs, const urlg_storage* s, int t,
+                               float* hidden, const float* noise, float* actions_out, const int64_t* step_base,
+                               int64_t step_offset, void* stream) {
+  if (!p || !obs || !s || !actions_out) return fail(URLG_EINVAL, "urlg_policy_act: null argument");
+  if (t < 0 || t >= s->T) return fail(URLG_EINVAL, "Rollout buffer overflow");
+  const urlg_policy_desc& d = p->desc;
+  const int N = s->N;
+  if (N > p->R) return fail(URLG_EINVAL, "urlg_policy_act: num_envs %d exceeds max_rows %d", N, p->R);
+  if (s->num_obs != d.num_actor_obs || s->num_actions != d.num_actions ||
+      (s->privileged_observations && s->num_priv != d.num_critic_obs))
+    return fail(URLG_EINVAL, "urlg_policy_act: storage shape does not match the policy");
+  cudaStream_t st = (cudaStream_t)stream;
+  const float* cobs = critic_obs ? critic_obs : obs;
+  float* store_o = s->observations + (size_t)t * N * s->num_obs;
+  float* store_p = s->privileged_observations ? s->privileged_observations + (size_t)t * N * s->num_priv : nullptr;
+  if (!d.recurrent) {
+    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
+    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
+  } else {
+    if (!hidden) return fail(URLG_EINVAL, "urlg_policy_act: recurrent policy needs hidden state");
+    const size_t HS = (size_t)N * d.rnn_hidden, slab = (size_t)t * HS;
+    if (!s->hid_a_h || !s->hid_a_c || !s->hid_c_h || !s->hid_c_c)
+      return fail(URLG_EINVAL, "urlg_policy_act: recurrent storage lacks saved hidden states");
+    if (int rc = lstm_rollout_step(p, 0, obs, N, store_o, hidden, hidden + HS, s->hid_a_h + slab, s->hid_a_c + slab, st)) return rc;
+    if (int rc = lstm_rollout_step(p, 1, cobs, N, store_p, hidden + 2 * HS, hidden + 3 * HS, s->hid_c_h + slab, s->hid_c_c + slab, st)) return rc;
+  }
+  if (int rc = mlp_forward(p, p->net[0], N, st)) return rc;
+  if (int rc = mlp_forward(p, p->net[1], N, st)) return rc;
+  sample_store_kernel<<<(N + 127) / 128, 128, 0, st>>>(p->net[0].out, p->net[1].out, p->params + d.std_off, noise, *s, t,
+                                                       actions_out, d.num_actions, d.seed_lo, d.seed_hi, d.env_offset,
+                                                       step_base, step_offset);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_policy_forward(urlg_policy* p, int which, const float* x, int64_t rows, float* hidden_h,
+                                   float* hidden_c, float* out, void* stream) {
+  if (!p || !x || !out || (which != 0 && which != 1)) return fail(URLG_EINVAL, "urlg_policy_forward: bad argument");
+  if (rows <= 0 || rows > p->R) return fail(URLG_EINVAL, "urlg_policy_forward: rows %lld outside 1..%d", (long long)rows, p->R);
+  cudaStream_t st = (cudaStream_t)stream;
+  const urlg_policy_desc& d = p->desc;
+  NetWs& n = p->net[which];
+  const int in = which == 0 ? d.num_actor_obs : d.num_critic_obs;
+  if (!d.recurrent) {
+    if (int rc = stage_obs(x, rows, in, nullptr, n.x, n.kpad[0], n.kpad[0], st)) return rc;
+  } else {
+    if (!hidden_h || !hidden_c) return fail(URLG_EINVAL, "urlg_policy_forward: recurrent policy needs hidden state");
+    if (int rc = lstm_rollout_step(p, which, x, rows, nullptr, hidden_h, hidden_c, nullptr, nullptr, st)) return rc;
+  }
+  if (int rc = mlp_forward(p, n, rows, st)) return rc;
+  URLG_CUDA(cudaMemcpyAsync(out, n.out, (size_t)rows * n.d.dims[n.d.num_layers] * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return URLG_OK;
+}

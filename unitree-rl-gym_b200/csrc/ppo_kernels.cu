@@ -1,0 +1,324 @@
+// PPO.update, one minibatch ([UPSTREAM rsl_rl v1.0.2] algorithms/ppo.py update, storage mini_batch_generator;
+// SURVEY.md §3.4, §8(a).6 R8/R10, kernels K6/K7):
+//   gather_obs_kernel   minibatch rows -> bf16 operand slabs (the other 7 tensors are read through the index
+//                       inside the loss head, never materialised)
+//   ppo_head_kernel     Gaussian log-prob / entropy / KL / clipped surrogate / clipped value loss and their
+//                       gradients wrt mu, value and std; last-layer bias gradients; loss sums
+//   backward            dgrad + wgrad on the tcgen05 GEMM (MN-major operands, ELU' and bias-gradient
+//                       column sums fused in the dgrad epilogue, split-K fp32 atomics for wgrad)
+//   apply               grad-norm, device-side adaptive-KL learning rate, clip, Adam, bf16 weight images
+#include "policy.cuh"
+
+namespace urlg {
+namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
+
+int lstm_update_forward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int env_count, cudaStream_t st);
+int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int env_count, cudaStream_t st);
+
+__device__ __forceinline__ int64_t row_index(const int64_t* __restrict__ indices, int64_t r, int N, int env_begin, int env_count) {
+  if (indices) return indices[r];
+  return (r / env_count) * (int64_t)N + env_begin + (r % env_count);
+}
+
+// ---------------------------------------------------------------- K6: gather
+__global__ void __launch_bounds__(256)
+gather_obs_kernel(const float* __restrict__ src, int cols, const int64_t* __restrict__ indices, int64_t rows,
+                  bf16* __restrict__ dst, int kpad) {
+  const int64_t total = rows * kpad;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / kpad;
+    const int c = (int)(i % kpad);
+    dst[i] = __float2bfloat16(c < cols ? src[indices[r] * cols + c] : 0.0f);
+  }
+}
+
+// ---------------------------------------------------------------- loss head
+constexpr int kHeadThreads = 256;
+constexpr int kMaxA = 32;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+
+__global__ void __launch_bounds__(kHeadThreads)
+ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_new, const float* __restrict__ std_param,
+                const urlg_storage s, const int64_t* __restrict__ indices, int64_t rows, int env_begin, int env_count,
+                const urlg_ppo_hparams hp, bf16* __restrict__ dmu, int ld_dmu, bf16* __restrict__ dval, int ld_dval,
+                float* __restrict__ g_std, float* __restrict__ g_bias_mu, float* __restrict__ g_bias_val,
+                float* __restrict__ stats) {
+  const int A = s.num_actions;
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const bool ok = r < rows;
+  const float inv_rows = 1.0f / (float)rows;
+  float kl = 0.0f, surr = 0.0f, vloss = 0.0f, ent = 0.0f, dv = 0.0f;
+  float dm[kMaxA], ds[kMaxA];
+#pragma unroll
+  for (int j = 0; j < kMaxA; ++j) { dm[j] = 0.0f; ds[j] = 0.0f; }
+  if (ok) {
+    const int64_t q = row_index(indices, r, s.N, env_begin, env_count);
+    float lp = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kMaxA; ++j) {
+      if (j < A) {
+        const float mu = mu_new[r * A + j], sd = std_param[j];
+        const float a = s.actions[q * A + j], mo = s.mu[q * A + j], so = s.sigma[q * A + j];
+        const float d = a - mu, var = sd * sd;
+        lp += -(d * d) / (2.0f * var) - logf(sd) - 0.918938533204672741780f;
+        ent += 0.5f + 0.918938533204672741780f + logf(sd);
+        kl += logf(sd / so + 1.e-5f) + (so * so + (mo - mu) * (mo - mu)) / (2.0f * var) - 0.5f;
+        dm[j] = d / var;                         // d logp / d mu
+        ds[j] = d * d / (var * sd) - 1.0f / sd;  // d logp / d sigma
+      }
+    }
+    const float adv = s.advantages[q], old_lp = s.actions_log_prob[q];
+    const float ratio = expf(lp - old_lp);
+    const float lo = 1.0f - hp.clip_param, hi = 1.0f + hp.clip_param;
+    const float rc = fminf(fmaxf(ratio, lo), hi);
+    const float s1 = -adv * ratio, s2 = -adv * rc;
+    surr = fmaxf(s1, s2);
+    // d max(s1,s2)/d ratio (torch.max splits ties evenly; clamp passes gradient on [lo,hi] inclusive)
+    const float in_rng = (ratio >= lo && ratio <= hi) ? 1.0f : 0.0f;
+    float dr;
+    if (s1 > s2) dr = -adv;
+    else if (s1 < s2) dr = -adv * in_rng;
+    else dr = 0.5f * (-adv) + 0.5f * (-adv) * in_rng;
+    const float dlp = dr * ratio * inv_rows;
+#pragma unroll
+    for (int j = 0; j < kMaxA; ++j) { dm[j] *= dlp; ds[j] *= dlp; }
+    const float v = val_new[r], ret = s.returns[q], vo = s.values[q];
+    if (hp.use_clipped_value_loss) {
+      const float dvv = v - vo;
+      const float vc = vo + fminf(fmaxf(dvv, -hp.clip_param), hp.clip_param);
+      const float l1 = (v - ret) * (v - ret), l2 = (vc - ret) * (vc - ret);
+      vloss = fmaxf(l1, l2);
+      const float in_v = (dvv >= -hp.clip_param && dvv <= hp.clip_param) ? 1.0f : 0.0f;
+      const float g1 = 2.0f * (v - ret), g2 = 2.0f * (vc - ret) * in_v;
+      dv = l1 > l2 ? g1 : (l1 < l2 ? g2 : 0.5f * g1 + 0.5f * g2);
+    } else {
+      vloss = (ret - v) * (ret - v);
+      dv = 2.0f * (v - ret);
+    }
+    dv *= hp.value_loss_coef * inv_rows;
+#pragma unroll
+    for (int j = 0; j < kMaxA; ++j)
+      if (j < A) dmu[r * ld_dmu + j] = __float2bfloat16(dm[j]);
+    for (int j = A; j < ld_dmu; ++j) dmu[r * ld_dmu + j] = __float2bfloat16(0.0f);
+    dval[r * ld_dval] = __float2bfloat16(dv);
+    for (int j = 1; j < ld_dval; ++j) dval[r * ld_dval + j] = __float2bfloat16(0.0f);
+  }
+  // block reductions -> atomics
+  __shared__ float red[kHeadThreads / 32][2 * kMaxA + 5];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  float t;
+  t = warp_sum(kl); if (l == 0) red[w][0] = t;
+  t = warp_sum(surr); if (l == 0) red[w][1] = t;
+  t = warp_sum(vloss); if (l == 0) red[w][2] = t;
+  t = warp_sum(ent); if (l == 0) red[w][3] = t;
+  t = warp_sum(dv); if (l == 0) red[w][4] = t;
+#pragma unroll
+  for (int j = 0; j < kMaxA; ++j) {
+    if (j < A) {
+      t = warp_sum(dm[j]); if (l == 0) red[w][5 + j] = t;
+      t = warp_sum(ds[j]); if (l == 0) red[w][5 + kMaxA + j] = t;
+    }
+  }
+  __syncthreads();
+  const int nslots = 5 + 2 * kMaxA;
+  for (int k = threadIdx.x; k < nslots; k += blockDim.x) {
+    if (k >= 5) { const int j = (k - 5) % kMaxA; if (j >= A) continue; }
+    float a = 0.0f;
+    for (int ww = 0; ww < kHeadThreads / 32; ++ww) a += red[ww][k];
+    if (k == 0) atomicAdd(stats + URLG_STAT_KL_SUM, a);
+    else if (k == 1) atomicAdd(stats + URLG_STAT_SURR_SUM, a);
+    else if (k == 2) atomicAdd(stats + URLG_STAT_VLOSS_SUM, a);
+    else if (k == 3) atomicAdd(stats + URLG_STAT_ENT_SUM, a);
+    else if (k == 4) atomicAdd(g_bias_val, a);
+    else if (k < 5 + kMaxA) atomicAdd(g_bias_mu + (k - 5), a);
+    else {
+      const int j = k - 5 - kMaxA;
+      if (blockIdx.x == 0) a += -hp.entropy_coef / std_param[j];   // d(-c_ent * mean entropy)/d sigma_j
+      atomicAdd(g_std + j, a);
+    }
+  }
+}
+
+}  // namespace urlg
+
+namespace urlg {
+
+// ---------------------------------------------------------------- MLP backward (dout already holds dL/d out)
+// Layer l: a_l = (l == 0 ? x : h[l]), G_l = dL/d(pre-activation of its output) = (l == L-1 ? dout : dz[l+1]).
+//   wgrad  dW_l[out,in] += G_l^T a_l          (A = G_l MN-major, B = a_l MN-major, split-K atomics)
+//   dgrad  dz[l] = (G_l W_l) * ELU'(h[l])     (B = W_l image MN-major), column sums -> db_{l-1}
+// dx_out (optional, bf16 [rows, dims[0]]): gradient wrt the network input (recurrent heads), no activation.
+int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st) {
+  const int L = n.d.num_layers;
+  for (int l = L - 1; l >= 0; --l) {
+    const bf16* G = l == L - 1 ? n.dout : n.dz[l + 1];
+    const int ldG = l == L - 1 ? n.opad : n.d.dims[l + 1];
+    const int nout = n.d.dims[l + 1], nin = n.d.dims[l];
+    {
+      urlg_gemm_desc g = {};
+      g.A = G; g.lda = ldG; g.a_mn = 1;
+      g.B = l == 0 ? (const void*)n.x : (const void*)n.h[l];
+      g.ldb = l == 0 ? n.kpad[0] : nin; g.b_mn = 1;
+      g.M = nout; g.N = nin; g.K = (int)rows;
+      g.out_f32 = p->grads + n.d.w_off[l]; g.ld_f32 = nin;
+      g.flags = URLG_GEMM_ATOMIC;
+      const int bn = nin > 256 ? 256 : round_up(nin, 64);
+      g.block_n = bn;
+      const int tiles = ((nout + 127) / 128) * ((nin + bn - 1) / bn);
+      int splits = (2 * kNumSMs + tiles - 1) / tiles;
+      const int kblocks = (int)((rows + 63) / 64);
+      if (splits > kblocks / 4) splits = kblocks / 4;
+      if (splits < 1) splits = 1;
+      g.k_splits = splits;
+      if (int rc = tc::launch_gemm(&g, st)) return rc;
+    }
+    if (l >= 1 || dx_out) {
+      urlg_gemm_desc g = {};
+      g.A = G; g.lda = ldG;
+      g.B = n.w[l]; g.ldb = n.kpad[l]; g.b_mn = 1;
+      g.M = (int)rows; g.N = nin; g.K = nout;
+      g.block_n = nin > 256 ? 256 : round_up(nin, 64);
+      if (l >= 1) {
+        g.out_bf16 = n.dz[l]; g.ld_bf16 = nin;
+        g.dact_ref = n.h[l]; g.ld_ref = nin;
+        g.colsum = p->grads + n.d.b_off[l - 1];
+      } else {
+        g.out_bf16 = dx_out; g.ld_bf16 = nin;
+      }
+      if (int rc = tc::launch_gemm(&g, st)) return rc;
+    }
+  }
+  return URLG_OK;
+}
+
+// ---------------------------------------------------------------- apply: norm, LR rule, clip, Adam
+__global__ void __launch_bounds__(256)
+grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ stats) {
+  float acc = 0.0f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float x = g[i] * scale;
+    acc += x * x;
+  }
+  acc = warp_sum(acc);
+  __shared__ float sh[8];
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.0f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) a += sh[k];
+    atomicAdd(stats + URLG_STAT_GNORM_SQ, a);
+  }
+}
+
+// One thread: the host-side scalar logic of PPO.update moved onto the device (no .item(), no KL branch sync).
+__global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hparams hp, float rows_total) {
+  float lr = stats[URLG_STAT_LR];
+  const float kl_mean = stats[URLG_STAT_KL_SUM] / rows_total;
+  stats[URLG_STAT_KL_MEAN] = kl_mean;
+  if (hp.adaptive_lr) {
+    if (kl_mean > hp.desired_kl * 2.0f) lr = fmaxf(hp.lr_min, lr / 1.5f);
+    else if (kl_mean < hp.desired_kl / 2.0f && kl_mean > 0.0f) lr = fminf(hp.lr_max, lr * 1.5f);
+  }
+  stats[URLG_STAT_LR] = lr;
+  const float step = stats[URLG_STAT_STEP] + 1.0f;
+  stats[URLG_STAT_STEP] = step;
+  stats[URLG_STAT_BC1] = 1.0f - powf(hp.beta1, step);
+  stats[URLG_STAT_BC2] = 1.0f - powf(hp.beta2, step);
+  const float total_norm = sqrtf(stats[URLG_STAT_GNORM_SQ]);
+  stats[URLG_STAT_CLIP_COEF] = hp.max_grad_norm > 0.0f ? fminf(hp.max_grad_norm / (total_norm + 1e-6f), 1.0f) : 1.0f;
+  stats[URLG_STAT_ACC_VLOSS] += stats[URLG_STAT_VLOSS_SUM] / rows_total;
+  stats[URLG_STAT_ACC_SURR] += stats[URLG_STAT_SURR_SUM] / rows_total;
+  stats[URLG_STAT_ACC_N] += 1.0f;
+}
+
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
+            const float* __restrict__ stats, const urlg_ppo_hparams hp) {
+  const float lr = stats[URLG_STAT_LR];
+  const float gs = hp.grad_scale * stats[URLG_STAT_CLIP_COEF];
+  const float step_size = lr / stats[URLG_STAT_BC1];
+  const float bc2_sqrt = sqrtf(stats[URLG_STAT_BC2]);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gs;
+    const float mi = m[i] + (gi - m[i]) * (1.0f - hp.beta1);          // exp_avg.lerp_(grad, 1-beta1)
+    const float vi = v[i] * hp.beta2 + (1.0f - hp.beta2) * gi * gi;   // mul_(beta2).addcmul_(grad, grad, 1-beta2)
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + hp.eps;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+
+__global__ void zero_minibatch_stats_kernel(float* stats) {
+  const int i = threadIdx.x;
+  if (i == URLG_STAT_KL_SUM || i == URLG_STAT_SURR_SUM || i == URLG_STAT_VLOSS_SUM || i == URLG_STAT_ENT_SUM ||
+      i == URLG_STAT_GNORM_SQ)
+    stats[i] = 0.0f;
+}
+
+}  // namespace urlg
+
+using namespace urlg;
+
+extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, const int64_t* indices, int64_t rows,
+                                        int32_t env_begin, int32_t env_count, const urlg_ppo_hparams* h, void* stream) {
+  if (!p || !s || !h) return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: null argument");
+  const urlg_policy_desc& d = p->desc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d.recurrent) {
+    if (env_count <= 0 || env_begin < 0 || env_begin + env_count > s->N)
+      return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: bad env slice [%d,+%d) of %d", env_begin, env_count, s->N);
+    rows = (int64_t)s->T * env_count;
+    indices = nullptr;
+  } else if (!indices || rows <= 0) {
+    return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: indices/rows are required for a feed-forward policy");
+  }
+  if (rows > p->R) return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: rows %lld exceed max_rows %d", (long long)rows, p->R);
+  URLG_CUDA(cudaMemsetAsync(p->grads, 0, (size_t)d.num_params * sizeof(float), st));
+  zero_minibatch_stats_kernel<<<1, 32, 0, st>>>(p->stats);
+  NetWs &na = p->net[0], &nc = p->net[1];
+  if (!d.recurrent) {
+    const float* cobs = s->privileged_observations ? s->privileged_observations : s->observations;
+    int blocks = (int)((rows * na.kpad[0] + 255) / 256);
+    gather_obs_kernel<<<blocks, 256, 0, st>>>(s->observations, d.num_actor_obs, indices, rows, na.x, na.kpad[0]);
+    blocks = (int)((rows * nc.kpad[0] + 255) / 256);
+    gather_obs_kernel<<<blocks, 256, 0, st>>>(cobs, d.num_critic_obs, indices, rows, nc.x, nc.kpad[0]);
+    URLG_LAUNCH_CHECK();
+  } else {
+    if (int rc = lstm_update_forward(p, 0, s, env_begin, env_count, st)) return rc;
+    if (int rc = lstm_update_forward(p, 1, s, env_begin, env_count, st)) return rc;
+  }
+  if (int rc = mlp_forward(p, na, rows, st)) return rc;
+  if (int rc = mlp_forward(p, nc, rows, st)) return rc;
+  ppo_head_kernel<<<(int)((rows + kHeadThreads - 1) / kHeadThreads), kHeadThreads, 0, st>>>(
+      na.out, nc.out, p->params + d.std_off, *s, indices, rows, env_begin, env_count, *h, na.dout, na.opad, nc.dout,
+      nc.opad, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
+      p->grads + nc.d.b_off[nc.d.num_layers - 1], p->stats);
+  URLG_LAUNCH_CHECK();
+  if (int rc = mlp_backward(p, na, rows, d.recurrent ? p->lstm[0].dx_head : nullptr, st)) return rc;
+  if (int rc = mlp_backward(p, nc, rows, d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
+  if (d.recurrent) {
+    if (int rc = lstm_update_backward(p, 0, s, env_begin, env_count, st)) return rc;
+    if (int rc = lstm_update_backward(p, 1, s, env_begin, env_count, st)) return rc;
+  }
+  p->last_rows = rows;
+  return URLG_OK;
+}
+
+extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* stream) {
+  if (!p || !h) return fail(URLG_EINVAL, "urlg_ppo_apply: null argument");
+  if (p->last_rows <= 0) return fail(URLG_EINVAL, "urlg_ppo_apply: no minibatch gradients pending");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n = p->desc.num_params;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+  grad_sumsq_kernel<<<blocks, 256, 0, st>>>(p->grads, n, h->grad_scale, p->stats);
+  ppo_scalars_kernel<<<1, 1, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale);
+  adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
+  URLG_LAUNCH_CHECK();
+  return sync_weights(p, st);
+}
