@@ -172,6 +172,12 @@ typedef struct urlg_gemm_desc {
   const void* dact_ref; int32_t ld_ref;   /* optional bf16 [M,N]: out *= ELU'(y), y = post-activation */
   float* colsum;                  /* optional [N]: += column sums of the stored values */
   int32_t flags;
+  /* split-bf16 ("bf16x3") mode, enabled when A_lo and B_lo are non-NULL: every operand is a (hi, lo) pair with
+   * x ~= hi + lo (lo = bf16(x - hi), same layout / ld as hi) and D = A_hi*B_hi + A_lo*B_hi + A_hi*B_lo, i.e. about
+   * 16 mantissa bits per operand on the bf16 tensor pipe (fp32 accumulate): what the 1e-3 PPO parity needs. */
+  const void* A_lo; const void* B_lo;
+  void* out_bf16_lo;              /* optional low part of out_bf16 */
+  const void* dact_ref_lo;        /* optional low part of dact_ref */
 } urlg_gemm_desc;
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 
@@ -204,6 +210,7 @@ typedef struct urlg_policy_desc {
   int32_t max_seq;                   /* recurrent: largest T of an update call */
   uint32_t seed_lo, seed_hi;         /* Philox key of the action-sampling stream */
   int64_t env_offset;                /* global id of local env 0 */
+  int32_t precision;                 /* 0: bf16 operands; 1: split bf16 (hi+lo, 3 MMAs, ~fp32 operand precision) */
 } urlg_policy_desc;
 
 /* RolloutStorage tensors ([UPSTREAM] storage/rollout_storage.py), time-major [T,N,...], fp32 unless noted. */

@@ -1,0 +1,339 @@
+"""Parity of the CUDA PPO half (through the C ABI, via the drop-in rsl_rl classes) against the oracle's
+restatement of rsl_rl v1.0.2 on the same seeded inputs.  Tolerances (north_star): returns / advantages
+1e-4; parameters after one PPO update 1e-3.  The tensor-core GEMMs run in split-bf16 ("bf16x3": hi+lo operand
+pairs, 3 MMAs, fp32 accumulate), measured at ~4e-6 forward / ~1e-5 gradient relative error against the fp32
+oracle (profiles/r1_ppo_parity_bf16x3.jsonl; plain bf16 for comparison in r1_ppo_parity_bf16.jsonl), so the
+intermediate quantities are held to 1e-4 / 1e-3 here."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+GO2 = dict(obs=48, priv=None, act=12, hidden=[512, 256, 128])
+ALG = dict(num_learning_epochs=5, num_mini_batches=4, clip_param=0.2, gamma=0.99, lam=0.95, value_loss_coef=1.0,
+           entropy_coef=0.01, learning_rate=1e-3, max_grad_norm=1.0, use_clipped_value_loss=True, schedule="adaptive",
+           desired_kl=0.01)
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, alg=ALG, seed=0, init_noise_std=1.0):
+    """(oracle PPO on CPU, product PPO on cuda) with identical parameters."""
+    from oracle import rsl_rl_port as O
+    from unitree_rl_gym_b200.rsl_rl import modules as M, algorithms as A
+    torch.manual_seed(seed)
+    n_c = n_priv if n_priv is not None else n_obs
+    if recurrent:
+        oac = O.ActorCriticRecurrent(n_obs, n_c, n_act, hidden, hidden, "elu", rnn_type="lstm", rnn_hidden_size=64,
+                                     rnn_num_layers=1, init_noise_std=init_noise_std)
+        pac = M.ActorCriticRecurrent(n_obs, n_c, n_act, hidden, hidden, "elu", rnn_type="lstm", rnn_hidden_size=64,
+                                     rnn_num_layers=1, init_noise_std=init_noise_std)
+    else:
+        oac = O.ActorCritic(n_obs, n_c, n_act, hidden, hidden, "elu", init_noise_std=init_noise_std)
+        pac = M.ActorCritic(n_obs, n_c, n_act, hidden, hidden, "elu", init_noise_std=init_noise_std)
+    pac.load_state_dict(copy.deepcopy(oac.state_dict()))
+    oppo = O.PPO(oac, device="cpu", **alg)
+    pppo = A.PPO(pac, device="cuda:0", **alg)
+    oppo.init_storage(N, T, [n_obs], [n_priv], [n_act])
+    pppo.init_storage(N, T, [n_obs], [n_priv], [n_act])
+    return oppo, pppo
+
+
+def rollout(oppo, pppo, N, T, n_obs, n_priv, n_act, seed=3, done_p=0.03, check=None):
+    """Drive both PPOs through T steps of a synthetic env (same obs / rewards / dones / noise)."""
+    g = torch.Generator().manual_seed(seed)
+    for t in range(T):
+        obs = torch.randn(N, n_obs, generator=g)
+        cobs = torch.randn(N, n_priv, generator=g) if n_priv is not None else obs
+        eps = torch.randn(N, n_act, generator=g)
+        oppo.sample_noise, pppo.sample_noise = eps, eps
+        with torch.no_grad():
+            a_o = oppo.act(obs, cobs)
+        a_p = pppo.act(obs.cuda(), cobs.cuda())
+        if check is not None:
+            check(t, a_o, a_p.cpu())
+        rew = torch.randn(N, generator=g)
+        dones = torch.rand(N, generator=g) < done_p
+        tos = dones & (torch.rand(N, generator=g) < 0.5)
+        with torch.no_grad():
+            oppo.process_env_step(rew, dones, {"time_outs": tos})
+        pppo.process_env_step(rew.cuda(), dones.cuda(), {"time_outs": tos.cuda()})
+    last = torch.randn(N, n_priv if n_priv is not None else n_obs, generator=g)
+    return last
+
+
+def copy_storage(src, dst):
+    """Make the product storage bit-identical to the oracle's (isolates the stage under test)."""
+    for name in ("observations", "privileged_observations", "actions", "mu", "sigma", "rewards", "values", "returns",
+                 "advantages", "actions_log_prob", "dones"):
+        s = getattr(src, name)
+        if s is not None:
+            getattr(dst, name).copy_(s)
+    if src.saved_hidden_states_a is not None:
+        for i in range(2):
+            dst.saved_hidden_states_a[i].copy_(src.saved_hidden_states_a[i])
+            dst.saved_hidden_states_c[i].copy_(src.saved_hidden_states_c[i])
+
+
+# ------------------------------------------------------------------ GAE (K5)
+@pytest.mark.parametrize("N,T", [(64, 24), (4097, 24), (1, 3), (300, 1)])
+def test_gae_matches_oracle(N, T):
+    from oracle.rsl_rl_port import RolloutStorage as ORS
+    from unitree_rl_gym_b200.rsl_rl.storage import RolloutStorage as PRS
+    g = torch.Generator().manual_seed(N + T)
+    o = ORS(N, T, [4], [None], [2], "cpu")
+    p = PRS(N, T, [4], [None], [2], "cuda:0")
+    o.rewards.copy_(torch.randn(T, N, 1, generator=g))
+    o.values.copy_(torch.randn(T, N, 1, generator=g))
+    o.dones.copy_((torch.rand(T, N, 1, generator=g) < 0.1).byte())
+    last = torch.randn(N, 1, generator=g)
+    copy_storage(o, p)
+    if N * T > 1:
+        o.compute_returns(last, 0.99, 0.95)
+        p.compute_returns(last.cuda(), 0.99, 0.95)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(p.returns.cpu().numpy(), o.returns.numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(p.advantages.cpu().numpy(), o.advantages.numpy(), rtol=1e-4, atol=1e-4)
+
+
+def test_gae_hand_case():
+    """T=3, N=2, one mid-rollout done: the hand-computable case of SURVEY.md §8c."""
+    from unitree_rl_gym_b200.rsl_rl.storage import RolloutStorage as PRS
+    p = PRS(2, 3, [1], [None], [1], "cuda:0")
+    r = torch.tensor([[1., 2.], [0.5, -1.], [2., 0.]]).view(3, 2, 1)
+    v = torch.tensor([[0.1, 0.2], [0.3, 0.4], [0.5, 0.6]]).view(3, 2, 1)
+    d = torch.tensor([[0, 0], [1, 0], [0, 0]], dtype=torch.uint8).view(3, 2, 1)
+    p.rewards.copy_(r), p.values.copy_(v), p.dones.copy_(d)
+    last = torch.tensor([[0.7], [0.8]])
+    gam, lam = 0.9, 0.8
+    ret = np.zeros((3, 2))
+    for e in range(2):
+        adv, nv = 0.0, float(last[e])
+        for t in (2, 1, 0):
+            nt = 1.0 - float(d[t, e])
+            delta = float(r[t, e]) + nt * gam * nv - float(v[t, e])
+            adv = delta + nt * gam * lam * adv
+            ret[t, e] = adv + float(v[t, e])
+            nv = float(v[t, e])
+    p.compute_returns(last.cuda(), gam, lam)
+    np.testing.assert_allclose(p.returns.cpu().numpy().reshape(3, 2), ret, rtol=1e-5)
+    a = ret - v.numpy().reshape(3, 2)
+    want = (a - a.mean()) / (a.std(ddof=1) + 1e-8)
+    np.testing.assert_allclose(p.advantages.cpu().numpy().reshape(3, 2), want, rtol=1e-4, atol=1e-6)
+
+
+# ------------------------------------------------------------------ rollout forward + store (K3/K4)
+@pytest.mark.parametrize("recurrent,n_obs,n_priv,n_act,hidden,N", [
+    (False, 48, None, 12, [512, 256, 128], 300),
+    (True, 47, 50, 12, [32], 257),
+    (True, 41, 44, 10, [32], 64),
+])
+def test_act_and_store_match_oracle(recurrent, n_obs, n_priv, n_act, hidden, N):
+    T = 6
+    oppo, pppo = make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, init_noise_std=0.8)
+    errs = []
+
+    def check(t, a_o, a_p):
+        errs.append(float((a_o - a_p).abs().max()))
+    rollout(oppo, pppo, N, T, n_obs, n_priv, n_act, check=check, done_p=0.1)
+    torch.cuda.synchronize()
+    so, sp = oppo.storage, pppo.storage
+    # exact copies
+    for name in ("observations", "privileged_observations", "dones"):
+        if getattr(so, name) is not None:
+            assert torch.equal(getattr(sp, name).cpu(), getattr(so, name)), name
+    # through the split-bf16 tensor-core GEMMs
+    for name, tol in (("mu", 1e-4), ("values", 1e-4), ("actions", 1e-4), ("actions_log_prob", 1e-3), ("rewards", 1e-4)):
+        a, b = getattr(sp, name).cpu().numpy(), getattr(so, name).numpy()
+        assert np.abs(a - b).max() < tol, (name, np.abs(a - b).max())
+    np.testing.assert_allclose(sp.sigma.cpu().numpy(), so.sigma.numpy(), rtol=1e-6)
+    if recurrent:
+        for i in range(2):
+            a, b = sp.saved_hidden_states_a[i].cpu().numpy(), so.saved_hidden_states_a[i].numpy()
+            assert np.abs(a - b).max() < 1e-4, ("hidden_a", i, np.abs(a - b).max())
+            a, b = sp.saved_hidden_states_c[i].cpu().numpy(), so.saved_hidden_states_c[i].numpy()
+            assert np.abs(a - b).max() < 1e-4, ("hidden_c", i, np.abs(a - b).max())
+    assert max(errs) < 1e-4
+
+
+def test_rollout_buffer_overflow_asserts():
+    oppo, pppo = make_pair(False, 8, None, 2, [16], 4, 1)
+    rollout(oppo, pppo, 4, 1, 8, None, 2)
+    with pytest.raises(AssertionError):
+        pppo.act(torch.zeros(4, 8).cuda(), torch.zeros(4, 8).cuda())
+
+
+# ------------------------------------------------------------------ LSTM known answers (motion.pt)
+@pytest.mark.parametrize("robot", ["g1", "h1", "h1_2"])
+def test_lstm_actor_matches_motion_pt(robot):
+    """The shipped TorchScript policies (deploy/pre_train/*/motion.pt, PolicyExporterLSTM exports of trained
+    rsl_rl models) through the fused LSTM + MLP actor: 8-step sequence with carried state."""
+    from unitree_rl_gym_b200.rsl_rl.modules import ActorCriticRecurrent
+    z = np.load(H.GOLDEN + "/motion_pt.npz")
+    sd = {k[len(robot) + 4:]: torch.from_numpy(z[k]) for k in z.files if k.startswith(robot + "/sd/")}
+    n_in, n_act = sd["memory.weight_ih_l0"].shape[1], sd["actor.2.weight"].shape[0]
+    ac = ActorCriticRecurrent(n_in, n_in, n_act, [32], [32], "elu", rnn_type="lstm", rnn_hidden_size=64, rnn_num_layers=1)
+    own = ac.state_dict()
+    for k in ("weight_ih_l0", "weight_hh_l0", "bias_ih_l0", "bias_hh_l0"):
+        own["memory_a.rnn." + k] = sd["memory." + k]
+    for k in ("actor.0.weight", "actor.0.bias", "actor.2.weight", "actor.2.bias"):
+        own[k] = sd[k]
+    ac.load_state_dict(own)
+    ac.to("cuda:0")
+    seq_in, seq_out = torch.from_numpy(z[robot + "/seq_in"]), z[robot + "/seq_out"]
+    outs = []
+    for t in range(seq_in.shape[0]):
+        outs.append(ac.act_inference(seq_in[t].cuda()).cpu().numpy())
+    got = np.stack(outs)
+    err = np.abs(got - seq_out)
+    assert err.max() < 1e-4, err.max()      # split-bf16 operands, fp32 accumulate, 8 recurrent steps
+
+
+# ------------------------------------------------------------------ one minibatch: gradients (K6/K7/K8)
+def oracle_minibatch_grads(oppo, perm_or_none):
+    """Gradients of the first minibatch of the oracle's update loop (loss.backward only)."""
+    ac = oppo.actor_critic
+    if ac.is_recurrent:
+        gen = oppo.storage.reccurent_mini_batch_generator(oppo.num_mini_batches, 1)
+    else:
+        gen = oppo.storage.mini_batch_generator(oppo.num_mini_batches, 1, perm_or_none)
+    (obs_b, cobs_b, act_b, tv_b, adv_b, ret_b, olp_b, omu_b, osig_b, hid_b, masks_b) = next(gen)
+    ac.act(obs_b, masks=masks_b, hidden_states=hid_b[0])
+    lp = ac.get_actions_log_prob(act_b)
+    val = ac.evaluate(cobs_b, masks=masks_b, hidden_states=hid_b[1])
+    ent = ac.entropy
+    ratio = torch.exp(lp - torch.squeeze(olp_b))
+    s1 = -torch.squeeze(adv_b) * ratio
+    s2 = -torch.squeeze(adv_b) * torch.clamp(ratio, 1 - oppo.clip_param, 1 + oppo.clip_param)
+    surr = torch.max(s1, s2).mean()
+    vc = tv_b + (val - tv_b).clamp(-oppo.clip_param, oppo.clip_param)
+    vl = torch.max((val - ret_b).pow(2), (vc - ret_b).pow(2)).mean()
+    loss = surr + oppo.value_loss_coef * vl - oppo.entropy_coef * ent.mean()
+    oppo.optimizer.zero_grad()
+    loss.backward()
+    return {n: p.grad.detach().clone() for n, p in ac.named_parameters()}, float(surr), float(vl)
+
+
+@pytest.mark.parametrize("recurrent,n_obs,n_priv,n_act,hidden,N,T", [
+    (False, 48, None, 12, [512, 256, 128], 512, 24),
+    (False, 48, None, 12, [512, 256, 128], 130, 7),
+    (True, 47, 50, 12, [32], 256, 24),
+    (True, 41, 44, 10, [32], 68, 9),
+])
+def test_minibatch_gradients_match_oracle(recurrent, n_obs, n_priv, n_act, hidden, N, T):
+    import ctypes as C
+    from unitree_rl_gym_b200 import _lib
+    oppo, pppo = make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, init_noise_std=0.8)
+    last = rollout(oppo, pppo, N, T, n_obs, n_priv, n_act, done_p=0.05)
+    with torch.no_grad():
+        oppo.compute_returns(last)
+    copy_storage(oppo.storage, pppo.storage)
+    # perturb the policy so that ratio != 1 and the clip branches are exercised
+    torch.manual_seed(5)
+    with torch.no_grad():
+        for p in oppo.actor_critic.parameters():
+            p.add_(0.02 * torch.randn_like(p) * p.abs().mean())
+    pppo.actor_critic.load_state_dict(copy.deepcopy(oppo.actor_critic.state_dict()))
+    mini = (N * T) // oppo.num_mini_batches
+    perm = torch.randperm(oppo.num_mini_batches * mini, generator=torch.Generator().manual_seed(1))
+    want, surr, vl = oracle_minibatch_grads(oppo, perm)
+    eng, s, h = pppo._check_engine(), pppo.storage, pppo._hparams()
+    if recurrent:
+        mb = N // pppo.num_mini_batches
+        args = (None, 0, 0, mb)
+        rows = T * mb
+    else:
+        ind = perm[:mini].cuda().contiguous()
+        args = (_lib.ptr(ind), mini, 0, 0)
+        rows = mini
+    _lib.check(_lib.lib().urlg_ppo_minibatch_grads(eng.handle, C.byref(s.desc()), *args, C.byref(h), _lib.cur_stream()))
+    torch.cuda.synchronize()
+    st = eng.stats.cpu().numpy()
+    assert abs(st[_lib.STAT_SURR_SUM] / rows - surr) < 1e-4 + 1e-4 * abs(surr)
+    assert abs(st[_lib.STAT_VLOSS_SUM] / rows - vl) < 1e-4 * abs(vl) + 1e-5
+    got = {n: p.grad.detach().cpu() for n, p in pppo.actor_critic.named_parameters()}
+    report = {n: rel_l2(got[n].numpy(), want[n].numpy()) for n in want}
+    worst = max(report.values())
+    assert worst < 1e-3, report      # measured ~1e-5 (split-bf16 operands, fp32 accumulate, atomics order)
+
+
+# ------------------------------------------------------------------ one full PPO update (north_star: 1e-3)
+@pytest.mark.parametrize("recurrent,n_obs,n_priv,n_act,hidden,N,T", [
+    (False, 48, None, 12, [512, 256, 128], 256, 24),
+    (True, 47, 50, 12, [32], 128, 24),
+])
+def test_one_update_matches_oracle(recurrent, n_obs, n_priv, n_act, hidden, N, T):
+    oppo, pppo = make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, init_noise_std=0.8)
+    last = rollout(oppo, pppo, N, T, n_obs, n_priv, n_act, done_p=0.05)
+    with torch.no_grad():
+        oppo.compute_returns(last)
+    copy_storage(oppo.storage, pppo.storage)
+    before = {n: p.detach().clone() for n, p in oppo.actor_critic.named_parameters()}
+    mini = (N * T) // oppo.num_mini_batches
+    perm = torch.randperm(oppo.num_mini_batches * mini, generator=torch.Generator().manual_seed(2))
+    oppo.perm, pppo.perm = perm, perm
+    ov, osur = oppo.update()
+    pv, psur = pppo.update()
+    torch.cuda.synchronize()
+    assert abs(pv - ov) < 1e-4 * abs(ov) + 1e-5 and abs(psur - osur) < 1e-4
+    # the device-side adaptive-KL rule took the same LR decisions as the oracle's host branch
+    assert abs(pppo.learning_rate - oppo.learning_rate) < 1e-9 + 1e-6 * oppo.learning_rate, \
+        (pppo.learning_rate, oppo.learning_rate, oppo.lr_trace)
+    worst = 0.0
+    for n, p in pppo.actor_critic.named_parameters():
+        a, b = p.detach().cpu().numpy(), dict(oppo.actor_critic.named_parameters())[n].detach().numpy()
+        assert rel_l2(a, b) < 1e-3, (n, rel_l2(a, b))                       # parameter vector, relative L2
+        d = np.abs(a - b)
+        worst = max(worst, d.max())
+        moved = np.abs(b - before[n].numpy()).max()
+        assert moved > 1e-3, (n, moved)                                     # the update did move this tensor
+    assert worst <= 1e-3, worst                                             # north_star: every parameter within 1e-3
+
+
+# ------------------------------------------------------------------ drop-in runner end to end
+@pytest.mark.parametrize("task", ["go2", "g1"])
+def test_runner_learn_save_load(task, tmp_path):
+    import bench
+    from unitree_rl_gym_b200.rsl_rl.runners import OnPolicyRunner
+    from unitree_rl_gym_b200.legged_gym.envs import robot_configs as rc
+    from unitree_rl_gym_b200.legged_gym.utils.helpers import class_to_dict
+    n = 256
+    spec, frames = bench.make_frames(task, n, 4)
+    env, cfg = bench.make_env(task, n, frames, "cuda:0")
+    tcfg = {"go2": rc.GO2RoughCfgPPO, "g1": rc.G1RoughCfgPPO}[task]()
+    runner = OnPolicyRunner(env, class_to_dict(tcfg), log_dir=str(tmp_path), device="cuda:0")
+    runner.learn(2, init_at_random_ep_len=True)
+    st = runner.last_stats
+    assert np.isfinite(st["mean_value_loss"]) and np.isfinite(st["mean_surrogate_loss"])
+    for p in runner.alg.actor_critic.parameters():
+        assert torch.isfinite(p).all()
+    path = str(tmp_path / "model_2.pt")
+    ck = torch.load(path, weights_only=False)
+    assert set(ck) == {"model_state_dict", "optimizer_state_dict", "iter", "infos"}
+    assert "actor.0.weight" in ck["model_state_dict"] and "std" in ck["model_state_dict"]
+    # the checkpoint loads into the oracle's (reference-layout) modules and torch.optim.Adam
+    from oracle import rsl_rl_port as O
+    pc = class_to_dict(tcfg)["policy"]
+    ncrit = env.num_privileged_obs if env.num_privileged_obs is not None else env.num_obs
+    cls = O.ActorCriticRecurrent if task == "g1" else O.ActorCritic
+    oac = cls(env.num_obs, ncrit, env.num_actions, **pc)
+    oac.load_state_dict({k: v.cpu() for k, v in ck["model_state_dict"].items()})
+    opt = torch.optim.Adam(oac.parameters(), lr=1e-3)
+    opt.load_state_dict(ck["optimizer_state_dict"])
+    # and back into a fresh runner
+    env2, _ = bench.make_env(task, n, frames, "cuda:0")
+    r2 = OnPolicyRunner(env2, class_to_dict(tcfg), log_dir=None, device="cuda:0")
+    r2.load(path)
+    for (n1, p1), (n2, p2) in zip(runner.alg.actor_critic.named_parameters(), r2.alg.actor_critic.named_parameters()):
+        assert torch.equal(p1, p2), n1
+    policy = r2.get_inference_policy(device="cuda:0")
+    a = policy(env2.get_observations())
+    assert a.shape == (n, env.num_actions) and torch.isfinite(a).all()

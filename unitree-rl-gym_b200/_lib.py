@@ -68,6 +68,7 @@ class GemmDesc(C.Structure):
         ("block_n", C.c_int32), ("k_splits", C.c_int32),
         ("out_f32", _P), ("ld_f32", C.c_int32), ("out_bf16", _P), ("ld_bf16", C.c_int32),
         ("bias", _P), ("dact_ref", _P), ("ld_ref", C.c_int32), ("colsum", _P), ("flags", C.c_int32),
+        ("A_lo", _P), ("B_lo", _P), ("out_bf16_lo", _P), ("dact_ref_lo", _P),
     ]
 
 
@@ -86,7 +87,7 @@ class PolicyDesc(C.Structure):
                 ("actor", MlpDesc), ("critic", MlpDesc), ("std_off", C.c_int64),
                 ("lstm_a_off", C.c_int64 * 4), ("lstm_c_off", C.c_int64 * 4), ("num_params", C.c_int64),
                 ("max_rows", C.c_int32), ("max_seq", C.c_int32), ("seed_lo", C.c_uint32), ("seed_hi", C.c_uint32),
-                ("env_offset", C.c_int64)]
+                ("env_offset", C.c_int64), ("precision", C.c_int32)]
 
 
 class Storage(C.Structure):

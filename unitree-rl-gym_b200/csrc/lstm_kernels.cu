@@ -17,7 +17,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf
 __global__ void __launch_bounds__(256)
 lstm_stage_rollout_kernel(const float* __restrict__ x, int64_t rows, int in, int in_pad, int H, float* __restrict__ store_x,
                           const float* __restrict__ h, const float* __restrict__ c, float* __restrict__ save_h,
-                          float* __restrict__ save_c, bf16* __restrict__ xcat) {
+                          float* __restrict__ save_c, bf16* __restrict__ xcat, int64_t lo_off) {
   const int kcat = in_pad + H;
   const int64_t total = rows * kcat;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -32,7 +32,7 @@ lstm_stage_rollout_kernel(const float* __restrict__ x, int64_t rows, int in, int
       v = h[r * H + j];
       if (save_h) { save_h[r * H + j] = v; save_c[r * H + j] = c[r * H + j]; }
     }
-    xcat[i] = __float2bfloat16(v);
+    store_split(xcat, lo_off, (size_t)i, v);
   }
 }
 
@@ -42,28 +42,29 @@ lstm_stage_update_kernel(const float* __restrict__ obs /* [T,N,in] */, int in, i
                          int env_count, const uint8_t* __restrict__ dones, const float* __restrict__ saved_h,
                          const float* __restrict__ saved_c, bf16* __restrict__ xcat /* rows of step t */,
                          const bf16* __restrict__ headx_prev /* h' of step t-1 [env_count,H] */,
-                         float* __restrict__ c_prev /* rows of step t */, const float* __restrict__ c_new_prev /* step t-1 */) {
+                         float* __restrict__ c_prev /* rows of step t */, const float* __restrict__ c_new_prev /* step t-1 */,
+                         int64_t lo_off) {
   const int kcat = in_pad + H;
   const int64_t total = (int64_t)env_count * kcat;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int e = (int)(i / kcat), col = (int)(i % kcat);
     const int env = env_begin + e;
-    bf16 v = __float2bfloat16(0.0f);
+    float v = 0.0f;
     if (col < in) {
-      v = __float2bfloat16(obs[((size_t)t * N + env) * in + col]);
+      v = obs[((size_t)t * N + env) * in + col];
     } else if (col >= in_pad) {
       const int j = col - in_pad;
       const bool reseed = t == 0 || dones[(size_t)(t - 1) * N + env] != 0;
       const size_t sv = ((size_t)t * N + env) * H + j;
       if (reseed) {
-        v = __float2bfloat16(saved_h[sv]);
+        v = saved_h[sv];
         c_prev[(size_t)e * H + j] = saved_c[sv];
       } else {
-        v = headx_prev[(size_t)e * H + j];
+        v = load_split(headx_prev, lo_off, (size_t)e * H + j);
         c_prev[(size_t)e * H + j] = c_new_prev[(size_t)e * H + j];
       }
     }
-    xcat[i] = v;
+    store_split(xcat, lo_off, (size_t)i, v);
   }
 }
 
@@ -71,7 +72,7 @@ lstm_stage_update_kernel(const float* __restrict__ obs /* [T,N,in] */, int in, i
 // gates: pre-activations in, activated (i,f,g,o) out (kept for the backward pass).
 __global__ void __launch_bounds__(256)
 lstm_cell_kernel(float* __restrict__ gates, int64_t rows, int H, const float* c_prev, float* c_new,
-                 float* __restrict__ h_out, bf16* __restrict__ headx, int ld_headx) {
+                 float* __restrict__ h_out, bf16* __restrict__ headx, int ld_headx, int64_t lo_off) {
   const int64_t total = rows * H;
   for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = idx / H;
@@ -83,7 +84,7 @@ lstm_cell_kernel(float* __restrict__ gates, int64_t rows, int H, const float* c_
     g[j] = i; g[H + j] = f; g[2 * H + j] = gg; g[3 * H + j] = o;
     c_new[idx] = c;
     if (h_out) h_out[idx] = h;
-    headx[r * ld_headx + j] = __float2bfloat16(h);
+    store_split(headx, lo_off, (size_t)(r * ld_headx + j), h);
   }
 }
 
@@ -93,7 +94,7 @@ lstm_cell_backward_kernel(const float* __restrict__ gates, int rows, int H, cons
                           const float* __restrict__ c_new, const bf16* __restrict__ dh_head, const float* __restrict__ dh_rec,
                           float* __restrict__ dc /* in: dL/dc_new from t+1, out: dL/dc_prev */,
                           const uint8_t* __restrict__ cut /* dones[t] of the slice: 1 = no gradient from t+1 */, int has_next,
-                          bf16* __restrict__ dgates, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh) {
+                          bf16* __restrict__ dgates, int64_t lo_off, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh) {
   extern __shared__ float acc[];   // [4H]
   for (int k = threadIdx.x; k < 4 * H; k += blockDim.x) acc[k] = 0.0f;
   __syncthreads();
@@ -102,7 +103,7 @@ lstm_cell_backward_kernel(const float* __restrict__ gates, int rows, int H, cons
   if (idx < total) {
     const int r = idx / H, j = idx % H;
     const bool carry = has_next && !cut[r];
-    const float dh = __bfloat162float(dh_head[idx]) + (carry ? dh_rec[idx] : 0.0f);
+    const float dh = load_split(dh_head, lo_off, (size_t)idx) + (carry ? dh_rec[idx] : 0.0f);
     const float dcn_in = carry ? dc[idx] : 0.0f;
     const float* g = gates + (size_t)r * 4 * H;
     const float i = g[j], f = g[H + j], gg = g[2 * H + j], o = g[3 * H + j];
@@ -113,8 +114,8 @@ lstm_cell_backward_kernel(const float* __restrict__ gates, int rows, int H, cons
     dc[idx] = dcn * f;
     const float pi = di * i * (1.0f - i), pf = df * f * (1.0f - f), pg = dg * (1.0f - gg * gg), po = d_o * o * (1.0f - o);
     bf16* dgr = dgates + (size_t)r * 4 * H;
-    dgr[j] = __float2bfloat16(pi); dgr[H + j] = __float2bfloat16(pf);
-    dgr[2 * H + j] = __float2bfloat16(pg); dgr[3 * H + j] = __float2bfloat16(po);
+    store_split(dgr, lo_off, j, pi); store_split(dgr, lo_off, H + j, pf);
+    store_split(dgr, lo_off, 2 * H + j, pg); store_split(dgr, lo_off, 3 * H + j, po);
     atomicAdd(acc + j, pi); atomicAdd(acc + H + j, pf); atomicAdd(acc + 2 * H + j, pg); atomicAdd(acc + 3 * H + j, po);
   }
   __syncthreads();
@@ -136,6 +137,7 @@ static int gates_gemm(urlg_policy* p, LstmWs& w, const bf16* xcat, float* gates,
   g.M = (int)rows; g.N = 4 * w.H; g.K = w.kcat;
   g.bias = w.bias;
   g.out_f32 = gates; g.ld_f32 = 4 * w.H;
+  with_lo(p, g);
   return tc::launch_gemm(&g, st);
 }
 
@@ -144,10 +146,10 @@ int lstm_rollout_step(urlg_policy* p, int k, const float* x, int64_t rows, float
   LstmWs& w = p->lstm[k];
   NetWs& n = p->net[k];
   lstm_stage_rollout_kernel<<<blocks_for(rows * w.kcat), 256, 0, st>>>(x, rows, w.in, w.in_pad, w.H, store_x, h, c, save_h,
-                                                                       save_c, w.xcat);
+                                                                       save_c, w.xcat, p->lo_off);
   URLG_LAUNCH_CHECK();
   if (int rc = gates_gemm(p, w, w.xcat, w.gates, rows, st)) return rc;
-  lstm_cell_kernel<<<blocks_for(rows * w.H), 256, 0, st>>>(w.gates, rows, w.H, c, c, h, n.x, n.kpad[0]);
+  lstm_cell_kernel<<<blocks_for(rows * w.H), 256, 0, st>>>(w.gates, rows, w.H, c, c, h, n.x, n.kpad[0], p->lo_off);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }
@@ -174,11 +176,11 @@ int lstm_update_forward(urlg_policy* p, int k, const urlg_storage* s, int env_be
     const size_t ro = (size_t)t * E;
     lstm_stage_update_kernel<<<blocks_for((int64_t)E * w.kcat), 256, 0, st>>>(
         obs, in, w.in_pad, H, t, s->N, env_begin, E, s->dones, sh, sc, w.xcat + ro * w.kcat,
-        t ? n.x + (ro - E) * n.kpad[0] : nullptr, c_prev + ro * H, t ? c_new + (ro - E) * H : nullptr);
+        t ? n.x + (ro - E) * n.kpad[0] : nullptr, c_prev + ro * H, t ? c_new + (ro - E) * H : nullptr, p->lo_off);
     URLG_LAUNCH_CHECK();
     if (int rc = gates_gemm(p, w, w.xcat + ro * w.kcat, w.gates + ro * 4 * H, E, st)) return rc;
     lstm_cell_kernel<<<blocks_for((int64_t)E * H), 256, 0, st>>>(w.gates + ro * 4 * H, E, H, c_prev + ro * H, c_new + ro * H,
-                                                                  nullptr, n.x + ro * n.kpad[0], n.kpad[0]);
+                                                                  nullptr, n.x + ro * n.kpad[0], n.kpad[0], p->lo_off);
     URLG_LAUNCH_CHECK();
   }
   return URLG_OK;
@@ -194,7 +196,7 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
     const size_t ro = (size_t)t * E;
     lstm_cell_backward_kernel<<<(total + 255) / 256, 256, 4 * H * sizeof(float), st>>>(
         w.gates + ro * 4 * H, E, H, c_prev + ro * H, c_new + ro * H, w.dx_head + ro * H, w.dhrec, w.dc,
-        s->dones + (size_t)t * s->N + env_begin, t < T - 1 ? 1 : 0, w.dgates + ro * 4 * H, p->grads + w.off[2],
+        s->dones + (size_t)t * s->N + env_begin, t < T - 1 ? 1 : 0, w.dgates + ro * 4 * H, p->lo_off, p->grads + w.off[2],
         p->grads + w.off[3]);
     URLG_LAUNCH_CHECK();
     if (t > 0) {   // dL/dh_{t-1} (recurrent part) = dgates_t * W_hh
@@ -204,6 +206,7 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
       g.M = E; g.N = H; g.K = 4 * H;
       g.block_n = round_up(H, 64);
       g.out_f32 = w.dhrec; g.ld_f32 = H;
+      with_lo(p, g);
       if (int rc = tc::launch_gemm(&g, st)) return rc;
     }
   }
@@ -221,6 +224,7 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
     const int kblocks = (T * E + 63) / 64;
     if (splits > kblocks / 4) splits = kblocks / 4;
     g.k_splits = splits < 1 ? 1 : splits;
+    with_lo(p, g);
     if (int rc = tc::launch_gemm(&g, st)) return rc;
   }
   return URLG_OK;

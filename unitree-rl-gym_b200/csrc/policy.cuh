@@ -49,12 +49,32 @@ struct urlg_policy {
   int R;                             // max rows
   int T;                             // max sequence length (recurrent update)
   float* red;                        // small fp32 scratch (head reductions)
+  int64_t lo_off;                    // split precision: element offset from a bf16 slab to its low-part twin (0 = off)
   int64_t last_rows;                 // rows of the pending minibatch gradient (set by minibatch_grads)
 };
 
 namespace urlg {
+// (hi, lo) split of an fp32 value over two bf16 slabs `lo_off` elements apart (lo_off == 0: plain bf16).
+__device__ __forceinline__ void store_split(bf16* p, int64_t lo_off, size_t i, float v) {
+  const bf16 h = __float2bfloat16(v);
+  p[i] = h;
+  if (lo_off) p[i + lo_off] = __float2bfloat16(v - __bfloat162float(h));
+}
+__device__ __forceinline__ float load_split(const bf16* p, int64_t lo_off, size_t i) {
+  float v = __bfloat162float(p[i]);
+  if (lo_off) v += __bfloat162float(p[i + lo_off]);
+  return v;
+}
+// Fill the low-part operand pointers of a GEMM whose bf16 operands live in the policy workspace.
+inline void with_lo(const urlg_policy* p, urlg_gemm_desc& g) {
+  if (!p->lo_off) return;
+  g.A_lo = static_cast<const bf16*>(g.A) + p->lo_off;
+  g.B_lo = static_cast<const bf16*>(g.B) + p->lo_off;
+  if (g.out_bf16) g.out_bf16_lo = static_cast<bf16*>(g.out_bf16) + p->lo_off;
+  if (g.dact_ref) g.dact_ref_lo = static_cast<const bf16*>(g.dact_ref) + p->lo_off;
+}
 int sync_weights(urlg_policy* p, cudaStream_t st);
 int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st);
 int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);
-int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int kpad, int ld, cudaStream_t st);
+int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld, cudaStream_t st);
 }

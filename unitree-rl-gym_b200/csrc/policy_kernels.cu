@@ -10,10 +10,15 @@ namespace urlg {
 namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
 
 // ---------------------------------------------------------------- workspace carving
+// bf16 slabs come from their own region so that, in split precision, the whole region can be duplicated
+// (hi half, then lo half `off16` bytes later); everything else comes from the fp32 region behind it.
 struct Carver {
-  uint8_t* base; int64_t off;
+  uint8_t *base16, *base32; int64_t off16, off32;
   template <typename T> T* take(int64_t n) {
-    off = (off + 255) & ~int64_t(255);
+    constexpr bool is16 = sizeof(T) == 2;
+    int64_t& off = is16 ? off16 : off32;
+    uint8_t* base = is16 ? base16 : base32;
+    off = (off + 1023) & ~int64_t(1023);
     T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
     off += n * (int64_t)sizeof(T);
     return p;
@@ -57,11 +62,26 @@ static void carve_lstm(Carver& c, LstmWs& w, int in, int H, const int64_t* off, 
   w.dx_head = c.take<bf16>((int64_t)R * H);
 }
 
+static int carve_pass(urlg_policy* p, Carver& c);
+
 static int carve(urlg_policy* p, uint8_t* base, int64_t* total) {
+  Carver c{nullptr, nullptr, 0, 0};
+  if (int rc = carve_pass(p, c)) return rc;
+  const int64_t s16 = (c.off16 + 1023) & ~int64_t(1023), s32 = (c.off32 + 1023) & ~int64_t(1023);
+  const int copies = p->desc.precision ? 2 : 1;
+  p->lo_off = p->desc.precision ? s16 / 2 : 0;      // in bf16 elements
+  *total = copies * s16 + s32;
+  if (base) {
+    Carver d{base, base + copies * s16, 0, 0};
+    return carve_pass(p, d);
+  }
+  return URLG_OK;
+}
+
+static int carve_pass(urlg_policy* p, Carver& c) {
   const urlg_policy_desc& d = p->desc;
   if (d.max_rows <= 0) return fail(URLG_EINVAL, "policy: max_rows must be positive");
   if (d.num_actions <= 0 || d.num_actions > 32) return fail(URLG_EINVAL, "policy: num_actions=%d unsupported (1..32)", d.num_actions);
-  Carver c{base, 0};
   p->R = d.max_rows;
   p->T = d.max_seq > 0 ? d.max_seq : 1;
   if (int rc = carve_net(c, p->net[0], d.actor, p->R)) return rc;
@@ -78,17 +98,17 @@ static int carve(urlg_policy* p, uint8_t* base, int64_t* total) {
     return fail(URLG_EINVAL, "policy: MLP input widths must equal the observation widths");
   }
   p->red = c.take<float>(256);
-  *total = (c.off + 255) & ~int64_t(255);
   return URLG_OK;
 }
 
 // ---------------------------------------------------------------- bf16 weight images
 __global__ void __launch_bounds__(256)
-weight_image_kernel(bf16* __restrict__ dst, const float* __restrict__ src, int rows, int cols, int kpad, int dst_col0, int ld) {
+weight_image_kernel(bf16* __restrict__ dst, int64_t lo_off, const float* __restrict__ src, int rows, int cols, int kpad,
+                    int dst_col0, int ld) {
   const int64_t total = (int64_t)rows * kpad;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int r = (int)(i / kpad), c = (int)(i % kpad);
-    dst[(size_t)r * ld + dst_col0 + c] = __float2bfloat16(c < cols ? src[(size_t)r * cols + c] : 0.0f);
+    store_split(dst, lo_off, (size_t)r * ld + dst_col0 + c, c < cols ? src[(size_t)r * cols + c] : 0.0f);
   }
 }
 __global__ void bias_sum_kernel(float* __restrict__ dst, const float* __restrict__ a, const float* __restrict__ b, int n) {
@@ -102,14 +122,14 @@ int sync_weights(urlg_policy* p, cudaStream_t st) {
     for (int l = 0; l < n.d.num_layers; ++l) {
       const int rows = n.d.dims[l + 1], cols = n.d.dims[l];
       const int64_t total = (int64_t)rows * n.kpad[l];
-      weight_image_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(n.w[l], p->params + n.d.w_off[l], rows, cols,
+      weight_image_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(n.w[l], p->lo_off, p->params + n.d.w_off[l], rows, cols,
                                                                       n.kpad[l], 0, n.kpad[l]);
     }
     if (p->desc.recurrent) {
       LstmWs& w = p->lstm[k];
       const int G = 4 * w.H;
-      weight_image_kernel<<<(G * w.in_pad + 255) / 256, 256, 0, st>>>(w.w, p->params + w.off[0], G, w.in, w.in_pad, 0, w.kcat);
-      weight_image_kernel<<<(G * w.H + 255) / 256, 256, 0, st>>>(w.w, p->params + w.off[1], G, w.H, w.H, w.in_pad, w.kcat);
+      weight_image_kernel<<<(G * w.in_pad + 255) / 256, 256, 0, st>>>(w.w, p->lo_off, p->params + w.off[0], G, w.in, w.in_pad, 0, w.kcat);
+      weight_image_kernel<<<(G * w.H + 255) / 256, 256, 0, st>>>(w.w, p->lo_off, p->params + w.off[1], G, w.H, w.H, w.in_pad, w.kcat);
       bias_sum_kernel<<<(G + 255) / 256, 256, 0, st>>>(w.bias, p->params + w.off[2], p->params + w.off[3], G);
     }
   }
@@ -130,6 +150,7 @@ int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st) {
     g.bias = p->params + n.d.b_off[l];
     if (l + 1 < L) { g.out_bf16 = n.h[l + 1]; g.ld_bf16 = n.d.dims[l + 1]; g.flags = URLG_GEMM_ELU; }
     else { g.out_f32 = n.out; g.ld_f32 = n.d.dims[L]; }
+    with_lo(p, g);
     if (int rc = tc::launch_gemm(&g, st)) return rc;
   }
   return URLG_OK;
@@ -138,7 +159,7 @@ int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st) {
 // ---------------------------------------------------------------- prep: obs -> storage slab + bf16 staging
 __global__ void __launch_bounds__(256)
 stage_obs_kernel(const float* __restrict__ src, int64_t rows, int cols, float* __restrict__ store, bf16* __restrict__ dst,
-                 int kpad, int ld) {
+                 int64_t lo_off, int kpad, int ld) {
   const int64_t total = rows * kpad;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / kpad;
@@ -148,15 +169,16 @@ stage_obs_kernel(const float* __restrict__ src, int64_t rows, int cols, float* _
       v = src[r * cols + c];
       if (store) store[r * cols + c] = v;
     }
-    dst[r * ld + c] = __float2bfloat16(v);
+    store_split(dst, lo_off, (size_t)(r * ld + c), v);
   }
 }
 
-int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int kpad, int ld, cudaStream_t st) {
+int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld,
+              cudaStream_t st) {
   const int64_t total = rows * kpad;
   int blocks = (int)((total + 255) / 256);
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  stage_obs_kernel<<<blocks, 256, 0, st>>>(src, rows, cols, store, dst, kpad, ld);
+  stage_obs_kernel<<<blocks, 256, 0, st>>>(src, rows, cols, store, dst, lo_off, kpad, ld);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }
@@ -214,7 +236,7 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
                                   urlg_policy** out) {
   if (!desc || !params || !grads || !exp_avg || !exp_avg_sq || !stats || !workspace || !out)
     return fail(URLG_EINVAL, "urlg_policy_create: null argument");
-  if ((uintptr_t)workspace & 255) return fail(URLG_EINVAL, "urlg_policy_create: workspace must be 256-byte aligned");
+  if ((uintptr_t)workspace & 1023) return fail(URLG_EINVAL, "urlg_policy_create: workspace must be 1024-byte aligned");
   urlg_policy* p = new (std::nothrow) urlg_policy();
   if (!p) return fail(URLG_ENOMEM, "urlg_policy_create: out of host memory");
   p->desc = *desc;
@@ -258,8 +280,8 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
   float* store_o = s->observations + (size_t)t * N * s->num_obs;
   float* store_p = s->privileged_observations ? s->privileged_observations + (size_t)t * N * s->num_priv : nullptr;
   if (!d.recurrent) {
-    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
-    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
+    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
+    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
   } else {
     if (!hidden) return fail(URLG_EINVAL, "urlg_policy_act: recurrent policy needs hidden state");
     const size_t HS = (size_t)N * d.rnn_hidden, slab = (size_t)t * HS;
@@ -286,7 +308,7 @@ extern "C" int urlg_policy_forward(urlg_policy* p, int which, const float* x, in
   NetWs& n = p->net[which];
   const int in = which == 0 ? d.num_actor_obs : d.num_critic_obs;
   if (!d.recurrent) {
-    if (int rc = stage_obs(x, rows, in, nullptr, n.x, n.kpad[0], n.kpad[0], st)) return rc;
+    if (int rc = stage_obs(x, rows, in, nullptr, n.x, p->lo_off, n.kpad[0], n.kpad[0], st)) return rc;
   } else {
     if (!hidden_h || !hidden_c) return fail(URLG_EINVAL, "urlg_policy_forward: recurrent policy needs hidden state");
     if (int rc = lstm_rollout_step(p, which, x, rows, nullptr, hidden_h, hidden_c, nullptr, nullptr, st)) return rc;

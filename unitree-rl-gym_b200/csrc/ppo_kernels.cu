@@ -23,12 +23,12 @@ __device__ __forceinline__ int64_t row_index(const int64_t* __restrict__ indices
 // ---------------------------------------------------------------- K6: gather
 __global__ void __launch_bounds__(256)
 gather_obs_kernel(const float* __restrict__ src, int cols, const int64_t* __restrict__ indices, int64_t rows,
-                  bf16* __restrict__ dst, int kpad) {
+                  bf16* __restrict__ dst, int64_t lo_off, int kpad) {
   const int64_t total = rows * kpad;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / kpad;
     const int c = (int)(i % kpad);
-    dst[i] = __float2bfloat16(c < cols ? src[indices[r] * cols + c] : 0.0f);
+    store_split(dst, lo_off, (size_t)i, c < cols ? src[indices[r] * cols + c] : 0.0f);
   }
 }
 
@@ -46,6 +46,7 @@ __global__ void __launch_bounds__(kHeadThreads)
 ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_new, const float* __restrict__ std_param,
                 const urlg_storage s, const int64_t* __restrict__ indices, int64_t rows, int env_begin, int env_count,
                 const urlg_ppo_hparams hp, bf16* __restrict__ dmu, int ld_dmu, bf16* __restrict__ dval, int ld_dval,
+                int64_t lo_off,
                 float* __restrict__ g_std, float* __restrict__ g_bias_mu, float* __restrict__ g_bias_val,
                 float* __restrict__ stats) {
   const int A = s.num_actions;
@@ -103,10 +104,10 @@ ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_
     dv *= hp.value_loss_coef * inv_rows;
 #pragma unroll
     for (int j = 0; j < kMaxA; ++j)
-      if (j < A) dmu[r * ld_dmu + j] = __float2bfloat16(dm[j]);
-    for (int j = A; j < ld_dmu; ++j) dmu[r * ld_dmu + j] = __float2bfloat16(0.0f);
-    dval[r * ld_dval] = __float2bfloat16(dv);
-    for (int j = 1; j < ld_dval; ++j) dval[r * ld_dval + j] = __float2bfloat16(0.0f);
+      if (j < A) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), dm[j]);
+    for (int j = A; j < ld_dmu; ++j) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), 0.0f);
+    store_split(dval, lo_off, (size_t)(r * ld_dval), dv);
+    for (int j = 1; j < ld_dval; ++j) store_split(dval, lo_off, (size_t)(r * ld_dval + j), 0.0f);
   }
   // block reductions -> atomics
   __shared__ float red[kHeadThreads / 32][2 * kMaxA + 5];
@@ -175,6 +176,7 @@ int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStrea
       if (splits > kblocks / 4) splits = kblocks / 4;
       if (splits < 1) splits = 1;
       g.k_splits = splits;
+      with_lo(p, g);
       if (int rc = tc::launch_gemm(&g, st)) return rc;
     }
     if (l >= 1 || dx_out) {
@@ -190,6 +192,7 @@ int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStrea
       } else {
         g.out_bf16 = dx_out; g.ld_bf16 = nin;
       }
+      with_lo(p, g);
       if (int rc = tc::launch_gemm(&g, st)) return rc;
     }
   }
@@ -284,9 +287,9 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   if (!d.recurrent) {
     const float* cobs = s->privileged_observations ? s->privileged_observations : s->observations;
     int blocks = (int)((rows * na.kpad[0] + 255) / 256);
-    gather_obs_kernel<<<blocks, 256, 0, st>>>(s->observations, d.num_actor_obs, indices, rows, na.x, na.kpad[0]);
+    gather_obs_kernel<<<blocks, 256, 0, st>>>(s->observations, d.num_actor_obs, indices, rows, na.x, p->lo_off, na.kpad[0]);
     blocks = (int)((rows * nc.kpad[0] + 255) / 256);
-    gather_obs_kernel<<<blocks, 256, 0, st>>>(cobs, d.num_critic_obs, indices, rows, nc.x, nc.kpad[0]);
+    gather_obs_kernel<<<blocks, 256, 0, st>>>(cobs, d.num_critic_obs, indices, rows, nc.x, p->lo_off, nc.kpad[0]);
     URLG_LAUNCH_CHECK();
   } else {
     if (int rc = lstm_update_forward(p, 0, s, env_begin, env_count, st)) return rc;
@@ -296,7 +299,7 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   if (int rc = mlp_forward(p, nc, rows, st)) return rc;
   ppo_head_kernel<<<(int)((rows + kHeadThreads - 1) / kHeadThreads), kHeadThreads, 0, st>>>(
       na.out, nc.out, p->params + d.std_off, *s, indices, rows, env_begin, env_count, *h, na.dout, na.opad, nc.dout,
-      nc.opad, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
+      nc.opad, p->lo_off, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
       p->grads + nc.d.b_off[nc.d.num_layers - 1], p->stats);
   URLG_LAUNCH_CHECK();
   if (int rc = mlp_backward(p, na, rows, d.recurrent ? p->lstm[0].dx_head : nullptr, st)) return rc;

@@ -61,7 +61,13 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   g.dact_ref = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref); g.ld_ref = d->ld_ref;
   g.colsum = d->colsum;
   g.flags = d->flags;
-  CUtensorMap ta, tb;
+  g.split = (d->A_lo && d->B_lo) ? 1 : 0;
+  if ((d->A_lo != nullptr) != (d->B_lo != nullptr)) return fail(URLG_EINVAL, "urlg_tc_gemm: A_lo and B_lo go together");
+  if (g.split && bn > 128) { bn = 128; g.block_n = bn; }       // two operand sets per stage: keep >= 3 stages in 227 KB
+  g.stages = gemm_stages_for(bn, g.split);
+  g.out_lo = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_lo);
+  g.dact_lo = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref_lo);
+  CUtensorMap ta, tb, tal, tbl;
   int rc;
   if (!g.a_mn) rc = make_tmap_bf16(&ta, d->A, d->K, d->M, d->lda, kBlockK, kBlockM);
   else rc = make_tmap_bf16(&ta, d->A, d->M, d->K, d->lda, 64, kBlockK);
@@ -69,13 +75,23 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   if (!g.b_mn) rc = make_tmap_bf16(&tb, d->B, d->K, d->N, d->ldb, kBlockK, bn);
   else rc = make_tmap_bf16(&tb, d->B, d->N, d->K, d->ldb, 64, kBlockK);
   if (rc) return rc;
+  if (g.split) {
+    if (!g.a_mn) rc = make_tmap_bf16(&tal, d->A_lo, d->K, d->M, d->lda, kBlockK, kBlockM);
+    else rc = make_tmap_bf16(&tal, d->A_lo, d->M, d->K, d->lda, 64, kBlockK);
+    if (rc) return rc;
+    if (!g.b_mn) rc = make_tmap_bf16(&tbl, d->B_lo, d->K, d->N, d->ldb, kBlockK, bn);
+    else rc = make_tmap_bf16(&tbl, d->B_lo, d->N, d->K, d->ldb, 64, kBlockK);
+    if (rc) return rc;
+  } else {
+    tal = ta; tbl = tb;
+  }
   static bool attr_set = false;
   if (!attr_set) {
-    URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(256)));
+    URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
   dim3 grid((d->M + kBlockM - 1) / kBlockM, (d->N + bn - 1) / bn, splits);
-  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn), st>>>(ta, tb, g);
+  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages), st>>>(ta, tb, tal, tbl, g);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

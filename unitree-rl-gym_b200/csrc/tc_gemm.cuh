@@ -11,7 +11,7 @@
 namespace urlg {
 namespace tc {
 
-constexpr int kBlockM = 128, kBlockK = 64, kStages = 4;
+constexpr int kBlockM = 128, kBlockK = 64, kMaxStages = 4;
 constexpr int kGemmThreads = 192;
 constexpr int kFlagElu = 1, kFlagAtomic = 2;
 
@@ -26,23 +26,36 @@ struct GemmArgs {
   const __nv_bfloat16* dact_ref; int ld_ref;      // value *= ELU'(y) with y = post-activation at the same (m,n)
   float* colsum;                                  // [N] += column sums of the stored values (bias gradients)
   int flags;
+  int split;             // 1: operands are (hi, lo) bf16 pairs, D = Ahi*Bhi + Alo*Bhi + Ahi*Blo (~fp32 operand precision)
+  int stages;            // smem pipeline depth (fits 227 KB)
+  __nv_bfloat16* out_lo; // split: low part of the bf16 output (same ld as out_bf16)
+  const __nv_bfloat16* dact_lo;   // split: low part of dact_ref
 };
 
 __host__ __device__ inline int stage_bytes_a() { return kBlockM * kBlockK * 2; }
 __host__ __device__ inline int stage_bytes_b(int block_n) { return block_n * kBlockK * 2; }
-inline int gemm_smem_bytes(int block_n) { return kStages * (stage_bytes_a() + stage_bytes_b(block_n)) + 1024 + 256; }
+inline int gemm_stage_bytes(int block_n, int split) { return (split ? 2 : 1) * (stage_bytes_a() + stage_bytes_b(block_n)); }
+inline int gemm_stages_for(int block_n, int split) {
+  int s = (227 * 1024 - 1024 - 256) / gemm_stage_bytes(block_n, split);
+  return s > kMaxStages ? kMaxStages : s;
+}
+inline int gemm_smem_bytes(int block_n, int split, int stages) { return stages * gemm_stage_bytes(block_n, split) + 1024 + 256; }
 
 __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : expm1f(x); }
 
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo, const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int bytes_a = stage_bytes_a(), bytes_b = stage_bytes_b(g.block_n);
+  const int kStages = g.stages;
+  // layout: A[stages] | B[stages] | (split) Alo[stages] | Blo[stages] | barriers
   const uint32_t sA = base, sB = base + kStages * bytes_a;
-  const uint32_t bars = sB + kStages * bytes_b;            // full[kStages], empty[kStages], tmem_full, tmem_ptr
-  const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tmem_full = bars + 16 * kStages;
+  const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (g.split ? kStages * bytes_a : 0);
+  const uint32_t bars = sBlo + (g.split ? kStages * bytes_b : 0);   // full[kStages], empty[kStages], tmem_full, tmem_ptr
+  const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tmem_full = bars + 16 * kMaxStages;
   const uint32_t tmem_slot = tmem_full + 8;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
@@ -57,6 +70,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (g.split) { tma_prefetch_desc(&tmAlo); tma_prefetch_desc(&tmBlo); }
     for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     mbar_init(tmem_full, 1);
     fence_mbar_init();
@@ -74,19 +88,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int s = kb % kStages, ph = (kb / kStages) & 1;
         mbar_wait(empty0 + 8 * s, ph ^ 1);
         const uint32_t full = full0 + 8 * s;
-        mbar_arrive_expect_tx(full, bytes_a + bytes_b);
+        mbar_arrive_expect_tx(full, (g.split ? 2 : 1) * (bytes_a + bytes_b));
         const int k0 = k_begin + kb * kBlockK;
-        const uint32_t a_dst = sA + s * bytes_a, b_dst = sB + s * bytes_b;
-        if (!g.a_mn) {
-          tma_load_2d(a_dst, &tmA, full, k0, m0);                        // box {64 k, 128 m}
-        } else {
-          tma_load_2d(a_dst, &tmA, full, m0, k0);                        // box {64 m, 64 k} x 2
-          tma_load_2d(a_dst + 8192, &tmA, full, m0 + 64, k0);
-        }
-        if (!g.b_mn) {
-          tma_load_2d(b_dst, &tmB, full, k0, n0);                        // box {64 k, block_n}
-        } else {
-          for (int j = 0; j < g.block_n / 64; ++j) tma_load_2d(b_dst + 8192 * j, &tmB, full, n0 + 64 * j, k0);
+        for (int part = 0; part <= g.split; ++part) {
+          const CUtensorMap* ta = part ? &tmAlo : &tmA;
+          const CUtensorMap* tb = part ? &tmBlo : &tmB;
+          const uint32_t a_dst = (part ? sAlo : sA) + s * bytes_a, b_dst = (part ? sBlo : sB) + s * bytes_b;
+          if (!g.a_mn) {
+            tma_load_2d(a_dst, ta, full, k0, m0);                        // box {64 k, 128 m}
+          } else {
+            tma_load_2d(a_dst, ta, full, m0, k0);                        // box {64 m, 64 k} x 2
+            tma_load_2d(a_dst + 8192, ta, full, m0 + 64, k0);
+          }
+          if (!g.b_mn) {
+            tma_load_2d(b_dst, tb, full, k0, n0);                        // box {64 k, block_n}
+          } else {
+            for (int j = 0; j < g.block_n / 64; ++j) tma_load_2d(b_dst + 8192 * j, tb, full, n0 + 64 * j, k0);
+          }
         }
       }
     }
@@ -101,11 +119,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(full0 + 8 * s, ph);
         tc_fence_after();
         const uint32_t a_src = sA + s * bytes_a, b_src = sB + s * bytes_b;
+        const uint32_t al_src = sAlo + s * bytes_a, bl_src = sBlo + s * bytes_b;
 #pragma unroll
         for (int k = 0; k < kBlockK / 16; ++k) {
           const uint64_t ad = make_sdesc_sw128(a_src + k * a_kstep, a_lbo, 1024);
           const uint64_t bd = make_sdesc_sw128(b_src + k * b_kstep, b_lbo, 1024);
           umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+          if (g.split) {
+            const uint64_t ald = make_sdesc_sw128(al_src + k * a_kstep, a_lbo, 1024);
+            const uint64_t bld = make_sdesc_sw128(bl_src + k * b_kstep, b_lbo, 1024);
+            umma_bf16(tmem_d, ald, bd, idesc, 1u);
+            umma_bf16(tmem_d, ad, bld, idesc, 1u);
+          }
         }
         umma_commit(empty0 + 8 * s);             // frees this smem stage when the MMAs retire
       }
@@ -136,7 +161,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (g.bias) x += g.bias[col0 + i];
           if (g.flags & kFlagElu) x = elu1(x);
           if (g.dact_ref && row_ok) {
-            const float y = __bfloat162float(g.dact_ref[(size_t)row * g.ld_ref + col0 + i]);
+            float y = __bfloat162float(g.dact_ref[(size_t)row * g.ld_ref + col0 + i]);
+            if (g.dact_lo) y += __bfloat162float(g.dact_lo[(size_t)row * g.ld_ref + col0 + i]);
             x *= (y > 0.0f ? 1.0f : y + 1.0f);
           }
           v[i] = row_ok ? x : 0.0f;
@@ -160,18 +186,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (g.out_bf16) {
           __nv_bfloat16* o = g.out_bf16 + (size_t)row * g.ld_bf16 + col0;
+          __nv_bfloat16* ol = g.out_lo ? g.out_lo + (size_t)row * g.ld_bf16 + col0 : nullptr;
           if (ncol == 16 && ((g.ld_bf16 & 7) == 0) && ((col0 & 7) == 0)) {
-            uint32_t p[8];
+            uint32_t p[8], q[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
               p[i] = *reinterpret_cast<uint32_t*>(&h);
+              __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * i] - __low2float(h), v[2 * i + 1] - __high2float(h));
+              q[i] = *reinterpret_cast<uint32_t*>(&l);
             }
             reinterpret_cast<uint4*>(o)[0] = make_uint4(p[0], p[1], p[2], p[3]);
             reinterpret_cast<uint4*>(o)[1] = make_uint4(p[4], p[5], p[6], p[7]);
+            if (ol) {
+              reinterpret_cast<uint4*>(ol)[0] = make_uint4(q[0], q[1], q[2], q[3]);
+              reinterpret_cast<uint4*>(ol)[1] = make_uint4(q[4], q[5], q[6], q[7]);
+            }
           } else {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) if (i < ncol) o[i] = __float2bfloat16(v[i]);
+            for (int i = 0; i < 16; ++i) if (i < ncol) {
+              const __nv_bfloat16 h = __float2bfloat16(v[i]);
+              o[i] = h;
+              if (ol) ol[i] = __float2bfloat16(v[i] - __bfloat162float(h));
+            }
           }
         }
       }

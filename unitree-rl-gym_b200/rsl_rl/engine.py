@@ -17,7 +17,7 @@ def _linears(seq):
 
 
 class PolicyEngine:
-    def __init__(self, actor_critic, max_rows, max_seq=1, seed=1, env_offset=0):
+    def __init__(self, actor_critic, max_rows, max_seq=1, seed=1, env_offset=0, precision=1):
         self.ac = actor_critic
         params = list(actor_critic.parameters())
         dev = params[0].device
@@ -68,13 +68,15 @@ class PolicyEngine:
         d.max_rows, d.max_seq = self.max_rows, self.max_seq
         d.seed_lo, d.seed_hi = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
         d.env_offset = env_offset
+        d.precision = int(precision)
+        self.precision = int(precision)
         self.desc = d
         L = _lib.lib()
         nbytes = L.urlg_policy_workspace_bytes(C.byref(d))
         if nbytes < 0:
             _lib.check(int(nbytes))
-        self.workspace = torch.zeros(int(nbytes) + 256, dtype=torch.uint8, device=dev)
-        base = (self.workspace.data_ptr() + 255) & ~255
+        self.workspace = torch.zeros(int(nbytes) + 1024, dtype=torch.uint8, device=dev)
+        base = (self.workspace.data_ptr() + 1023) & ~1023
         h = C.c_void_p()
         _lib.check(L.urlg_policy_create(C.byref(d), _lib.ptr(self.flat), _lib.ptr(self.grads), _lib.ptr(self.exp_avg),
                                         _lib.ptr(self.exp_avg_sq), _lib.ptr(self.stats), C.c_void_p(base), int(nbytes),

@@ -50,13 +50,17 @@ class ActorCritic(nn.Module):
         self.distribution = None
         Normal.set_default_validate_args = False
         self._engine = None
-        self._engine_args = dict(max_rows=4096, max_seq=1, seed=1, env_offset=0)
+        # precision 1 = split bf16 (hi+lo operands, 3 MMAs: ~fp32 operand precision, what the 1e-3 update parity
+        # needs); 0 = plain bf16 operands.  URLG_PRECISION=bf16 selects 0.
+        import os
+        self._engine_args = dict(max_rows=4096, max_seq=1, seed=1, env_offset=0,
+                                 precision=0 if os.environ.get("URLG_PRECISION", "bf16x3") == "bf16" else 1)
 
     # ---- binding to the CUDA policy handle
     def engine(self, **kw):
         """The PolicyEngine bound to this module; (re)built when shapes grow or the parameters moved."""
         grow = any(kw.get(k, 0) > self._engine_args[k] for k in ("max_rows", "max_seq"))
-        changed = any(k in kw and kw[k] != self._engine_args[k] for k in ("seed", "env_offset"))
+        changed = any(k in kw and kw[k] != self._engine_args[k] for k in ("seed", "env_offset", "precision"))
         if self._engine is None or grow or changed or not self._engine.owns(self):
             for k, v in kw.items():
                 self._engine_args[k] = max(v, self._engine_args[k]) if k in ("max_rows", "max_seq") else v
