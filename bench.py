@@ -108,3 +108,329 @@ def make_env(task, n, frames, device, env_offset=0):
     gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames)
     cls = {"go2": LeggedRobot, "h1": H1Robot, "h1_2": H1_2Robot, "g1": G1Robot}[task]
     return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device=device, headless=True), cfg
+
+
+def train_cfg_dict(task, cuda_graph=False):
+    from unitree_rl_gym_b200.legged_gym.envs import robot_configs as rc
+    from unitree_rl_gym_b200.legged_gym.utils.helpers import class_to_dict
+    t = {"go2": rc.GO2RoughCfgPPO, "h1": rc.H1RoughCfgPPO, "g1": rc.G1RoughCfgPPO, "h1_2": rc.H1_2RoughCfgPPO}[task]()
+    d = class_to_dict(t)
+    d["runner"]["cuda_graph"] = bool(cuda_graph)
+    return d
+
+
+def config_dict(task, n, world, graph):
+    from unitree_rl_gym_b200.robots import ROBOTS
+    pol = "MLP actor/critic [512,256,128]" if task == "go2" else "ActorCriticRecurrent LSTM(64)+[32]"
+    return {"workload": f"{task} flat terrain, {n} envs/GPU, decimation {DECIM[task]}, {ROLLOUT}-step rollout, {pol}; "
+                        "synthetic root/dof/contact state frames (PhysX is external to the path)",
+            "task": task, "envs_per_gpu": n, "rollout_steps": ROLLOUT, "epochs": 5, "mini_batches": 4,
+            "parallelism": f"dp{world} (env shards, flat-gradient all-reduce)" if world > 1 else "single GPU",
+            "rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph)" if graph else "eager",
+            "l2_policy": "working set per iteration (35 MB rollout storage + 8-frame physics pool) is cycled; every timed "
+                         "iteration additionally starts after a 256 MiB L2 flush write outside the event bracket"}
+
+
+DECIM = {"go2": 4, "h1": 4, "g1": 4, "h1_2": 8}
+# algorithmic bytes per env: K2 post-physics per env-step, K1 per substep
+K2_BYTES = {"go2": 1102, "g1": 1338, "h1_2": 1338, "h1": 1194}
+K1_BYTES = {"go2": 192, "g1": 192, "h1_2": 192, "h1": 160}
+MLP_FLOP_PER_ENV_STEP = {"go2": 756992, "h1": 117952, "g1": 124224, "h1_2": 124224}
+
+
+# ------------------------------------------------------------------ reference arm / cpu baseline (oracle port on host cores)
+def cpu_run(task, n, iterations, warmup):
+    import torch
+    from oracle import cpu_bench
+    spec, frames = make_frames(task, n, POOL_FRAMES)
+    out = cpu_bench.run(spec, frames, train_cfg_dict(task), iterations, warmup, threads=os.cpu_count())
+    roll = sum(out["rollout_s"]) / len(out["rollout_s"])
+    upd = sum(out["update_s"]) / len(out["update_s"])
+    return {"env_steps_per_s": n * ROLLOUT / roll, "rollout_ms": roll * 1e3, "update_ms": upd * 1e3,
+            "iter_ms": (roll + upd) * 1e3, "threads": out["threads"], "cores": os.cpu_count()}
+
+
+def reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = cpu_run(a.task, a.envs, max(a.steps, 1), a.warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": r["env_steps_per_s"], "unit": "env-steps/s",
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["iter_ms"],
+            "ppo_iter_ms": r["iter_ms"], "rollout_ms": r["rollout_ms"], "update_ms": r["update_ms"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(a.task, a.envs, 1, False),
+            "cpu_baseline": {"value": r["env_steps_per_s"], "unit": "env-steps/s", "cores": r["threads"], "kind": "port",
+                             "sample": f"{a.steps} full PPO iteration(s) ({a.envs} envs x {ROLLOUT} steps + 5x4 minibatch "
+                                       f"update) after {a.warmup} warm-up, torch CPU with {r['threads']} threads of "
+                                       f"{r['cores']} cores; the unmodified reference cannot run on this box (imports "
+                                       "isaacgym; /root/reference absent), so the oracle port pinned to it by "
+                                       "tests/golden stands in"},
+            "e2e": {"value": r["env_steps_per_s"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ own arm
+def own_arm(a):
+    import torch
+    import torch.distributed as dist
+    from unitree_rl_gym_b200 import _lib
+    from unitree_rl_gym_b200.rsl_rl.runners import OnPolicyRunner
+    from unitree_rl_gym_b200.rsl_rl.runners.rollout_graph import RolloutGraph
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device (the product path has no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    L = _lib.lib()
+    task, n, T = a.task, a.envs, ROLLOUT
+    hbm, tf_burst, tf_sus, peak_src = measured_peaks()
+
+    spec, frames = make_frames(task, n, POOL_FRAMES, seed=1 + rank)
+    env, cfg = make_env(task, n, frames, dev, env_offset=rank * n)
+    runner = OnPolicyRunner(env, train_cfg_dict(task), log_dir=None, device=dev)
+    alg = runner.alg
+    env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    use_graph = (not a.no_graph) and RolloutGraph.supported(runner)
+
+    def eager_rollout():
+        obs = env.get_observations()
+        priv = env.get_privileged_observations()
+        cobs = priv if priv is not None else obs
+        with torch.inference_mode():
+            for _ in range(T):
+                act = alg.act(obs, cobs)
+                obs, priv, rew, dones, infos = env.step(act)
+                cobs = priv if priv is not None else obs
+                alg.process_env_step(rew, dones, infos)
+        return obs, cobs
+
+    def finish(cobs):
+        with torch.inference_mode():
+            alg.compute_returns(cobs)
+        return alg.update()
+
+    # one eager iteration first (allocations, lazy module loads), then capture
+    _, cobs = eager_rollout()
+    finish(cobs)
+    graph = RolloutGraph(runner).capture() if use_graph else None
+    rollout = (lambda: graph.replay()) if graph is not None else eager_rollout
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        _, cobs = rollout()
+        finish(cobs)
+    barrier()
+
+    # ---- timed region: exactly K iterations; device events per phase; wall clock across (barrier + sync both sides)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    marks = []
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n_launch0 = L.urlg_launch_count()
+    barrier()
+    w0 = ev(); w0.record()
+    t_wall0 = time.perf_counter()
+    for _ in range(a.steps):
+        flush.zero_()                      # L2 flush, outside the per-phase brackets (inside the wall bracket)
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        _, cobs = rollout()
+        e1.record()
+        finish(cobs)
+        e2.record()
+        marks.append((e0, e1, e2))
+    w1 = ev(); w1.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    eager_launches = L.urlg_launch_count() - n_launch0
+    clocks = sampler.stop() if rank == 0 else None
+    roll_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in marks) / a.steps
+    upd_ms = sum(e1.elapsed_time(e2) for _, e1, e2 in marks) / a.steps
+    total_ms = w0.elapsed_time(w1) / a.steps
+    t = torch.tensor([roll_ms, upd_ms, total_ms, t_wall * 1e3 / a.steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    roll_ms, upd_ms, total_ms, wall_ms = t.tolist()
+    launches = eager_launches + (graph.launches * a.steps if graph is not None else 0)
+
+    # ---- e2e: the same rollout through the public API (eager), physics frames arriving from pinned HOST memory
+    #      every env step (H2D inside the timed region) and rewards / dones read back to the host every step
+    pin = {k: v.pin_memory() for k, v in frames.items() if v is not None and (k != "rigid_body" or spec.family == 1)}
+    pool = env.gym.frames
+    D = spec.decimation
+    rew_h = torch.empty(n, dtype=torch.float, pin_memory=True)
+    done_h = torch.empty(n, dtype=torch.bool, pin_memory=True)
+    h2d = sum(v[0].numel() * 4 for v in pin.values())
+    d2h = n * 4 + n
+
+    def e2e_rollout():
+        obs = env.get_observations()
+        priv = env.get_privileged_observations()
+        cobs = priv if priv is not None else obs
+        with torch.inference_mode():
+            for i in range(T):
+                f = ((env.gym.sim_calls + base_host) // D) % POOL_FRAMES
+                for k, v in pin.items():
+                    pool[k][f].copy_(v[f], non_blocking=True)
+                act = alg.act(obs, cobs)
+                obs, priv, rew, dones, infos = env.step(act)
+                cobs = priv if priv is not None else obs
+                alg.process_env_step(rew, dones, infos)
+                rew_h.copy_(rew, non_blocking=True)
+                done_h.copy_(dones, non_blocking=True)
+        return obs, cobs
+
+    env.gym.begin_relative()
+    base_host = int(env.gym.calls_base.item())      # device part of the simulate() counter (advanced by the graph replays)
+    e2e_ms = []
+    for i in range(2 + min(a.steps, 5)):
+        barrier()
+        e0, e1 = ev(), ev()
+        e0.record()
+        _, cobs = e2e_rollout()
+        e1.record()
+        e1.synchronize()
+        if i >= 2:
+            e2e_ms.append(e0.elapsed_time(e1))
+        finish(cobs)
+    t = torch.tensor([sum(e2e_ms) / len(e2e_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_roll_ms = t.item()
+
+    # ---- roofline of the dominant env kernel (K2 fused post-physics), timed alone with CUDA events on its stream
+    roof = None
+    extra = {}
+    if rank == 0:
+        st = _lib.cur_stream()
+        iters = 200
+
+        def time_call(fn, reps):
+            for _ in range(5):
+                fn()
+            e0, e1 = ev(), ev()
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1) * 1e3 / reps      # us per call
+
+        def post():
+            env.common_step_counter += 1
+            env._obs_slot ^= 1
+            _lib.check(L.urlg_post_physics(env._handle, _lib.ptr(env._step_base), env.common_step_counter,
+                                           env._obs_slot, st))
+        raw_act = torch.randn(n, env.num_actions, device=dev)
+        us_post = time_call(post, iters)
+        us_pd = time_call(lambda: _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(raw_act), st)), iters)
+        b2 = K2_BYTES[task] * n
+        roof = {"kernel": "post_physics_kernel (+finalize_step_kernel), K2 of SURVEY.md §8(a).7", "bound": "hbm",
+                "achieved": b2 / us_post / 1e3, "peak": hbm, "unit": "GB/s", "frac": b2 / us_post / 1e3 / hbm,
+                "traffic": None, "alg_bytes_per_launch": b2, "us_per_launch": us_post, "peak_source": peak_src,
+                "note": f"{n} envs x {K2_BYTES[task]} B = {b2 / 1e6:.1f} MB is L2-resident and below launch latency "
+                        "(SURVEY.md §7): HBM fraction at this size measures latency, not bandwidth; see roofline_large"}
+        extra["k1_pd"] = {"us_per_launch": us_pd, "alg_bytes": K1_BYTES[task] * n,
+                          "gbs": K1_BYTES[task] * n / us_pd / 1e3}
+        # tensor side: update phase flops / time
+        flop_upd = MLP_FLOP_PER_ENV_STEP[task] * 3 * n * T * 5
+        extra["update_tensor"] = {"bound": "tensor", "achieved": flop_upd / (upd_ms * 1e-3) / 1e12, "peak": tf_sus,
+                                  "unit": "TFLOP/s", "frac": flop_upd / (upd_ms * 1e-3) / 1e12 / tf_sus,
+                                  "note": "whole update phase (20 minibatches: gather, fwd, head, bwd, Adam; split-bf16 = "
+                                          "3 MMAs per product, counted once) vs sustained bf16 peak"}
+        flop_fwd = MLP_FLOP_PER_ENV_STEP[task] * n * T
+        extra["rollout_policy_flops_frac"] = flop_fwd / (roll_ms * 1e-3) / 1e12 / tf_sus
+        if not a.no_large:
+            del raw_act
+            big = a.large_envs
+            spec_b, frames_b = make_frames(task, big, 2)
+            env_b, _ = make_env(task, big, frames_b, dev)
+            env_b.reset()
+            env_b.episode_length_buf = torch.randint(0, 1000, (big,), device=dev)
+            act_b = torch.randn(big, env_b.num_actions, device=dev)
+            for _ in range(2):
+                env_b.step(act_b)
+
+            def post_b():
+                env_b.common_step_counter += 1
+                env_b._obs_slot ^= 1
+                _lib.check(L.urlg_post_physics(env_b._handle, _lib.ptr(env_b._step_base), env_b.common_step_counter,
+                                               env_b._obs_slot, st))
+            us_b = time_call(post_b, 20)
+            us_pd_b = time_call(lambda: _lib.check(L.urlg_pd_torques(env_b._handle, _lib.ptr(act_b), st)), 20)
+            bb = K2_BYTES[task] * big
+            extra["roofline_large"] = {"kernel": "post_physics_kernel (+finalize)", "envs": big, "bound": "hbm",
+                                       "achieved": bb / us_b / 1e3, "peak": hbm, "unit": "GB/s",
+                                       "frac": bb / us_b / 1e3 / hbm, "us_per_launch": us_b,
+                                       "alg_bytes_per_launch": bb,
+                                       "k1_pd": {"us_per_launch": us_pd_b, "gbs": K1_BYTES[task] * big / us_pd_b / 1e3,
+                                                 "frac": K1_BYTES[task] * big / us_pd_b / 1e3 / hbm},
+                                       "note": "working set >> 126 MB L2, back-to-back launches"}
+            del env_b, frames_b, act_b
+            torch.cuda.empty_cache()
+
+    # ---- CPU baseline (rank 0, N=1 only): the oracle port on the host cores, bounded sample
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu:
+        r = cpu_run(task, n, 1, 1)
+        cpu = {"value": r["env_steps_per_s"], "unit": "env-steps/s", "cores": r["threads"], "kind": "port",
+               "ppo_iter_ms": r["iter_ms"], "rollout_ms": r["rollout_ms"], "update_ms": r["update_ms"],
+               "sample": f"1 full PPO iteration ({n} envs x {T} steps + 5x4 minibatch update) after 1 warm-up iteration, "
+                         f"torch CPU {r['threads']} threads / {r['cores']} cores (oracle port; see --impl reference)"}
+
+    if rank == 0:
+        value = n * T * world / (roll_ms * 1e-3)
+        line = {"metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": a.steps,
+                "warmup": max(a.warmup, 3), "ms_per_step": total_ms, "ppo_iter_ms": total_ms, "rollout_ms": roll_ms,
+                "update_ms": upd_ms, "wall_ms_per_step": wall_ms, "train_env_steps_per_s": n * T * world / (total_ms * 1e-3),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 env path; split-bf16 (hi+lo) tensor-core operands, fp32 accumulate, policy/PPO",
+                "data": "synthetic", "config": config_dict(task, n, world, graph is not None),
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": n * T * world / (e2e_roll_ms * 1e-3), "unit": "env-steps/s",
+                        "h2d_bytes_per_step": int(h2d * T), "d2h_bytes_per_step": int(d2h * T), "rollout_ms": e2e_roll_ms,
+                        "note": "eager public API (PPO.act / LeggedRobot.step / PPO.process_env_step); per env step the "
+                                "physics frame (root, dof x decimation, contact) is copied from pinned host memory and "
+                                "rewards + dones are read back to pinned host memory; bytes are per 24-step rollout"},
+                "roofline": roof, "cpu_baseline": cpu}
+        line.update(extra)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--task", default=TASK)
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU)
+    ap.add_argument("--no-graph", action="store_true", help="eager rollout instead of CUDA-graph replay")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-large", action="store_true", help="skip the large-N roofline point")
+    ap.add_argument("--large-envs", type=int, default=1 << 18)
+    a = ap.parse_args()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        own_arm(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -121,6 +121,9 @@ typedef struct urlg_env urlg_env;
 
 int urlg_version(void);
 const char* urlg_last_error(void);
+/* Number of kernels this library has launched (or recorded into a CUDA graph under capture) since load:
+ * bench.py's gpu_launches evidence. */
+int64_t urlg_launch_count(void);
 
 /* ---- env half: replaces LeggedRobot.step minus PhysX (legged_robot.py:615-811) ---- */
 int urlg_env_create(const urlg_env_desc* desc, urlg_env** out);

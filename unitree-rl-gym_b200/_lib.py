@@ -118,6 +118,7 @@ _I64P = C.c_void_p
 SIGNATURES = {
     "urlg_version": (C.c_int, []),
     "urlg_last_error": (C.c_char_p, []),
+    "urlg_launch_count": (C.c_int64, []),
     "urlg_env_create": (C.c_int, [C.POINTER(EnvDesc), C.POINTER(C.c_void_p)]),
     "urlg_env_bind": (C.c_int, [C.c_void_p, C.POINTER(EnvBuffers)]),
     "urlg_env_destroy": (None, [C.c_void_p]),

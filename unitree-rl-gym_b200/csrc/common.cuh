@@ -9,6 +9,7 @@
 namespace urlg {
 
 extern thread_local char g_err[512];
+extern long long g_launches;   // kernels launched by this library since load (urlg_launch_count)
 
 inline int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -26,7 +27,11 @@ inline int fail(int code, const char* fmt, ...) {
                         cudaGetErrorString(e__));                                        \
   } while (0)
 
-#define URLG_LAUNCH_CHECK() URLG_CUDA(cudaGetLastError())
+#define URLG_LAUNCH_CHECK()          \
+  do {                               \
+    ++urlg::g_launches;              \
+    URLG_CUDA(cudaGetLastError());   \
+  } while (0)
 
 __device__ __forceinline__ int64_t eff_step(const int64_t* base, int64_t off) {
   return (base ? *base : 0) + off;

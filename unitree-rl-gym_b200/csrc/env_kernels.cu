@@ -14,6 +14,7 @@
 namespace urlg {
 
 thread_local char g_err[512] = "";
+long long g_launches = 0;
 
 constexpr int kWarp = 32;
 constexpr int kMaxFeet = 8;
@@ -618,6 +619,7 @@ using namespace urlg;
 
 extern "C" int urlg_version(void) { return URLG_ABI_VERSION; }
 extern "C" const char* urlg_last_error(void) { return g_err; }
+extern "C" int64_t urlg_launch_count(void) { return (int64_t)g_launches; }
 
 extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
   if (!d || !out) return fail(URLG_EINVAL, "urlg_env_create: null argument");

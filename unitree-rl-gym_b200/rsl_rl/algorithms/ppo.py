@@ -154,6 +154,19 @@ class PPO:
             self.engine.stats[_lib.STAT_LR] = self._lr_host
         return self.engine
 
+    # ---- CUDA-graph support: the Philox step of act() is (device base + host offset), like the env's counters
+    def begin_relative(self):
+        """Fold the host act() counter into the device base (call before capturing a rollout graph)."""
+        self._act_base += self._act_calls
+        self._act_calls = 0
+
+    def advance_base(self):
+        """Captured as a node of the graph: base += act() calls made inside the graph."""
+        self._act_base += self._act_calls
+
+    def end_relative(self):
+        self._act_calls = 0
+
     def test_mode(self):
         self.actor_critic.test()
 

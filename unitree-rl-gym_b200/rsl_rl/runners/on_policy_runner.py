@@ -74,10 +74,19 @@ class OnPolicyRunner:
         fin_len = torch.empty(T, N, device=self.device)
         nan = float("nan")
         tot_iter = self.current_learning_iteration + num_learning_iterations
+        # opt-in (runner cfg key `cuda_graph`): the whole rollout replayed as one CUDA graph (rollout_graph.py);
+        # per-step logging needs host-visible per-step values, so it is only used when log_dir is None
+        graph = None
+        if self.cfg.get("cuda_graph", False) and self.log_dir is None:
+            from .rollout_graph import RolloutGraph
+            if RolloutGraph.supported(self):
+                graph = self._rollout_graph = RolloutGraph(self).capture()
         for it in range(self.current_learning_iteration, tot_iter):
             start = time.time()
             with torch.inference_mode():
-                for i in range(T):
+                if graph is not None:
+                    obs, critic_obs = graph.replay()
+                for i in range(T if graph is None else 0):
                     actions = alg.act(obs, critic_obs)
                     obs, privileged_obs, rewards, dones, infos = env.step(actions)
                     critic_obs = privileged_obs if privileged_obs is not None else obs

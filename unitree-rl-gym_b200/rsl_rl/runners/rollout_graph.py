@@ -1,0 +1,73 @@
+"""One rollout (num_steps_per_env x [PPO.act -> env.step -> PPO.process_env_step]) captured once as a CUDA
+graph and replayed per PPO iteration.
+
+Everything in the loop is stream-ordered device work with no host read (the reference's three host syncs per
+env step, SURVEY.md §7, are gone), and every per-step counter the kernels consume is (device base + host offset)
+(include/urlg_b200.h conventions), so the loop of OnPolicyRunner.learn ([UPSTREAM rsl_rl v1.0.2]
+runners/on_policy_runner.py) is capturable as-is.  The graph's last nodes advance the device
+bases, so successive replays continue the env-step / act-step / physics-frame sequences exactly like the eager
+loop would.
+
+Requirements (checked): the env exposes begin_relative / advance_base / end_relative (the drop-in LeggedRobot
+does) and num_steps_per_env is even (the obs ping-pong slot must return to its starting slot so the graph's
+first act() reads the buffer the previous replay wrote last).
+"""
+import torch
+
+
+class RolloutGraph:
+    def __init__(self, runner):
+        self.runner = runner
+        self.graph = None
+        self.launches = 0           # library kernels recorded in the graph (urlg_launch_count delta)
+
+    @staticmethod
+    def supported(runner):
+        env = runner.env
+        return (all(hasattr(env, m) for m in ("begin_relative", "advance_base", "end_relative"))
+                and runner.num_steps_per_env % 2 == 0 and torch.device(runner.device).type == "cuda")
+
+    def _loop(self, obs, critic_obs):
+        env, alg = self.runner.env, self.runner.alg
+        for _ in range(self.runner.num_steps_per_env):
+            actions = alg.act(obs, critic_obs)
+            obs, privileged_obs, rewards, dones, infos = env.step(actions)
+            critic_obs = privileged_obs if privileged_obs is not None else obs
+            alg.process_env_step(rewards, dones, infos)
+        return obs, critic_obs
+
+    def capture(self):
+        from ... import _lib
+        r = self.runner
+        env, alg = r.env, r.alg
+        if not self.supported(r):
+            raise RuntimeError("RolloutGraph: env / runner configuration is not capturable")
+        if alg.storage.step != 0:
+            raise RuntimeError("RolloutGraph.capture: storage must be empty (call after update())")
+        obs = env.get_observations()
+        priv = env.get_privileged_observations()
+        critic_obs = priv if priv is not None else obs
+        slot0 = env._obs_slot
+        torch.cuda.synchronize()
+        env.begin_relative()
+        alg.begin_relative()
+        g = torch.cuda.CUDAGraph()
+        n0 = _lib.lib().urlg_launch_count()
+        with torch.inference_mode(), torch.cuda.graph(g):
+            obs_out, critic_out = self._loop(obs, critic_obs)
+            env.advance_base()
+            alg.advance_base()
+        self.launches = _lib.lib().urlg_launch_count() - n0
+        env.end_relative()
+        alg.end_relative()
+        alg.storage.clear()         # capture recorded work but executed nothing
+        assert env._obs_slot == slot0
+        self.graph = g
+        self.obs_out, self.critic_out = obs_out, critic_out
+        return self
+
+    def replay(self):
+        """Run one rollout; returns (obs, critic_obs) after the last step (inputs of compute_returns)."""
+        self.graph.replay()
+        self.runner.alg.storage.step = self.runner.num_steps_per_env
+        return self.obs_out, self.critic_out
