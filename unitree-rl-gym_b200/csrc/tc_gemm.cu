@@ -46,7 +46,16 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   g.M = d->M; g.N = d->N; g.K = d->K;
   g.a_mn = d->a_mn ? 1 : 0; g.b_mn = d->b_mn ? 1 : 0;
   int bn = d->block_n;
-  if (bn <= 0) bn = g.b_mn ? ((d->N + 63) / 64) * 64 : ((d->N + 15) / 16) * 16;
+  if (bn <= 0) {
+    // auto: the widest tile that still gives every SM a tile (the epilogue, not the MMA, is the cost here)
+    bn = g.b_mn ? ((d->N + 63) / 64) * 64 : ((d->N + 15) / 16) * 16;
+    if (bn > 128) bn = 128;
+    const int tm = (d->M + kBlockM - 1) / kBlockM;
+    const int min_bn = g.b_mn ? 64 : 32;
+    while (bn > min_bn && (bn % 2 == 0) && ((bn / 2) % (g.b_mn ? 64 : 16) == 0) &&
+           tm * ((d->N + bn - 1) / bn) < (kNumSMs * 3) / 4)
+      bn /= 2;
+  }
   if (bn > 256) bn = 256;
   if ((bn & 15) || (g.b_mn && (bn & 63))) return fail(URLG_EINVAL, "urlg_tc_gemm: block_n=%d invalid", bn);
   g.block_n = bn;
@@ -90,7 +99,11 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
     URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  dim3 grid((d->M + kBlockM - 1) / kBlockM, (d->N + bn - 1) / bn, splits);
+  g.tiles_m = (d->M + kBlockM - 1) / kBlockM;
+  g.tiles_n = (d->N + bn - 1) / bn;
+  g.splits = splits;
+  const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
+  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);     // persistent: one CTA per SM walks the tiles
   gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages), st>>>(ta, tb, tal, tbl, g);
   URLG_LAUNCH_CHECK();
   return URLG_OK;

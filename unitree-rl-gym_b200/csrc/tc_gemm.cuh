@@ -1,6 +1,7 @@
 // Warp-specialised tcgen05 GEMM for the PPO half: D[M,N] = sum_k A[m,k] * B[n,k], bf16 operands staged
 // in shared memory by TMA (SWIZZLE_128B), fp32 accumulator in TMEM, fused epilogue.
-//   warp 0 : TMA producer     warp 1 : TMEM alloc + single-thread MMA issue     warps 2-5 : epilogue
+//   warp 0 : TMA producer     warp 1 : TMEM alloc + single-thread MMA issue     warps 2-17 : epilogue
+// Persistent over tiles with a double-buffered TMEM accumulator.
 // Either operand may be K-major (row-major [rows, k]) or MN-major (row-major [k, rows]); the second form is
 // what dgrad (B = W[N_out, K_in]) and wgrad (A = dY[batch, N_out], B = X[batch, K_in]) need, so no transposed
 // copies of weights or activations are ever made.
@@ -12,7 +13,8 @@ namespace urlg {
 namespace tc {
 
 constexpr int kBlockM = 128, kBlockK = 64, kMaxStages = 4;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 16;                     // 4 per TMEM lane quarter, each a quarter of the tile's column chunks
+constexpr int kGemmThreads = (2 + kEpiWarps) * 32;
 constexpr int kFlagElu = 1, kFlagAtomic = 2;
 
 struct GemmArgs {
@@ -20,6 +22,7 @@ struct GemmArgs {
   int a_mn, b_mn;        // 0 = K-major, 1 = MN-major
   int block_n;           // UMMA N (multiple of 16, <= 256; multiple of 64 when b_mn)
   int k_per_split;       // multiple of 64
+  int tiles_m, tiles_n, splits;   // persistent tile space: tile id = (z * tiles_n + y) * tiles_m + x
   float* out_f32; int ld_f32;
   __nv_bfloat16* out_bf16; int ld_bf16;
   const float* bias;                              // [N] added before the activation
@@ -42,7 +45,13 @@ inline int gemm_stages_for(int block_n, int split) {
 inline int gemm_smem_bytes(int block_n, int split, int stages) { return stages * gemm_stage_bytes(block_n, split) + 1024 + 256; }
 
 __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : expm1f(x); }
+__device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
+// Persistent kernel: each CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The accumulator is double
+// buffered in TMEM (2 x tmem_cols_for(block_n) columns), so the MMAs of tile i+1 run under the epilogue of tile i;
+// the epilogue (the expensive part for these skinny GEMMs: bias, ELU / ELU', hi+lo split, column sums) is spread
+// over 16 warps = 4 per scheduler.
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo, const GemmArgs g) {
@@ -54,56 +63,63 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // layout: A[stages] | B[stages] | (split) Alo[stages] | Blo[stages] | barriers
   const uint32_t sA = base, sB = base + kStages * bytes_a;
   const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (g.split ? kStages * bytes_a : 0);
-  const uint32_t bars = sBlo + (g.split ? kStages * bytes_b : 0);   // full[kStages], empty[kStages], tmem_full, tmem_ptr
-  const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tmem_full = bars + 16 * kMaxStages;
-  const uint32_t tmem_slot = tmem_full + 8;
+  const uint32_t bars = sBlo + (g.split ? kStages * bytes_b : 0);
+  // full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2], tmem_ptr
+  const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tfull0 = bars + 16 * kMaxStages;
+  const uint32_t tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * kBlockM, n0 = blockIdx.y * g.block_n;
-  const int k_begin = blockIdx.z * g.k_per_split;
-  const int k_end = min(g.K, k_begin + g.k_per_split);
-  const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
-  const uint32_t ncols = tmem_cols_for(g.block_n);
+  const uint32_t acc_stride = tmem_cols_for(g.block_n);
+  const uint32_t ncols = 2 * acc_stride;
+  const int num_tiles = g.tiles_m * g.tiles_n * g.splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (g.split) { tma_prefetch_desc(&tmAlo); tma_prefetch_desc(&tmBlo); }
     for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    mbar_init(tmem_full, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, ncols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d = *tmem_slot_ptr;
+  const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages, ph = (kb / kStages) & 1;
-        mbar_wait(empty0 + 8 * s, ph ^ 1);
-        const uint32_t full = full0 + 8 * s;
-        mbar_arrive_expect_tx(full, (g.split ? 2 : 1) * (bytes_a + bytes_b));
-        const int k0 = k_begin + kb * kBlockK;
-        for (int part = 0; part <= g.split; ++part) {
-          const CUtensorMap* ta = part ? &tmAlo : &tmA;
-          const CUtensorMap* tb = part ? &tmBlo : &tmB;
-          const uint32_t a_dst = (part ? sAlo : sA) + s * bytes_a, b_dst = (part ? sBlo : sB) + s * bytes_b;
-          if (!g.a_mn) {
-            tma_load_2d(a_dst, ta, full, k0, m0);                        // box {64 k, 128 m}
-          } else {
-            tma_load_2d(a_dst, ta, full, m0, k0);                        // box {64 m, 64 k} x 2
-            tma_load_2d(a_dst + 8192, ta, full, m0 + 64, k0);
-          }
-          if (!g.b_mn) {
-            tma_load_2d(b_dst, tb, full, k0, n0);                        // box {64 k, block_n}
-          } else {
-            for (int j = 0; j < g.block_n / 64; ++j) tma_load_2d(b_dst + 8192 * j, tb, full, n0 + 64 * j, k0);
+      int kbt = 0;                                                       // k-blocks issued so far (all tiles)
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tx = tile % g.tiles_m, ty = (tile / g.tiles_m) % g.tiles_n, tz = tile / (g.tiles_m * g.tiles_n);
+        const int m0 = tx * kBlockM, n0 = ty * g.block_n;
+        const int k_begin = tz * g.k_per_split;
+        const int k_end = min(g.K, k_begin + g.k_per_split);
+        const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
+        for (int kb = 0; kb < num_kb; ++kb, ++kbt) {
+          const int s = kbt % kStages, ph = (kbt / kStages) & 1;
+          mbar_wait(empty0 + 8 * s, ph ^ 1);
+          const uint32_t full = full0 + 8 * s;
+          mbar_arrive_expect_tx(full, (g.split ? 2 : 1) * (bytes_a + bytes_b));
+          const int k0 = k_begin + kb * kBlockK;
+          for (int part = 0; part <= g.split; ++part) {
+            const CUtensorMap* ta = part ? &tmAlo : &tmA;
+            const CUtensorMap* tb = part ? &tmBlo : &tmB;
+            const uint32_t a_dst = (part ? sAlo : sA) + s * bytes_a, b_dst = (part ? sBlo : sB) + s * bytes_b;
+            if (!g.a_mn) {
+              tma_load_2d(a_dst, ta, full, k0, m0);                        // box {64 k, 128 m}
+            } else {
+              tma_load_2d(a_dst, ta, full, m0, k0);                        // box {64 m, 64 k} x 2
+              tma_load_2d(a_dst + 8192, ta, full, m0 + 64, k0);
+            }
+            if (!g.b_mn) {
+              tma_load_2d(b_dst, tb, full, k0, n0);                        // box {64 k, block_n}
+            } else {
+              for (int j = 0; j < g.block_n / 64; ++j) tma_load_2d(b_dst + 8192 * j, tb, full, n0 + 64 * j, k0);
+            }
           }
         }
       }
@@ -114,118 +130,196 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t idesc = make_idesc_bf16(kBlockM, g.block_n, g.a_mn, g.b_mn);
       const uint32_t a_lbo = g.a_mn ? 8192u : 16u, b_lbo = g.b_mn ? 8192u : 16u;
       const uint32_t a_kstep = g.a_mn ? 2048u : 32u, b_kstep = g.b_mn ? 2048u : 32u;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages, ph = (kb / kStages) & 1;
-        mbar_wait(full0 + 8 * s, ph);
+      int kbt = 0, it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int tz = tile / (g.tiles_m * g.tiles_n);
+        const int k_begin = tz * g.k_per_split;
+        const int k_end = min(g.K, k_begin + g.k_per_split);
+        const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
+        const int acc = it & 1;
+        mbar_wait(tempty0 + 8 * acc, ((it >> 1) & 1) ^ 1);               // epilogue drained this accumulator
         tc_fence_after();
-        const uint32_t a_src = sA + s * bytes_a, b_src = sB + s * bytes_b;
-        const uint32_t al_src = sAlo + s * bytes_a, bl_src = sBlo + s * bytes_b;
+        const uint32_t tmem_d = tmem_base + acc * acc_stride;
+        for (int kb = 0; kb < num_kb; ++kb, ++kbt) {
+          const int s = kbt % kStages, ph = (kbt / kStages) & 1;
+          mbar_wait(full0 + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_src = sA + s * bytes_a, b_src = sB + s * bytes_b;
+          const uint32_t al_src = sAlo + s * bytes_a, bl_src = sBlo + s * bytes_b;
 #pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k) {
-          const uint64_t ad = make_sdesc_sw128(a_src + k * a_kstep, a_lbo, 1024);
-          const uint64_t bd = make_sdesc_sw128(b_src + k * b_kstep, b_lbo, 1024);
-          umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
-          if (g.split) {
-            const uint64_t ald = make_sdesc_sw128(al_src + k * a_kstep, a_lbo, 1024);
-            const uint64_t bld = make_sdesc_sw128(bl_src + k * b_kstep, b_lbo, 1024);
-            umma_bf16(tmem_d, ald, bd, idesc, 1u);
-            umma_bf16(tmem_d, ad, bld, idesc, 1u);
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t ad = make_sdesc_sw128(a_src + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = make_sdesc_sw128(b_src + k * b_kstep, b_lbo, 1024);
+            umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            if (g.split) {
+              const uint64_t ald = make_sdesc_sw128(al_src + k * a_kstep, a_lbo, 1024);
+              const uint64_t bld = make_sdesc_sw128(bl_src + k * b_kstep, b_lbo, 1024);
+              umma_bf16(tmem_d, ald, bd, idesc, 1u);
+              umma_bf16(tmem_d, ad, bld, idesc, 1u);
+            }
           }
+          umma_commit(empty0 + 8 * s);             // frees this smem stage when the MMAs retire
         }
-        umma_commit(empty0 + 8 * s);             // frees this smem stage when the MMAs retire
+        umma_commit(tfull0 + 8 * acc);              // accumulator complete
       }
-      umma_commit(tmem_full);                     // accumulator complete
     }
   } else {
     // ===== epilogue: TMEM -> registers -> global =====
-    const int lg = warp & 3;                       // TMEM lane quarter this warp may access
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const int row = m0 + lg * 32 + lane;
-    const bool row_ok = row < g.M;
-    for (int c0 = 0; c0 < g.block_n; c0 += 16) {
-      const int col0 = n0 + c0;
-      if (col0 >= g.N) break;                      // uniform across the warp
-      float v[16];
-      if (num_kb > 0) {
+    const int lg = warp & 3;                       // TMEM lane quarter this warp may access (warp id % 4)
+    const int cg = (warp - 2) >> 2;                // column group 0..3: chunks cg, cg+4, ...
+    const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int tx = tile % g.tiles_m, ty = (tile / g.tiles_m) % g.tiles_n;
+      const int m0 = tx * kBlockM, n0 = ty * g.block_n;
+      const int acc = it & 1;
+      mbar_wait(tfull0 + 8 * acc, (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * acc_stride;
+      const int row = m0 + lg * 32 + lane;
+      const bool row_ok = row < g.M;
+      for (int c0 = 16 * cg; c0 < g.block_n; c0 += 64) {
+        const int col0 = n0 + c0;
+        if (col0 >= g.N) break;                      // uniform across the warp
+        float v[16];
         tmem_ld16(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
-      } else {
+        const int ncol = min(16, g.N - col0);
+        const bool full = ncol == 16;
+        if (g.bias) {
+          if (full && ((uintptr_t)(g.bias + col0) & 15) == 0) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = 0.0f;
-      }
-      const int ncol = min(16, g.N - col0);
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        if (i < ncol) {
-          float x = v[i];
-          if (g.bias) x += g.bias[col0 + i];
-          if (g.flags & kFlagElu) x = elu1(x);
-          if (g.dact_ref && row_ok) {
-            float y = __bfloat162float(g.dact_ref[(size_t)row * g.ld_ref + col0 + i]);
-            if (g.dact_lo) y += __bfloat162float(g.dact_lo[(size_t)row * g.ld_ref + col0 + i]);
-            x *= (y > 0.0f ? 1.0f : y + 1.0f);
-          }
-          v[i] = row_ok ? x : 0.0f;
-        } else {
-          v[i] = 0.0f;
-        }
-      }
-      if (row_ok) {
-        if (g.out_f32) {
-          float* o = g.out_f32 + (size_t)row * g.ld_f32 + col0;
-          if (g.flags & kFlagAtomic) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) if (i < ncol) atomicAdd(o + i, v[i]);
-          } else if (ncol == 16 && ((g.ld_f32 & 3) == 0) && ((col0 & 3) == 0)) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            for (int i = 0; i < 4; ++i) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col0) + i);
+              v[4 * i] += b4.x; v[4 * i + 1] += b4.y; v[4 * i + 2] += b4.z; v[4 * i + 3] += b4.w;
+            }
           } else {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) if (i < ncol) o[i] = v[i];
+            for (int i = 0; i < 16; ++i) if (i < ncol) v[i] += g.bias[col0 + i];
           }
         }
-        if (g.out_bf16) {
-          __nv_bfloat16* o = g.out_bf16 + (size_t)row * g.ld_bf16 + col0;
-          __nv_bfloat16* ol = g.out_lo ? g.out_lo + (size_t)row * g.ld_bf16 + col0 : nullptr;
-          if (ncol == 16 && ((g.ld_bf16 & 7) == 0) && ((col0 & 7) == 0)) {
-            uint32_t p[8], q[8];
+        if (g.flags & kFlagElu) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-              p[i] = *reinterpret_cast<uint32_t*>(&h);
-              __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * i] - __low2float(h), v[2 * i + 1] - __high2float(h));
-              q[i] = *reinterpret_cast<uint32_t*>(&l);
-            }
-            reinterpret_cast<uint4*>(o)[0] = make_uint4(p[0], p[1], p[2], p[3]);
-            reinterpret_cast<uint4*>(o)[1] = make_uint4(p[4], p[5], p[6], p[7]);
-            if (ol) {
-              reinterpret_cast<uint4*>(ol)[0] = make_uint4(q[0], q[1], q[2], q[3]);
-              reinterpret_cast<uint4*>(ol)[1] = make_uint4(q[4], q[5], q[6], q[7]);
+          for (int i = 0; i < 16; ++i) v[i] = elu1(v[i]);
+        }
+        if (g.dact_ref && row_ok) {
+          const __nv_bfloat16* rp = g.dact_ref + (size_t)row * g.ld_ref + col0;
+          const __nv_bfloat16* rl = g.dact_lo ? g.dact_lo + (size_t)row * g.ld_ref + col0 : nullptr;
+          if (full && vec_ref && (((uintptr_t)rp | (uintptr_t)rl) & 15) == 0) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const uint4 a = __ldg(reinterpret_cast<const uint4*>(rp) + h);
+              uint4 b = make_uint4(0, 0, 0, 0);
+              if (rl) b = __ldg(reinterpret_cast<const uint4*>(rl) + h);
+              const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float y0 = bf16lo(aw[i]) + bf16lo(bw[i]), y1 = bf16hi(aw[i]) + bf16hi(bw[i]);
+                v[8 * h + 2 * i] *= (y0 > 0.0f ? 1.0f : y0 + 1.0f);
+                v[8 * h + 2 * i + 1] *= (y1 > 0.0f ? 1.0f : y1 + 1.0f);
+              }
             }
           } else {
 #pragma unroll
             for (int i = 0; i < 16; ++i) if (i < ncol) {
-              const __nv_bfloat16 h = __float2bfloat16(v[i]);
-              o[i] = h;
-              if (ol) ol[i] = __float2bfloat16(v[i] - __bfloat162float(h));
+              float y = __bfloat162float(rp[i]);
+              if (rl) y += __bfloat162float(rl[i]);
+              v[i] *= (y > 0.0f ? 1.0f : y + 1.0f);
             }
           }
         }
-      }
-      if (g.colsum) {
+        if (!row_ok || !full) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float s = v[i];
+          for (int i = 0; i < 16; ++i) if (!row_ok || i >= ncol) v[i] = 0.0f;
+        }
+        if (row_ok) {
+          if (g.out_f32) {
+            float* o = g.out_f32 + (size_t)row * g.ld_f32 + col0;
+            const bool v4 = full && vec_f32 && ((uintptr_t)o & 15) == 0;
+            if (g.flags & kFlagAtomic) {
+              if (v4) {
 #pragma unroll
-          for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-          if (lane == 0 && i < ncol) atomicAdd(g.colsum + col0 + i, s);
+                for (int i = 0; i < 4; ++i)
+                  atomicAdd(reinterpret_cast<float4*>(o) + i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
+              } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) if (i < ncol) atomicAdd(o + i, v[i]);
+              }
+            } else if (v4) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) if (i < ncol) o[i] = v[i];
+            }
+          }
+          if (g.out_bf16) {
+            __nv_bfloat16* o = g.out_bf16 + (size_t)row * g.ld_bf16 + col0;
+            __nv_bfloat16* ol = g.out_lo ? g.out_lo + (size_t)row * g.ld_bf16 + col0 : nullptr;
+            if (full && vec_bf16 && (((uintptr_t)o | (uintptr_t)ol) & 15) == 0) {
+              uint32_t p[8], q[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                p[i] = *reinterpret_cast<uint32_t*>(&h);
+                __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * i] - bf16lo(p[i]), v[2 * i + 1] - bf16hi(p[i]));
+                q[i] = *reinterpret_cast<uint32_t*>(&l);
+              }
+              reinterpret_cast<uint4*>(o)[0] = make_uint4(p[0], p[1], p[2], p[3]);
+              reinterpret_cast<uint4*>(o)[1] = make_uint4(p[4], p[5], p[6], p[7]);
+              if (ol) {
+                reinterpret_cast<uint4*>(ol)[0] = make_uint4(q[0], q[1], q[2], q[3]);
+                reinterpret_cast<uint4*>(ol)[1] = make_uint4(q[4], q[5], q[6], q[7]);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) if (i < ncol) {
+                const __nv_bfloat16 h = __float2bfloat16(v[i]);
+                o[i] = h;
+                if (ol) ol[i] = __float2bfloat16(v[i] - __bfloat162float(h));
+              }
+            }
+          }
+        }
+        if (g.colsum) {
+          // 16 columns x 32 rows -> 16 sums with a transposing butterfly (16 shuffles): after the steps below lane l
+          // (l even) holds the sum of column 8*b4 + 4*b3 + 2*b2 + b1 (bK = bit K of l).
+          float w8[8], w4[4], w2[2], w1;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const bool up = lane & 16;
+            const float send = up ? v[i] : v[i + 8], keep = up ? v[i + 8] : v[i];
+            w8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const bool up = lane & 8;
+            const float send = up ? w8[i] : w8[i + 4], keep = up ? w8[i + 4] : w8[i];
+            w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+          }
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const bool up = lane & 4;
+            const float send = up ? w4[i] : w4[i + 2], keep = up ? w4[i + 2] : w4[i];
+            w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          }
+          {
+            const bool up = lane & 2;
+            const float send = up ? w2[0] : w2[1], keep = up ? w2[1] : w2[0];
+            w1 = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+          }
+          w1 += __shfl_xor_sync(0xffffffffu, w1, 1);
+          const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+          if ((lane & 1) == 0 && c < ncol) atomicAdd(g.colsum + col0 + c, w1);
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8 * acc);     // this warp is done reading accumulator `acc`
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_d, ncols);
+  if (warp == 1) tmem_dealloc(tmem_base, ncols);
 }
 
 }  // namespace tc
