@@ -16,7 +16,6 @@ namespace urlg {
 thread_local char g_err[512] = "";
 long long g_launches = 0;
 
-constexpr int kWarp = 32;
 constexpr int kMaxFeet = 8;
 constexpr float kPi = 3.14159274101257324f;      // float32(np.pi)
 constexpr float kTwoPi = 6.28318548202636719f;   // float32(2*np.pi)
@@ -36,64 +35,71 @@ struct urlg_env {
   urlg::StepScratch* scratch;
   int bound;
   int smem_bytes;
+  int vec_ok;      // every row tensor K2 stages / stores in bulk is 16-byte aligned (set at bind)
 };
 
 namespace urlg {
 
-// ---------------------------------------------------------------- shared-memory layout
+// ---------------------------------------------------------------- shared-memory layout (K2)
+// One block = 32 consecutive envs x 4 lanes per env (128 threads).  The row tensors of those 32 envs are
+// contiguous in global memory, so each is ONE 1-D bulk-TMA copy (cp.async.bulk) into an unpadded shared image;
+// outputs with row structure (obs, privileged obs, last_actions, last_dof_vel) are assembled in shared memory and
+// leave as flat 16-byte vector stores.
+constexpr int kEnvsPerBlock = 32, kLanesPerEnv = 4, kK2Threads = kEnvsPerBlock * kLanesPerEnv;
+
 struct Layout {
-  int sRoot, sDof, sCon, sA, sRb, sObs, sPriv;
-  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, total;
+  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, oBar, total;   // float offsets
 };
 
 __host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
   Layout L;
-  const int A = c.num_dof;
-  L.sRoot = 13;
-  L.sDof = 2 * A + 1;
-  L.sCon = (3 * c.num_bodies) | 1;
-  L.sA = A | 1;
-  L.sRb = c.family == 1 ? ((c.num_feet * 13) | 1) : 0;
-  L.sObs = c.num_obs | 1;
-  L.sPriv = c.num_priv ? (c.num_priv | 1) : 0;
+  const int A = c.num_dof, R = kEnvsPerBlock;
   int o = 0;
-  L.oRoot = o; o += kWarp * L.sRoot;
-  L.oDof = o; o += kWarp * L.sDof;
-  L.oCon = o; o += kWarp * L.sCon;
-  L.oAct = o; o += kWarp * L.sA;
-  L.oLact = o; o += kWarp * L.sA;
-  L.oLdv = o; o += kWarp * L.sA;
-  L.oTq = o; o += kWarp * L.sA;
-  L.oRb = o; o += kWarp * L.sRb;
-  L.oObs = o; o += kWarp * L.sObs;
-  L.oPriv = o; o += kWarp * L.sPriv;
+  L.oRoot = o; o += R * 13;
+  L.oDof = o; o += R * 2 * A;
+  L.oCon = o; o += R * 3 * c.num_bodies;
+  L.oAct = o; o += R * A;
+  L.oLact = o; o += R * A;
+  L.oLdv = o; o += R * A;
+  L.oTq = o; o += R * A;
+  L.oRb = o; o += c.family == 1 ? R * c.num_feet * 13 : 0;
+  o = (o + 3) & ~3;
+  L.oObs = o; o += R * c.num_obs;
+  L.oPriv = o; o += R * c.num_priv;
+  o = (o + 3) & ~3;
+  L.oBar = o; o += 4;
   L.total = o;
   return L;
 }
 
-// Coalesced copy of `nrows` contiguous rows of `w` words into padded shared rows.
-__device__ __forceinline__ void stage_in(float* __restrict__ s, const float* __restrict__ g, int w, int stride,
-                                         int nrows, int lane) {
-  const int total = nrows * w;
-  int r = 0, col = lane;
-  while (col >= w) { col -= w; ++r; }
-  for (int i = lane; i < total; i += kWarp) {
-    s[r * stride + col] = g[i];
-    col += kWarp;
-    while (col >= w) { col -= w; ++r; }
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bulk_g2s(float* dst, const float* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_addr(dst)), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar) : "memory");
+}
+// Flat copy of `n` floats (tail / unaligned fallback and the copy-out path).
+__device__ __forceinline__ void flat_in(float* __restrict__ s, const float* __restrict__ g, int n, int n_pad, int tid) {
+  for (int i = tid; i < n_pad; i += kK2Threads) s[i] = i < n ? g[i] : 0.0f;
+}
+__device__ __forceinline__ void flat_out(float* __restrict__ g, const float* __restrict__ s, int n, bool vec, int tid) {
+  if (vec) {
+    const float4* s4 = reinterpret_cast<const float4*>(s);
+    float4* g4 = reinterpret_cast<float4*>(g);
+    for (int i = tid; i < (n >> 2); i += kK2Threads) g4[i] = s4[i];
+  } else {
+    for (int i = tid; i < n; i += kK2Threads) g[i] = s[i];
   }
 }
-
-__device__ __forceinline__ void stage_out(float* __restrict__ g, const float* __restrict__ s, int w, int stride,
-                                          int nrows, int lane) {
-  const int total = nrows * w;
-  int r = 0, col = lane;
-  while (col >= w) { col -= w; ++r; }
-  for (int i = lane; i < total; i += kWarp) {
-    g[i] = s[r * stride + col];
-    col += kWarp;
-    while (col >= w) { col -= w; ++r; }
-  }
+// Sum over the 4 lanes of an env; every lane gets the same bits (commutative pairwise adds).
+__device__ __forceinline__ float qsum(float x) {
+  x += __shfl_xor_sync(0xffffffffu, x, 1);
+  x += __shfl_xor_sync(0xffffffffu, x, 2);
+  return x;
+}
+// episode_length_buf % period (period > 0); the counters are small, so avoid the 64-bit division.
+__device__ __forceinline__ bool divisible(int64_t len, int period) {
+  if ((uint64_t)len <= 0x7fffffffull) return ((uint32_t)len % (uint32_t)period) == 0u;
+  return (len % period) == 0;
 }
 
 // torch.remainder for floats: fmod then fix the sign (ATen BinaryOpsKernel remainder_kernel).
@@ -164,308 +170,393 @@ __device__ __forceinline__ void resample_commands(const urlg_env_desc& c, SlotRn
 namespace urlg {
 
 // ---------------------------------------------------------------- K2: fused post-physics step
-__global__ void __launch_bounds__(kWarp) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
-                                                             const __grid_constant__ urlg_env_buffers b,
-                                                             StepScratch* __restrict__ scratch,
-                                                             const int64_t* __restrict__ step_base, int64_t step_off,
-                                                             int obs_slot, int num_slots) {
-  extern __shared__ float sm[];
+// Thread layout: tid = 4 * local_env + g.  Lane g of an env owns DOFs / bodies / feet / episode-sum rows
+// g, g+4, g+8, ... and the observation columns [g*ceil(num_obs/4), ...); per-env scalars (frame transforms,
+// commands, termination) are computed by all four lanes on identical inputs, so every lane holds identical bits
+// and the quad never diverges on an env-level decision.
+__global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+                                                                 const __grid_constant__ urlg_env_buffers b,
+                                                                 StepScratch* __restrict__ scratch,
+                                                                 const int64_t* __restrict__ step_base, int64_t step_off,
+                                                                 int obs_slot, int num_slots, int vec_ok) {
+  extern __shared__ __align__(128) float sm[];
   const Layout L = make_layout(c);
-  const int lane = threadIdx.x;
-  const int env0 = blockIdx.x * kWarp;
-  const int nrows = min(kWarp, c.num_envs - env0);
+  const int tid = threadIdx.x;
+  const int env0 = blockIdx.x * kEnvsPerBlock;
+  const int nrows = min(kEnvsPerBlock, c.num_envs - env0);
   const int A = c.num_dof, B = c.num_bodies, F = c.num_feet, N = c.num_envs;
   const int64_t step = eff_step(step_base, step_off);
   const int acc = (int)(step & 1);
+  const bool bulk = vec_ok && nrows == kEnvsPerBlock;
 
-  // ---- stage the row tensors of this warp's 32 envs (coalesced) ----
-  stage_in(sm + L.oRoot, b.root_states + (size_t)env0 * 13, 13, L.sRoot, nrows, lane);
-  stage_in(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, 2 * A, L.sDof, nrows, lane);
-  stage_in(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, 3 * B, L.sCon, nrows, lane);
-  stage_in(sm + L.oAct, b.actions + (size_t)env0 * A, A, L.sA, nrows, lane);
-  stage_in(sm + L.oLact, b.last_actions + (size_t)env0 * A, A, L.sA, nrows, lane);
-  stage_in(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, A, L.sA, nrows, lane);
-  stage_in(sm + L.oTq, b.torques + (size_t)env0 * A, A, L.sA, nrows, lane);
-  if (c.family == 1) {   // only the feet rows of rigid_body_states (h1_env.py:51-53)
+  // ---- stage the row tensors of this block's 32 envs ----
+  const uint32_t bar = smem_addr(sm + L.oBar);
+  if (bulk) {
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      const uint32_t bytes = (uint32_t)(kEnvsPerBlock * (13 + 2 * A + 3 * B + 4 * A) * sizeof(float));
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+      const uint32_t rA = kEnvsPerBlock * A * sizeof(float);
+      bulk_g2s(sm + L.oRoot, b.root_states + (size_t)env0 * 13, kEnvsPerBlock * 13 * sizeof(float), bar);
+      bulk_g2s(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, 2 * rA, bar);
+      bulk_g2s(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, kEnvsPerBlock * 3 * B * sizeof(float), bar);
+      bulk_g2s(sm + L.oAct, b.actions + (size_t)env0 * A, rA, bar);
+      bulk_g2s(sm + L.oLact, b.last_actions + (size_t)env0 * A, rA, bar);
+      bulk_g2s(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, rA, bar);
+      bulk_g2s(sm + L.oTq, b.torques + (size_t)env0 * A, rA, bar);
+    }
+  } else {
+    flat_in(sm + L.oRoot, b.root_states + (size_t)env0 * 13, nrows * 13, kEnvsPerBlock * 13, tid);
+    flat_in(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, nrows * 2 * A, kEnvsPerBlock * 2 * A, tid);
+    flat_in(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, nrows * 3 * B, kEnvsPerBlock * 3 * B, tid);
+    flat_in(sm + L.oAct, b.actions + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
+    flat_in(sm + L.oLact, b.last_actions + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
+    flat_in(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
+    flat_in(sm + L.oTq, b.torques + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
+  }
+  if (c.family == 1) {   // only the feet rows of rigid_body_states (h1_env.py:51-53): 52-byte rows, plain loads
     const int w = F * 13;
-    for (int i = lane; i < nrows * w; i += kWarp) {
+    for (int i = tid; i < kEnvsPerBlock * w; i += kK2Threads) {
       const int r = i / w, rem = i - r * w, f = rem / 13, k = rem - f * 13;
-      sm[L.oRb + r * L.sRb + rem] = b.rigid_body_states[((size_t)(env0 + r) * B + c.feet_idx[f]) * 13 + k];
+      sm[L.oRb + i] = r < nrows ? b.rigid_body_states[((size_t)(env0 + r) * B + c.feet_idx[f]) * 13 + k] : 0.0f;
     }
   }
-  __syncwarp();
-
-  bool push_due = false;
-  if (lane < nrows) {
-    const int e = env0 + lane;
-    float* root = sm + L.oRoot + lane * L.sRoot;
-    float* dof = sm + L.oDof + lane * L.sDof;
-    const float* con = sm + L.oCon + lane * L.sCon;
-    float* act = sm + L.oAct + lane * L.sA;
-    float* lact = sm + L.oLact + lane * L.sA;
-    float* ldv = sm + L.oLdv + lane * L.sA;
-    const float* tq = sm + L.oTq + lane * L.sA;
-    const float* rb = sm + L.oRb + lane * L.sRb;
-    float* obs = sm + L.oObs + lane * L.sObs;
-    float* priv = sm + L.oPriv + lane * L.sPriv;
-
-    SlotRng rng;
-    rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
-             b.rng_override ? b.rng_override + (size_t)e * num_slots : nullptr);
-
-    int64_t len = b.episode_length_buf[e] + 1;                       // :681
-    const float flen = (float)len;
-
-    // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
-    const float qx = root[3], qy = root[4], qz = root[5], qw = root[6];
-    const float roll = atan2f(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
-    const float sinp = 2.0f * (qw * qy - qz * qx);
-    const float pitch = fabsf(sinp) >= 1.0f ? copysignf(kHalfPi, sinp) : asinf(sinp);
-    const float yaw = atan2f(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
-    float lvx, lvy, lvz, avx, avy, avz, gx, gy, gz;
-    rot_inv(qx, qy, qz, qw, root[7], root[8], root[9], lvx, lvy, lvz);
-    rot_inv(qx, qy, qz, qw, root[10], root[11], root[12], avx, avy, avz);
-    rot_inv(qx, qy, qz, qw, 0.0f, 0.0f, -1.0f, gx, gy, gz);
-
-    // ---- E5 callback: gait phase (h1_env.py:58-63), resample (:511-512), heading (:513-516) ----
-    float phase = 0.0f, leg_phase[2] = {0.0f, 0.0f};
-    if (c.family == 1) {
-      phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
-      leg_phase[0] = phase;
-      leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
+  __syncthreads();
+  if (bulk) {
+    uint32_t ok = 0;
+    while (!ok) {
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                   : "=r"(ok) : "r"(bar) : "memory");
     }
-    float cmd[4];
-    {
-      const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
-      cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
-    }
-    if (len % c.resample_steps == 0) resample_commands(c, rng, 0, cmd);
-    if (c.heading_command) {
-      // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
-      const float ty = qz * 2.0f, tz = -qy * 2.0f;
-      const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
-      const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
-      const float heading = atan2f(fy, fx);
-      float a = py_remainder(cmd[3] - heading, kTwoPi);
-      a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
-      cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
-    }
+  }
 
-    // ---- E7 termination :715-721 ----
-    bool reset = false;
-    for (int k = 0; k < c.num_term_bodies; ++k) {
-      const float* f3 = con + 3 * c.term_idx[k];
-      reset |= norm3(f3[0], f3[1], f3[2]) > 1.0f;
-    }
-    reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
-    const bool time_out = flen > c.max_episode_length;
-    reset |= time_out;
+  const int le = tid >> 2, g = tid & 3;
+  const int e = env0 + le;
+  const bool live = le < nrows;            // tail block: dead quads compute on zeros and store nothing
+  float* root = sm + L.oRoot + le * 13;
+  float* dof = sm + L.oDof + le * 2 * A;
+  const float* con = sm + L.oCon + le * 3 * B;
+  float* act = sm + L.oAct + le * A;
+  float* lact = sm + L.oLact + le * A;
+  float* ldv = sm + L.oLdv + le * A;
+  const float* tq = sm + L.oTq + le * A;
+  const float* rb = sm + L.oRb + le * F * 13;
+  float* obs = sm + L.oObs + le * c.num_obs;
+  float* priv = sm + L.oPriv + le * c.num_priv;
 
-    // ---- E8/E9 rewards, alphabetical, :775-787 ----
-    float air[kMaxFeet];
-    uint8_t lastc[kMaxFeet];
-    for (int f = 0; f < F; ++f) {
-      air[f] = b.feet_air_time[(size_t)e * F + f];
-      lastc[f] = b.last_contacts[(size_t)e * F + f];
+  SlotRng rng;
+  rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
+           (b.rng_override && live) ? b.rng_override + (size_t)e * num_slots : nullptr);
+
+  int64_t len = (live ? b.episode_length_buf[e] : 0) + 1;              // :681
+  const float flen = (float)len;
+
+  // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
+  const float qx = root[3], qy = root[4], qz = root[5], qw = root[6];
+  const float roll = atan2f(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
+  const float sinp = 2.0f * (qw * qy - qz * qx);
+  const float pitch = fabsf(sinp) >= 1.0f ? copysignf(kHalfPi, sinp) : asinf(sinp);
+  const float yaw = atan2f(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
+  float lvx, lvy, lvz, avx, avy, avz, gx, gy, gz;
+  rot_inv(qx, qy, qz, qw, root[7], root[8], root[9], lvx, lvy, lvz);
+  rot_inv(qx, qy, qz, qw, root[10], root[11], root[12], avx, avy, avz);
+  rot_inv(qx, qy, qz, qw, 0.0f, 0.0f, -1.0f, gx, gy, gz);
+  const float root_z = root[2];
+
+  // ---- E5 callback: gait phase (h1_env.py:58-63), resample (:511-512), heading (:513-516) ----
+  float phase = 0.0f, leg_phase[2] = {0.0f, 0.0f};
+  if (c.family == 1) {
+    phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
+    leg_phase[0] = phase;
+    leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
+  }
+  float cmd[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  if (live) {
+    const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
+    cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
+  }
+  if (divisible(len, c.resample_steps)) resample_commands(c, rng, 0, cmd);
+  if (c.heading_command) {
+    // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
+    const float ty = qz * 2.0f, tz = -qy * 2.0f;
+    const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
+    const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
+    const float heading = atan2f(fy, fx);
+    float a = py_remainder(cmd[3] - heading, kTwoPi);
+    a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
+    cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
+  }
+
+  // ---- E7 termination :715-721 ----
+  float hits = 0.0f;
+  for (int k = g; k < c.num_term_bodies; k += kLanesPerEnv) {
+    const float* f3 = con + 3 * c.term_idx[k];
+    hits += norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
+  }
+  bool reset = qsum(hits) > 0.0f;
+  reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
+  const bool time_out = flen > c.max_episode_length;
+  reset |= time_out;
+
+  // ---- E8/E9 rewards, alphabetical, :775-787.  Lane g owns feet g and g+4. ----
+  float air[2] = {0.0f, 0.0f};
+  uint8_t lastc[2] = {0, 0};
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int f = g + 4 * q;
+    if (f < F && live) {
+      air[q] = b.feet_air_time[(size_t)e * F + f];
+      lastc[q] = b.last_contacts[(size_t)e * F + f];
     }
-    float rew = 0.0f;
-    for (int t = 0; t < c.num_terms; ++t) {
-      float r = 0.0f;
-      switch (c.term_ids[t]) {
-        case URLG_T_ACTION_RATE:
-          for (int j = 0; j < A; ++j) { const float d = lact[j] - act[j]; r += d * d; }
-          break;
-        case URLG_T_ALIVE: r = 1.0f; break;
-        case URLG_T_ANG_VEL_XY: r = avx * avx + avy * avy; break;
-        case URLG_T_BASE_HEIGHT: { const float d = root[2] - c.base_height_target; r = d * d; } break;
-        case URLG_T_COLLISION:
-          for (int k = 0; k < c.num_pen; ++k) {
-            const float* f3 = con + 3 * c.pen_idx[k];
-            r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
-          }
-          break;
-        case URLG_T_CONTACT:
-          for (int f = 0; f < F && f < 2; ++f) {
-            const bool stance = leg_phase[f] < 0.55f;
+  }
+  const float cmd_xy = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]);
+  float rew = 0.0f;
+  for (int t = 0; t < c.num_terms; ++t) {
+    float r = 0.0f;
+    switch (c.term_ids[t]) {
+      case URLG_T_ACTION_RATE:
+        for (int j = g; j < A; j += kLanesPerEnv) { const float d = lact[j] - act[j]; r += d * d; }
+        r = qsum(r);
+        break;
+      case URLG_T_ALIVE: r = 1.0f; break;
+      case URLG_T_ANG_VEL_XY: r = avx * avx + avy * avy; break;
+      case URLG_T_BASE_HEIGHT: { const float d = root_z - c.base_height_target; r = d * d; } break;
+      case URLG_T_COLLISION:
+        for (int k = g; k < c.num_pen; k += kLanesPerEnv) {
+          const float* f3 = con + 3 * c.pen_idx[k];
+          r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_CONTACT:
+        if (g < F && g < 2) {
+          const bool stance = leg_phase[g] < 0.55f;
+          const bool contact = con[3 * c.feet_idx[g] + 2] > 1.0f;
+          r = (contact != stance) ? 0.0f : 1.0f;
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_CONTACT_NO_VEL:
+        for (int f = g; f < F; f += kLanesPerEnv) {
+          const float* f3 = con + 3 * c.feet_idx[f];
+          const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
+          for (int k = 0; k < 3; ++k) { const float v = rb[f * 13 + 7 + k] * m; r += v * v; }
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_DOF_ACC:
+        for (int j = g; j < A; j += kLanesPerEnv) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
+        r = qsum(r);
+        break;
+      case URLG_T_DOF_POS_LIMITS:
+        for (int j = g; j < A; j += kLanesPerEnv) {
+          const float q = dof[2 * j];
+          r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_DOF_VEL:
+        for (int j = g; j < A; j += kLanesPerEnv) { const float v = dof[2 * j + 1]; r += v * v; }
+        r = qsum(r);
+        break;
+      case URLG_T_DOF_VEL_LIMITS:
+        for (int j = g; j < A; j += kLanesPerEnv)
+          r += fminf(fmaxf(fabsf(dof[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
+        r = qsum(r);
+        break;
+      case URLG_T_FEET_AIR_TIME: {   // stateful, :912-923
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          const int f = g + 4 * q;
+          if (f < F) {
             const bool contact = con[3 * c.feet_idx[f] + 2] > 1.0f;
-            r += (contact != stance) ? 0.0f : 1.0f;
+            const bool filt = contact || lastc[q];
+            lastc[q] = contact;
+            const float first = (air[q] > 0.0f && filt) ? 1.0f : 0.0f;
+            air[q] += c.dt;
+            r += (air[q] - 0.5f) * first;
+            air[q] *= filt ? 0.0f : 1.0f;
           }
-          break;
-        case URLG_T_CONTACT_NO_VEL:
-          for (int f = 0; f < F; ++f) {
-            const float* f3 = con + 3 * c.feet_idx[f];
-            const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
-            for (int k = 0; k < 3; ++k) { const float v = rb[f * 13 + 7 + k] * m; r += v * v; }
-          }
-          break;
-        case URLG_T_DOF_ACC:
-          for (int j = 0; j < A; ++j) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
-          break;
-        case URLG_T_DOF_POS_LIMITS:
-          for (int j = 0; j < A; ++j) {
-            const float q = dof[2 * j];
-            r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
-          }
-          break;
-        case URLG_T_DOF_VEL:
-          for (int j = 0; j < A; ++j) { const float v = dof[2 * j + 1]; r += v * v; }
-          break;
-        case URLG_T_DOF_VEL_LIMITS:
-          for (int j = 0; j < A; ++j)
-            r += fminf(fmaxf(fabsf(dof[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
-          break;
-        case URLG_T_FEET_AIR_TIME: {   // stateful, :912-923
-          for (int f = 0; f < F; ++f) {
-            const bool contact = con[3 * c.feet_idx[f] + 2] > 1.0f;
-            const bool filt = contact || lastc[f];
-            lastc[f] = contact;
-            const float first = (air[f] > 0.0f && filt) ? 1.0f : 0.0f;
-            air[f] += c.dt;
-            r += (air[f] - 0.5f) * first;
-            air[f] *= filt ? 0.0f : 1.0f;
-          }
-          r *= sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) > 0.1f ? 1.0f : 0.0f;
-        } break;
-        case URLG_T_FEET_CONTACT_FORCES:
-          for (int f = 0; f < F; ++f) {
-            const float* f3 = con + 3 * c.feet_idx[f];
-            r += fmaxf(norm3(f3[0], f3[1], f3[2]) - c.max_contact_force, 0.0f);
-          }
-          break;
-        case URLG_T_FEET_SWING_HEIGHT:
-          for (int f = 0; f < F; ++f) {
-            const float* f3 = con + 3 * c.feet_idx[f];
-            const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 0.0f : 1.0f;
-            const float d = rb[f * 13 + 2] - 0.08f;
-            r += d * d * m;
-          }
-          break;
-        case URLG_T_HIP_POS:
-          for (int k = 0; k < c.num_hip; ++k) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
-          break;
-        case URLG_T_LIN_VEL_Z: r = lvz * lvz; break;
-        case URLG_T_ORIENTATION: r = gx * gx + gy * gy; break;
-        case URLG_T_STAND_STILL:
-          for (int j = 0; j < A; ++j) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
-          r *= sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) < 0.1f ? 1.0f : 0.0f;
-          break;
-        case URLG_T_STUMBLE: {
-          bool any = false;
-          for (int f = 0; f < F; ++f) {
-            const float* f3 = con + 3 * c.feet_idx[f];
-            any |= sqrtf(f3[0] * f3[0] + f3[1] * f3[1]) > 5.0f * fabsf(f3[2]);
-          }
-          r = any ? 1.0f : 0.0f;
-        } break;
-        case URLG_T_TORQUE_LIMITS:
-          for (int j = 0; j < A; ++j) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
-          break;
-        case URLG_T_TORQUES:
-          for (int j = 0; j < A; ++j) r += tq[j] * tq[j];
-          break;
-        case URLG_T_TRACKING_ANG_VEL: { const float d = cmd[2] - avz; r = expf(-(d * d) / c.tracking_sigma); } break;
-        case URLG_T_TRACKING_LIN_VEL: {
-          const float dx = cmd[0] - lvx, dy = cmd[1] - lvy;
-          r = expf(-(dx * dx + dy * dy) / c.tracking_sigma);
-        } break;
-        default: break;
-      }
-      r *= c.term_scales[t];
-      rew += r;
-      b.episode_sums[(size_t)c.term_sum_row[t] * N + e] += r;
+        }
+        r = qsum(r);
+        r *= cmd_xy > 0.1f ? 1.0f : 0.0f;
+      } break;
+      case URLG_T_FEET_CONTACT_FORCES:
+        for (int f = g; f < F; f += kLanesPerEnv) {
+          const float* f3 = con + 3 * c.feet_idx[f];
+          r += fmaxf(norm3(f3[0], f3[1], f3[2]) - c.max_contact_force, 0.0f);
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_FEET_SWING_HEIGHT:
+        for (int f = g; f < F; f += kLanesPerEnv) {
+          const float* f3 = con + 3 * c.feet_idx[f];
+          const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 0.0f : 1.0f;
+          const float d = rb[f * 13 + 2] - 0.08f;
+          r += d * d * m;
+        }
+        r = qsum(r);
+        break;
+      case URLG_T_HIP_POS:
+        for (int k = g; k < c.num_hip; k += kLanesPerEnv) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
+        r = qsum(r);
+        break;
+      case URLG_T_LIN_VEL_Z: r = lvz * lvz; break;
+      case URLG_T_ORIENTATION: r = gx * gx + gy * gy; break;
+      case URLG_T_STAND_STILL:
+        for (int j = g; j < A; j += kLanesPerEnv) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
+        r = qsum(r);
+        r *= cmd_xy < 0.1f ? 1.0f : 0.0f;
+        break;
+      case URLG_T_STUMBLE: {
+        for (int f = g; f < F; f += kLanesPerEnv) {
+          const float* f3 = con + 3 * c.feet_idx[f];
+          r += sqrtf(f3[0] * f3[0] + f3[1] * f3[1]) > 5.0f * fabsf(f3[2]) ? 1.0f : 0.0f;
+        }
+        r = qsum(r) > 0.0f ? 1.0f : 0.0f;
+      } break;
+      case URLG_T_TORQUE_LIMITS:
+        for (int j = g; j < A; j += kLanesPerEnv) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
+        r = qsum(r);
+        break;
+      case URLG_T_TORQUES:
+        for (int j = g; j < A; j += kLanesPerEnv) r += tq[j] * tq[j];
+        r = qsum(r);
+        break;
+      case URLG_T_TRACKING_ANG_VEL: { const float d = cmd[2] - avz; r = expf(-(d * d) / c.tracking_sigma); } break;
+      case URLG_T_TRACKING_LIN_VEL: {
+        const float dx = cmd[0] - lvx, dy = cmd[1] - lvy;
+        r = expf(-(dx * dx + dy * dy) / c.tracking_sigma);
+      } break;
+      default: break;
     }
-    if (c.only_positive) rew = fmaxf(rew, 0.0f);
-    if (c.has_termination) {
-      const float r = ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale;
-      rew += r;
-      b.episode_sums[(size_t)c.termination_sum_row * N + e] += r;
-    }
+    r *= c.term_scales[t];
+    rew += r;
+    const int row = c.term_sum_row[t];
+    if (live && (row & 3) == g) b.episode_sums[(size_t)row * N + e] += r;   // row k is always touched by lane k & 3
+  }
+  if (c.only_positive) rew = fmaxf(rew, 0.0f);
+  if (c.has_termination) {
+    const float r = ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale;
+    rew += r;
+    if (live && (c.termination_sum_row & 3) == g) b.episode_sums[(size_t)c.termination_sum_row * N + e] += r;
+  }
 
-    // ---- E10 reset_idx for this env :723-768 ----
-    if (reset) {
-      for (int k = 0; k < c.num_sums; ++k) {
+  // ---- E10 reset_idx for this env :723-768 (quad-uniform branch) ----
+  if (reset) {
+    if (live) {
+      for (int k = g; k < c.num_sums; k += kLanesPerEnv) {
         float* s = b.episode_sums + (size_t)k * N + e;
         atomicAdd(&scratch->ep_acc[acc][k], *s);
         *s = 0.0f;
       }
-      atomicAdd(&scratch->ep_acc[acc][URLG_MAX_TERMS], 1.0f);
-      const int pos = atomicAdd(&scratch->reset_cnt[acc], 1);
-      if (b.reset_ids) b.reset_ids[pos] = e;
-      float* gdof = b.dof_state + (size_t)e * 2 * A;
-      for (int j = 0; j < A; ++j) {                                  // _reset_dofs :566-567
-        const float p = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
-        dof[2 * j] = p; dof[2 * j + 1] = 0.0f;
-        gdof[2 * j] = p; gdof[2 * j + 1] = 0.0f;
+      if (g == 0) {
+        atomicAdd(&scratch->ep_acc[acc][URLG_MAX_TERMS], 1.0f);
+        const int pos = atomicAdd(&scratch->reset_cnt[acc], 1);
+        if (b.reset_ids) b.reset_ids[pos] = e;
       }
-      float* groot = b.root_states + (size_t)e * 13;                 // _reset_root_states :587-590
-      for (int k = 0; k < 13; ++k) root[k] = c.base_init_state[k];
-      for (int k = 0; k < 3; ++k) root[k] += b.env_origins[(size_t)e * 3 + k];
-      for (int k = 0; k < 6; ++k) root[7 + k] = (0.5f - (-0.5f)) * rng.uniform(3 + A + k) + (-0.5f);
-      for (int k = 0; k < 13; ++k) groot[k] = root[k];
-      resample_commands(c, rng, 9 + A, cmd);                         // :749
-      float* gact = b.actions + (size_t)e * A;
-      for (int j = 0; j < A; ++j) { act[j] = 0.0f; gact[j] = 0.0f; } // :752 (last_* follow from the tail copies)
-      for (int f = 0; f < F; ++f) air[f] = 0.0f;                     // :755
-      len = 0;                                                        // :756
     }
-    push_due = c.push_robots && (len % c.push_interval == 0);        // :545, evaluated after the reset
+    float* gdof = b.dof_state + (size_t)e * 2 * A;
+    float* gact = b.actions + (size_t)e * A;
+    for (int j = g; j < A; j += kLanesPerEnv) {                        // _reset_dofs :566-567, actions :752
+      const float p = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
+      dof[2 * j] = p; dof[2 * j + 1] = 0.0f;
+      act[j] = 0.0f;
+      if (live) { gdof[2 * j] = p; gdof[2 * j + 1] = 0.0f; gact[j] = 0.0f; }
+    }
+    float* groot = b.root_states + (size_t)e * 13;                     // _reset_root_states :587-590
+    for (int k = g; k < 13; k += kLanesPerEnv) {
+      float v = c.base_init_state[k];
+      if (k < 3 && live) v += b.env_origins[(size_t)e * 3 + k];
+      if (k >= 7) v = (0.5f - (-0.5f)) * rng.uniform(3 + A + (k - 7)) + (-0.5f);
+      if (live) groot[k] = v;
+    }
+    resample_commands(c, rng, 9 + A, cmd);                             // :749
+    air[0] = 0.0f; air[1] = 0.0f;                                      // :755
+    len = 0;                                                            // :756
+  }
+  const bool push_due = live && c.push_robots && divisible(len, c.push_interval);   // :545, evaluated after the reset
 
-    // ---- E12 observations :789-811 / h1_env.py:68-95, then the clips of step() :643-646 ----
-    int o = 0;
-    float* dst = (c.family == 1) ? priv : obs;     // H1 family: privileged = [lin_vel] ++ obs
-    dst[o++] = lvx * c.obs_scale_lin_vel; dst[o++] = lvy * c.obs_scale_lin_vel; dst[o++] = lvz * c.obs_scale_lin_vel;
-    if (c.family == 1) { dst = obs; o = 0; }
-    dst[o++] = avx * c.obs_scale_ang_vel; dst[o++] = avy * c.obs_scale_ang_vel; dst[o++] = avz * c.obs_scale_ang_vel;
-    dst[o++] = gx; dst[o++] = gy; dst[o++] = gz;
-    dst[o++] = cmd[0] * c.obs_scale_lin_vel; dst[o++] = cmd[1] * c.obs_scale_lin_vel; dst[o++] = cmd[2] * c.obs_scale_ang_vel;
-    for (int j = 0; j < A; ++j) dst[o++] = (dof[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
-    for (int j = 0; j < A; ++j) dst[o++] = dof[2 * j + 1] * c.obs_scale_dof_vel;
-    for (int j = 0; j < A; ++j) dst[o++] = act[j];
-    if (c.family == 1) {
-      dst[o++] = sinf(kTwoPi * phase);
-      dst[o++] = cosf(kTwoPi * phase);
-      for (int i = 0; i < c.num_obs; ++i) priv[3 + i] = fminf(fmaxf(obs[i], -c.clip_obs), c.clip_obs);
-      for (int i = 0; i < 3; ++i) priv[i] = fminf(fmaxf(priv[i], -c.clip_obs), c.clip_obs);
+  // ---- E12 observations :789-811 / h1_env.py:68-95 into the shared rows (raw), then noise + the clips of
+  //      step() :643-646 over this lane's contiguous column range ----
+  {
+    const int o0 = c.family == 1 ? 0 : 3;          // column of ang_vel
+    if (g == 0) {
+      if (c.family == 0) {
+        obs[0] = lvx * c.obs_scale_lin_vel; obs[1] = lvy * c.obs_scale_lin_vel; obs[2] = lvz * c.obs_scale_lin_vel;
+      }
+      obs[o0 + 0] = avx * c.obs_scale_ang_vel; obs[o0 + 1] = avy * c.obs_scale_ang_vel; obs[o0 + 2] = avz * c.obs_scale_ang_vel;
+      obs[o0 + 3] = gx; obs[o0 + 4] = gy; obs[o0 + 5] = gz;
+      obs[o0 + 6] = cmd[0] * c.obs_scale_lin_vel; obs[o0 + 7] = cmd[1] * c.obs_scale_lin_vel;
+      obs[o0 + 8] = cmd[2] * c.obs_scale_ang_vel;
+      if (c.family == 1) {
+        obs[9 + 3 * A] = sinf(kTwoPi * phase);
+        obs[10 + 3 * A] = cosf(kTwoPi * phase);
+        const float cl = c.clip_obs;
+        priv[0] = fminf(fmaxf(lvx * c.obs_scale_lin_vel, -cl), cl);
+        priv[1] = fminf(fmaxf(lvy * c.obs_scale_lin_vel, -cl), cl);
+        priv[2] = fminf(fmaxf(lvz * c.obs_scale_lin_vel, -cl), cl);
+      }
     }
-    for (int i = 0; i < c.num_obs; ++i) {
+    for (int j = g; j < A; j += kLanesPerEnv) {
+      const float qv = dof[2 * j + 1];
+      obs[o0 + 9 + j] = (dof[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
+      obs[o0 + 9 + A + j] = qv * c.obs_scale_dof_vel;
+      obs[o0 + 9 + 2 * A + j] = act[j];
+      lact[j] = act[j];                                                 // tail copies :707-708
+      ldv[j] = qv;
+    }
+    __syncwarp();
+    const int chunk = (c.num_obs + kLanesPerEnv - 1) / kLanesPerEnv;
+    const int i1 = min(c.num_obs, (g + 1) * chunk);
+    const float cl = c.clip_obs;
+    for (int i = g * chunk; i < i1; ++i) {
       float v = obs[i];
+      if (c.family == 1) priv[3 + i] = fminf(fmaxf(v, -cl), cl);       // privileged obs carry no noise
       const float ns = c.noise_scale_vec[i];
       if (c.add_noise && ns != 0.0f) v += (2.0f * rng.uniform(14 + A + i) - 1.0f) * ns;
-      obs[i] = fminf(fmaxf(v, -c.clip_obs), c.clip_obs);
-    }
-
-    // ---- tail copies :707-708 (in shared; stored coalesced below) ----
-    for (int j = 0; j < A; ++j) { lact[j] = act[j]; ldv[j] = dof[2 * j + 1]; }
-
-    // ---- per-env scalars and short rows (already coalesced) ----
-    b.episode_length_buf[e] = len;
-    b.rew_buf[e] = rew;
-    b.reset_buf[e] = reset ? 1 : 0;
-    b.time_out_buf[e] = time_out ? 1 : 0;
-    reinterpret_cast<float4*>(b.commands)[e] = make_float4(cmd[0], cmd[1], cmd[2], cmd[3]);
-    for (int f = 0; f < F; ++f) {
-      b.feet_air_time[(size_t)e * F + f] = air[f];
-      b.last_contacts[(size_t)e * F + f] = lastc[f];
-    }
-    float* o3 = b.rpy + (size_t)e * 3; o3[0] = roll; o3[1] = pitch; o3[2] = yaw;
-    o3 = b.base_lin_vel + (size_t)e * 3; o3[0] = lvx; o3[1] = lvy; o3[2] = lvz;
-    o3 = b.base_ang_vel + (size_t)e * 3; o3[0] = avx; o3[1] = avy; o3[2] = avz;
-    o3 = b.projected_gravity + (size_t)e * 3; o3[0] = gx; o3[1] = gy; o3[2] = gz;
-    if (c.family == 1) {
-      b.phase[e] = phase;
-      b.leg_phase[(size_t)e * 2] = leg_phase[0];
-      b.leg_phase[(size_t)e * 2 + 1] = leg_phase[1];
+      obs[i] = fminf(fmaxf(v, -cl), cl);
     }
   }
-  if (__any_sync(0xffffffffu, push_due) && lane == 0) atomicOr(&scratch->push_flag[acc], 1);
-  __syncwarp();
 
-  // ---- coalesced stores of the row outputs ----
-  stage_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, c.num_obs, L.sObs, nrows, lane);
+  // ---- per-env scalars and short rows ----
+  if (live) {
+    if (g == 0) {
+      b.episode_length_buf[e] = len;
+      b.rew_buf[e] = rew;
+      b.reset_buf[e] = reset ? 1 : 0;
+      b.time_out_buf[e] = time_out ? 1 : 0;
+      reinterpret_cast<float4*>(b.commands)[e] = make_float4(cmd[0], cmd[1], cmd[2], cmd[3]);
+      if (c.family == 1) {
+        b.phase[e] = phase;
+        b.leg_phase[(size_t)e * 2] = leg_phase[0];
+        b.leg_phase[(size_t)e * 2 + 1] = leg_phase[1];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int f = g + 4 * q;
+      if (f < F) {
+        b.feet_air_time[(size_t)e * F + f] = air[q];
+        b.last_contacts[(size_t)e * F + f] = lastc[q];
+      }
+    }
+    // lane g stores the g-th of (rpy, base_lin_vel, base_ang_vel, projected_gravity)
+    float* o3 = (g == 0 ? b.rpy : g == 1 ? b.base_lin_vel : g == 2 ? b.base_ang_vel : b.projected_gravity) + (size_t)e * 3;
+    o3[0] = g == 0 ? roll : g == 1 ? lvx : g == 2 ? avx : gx;
+    o3[1] = g == 0 ? pitch : g == 1 ? lvy : g == 2 ? avy : gy;
+    o3[2] = g == 0 ? yaw : g == 1 ? lvz : g == 2 ? avz : gz;
+  }
+  if (__any_sync(0xffffffffu, push_due) && (tid & 31) == 0) atomicOr(&scratch->push_flag[acc], 1);
+  __syncthreads();
+
+  // ---- flat stores of the row outputs ----
+  flat_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, nrows * c.num_obs, bulk, tid);
   if (c.num_priv)
-    stage_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, c.num_priv, L.sPriv, nrows, lane);
-  stage_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, A, L.sA, nrows, lane);
-  stage_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, A, L.sA, nrows, lane);
+    flat_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, nrows * c.num_priv, bulk, tid);
+  flat_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, nrows * A, bulk, tid);
+  flat_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, nrows * A, bulk, tid);
 }
 
 // ---------------------------------------------------------------- K2b: finalize
@@ -666,6 +757,13 @@ extern "C" int urlg_env_bind(urlg_env* env, const urlg_env_buffers* b) {
   if (((uintptr_t)b->commands & 15) || ((uintptr_t)b->dof_state & 7))
     return fail(URLG_EINVAL, "urlg_env_bind: commands must be 16-byte and dof_state 8-byte aligned");
   env->bufs = *b;
+  {
+    const void* al[] = {b->root_states, b->dof_state, b->contact_forces, b->actions, b->last_actions, b->last_dof_vel,
+                        b->torques, b->obs_buf[0], b->obs_buf[1], b->priv_obs_buf[0], b->priv_obs_buf[1]};
+    uintptr_t bits = 0;
+    for (size_t i = 0; i < sizeof(al) / sizeof(al[0]); ++i) bits |= (uintptr_t)al[i];
+    env->vec_ok = (bits & 15) == 0;
+  }
   env->bound = 1;
   return URLG_OK;
 }
@@ -695,8 +793,8 @@ extern "C" int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_
   const int N = env->desc.num_envs;
   const int slots = urlg_env_num_rng_slots(env);
   cudaStream_t st = (cudaStream_t)stream;
-  post_physics_kernel<<<(N + kWarp - 1) / kWarp, kWarp, env->smem_bytes, st>>>(env->desc, env->bufs, env->scratch,
-                                                                             step_base, step_offset, obs_slot, slots);
+  post_physics_kernel<<<(N + kEnvsPerBlock - 1) / kEnvsPerBlock, kK2Threads, env->smem_bytes, st>>>(
+      env->desc, env->bufs, env->scratch, step_base, step_offset, obs_slot, slots, env->vec_ok);
   URLG_LAUNCH_CHECK();
   finalize_step_kernel<<<grid_for(N, 256), 256, 0, st>>>(env->desc, env->bufs, env->scratch, step_base, step_offset,
                                                         slots);
