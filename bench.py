@@ -316,28 +316,35 @@ def own_arm(a):
     roof = None
     extra = {}
     if rank == 0:
-        st = _lib.cur_stream()
         iters = 200
 
         def time_call(fn, reps):
-            for _ in range(5):
+            """us per call: `reps` back-to-back launches captured in one CUDA graph (no host launch cost in the
+            bracket), CUDA events on the replaying stream."""
+            for _ in range(3):
                 fn()
+            torch.cuda.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                for _ in range(reps):
+                    fn()
+            gr.replay()
+            torch.cuda.synchronize()
             e0, e1 = ev(), ev()
             e0.record()
-            for _ in range(reps):
-                fn()
+            gr.replay()
             e1.record()
             e1.synchronize()
-            return e0.elapsed_time(e1) * 1e3 / reps      # us per call
+            return e0.elapsed_time(e1) * 1e3 / reps
 
         def post():
             env.common_step_counter += 1
             env._obs_slot ^= 1
             _lib.check(L.urlg_post_physics(env._handle, _lib.ptr(env._step_base), env.common_step_counter,
-                                           env._obs_slot, st))
+                                           env._obs_slot, _lib.cur_stream()))
         raw_act = torch.randn(n, env.num_actions, device=dev)
         us_post = time_call(post, iters)
-        us_pd = time_call(lambda: _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(raw_act), st)), iters)
+        us_pd = time_call(lambda: _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(raw_act), _lib.cur_stream())), iters)
         b2 = K2_BYTES[task] * n
         roof = {"kernel": "post_physics_kernel (+finalize_step_kernel), K2 of SURVEY.md §8(a).7", "bound": "hbm",
                 "achieved": b2 / us_post / 1e3, "peak": hbm, "unit": "GB/s", "frac": b2 / us_post / 1e3 / hbm,
@@ -369,9 +376,9 @@ def own_arm(a):
                 env_b.common_step_counter += 1
                 env_b._obs_slot ^= 1
                 _lib.check(L.urlg_post_physics(env_b._handle, _lib.ptr(env_b._step_base), env_b.common_step_counter,
-                                               env_b._obs_slot, st))
+                                               env_b._obs_slot, _lib.cur_stream()))
             us_b = time_call(post_b, 20)
-            us_pd_b = time_call(lambda: _lib.check(L.urlg_pd_torques(env_b._handle, _lib.ptr(act_b), st)), 20)
+            us_pd_b = time_call(lambda: _lib.check(L.urlg_pd_torques(env_b._handle, _lib.ptr(act_b), _lib.cur_stream())), 20)
             bb = K2_BYTES[task] * big
             extra["roofline_large"] = {"kernel": "post_physics_kernel (+finalize)", "envs": big, "bound": "hbm",
                                        "achieved": bb / us_b / 1e3, "peak": hbm, "unit": "GB/s",

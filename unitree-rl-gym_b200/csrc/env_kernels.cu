@@ -48,7 +48,7 @@ namespace urlg {
 constexpr int kEnvsPerBlock = 32, kLanesPerEnv = 4, kK2Threads = kEnvsPerBlock * kLanesPerEnv;
 
 struct Layout {
-  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, oBar, total;   // float offsets
+  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, oTerm, oBar, total;   // float offsets
 };
 
 __host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
@@ -67,6 +67,7 @@ __host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
   L.oObs = o; o += R * c.num_obs;
   L.oPriv = o; o += R * c.num_priv;
   o = (o + 3) & ~3;
+  L.oTerm = o; o += R * URLG_MAX_TERMS;      // this step's scaled term values per env (episode_sums increments)
   L.oBar = o; o += 4;
   L.total = o;
   return L;
@@ -77,7 +78,11 @@ __device__ __forceinline__ void bulk_g2s(float* dst, const float* src, uint32_t 
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_addr(dst)), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar) : "memory");
 }
-// Flat copy of `n` floats (tail / unaligned fallback and the copy-out path).
+__device__ __forceinline__ void bulk_s2g(float* dst, const float* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(reinterpret_cast<uint64_t>(dst)), "r"(smem_addr(src)), "r"(bytes) : "memory");
+}
+// Flat copy of `n` floats (tail / unaligned fallback).
 __device__ __forceinline__ void flat_in(float* __restrict__ s, const float* __restrict__ g, int n, int n_pad, int tid) {
   for (int i = tid; i < n_pad; i += kK2Threads) s[i] = i < n ? g[i] : 0.0f;
 }
@@ -123,13 +128,60 @@ __device__ __forceinline__ void rot_inv(float qx, float qy, float qz, float qw, 
 }
 
 // ---------------------------------------------------------------- K1: PD torques
-// One thread per (env, dof); actions / torques coalesced, dof_state read as float2.
+// One element: clip + store the action (first substep), PD law, torque-limit clip (legged_robot.py:649-671).
+__device__ __forceinline__ float pd_one(const urlg_env_desc& c, int j, float a, float q, float qd, float last_qd) {
+  const float as = a * c.action_scale;
+  float tq;
+  if (c.control_type == 'P') {
+    tq = c.p_gains[j] * (as + c.default_dof_pos[j] - q) - c.d_gains[j] * qd;
+  } else if (c.control_type == 'V') {
+    tq = c.p_gains[j] * (as - qd) - c.d_gains[j] * (qd - last_qd) / c.sim_dt;
+  } else {
+    tq = as;
+  }
+  const float lim = c.torque_limits[j];
+  return fminf(fmaxf(tq, -lim), lim);
+}
+
+// Vector form (num_dof % 4 == 0, 16-byte aligned tensors): one thread per 4 consecutive DOFs of an env -- one float4 of
+// actions, two float4 of interleaved (pos, vel) pairs in, one float4 of torques out; one element per thread, no loop,
+// so every load of the grid is in flight at once.
+__global__ void __launch_bounds__(256) pd_torques_vec4_kernel(const __grid_constant__ urlg_env_desc c,
+                                                              const __grid_constant__ urlg_env_buffers b,
+                                                              const float* __restrict__ raw_actions, uint32_t total4) {
+  const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+  if (i >= total4) return;
+  const uint32_t quads = (uint32_t)c.num_dof >> 2;
+  const int j0 = (int)(i % quads) * 4;
+  float4 a;
+  if (raw_actions) {
+    a = __ldg(reinterpret_cast<const float4*>(raw_actions) + i);
+    const float cl = c.clip_actions;
+    a.x = fminf(fmaxf(a.x, -cl), cl); a.y = fminf(fmaxf(a.y, -cl), cl);
+    a.z = fminf(fmaxf(a.z, -cl), cl); a.w = fminf(fmaxf(a.w, -cl), cl);
+    reinterpret_cast<float4*>(b.actions)[i] = a;
+  } else {
+    a = reinterpret_cast<const float4*>(b.actions)[i];
+  }
+  const float4 s0 = reinterpret_cast<const float4*>(b.dof_state)[2 * (size_t)i];
+  const float4 s1 = reinterpret_cast<const float4*>(b.dof_state)[2 * (size_t)i + 1];
+  float4 l = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  if (c.control_type == 'V') l = reinterpret_cast<const float4*>(b.last_dof_vel)[i];
+  float4 t;
+  t.x = pd_one(c, j0, a.x, s0.x, s0.y, l.x);
+  t.y = pd_one(c, j0 + 1, a.y, s0.z, s0.w, l.y);
+  t.z = pd_one(c, j0 + 2, a.z, s1.x, s1.y, l.z);
+  t.w = pd_one(c, j0 + 3, a.w, s1.z, s1.w, l.w);
+  reinterpret_cast<float4*>(b.torques)[i] = t;
+}
+
+// Scalar form: one thread per (env, dof); actions / torques coalesced, dof_state read as float2.
 __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__ urlg_env_desc c,
                                                          const __grid_constant__ urlg_env_buffers b,
                                                          const float* __restrict__ raw_actions) {
   const int64_t total = (int64_t)c.num_envs * c.num_dof;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int j = (int)(i % c.num_dof);
+    const int j = (int)((uint64_t)i <= 0xffffffffull ? (uint32_t)i % (uint32_t)c.num_dof : i % c.num_dof);
     float a;
     if (raw_actions) {
       a = fminf(fmaxf(raw_actions[i], -c.clip_actions), c.clip_actions);
@@ -138,17 +190,7 @@ __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__
       a = b.actions[i];
     }
     const float2 pv = reinterpret_cast<const float2*>(b.dof_state)[i];
-    const float as = a * c.action_scale;
-    float tq;
-    if (c.control_type == 'P') {
-      tq = c.p_gains[j] * (as + c.default_dof_pos[j] - pv.x) - c.d_gains[j] * pv.y;
-    } else if (c.control_type == 'V') {
-      tq = c.p_gains[j] * (as - pv.y) - c.d_gains[j] * (pv.y - b.last_dof_vel[i]) / c.sim_dt;
-    } else {
-      tq = as;
-    }
-    const float lim = c.torque_limits[j];
-    b.torques[i] = fminf(fmaxf(tq, -lim), lim);
+    b.torques[i] = pd_one(c, j, a, pv.x, pv.y, c.control_type == 'V' ? b.last_dof_vel[i] : 0.0f);
   }
 }
 
@@ -174,7 +216,7 @@ namespace urlg {
 // g, g+4, g+8, ... and the observation columns [g*ceil(num_obs/4), ...); per-env scalars (frame transforms,
 // commands, termination) are computed by all four lanes on identical inputs, so every lane holds identical bits
 // and the quad never diverges on an env-level decision.
-__global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+__global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
                                                                  const __grid_constant__ urlg_env_buffers b,
                                                                  StepScratch* __restrict__ scratch,
                                                                  const int64_t* __restrict__ step_base, int64_t step_off,
@@ -222,6 +264,32 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
       sm[L.oRb + i] = r < nrows ? b.rigid_body_states[((size_t)(env0 + r) * B + c.feet_idx[f]) * 13 + k] : 0.0f;
     }
   }
+  const int le = tid >> 2, g = tid & 3;
+  const int e = env0 + le;
+  const bool live = le < nrows;            // tail block: dead quads compute on zeros and store nothing
+  // ---- per-env scalars straight from global, issued before the wait so their latency hides under the bulk copy ----
+  int64_t len = (live ? b.episode_length_buf[e] : 0) + 1;              // :681
+  float cmd[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  if (live) {
+    const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
+    cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
+  }
+  float air[2] = {0.0f, 0.0f};
+  uint8_t lastc[2] = {0, 0};
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int f = g + 4 * q;
+    if (f < F && live) {
+      air[q] = b.feet_air_time[(size_t)e * F + f];
+      lastc[q] = b.last_contacts[(size_t)e * F + f];
+    }
+  }
+  float sums[URLG_MAX_TERMS / kLanesPerEnv];      // episode_sums rows g, g+4, ... of this env
+#pragma unroll
+  for (int q = 0; q < URLG_MAX_TERMS / kLanesPerEnv; ++q) {
+    const int k = g + kLanesPerEnv * q;
+    sums[q] = (live && k < c.num_sums) ? b.episode_sums[(size_t)k * N + e] : 0.0f;
+  }
   __syncthreads();
   if (bulk) {
     uint32_t ok = 0;
@@ -231,9 +299,6 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
     }
   }
 
-  const int le = tid >> 2, g = tid & 3;
-  const int e = env0 + le;
-  const bool live = le < nrows;            // tail block: dead quads compute on zeros and store nothing
   float* root = sm + L.oRoot + le * 13;
   float* dof = sm + L.oDof + le * 2 * A;
   const float* con = sm + L.oCon + le * 3 * B;
@@ -244,12 +309,11 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
   const float* rb = sm + L.oRb + le * F * 13;
   float* obs = sm + L.oObs + le * c.num_obs;
   float* priv = sm + L.oPriv + le * c.num_priv;
+  float* term = sm + L.oTerm + le * URLG_MAX_TERMS;
 
   SlotRng rng;
   rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
            (b.rng_override && live) ? b.rng_override + (size_t)e * num_slots : nullptr);
-
-  int64_t len = (live ? b.episode_length_buf[e] : 0) + 1;              // :681
   const float flen = (float)len;
 
   // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
@@ -270,11 +334,6 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
     phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
     leg_phase[0] = phase;
     leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
-  }
-  float cmd[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-  if (live) {
-    const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
-    cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
   }
   if (divisible(len, c.resample_steps)) resample_commands(c, rng, 0, cmd);
   if (c.heading_command) {
@@ -300,16 +359,6 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
   reset |= time_out;
 
   // ---- E8/E9 rewards, alphabetical, :775-787.  Lane g owns feet g and g+4. ----
-  float air[2] = {0.0f, 0.0f};
-  uint8_t lastc[2] = {0, 0};
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int f = g + 4 * q;
-    if (f < F && live) {
-      air[q] = b.feet_air_time[(size_t)e * F + f];
-      lastc[q] = b.last_contacts[(size_t)e * F + f];
-    }
-  }
   const float cmd_xy = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]);
   float rew = 0.0f;
   for (int t = 0; t < c.num_terms; ++t) {
@@ -433,24 +482,18 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
     }
     r *= c.term_scales[t];
     rew += r;
-    const int row = c.term_sum_row[t];
-    if (live && (row & 3) == g) b.episode_sums[(size_t)row * N + e] += r;   // row k is always touched by lane k & 3
+    if (g == 0) term[c.term_sum_row[t]] = r;
   }
   if (c.only_positive) rew = fmaxf(rew, 0.0f);
   if (c.has_termination) {
     const float r = ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale;
     rew += r;
-    if (live && (c.termination_sum_row & 3) == g) b.episode_sums[(size_t)c.termination_sum_row * N + e] += r;
+    if (g == 0) term[c.termination_sum_row] = r;
   }
 
   // ---- E10 reset_idx for this env :723-768 (quad-uniform branch) ----
   if (reset) {
     if (live) {
-      for (int k = g; k < c.num_sums; k += kLanesPerEnv) {
-        float* s = b.episode_sums + (size_t)k * N + e;
-        atomicAdd(&scratch->ep_acc[acc][k], *s);
-        *s = 0.0f;
-      }
       if (g == 0) {
         atomicAdd(&scratch->ep_acc[acc][URLG_MAX_TERMS], 1.0f);
         const int pos = atomicAdd(&scratch->reset_cnt[acc], 1);
@@ -477,6 +520,18 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
     len = 0;                                                            // :756
   }
   const bool push_due = live && c.push_robots && divisible(len, c.push_interval);   // :545, evaluated after the reset
+
+  // ---- episode_sums rows g, g+4, ...: += this step's term (:779-780, 786); reset envs publish and clear (:759-763) ----
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < URLG_MAX_TERMS / kLanesPerEnv; ++q) {
+    const int k = g + kLanesPerEnv * q;
+    if (live && k < c.num_sums) {
+      float v = sums[q] + term[k];
+      if (reset) { atomicAdd(&scratch->ep_acc[acc][k], v); v = 0.0f; }
+      b.episode_sums[(size_t)k * N + e] = v;
+    }
+  }
 
   // ---- E12 observations :789-811 / h1_env.py:68-95 into the shared rows (raw), then noise + the clips of
   //      step() :643-646 over this lane's contiguous column range ----
@@ -549,9 +604,24 @@ __global__ void __launch_bounds__(kK2Threads) post_physics_kernel(const __grid_c
     o3[2] = g == 0 ? yaw : g == 1 ? lvz : g == 2 ? avz : gz;
   }
   if (__any_sync(0xffffffffu, push_due) && (tid & 31) == 0) atomicOr(&scratch->push_flag[acc], 1);
+  if (bulk) {
+    // ---- row outputs leave as 1-D bulk-TMA stores (shared -> global), issued by one thread ----
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, kEnvsPerBlock * c.num_obs * sizeof(float));
+      if (c.num_priv)
+        bulk_s2g(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, kEnvsPerBlock * c.num_priv * sizeof(float));
+      bulk_s2g(b.last_actions + (size_t)env0 * A, sm + L.oLact, kEnvsPerBlock * A * sizeof(float));
+      bulk_s2g(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, kEnvsPerBlock * A * sizeof(float));
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+    return;
+  }
   __syncthreads();
 
-  // ---- flat stores of the row outputs ----
+  // ---- tail block / unaligned fallback: flat stores of the row outputs ----
   flat_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, nrows * c.num_obs, bulk, tid);
   if (c.num_priv)
     flat_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, nrows * c.num_priv, bulk, tid);
@@ -781,7 +851,15 @@ extern "C" int urlg_env_num_rng_slots(const urlg_env* env) {
 extern "C" int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream) {
   if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_pd_torques: env not bound");
   const int64_t total = (int64_t)env->desc.num_envs * env->desc.num_dof;
-  pd_torques_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions);
+  const urlg_env_buffers& eb = env->bufs;
+  const uintptr_t bits = (uintptr_t)raw_actions | (uintptr_t)eb.actions | (uintptr_t)eb.dof_state | (uintptr_t)eb.torques |
+                         (uintptr_t)eb.last_dof_vel;
+  if ((env->desc.num_dof & 3) == 0 && (bits & 15) == 0 && total / 4 < 0x7fffffffll) {
+    const uint32_t total4 = (uint32_t)(total / 4);
+    pd_torques_vec4_kernel<<<(total4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions, total4);
+  } else {
+    pd_torques_kernel<<<grid_for(total, 256, 64), 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions);
+  }
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }
