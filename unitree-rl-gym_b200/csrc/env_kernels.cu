@@ -83,17 +83,13 @@ __device__ __forceinline__ void bulk_s2g(float* dst, const float* src, uint32_t 
                ::"l"(reinterpret_cast<uint64_t>(dst)), "r"(smem_addr(src)), "r"(bytes) : "memory");
 }
 // Flat copy of `n` floats (tail / unaligned fallback).
-__device__ __forceinline__ void flat_in(float* __restrict__ s, const float* __restrict__ g, int n, int n_pad, int tid) {
+static __device__ __noinline__ void flat_in(float* __restrict__ s, const float* __restrict__ g, int n, int n_pad, int tid) {
+#pragma unroll 1
   for (int i = tid; i < n_pad; i += kK2Threads) s[i] = i < n ? g[i] : 0.0f;
 }
-__device__ __forceinline__ void flat_out(float* __restrict__ g, const float* __restrict__ s, int n, bool vec, int tid) {
-  if (vec) {
-    const float4* s4 = reinterpret_cast<const float4*>(s);
-    float4* g4 = reinterpret_cast<float4*>(g);
-    for (int i = tid; i < (n >> 2); i += kK2Threads) g4[i] = s4[i];
-  } else {
-    for (int i = tid; i < n; i += kK2Threads) g[i] = s[i];
-  }
+static __device__ __noinline__ void flat_out(float* __restrict__ g, const float* __restrict__ s, int n, int tid) {
+#pragma unroll 1
+  for (int i = tid; i < n; i += kK2Threads) g[i] = s[i];
 }
 // Sum over the 4 lanes of an env; every lane gets the same bits (commutative pairwise adds).
 __device__ __forceinline__ float qsum(float x) {
@@ -108,12 +104,15 @@ __device__ __forceinline__ bool divisible(int64_t len, int period) {
 }
 
 // torch.remainder for floats: fmod then fix the sign (ATen BinaryOpsKernel remainder_kernel).
-__device__ __forceinline__ float py_remainder(float a, float b) {
+static __device__ __noinline__ float py_remainder(float a, float b) {
   float m = fmodf(a, b);
   if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m += b;
   return m;
 }
 
+// One out-of-line copy each of the libm-heavy helpers: K2 is latency-bound at 4096 envs and an I-cache miss costs more
+// than a call (ncu: 45% of stall samples were no_instructions with everything inlined, 10k SASS instructions).
+static __device__ __noinline__ float atan2_ni(float y, float x) { return atan2f(y, x); }
 __device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
 
 // [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw
@@ -179,9 +178,9 @@ __global__ void __launch_bounds__(256) pd_torques_vec4_kernel(const __grid_const
 __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__ urlg_env_desc c,
                                                          const __grid_constant__ urlg_env_buffers b,
                                                          const float* __restrict__ raw_actions) {
-  const int64_t total = (int64_t)c.num_envs * c.num_dof;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int j = (int)((uint64_t)i <= 0xffffffffull ? (uint32_t)i % (uint32_t)c.num_dof : i % c.num_dof);
+  const uint32_t total = (uint32_t)c.num_envs * (uint32_t)c.num_dof;      // host checks num_envs * num_dof < 2^31
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int j = (int)(i % (uint32_t)c.num_dof);
     float a;
     if (raw_actions) {
       a = fminf(fmaxf(raw_actions[i], -c.clip_actions), c.clip_actions);
@@ -195,7 +194,7 @@ __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__
 }
 
 // ---------------------------------------------------------------- command resampling (E6)
-__device__ __forceinline__ void resample_commands(const urlg_env_desc& c, SlotRng& rng, int slot, float* cmd) {
+static __device__ __noinline__ void resample_commands(const urlg_env_desc& c, SlotRng& rng, int slot, float* cmd) {
   cmd[0] = (c.cmd_x[1] - c.cmd_x[0]) * rng.uniform(slot) + c.cmd_x[0];
   cmd[1] = (c.cmd_y[1] - c.cmd_y[0]) * rng.uniform(slot + 1) + c.cmd_y[0];
   if (c.heading_command)
@@ -318,10 +317,10 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
 
   // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
   const float qx = root[3], qy = root[4], qz = root[5], qw = root[6];
-  const float roll = atan2f(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
+  const float roll = atan2_ni(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
   const float sinp = 2.0f * (qw * qy - qz * qx);
   const float pitch = fabsf(sinp) >= 1.0f ? copysignf(kHalfPi, sinp) : asinf(sinp);
-  const float yaw = atan2f(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
+  const float yaw = atan2_ni(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
   float lvx, lvy, lvz, avx, avy, avz, gx, gy, gz;
   rot_inv(qx, qy, qz, qw, root[7], root[8], root[9], lvx, lvy, lvz);
   rot_inv(qx, qy, qz, qw, root[10], root[11], root[12], avx, avy, avz);
@@ -341,7 +340,7 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
     const float ty = qz * 2.0f, tz = -qy * 2.0f;
     const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
     const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
-    const float heading = atan2f(fy, fx);
+    const float heading = atan2_ni(fy, fx);
     float a = py_remainder(cmd[3] - heading, kTwoPi);
     a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
     cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
@@ -349,7 +348,7 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
 
   // ---- E7 termination :715-721 ----
   float hits = 0.0f;
-  for (int k = g; k < c.num_term_bodies; k += kLanesPerEnv) {
+  _Pragma("unroll 1") for (int k = g; k < c.num_term_bodies; k += kLanesPerEnv) {
     const float* f3 = con + 3 * c.term_idx[k];
     hits += norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
   }
@@ -365,14 +364,14 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
     float r = 0.0f;
     switch (c.term_ids[t]) {
       case URLG_T_ACTION_RATE:
-        for (int j = g; j < A; j += kLanesPerEnv) { const float d = lact[j] - act[j]; r += d * d; }
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float d = lact[j] - act[j]; r += d * d; }
         r = qsum(r);
         break;
       case URLG_T_ALIVE: r = 1.0f; break;
       case URLG_T_ANG_VEL_XY: r = avx * avx + avy * avy; break;
       case URLG_T_BASE_HEIGHT: { const float d = root_z - c.base_height_target; r = d * d; } break;
       case URLG_T_COLLISION:
-        for (int k = g; k < c.num_pen; k += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int k = g; k < c.num_pen; k += kLanesPerEnv) {
           const float* f3 = con + 3 * c.pen_idx[k];
           r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
         }
@@ -387,7 +386,7 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
         r = qsum(r);
         break;
       case URLG_T_CONTACT_NO_VEL:
-        for (int f = g; f < F; f += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
           const float* f3 = con + 3 * c.feet_idx[f];
           const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
           for (int k = 0; k < 3; ++k) { const float v = rb[f * 13 + 7 + k] * m; r += v * v; }
@@ -395,22 +394,22 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
         r = qsum(r);
         break;
       case URLG_T_DOF_ACC:
-        for (int j = g; j < A; j += kLanesPerEnv) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
         r = qsum(r);
         break;
       case URLG_T_DOF_POS_LIMITS:
-        for (int j = g; j < A; j += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {
           const float q = dof[2 * j];
           r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
         }
         r = qsum(r);
         break;
       case URLG_T_DOF_VEL:
-        for (int j = g; j < A; j += kLanesPerEnv) { const float v = dof[2 * j + 1]; r += v * v; }
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float v = dof[2 * j + 1]; r += v * v; }
         r = qsum(r);
         break;
       case URLG_T_DOF_VEL_LIMITS:
-        for (int j = g; j < A; j += kLanesPerEnv)
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv)
           r += fminf(fmaxf(fabsf(dof[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
         r = qsum(r);
         break;
@@ -432,14 +431,14 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
         r *= cmd_xy > 0.1f ? 1.0f : 0.0f;
       } break;
       case URLG_T_FEET_CONTACT_FORCES:
-        for (int f = g; f < F; f += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
           const float* f3 = con + 3 * c.feet_idx[f];
           r += fmaxf(norm3(f3[0], f3[1], f3[2]) - c.max_contact_force, 0.0f);
         }
         r = qsum(r);
         break;
       case URLG_T_FEET_SWING_HEIGHT:
-        for (int f = g; f < F; f += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
           const float* f3 = con + 3 * c.feet_idx[f];
           const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 0.0f : 1.0f;
           const float d = rb[f * 13 + 2] - 0.08f;
@@ -448,29 +447,29 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
         r = qsum(r);
         break;
       case URLG_T_HIP_POS:
-        for (int k = g; k < c.num_hip; k += kLanesPerEnv) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
+        _Pragma("unroll 1") for (int k = g; k < c.num_hip; k += kLanesPerEnv) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
         r = qsum(r);
         break;
       case URLG_T_LIN_VEL_Z: r = lvz * lvz; break;
       case URLG_T_ORIENTATION: r = gx * gx + gy * gy; break;
       case URLG_T_STAND_STILL:
-        for (int j = g; j < A; j += kLanesPerEnv) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
         r = qsum(r);
         r *= cmd_xy < 0.1f ? 1.0f : 0.0f;
         break;
       case URLG_T_STUMBLE: {
-        for (int f = g; f < F; f += kLanesPerEnv) {
+        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
           const float* f3 = con + 3 * c.feet_idx[f];
           r += sqrtf(f3[0] * f3[0] + f3[1] * f3[1]) > 5.0f * fabsf(f3[2]) ? 1.0f : 0.0f;
         }
         r = qsum(r) > 0.0f ? 1.0f : 0.0f;
       } break;
       case URLG_T_TORQUE_LIMITS:
-        for (int j = g; j < A; j += kLanesPerEnv) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
         r = qsum(r);
         break;
       case URLG_T_TORQUES:
-        for (int j = g; j < A; j += kLanesPerEnv) r += tq[j] * tq[j];
+        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += tq[j] * tq[j];
         r = qsum(r);
         break;
       case URLG_T_TRACKING_ANG_VEL: { const float d = cmd[2] - avz; r = expf(-(d * d) / c.tracking_sigma); } break;
@@ -502,14 +501,14 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
     }
     float* gdof = b.dof_state + (size_t)e * 2 * A;
     float* gact = b.actions + (size_t)e * A;
-    for (int j = g; j < A; j += kLanesPerEnv) {                        // _reset_dofs :566-567, actions :752
+    _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {                        // _reset_dofs :566-567, actions :752
       const float p = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
       dof[2 * j] = p; dof[2 * j + 1] = 0.0f;
       act[j] = 0.0f;
       if (live) { gdof[2 * j] = p; gdof[2 * j + 1] = 0.0f; gact[j] = 0.0f; }
     }
     float* groot = b.root_states + (size_t)e * 13;                     // _reset_root_states :587-590
-    for (int k = g; k < 13; k += kLanesPerEnv) {
+    _Pragma("unroll 1") for (int k = g; k < 13; k += kLanesPerEnv) {
       float v = c.base_init_state[k];
       if (k < 3 && live) v += b.env_origins[(size_t)e * 3 + k];
       if (k >= 7) v = (0.5f - (-0.5f)) * rng.uniform(3 + A + (k - 7)) + (-0.5f);
@@ -554,7 +553,7 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
         priv[2] = fminf(fmaxf(lvz * c.obs_scale_lin_vel, -cl), cl);
       }
     }
-    for (int j = g; j < A; j += kLanesPerEnv) {
+    _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {
       const float qv = dof[2 * j + 1];
       obs[o0 + 9 + j] = (dof[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
       obs[o0 + 9 + A + j] = qv * c.obs_scale_dof_vel;
@@ -622,11 +621,11 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
   __syncthreads();
 
   // ---- tail block / unaligned fallback: flat stores of the row outputs ----
-  flat_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, nrows * c.num_obs, bulk, tid);
+  flat_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, nrows * c.num_obs, tid);
   if (c.num_priv)
-    flat_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, nrows * c.num_priv, bulk, tid);
-  flat_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, nrows * A, bulk, tid);
-  flat_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, nrows * A, bulk, tid);
+    flat_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, nrows * c.num_priv, tid);
+  flat_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, nrows * A, tid);
+  flat_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, nrows * A, tid);
 }
 
 // ---------------------------------------------------------------- K2b: finalize
@@ -851,10 +850,11 @@ extern "C" int urlg_env_num_rng_slots(const urlg_env* env) {
 extern "C" int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream) {
   if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_pd_torques: env not bound");
   const int64_t total = (int64_t)env->desc.num_envs * env->desc.num_dof;
+  if (total >= 0x7fffffffll) return fail(URLG_EINVAL, "urlg_pd_torques: num_envs * num_dof must be < 2^31");
   const urlg_env_buffers& eb = env->bufs;
   const uintptr_t bits = (uintptr_t)raw_actions | (uintptr_t)eb.actions | (uintptr_t)eb.dof_state | (uintptr_t)eb.torques |
                          (uintptr_t)eb.last_dof_vel;
-  if ((env->desc.num_dof & 3) == 0 && (bits & 15) == 0 && total / 4 < 0x7fffffffll) {
+  if ((env->desc.num_dof & 3) == 0 && (bits & 15) == 0) {
     const uint32_t total4 = (uint32_t)(total / 4);
     pd_torques_vec4_kernel<<<(total4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions, total4);
   } else {
