@@ -312,10 +312,34 @@ def own_arm(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_roll_ms = t.item()
 
-    # ---- roofline of the dominant env kernel (K2 fused post-physics), timed alone with CUDA events on its stream
+    # ---- roofline of the dominant kernel.  By the ncu launch list (profiles/) the tcgen05 GEMM is ~70% of the GPU time
+    #      of a step, so `roofline` is the GEMM against the tensor peak: CUDA events around every GEMM launch of one
+    #      eager iteration (library hook urlg_gemm_timing), achieved = sum(2*M*N*K) / sum(duration).  The fused env
+    #      kernels (K2 + K2b, K1) are timed alone under graph replay against the HBM peak: `roofline_env*`.
     roof = None
     extra = {}
     if rank == 0:
+        import ctypes as C
+
+        def gemm_timed(fn):
+            _lib.check(L.urlg_gemm_timing(1))
+            out = fn()
+            torch.cuda.synchronize()
+            ms, cnt, fl = C.c_double(), C.c_int64(), C.c_double()
+            _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl)))
+            _lib.check(L.urlg_gemm_timing(0))
+            return out, ms.value, cnt.value, fl.value
+        (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
+        _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
+        tf = (fl_r + fl_u) / ((ms_r + ms_u) * 1e-3) / 1e12
+        roof = {"kernel": "tc::gemm_bf16_kernel (tcgen05/TMA GEMM: every Linear / LSTM-gate forward, dgrad, wgrad of the step)",
+                "bound": "tensor", "achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus, "traffic": None,
+                "launches_per_step": int(n_r + n_u), "us_per_launch": (ms_r + ms_u) * 1e3 / max(n_r + n_u, 1),
+                "flops_per_step": fl_r + fl_u, "peak_source": peak_src + " (sustained bf16, kernel timed inside a long step)",
+                "rollout": {"launches": int(n_r), "ms": ms_r, "tflops": fl_r / (ms_r * 1e-3) / 1e12 if ms_r else None},
+                "update": {"launches": int(n_u), "ms": ms_u, "tflops": fl_u / (ms_u * 1e-3) / 1e12 if ms_u else None},
+                "note": "algorithmic flops 2*M*N*K counted once per GEMM (the split-bf16 scheme issues 3 MMAs per product); "
+                        "skinny shapes (K=48..512, N=1..512) make these GEMMs epilogue- and HBM-traffic-bound, see DESIGN.md"}
         iters = 200
 
         def time_call(fn, reps):
@@ -346,11 +370,12 @@ def own_arm(a):
         us_post = time_call(post, iters)
         us_pd = time_call(lambda: _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(raw_act), _lib.cur_stream())), iters)
         b2 = K2_BYTES[task] * n
-        roof = {"kernel": "post_physics_kernel (+finalize_step_kernel), K2 of SURVEY.md §8(a).7", "bound": "hbm",
-                "achieved": b2 / us_post / 1e3, "peak": hbm, "unit": "GB/s", "frac": b2 / us_post / 1e3 / hbm,
-                "traffic": None, "alg_bytes_per_launch": b2, "us_per_launch": us_post, "peak_source": peak_src,
-                "note": f"{n} envs x {K2_BYTES[task]} B = {b2 / 1e6:.1f} MB is L2-resident and below launch latency "
-                        "(SURVEY.md §7): HBM fraction at this size measures latency, not bandwidth; see roofline_large"}
+        extra["roofline_env"] = {
+            "kernel": "post_physics_kernel (+finalize_step_kernel), K2 of SURVEY.md 8(a).7", "bound": "hbm",
+            "achieved": b2 / us_post / 1e3, "peak": hbm, "unit": "GB/s", "frac": b2 / us_post / 1e3 / hbm,
+            "traffic": None, "alg_bytes_per_launch": b2, "us_per_launch": us_post, "peak_source": peak_src,
+            "note": f"{n} envs x {K2_BYTES[task]} B = {b2 / 1e6:.1f} MB is L2-resident and below launch latency "
+                    "(SURVEY.md 7): HBM fraction at this size measures latency, not bandwidth; see roofline_env_large"}
         extra["k1_pd"] = {"us_per_launch": us_pd, "alg_bytes": K1_BYTES[task] * n,
                           "gbs": K1_BYTES[task] * n / us_pd / 1e3}
         # tensor side: update phase flops / time
@@ -380,7 +405,7 @@ def own_arm(a):
             us_b = time_call(post_b, 20)
             us_pd_b = time_call(lambda: _lib.check(L.urlg_pd_torques(env_b._handle, _lib.ptr(act_b), _lib.cur_stream())), 20)
             bb = K2_BYTES[task] * big
-            extra["roofline_large"] = {"kernel": "post_physics_kernel (+finalize)", "envs": big, "bound": "hbm",
+            extra["roofline_env_large"] = {"kernel": "post_physics_kernel (+finalize)", "envs": big, "bound": "hbm",
                                        "achieved": bb / us_b / 1e3, "peak": hbm, "unit": "GB/s",
                                        "frac": bb / us_b / 1e3 / hbm, "us_per_launch": us_b,
                                        "alg_bytes_per_launch": bb,

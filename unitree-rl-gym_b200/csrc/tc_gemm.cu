@@ -3,6 +3,8 @@
 #include "common.cuh"
 #include "tc_gemm.cuh"
 #include <cudaTypedefs.h>
+#include <utility>
+#include <vector>
 
 namespace urlg {
 namespace tc {
@@ -40,7 +42,32 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
   return URLG_OK;
 }
 
+// Optional per-launch timing (bench.py's roofline leg): CUDA events recorded on the launching stream around every
+// GEMM launch while enabled (never under graph capture), summed on read.
+static bool g_timing = false;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
+static double g_flops = 0.0;
+static size_t g_used = 0;
+
+int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st);
+
 int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
+  if (!g_timing) return launch_gemm_impl(d, st);
+  if (g_used == g_events.size()) {
+    cudaEvent_t a, b;
+    URLG_CUDA(cudaEventCreate(&a));
+    URLG_CUDA(cudaEventCreate(&b));
+    g_events.emplace_back(a, b);
+  }
+  URLG_CUDA(cudaEventRecord(g_events[g_used].first, st));
+  const int rc = launch_gemm_impl(d, st);
+  URLG_CUDA(cudaEventRecord(g_events[g_used].second, st));
+  ++g_used;
+  if (d) g_flops += 2.0 * d->M * d->N * d->K;
+  return rc;
+}
+
+int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   if (!d || !d->A || !d->B || d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(URLG_EINVAL, "urlg_tc_gemm: bad argument");
   GemmArgs g;
   g.M = d->M; g.N = d->N; g.K = d->K;
@@ -111,6 +138,28 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
 
 }  // namespace tc
 }  // namespace urlg
+
+extern "C" int urlg_gemm_timing(int enable) {
+  using namespace urlg::tc;
+  g_timing = enable != 0;
+  if (g_timing) { g_used = 0; g_flops = 0.0; }
+  return URLG_OK;
+}
+
+extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops) {
+  using namespace urlg::tc;
+  double ms = 0.0;
+  for (size_t i = 0; i < g_used; ++i) {
+    URLG_CUDA(cudaEventSynchronize(g_events[i].second));
+    float t = 0.0f;
+    URLG_CUDA(cudaEventElapsedTime(&t, g_events[i].first, g_events[i].second));
+    ms += t;
+  }
+  if (total_ms) *total_ms = ms;
+  if (launches) *launches = (int64_t)g_used;
+  if (flops) *flops = g_flops;
+  return URLG_OK;
+}
 
 extern "C" int urlg_tc_gemm(const urlg_gemm_desc* d, void* stream) {
   return urlg::tc::launch_gemm(d, (cudaStream_t)stream);

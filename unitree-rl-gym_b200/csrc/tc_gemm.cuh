@@ -44,7 +44,10 @@ inline int gemm_stages_for(int block_n, int split) {
 }
 inline int gemm_smem_bytes(int block_n, int split, int stages) { return stages * gemm_stage_bytes(block_n, split) + 1024 + 256; }
 
-__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : expm1f(x); }
+// ELU(x) = x > 0 ? x : exp(x) - 1.  The epilogue is instruction-bound (ncu: IPC-limited, tensor pipe ~10% busy), and
+// expm1f is ~20 of its ~35 instructions per element; ex2.approx (2 ulp) - 1 has an absolute error <= 2.5e-7, far inside
+// the 1e-4 forward / 1e-3 update tolerances (the values feed bf16 hi+lo operands of ~2^-17 relative resolution).
+__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
 __device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
