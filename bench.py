@@ -318,19 +318,21 @@ def own_arm(a):
     #      kernels (K2 + K2b, K1) are timed alone under graph replay against the HBM peak: `roofline_env*`.
     roof = None
     extra = {}
-    if rank == 0:
-        import ctypes as C
+    import ctypes as C
 
-        def gemm_timed(fn):
-            _lib.check(L.urlg_gemm_timing(1))
-            out = fn()
-            torch.cuda.synchronize()
-            ms, cnt, fl = C.c_double(), C.c_int64(), C.c_double()
-            _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl)))
-            _lib.check(L.urlg_gemm_timing(0))
-            return out, ms.value, cnt.value, fl.value
-        (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
-        _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
+    def gemm_timed(fn):
+        _lib.check(L.urlg_gemm_timing(1))
+        out = fn()
+        torch.cuda.synchronize()
+        ms, cnt, fl = C.c_double(), C.c_int64(), C.c_double()
+        _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl)))
+        _lib.check(L.urlg_gemm_timing(0))
+        return out, ms.value, cnt.value, fl.value
+    # every rank runs this iteration (the update holds collectives); rank 0 reports its own GEMM times
+    (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
+    _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
+    barrier()
+    if rank == 0:
         tf = (fl_r + fl_u) / ((ms_r + ms_u) * 1e-3) / 1e12
         roof = {"kernel": "tc::gemm_bf16_kernel (tcgen05/TMA GEMM: every Linear / LSTM-gate forward, dgrad, wgrad of the step)",
                 "bound": "tensor", "achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus, "traffic": None,
@@ -442,6 +444,7 @@ def own_arm(a):
         line.update(extra)
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
