@@ -126,7 +126,8 @@ def config_dict(task, n, world, graph):
                         "synthetic root/dof/contact state frames (PhysX is external to the path)",
             "task": task, "envs_per_gpu": n, "rollout_steps": ROLLOUT, "epochs": 5, "mini_batches": 4,
             "parallelism": f"dp{world} (env shards, flat-gradient all-reduce)" if world > 1 else "single GPU",
-            "rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph)" if graph else "eager",
+            "rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph; the 20 minibatch steps of "
+                              "the update as a second graph when single-process)" if graph else "eager",
             "l2_policy": "working set per iteration (35 MB rollout storage + 8-frame physics pool) is cycled; every timed "
                          "iteration additionally starts after a 256 MiB L2 flush write outside the event bracket"}
 
@@ -199,6 +200,7 @@ def own_arm(a):
     env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     use_graph = (not a.no_graph) and RolloutGraph.supported(runner)
+    alg.cuda_graph_update = use_graph      # PPO.update replays its 20 minibatch steps as one graph (single process)
 
     def eager_rollout():
         obs = env.get_observations()
@@ -266,6 +268,8 @@ def own_arm(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     roll_ms, upd_ms, total_ms, wall_ms = t.tolist()
     launches = eager_launches + (graph.launches * a.steps if graph is not None else 0)
+    if alg.cuda_graph_update and alg._update_graph is not None:
+        launches += alg.update_graph_launches * a.steps
 
     # ---- e2e: the same rollout through the public API (eager), physics frames arriving from pinned HOST memory
     #      every env step (H2D inside the timed region) and rewards / dones read back to the host every step
@@ -329,6 +333,7 @@ def own_arm(a):
         _lib.check(L.urlg_gemm_timing(0))
         return out, ms.value, cnt.value, fl.value
     # every rank runs this iteration (the update holds collectives); rank 0 reports its own GEMM times
+    alg.cuda_graph_update = False          # the hook needs real launches, not graph replays
     (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
     _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
     barrier()

@@ -108,6 +108,11 @@ class PPO:
         self._act_base = None
         self.sample_noise = None     # parity hook: N(0,1) [N, A] used instead of Philox for the next act()
         self.perm = None             # parity hook: minibatch permutation [T*N] used instead of randperm
+        self.cuda_graph_update = False
+        self.update_graph_launches = 0
+        self._idx_buf = None
+        self._update_graph = None
+        self._update_warm = None
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank() if self.world > 1 else 0
 
@@ -237,24 +242,20 @@ class PPO:
                                      reduce_moments=self._reduce_moments if self.world > 1 else None)
 
     # ---- update
-    def update(self):
-        eng, s = self._check_engine(), self.storage
+    def _minibatch_loop(self, idx):
+        """num_learning_epochs x num_mini_batches of (gather + forward + loss + backward) -> (all-reduce) -> (LR rule,
+        clip, Adam).  Pure stream-ordered device work: capturable as one CUDA graph."""
+        eng, s = self.engine, self.storage
         L, st = _lib.lib(), _lib.cur_stream()
-        ac = self.actor_critic
         h = self._hparams()
         T, N = s.num_transitions_per_env, s.num_envs
         eng.stats[_lib.STAT_ACC_VLOSS:_lib.STAT_ACC_N + 1] = 0.0
         sd = s.desc()
-        if ac.is_recurrent:
+        if self.actor_critic.is_recurrent:
             mb = N // self.num_mini_batches
             batches = [(None, 0, i * mb, mb) for i in range(self.num_mini_batches)]
         else:
             mini = (N * T) // self.num_mini_batches
-            if self.perm is not None:
-                idx = self.perm.to(device=eng.device, dtype=torch.int64).contiguous()
-            else:
-                idx = torch.randperm(self.num_mini_batches * mini, device=eng.device)
-            self._indices = idx
             batches = [(idx[i * mini:(i + 1) * mini], mini, 0, 0) for i in range(self.num_mini_batches)]
         for _ in range(self.num_learning_epochs):
             for ind, rows, e0, ec in batches:
@@ -264,6 +265,46 @@ class PPO:
                     dist.all_reduce(eng.grads)
                     dist.all_reduce(eng.stats[_lib.STAT_KL_SUM:_lib.STAT_ENT_SUM + 1])
                 _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), st))
+
+    def update(self):
+        eng, s = self._check_engine(), self.storage
+        ac = self.actor_critic
+        T, N = s.num_transitions_per_env, s.num_envs
+        idx = None
+        if not ac.is_recurrent:
+            mini = (N * T) // self.num_mini_batches
+            if self.perm is not None:
+                idx = self.perm.to(device=eng.device, dtype=torch.int64).contiguous()
+            else:
+                idx = torch.randperm(self.num_mini_batches * mini, device=eng.device)
+            if self._idx_buf is None or self._idx_buf.numel() != idx.numel():
+                self._idx_buf = torch.empty_like(idx)
+                self._update_graph = None
+            self._idx_buf.copy_(idx)           # static buffer: the captured graph gathers through it
+            idx = self._indices = self._idx_buf
+        # opt-in (`cuda_graph_update`, set by the runner's `cuda_graph` cfg key): the 20 minibatch steps (~800 launches
+        # for the MLP, ~8000 for the LSTM's per-step BPTT) replayed as one graph; single process only (NCCL calls are
+        # left eager), and invalidated when the engine / storage it captured is replaced
+        key = (id(eng), s.desc().observations, self.clip_param, self.value_loss_coef, self.entropy_coef, self.max_grad_norm,
+               self.desired_kl, self.schedule, self.num_learning_epochs, self.num_mini_batches, self.use_clipped_value_loss)
+        if self.cuda_graph_update and self.world == 1:
+            if self._update_graph is None or self._update_graph[0] != key:
+                if self._update_warm != key:
+                    self._minibatch_loop(idx)          # first update runs eagerly (lazy init, warm-up), capture on the next
+                    self._update_warm = key
+                else:
+                    torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    n0 = _lib.lib().urlg_launch_count()
+                    with torch.cuda.graph(g):
+                        self._minibatch_loop(idx)
+                    self.update_graph_launches = _lib.lib().urlg_launch_count() - n0
+                    self._update_graph = (key, g)
+                    g.replay()
+            else:
+                self._update_graph[1].replay()
+        else:
+            self._minibatch_loop(idx)
         stats = eng.stats.tolist()        # the one host read of the update
         n = max(stats[_lib.STAT_ACC_N], 1.0)
         self._lr_host = stats[_lib.STAT_LR]

@@ -35,6 +35,7 @@ class OnPolicyRunner:
         actor_critic = actor_critic_class(self.env.num_obs, num_critic_obs, self.env.num_actions,
                                           **self.policy_cfg).to(self.device)
         self.alg = alg_class(actor_critic, device=self.device, **self.alg_cfg)
+        self.alg.cuda_graph_update = bool(self.cfg.get("cuda_graph", False))
         seed = train_cfg.get("seed", 1)
         self.alg.seed = seed if seed is not None and seed >= 0 else 1
         self.num_steps_per_env = self.cfg["num_steps_per_env"]
