@@ -42,7 +42,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except OSError:
@@ -328,25 +328,38 @@ def own_arm(a):
         _lib.check(L.urlg_gemm_timing(1))
         out = fn()
         torch.cuda.synchronize()
-        ms, cnt, fl = C.c_double(), C.c_int64(), C.c_double()
-        _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl)))
+        ms, cnt, fl, by = C.c_double(), C.c_int64(), C.c_double(), C.c_double()
+        _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl), C.byref(by)))
         _lib.check(L.urlg_gemm_timing(0))
-        return out, ms.value, cnt.value, fl.value
+        return out, ms.value, cnt.value, (fl.value, by.value)
     # every rank runs this iteration (the update holds collectives); rank 0 reports its own GEMM times
     alg.cuda_graph_update = False          # the hook needs real launches, not graph replays
     (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
     _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
     barrier()
     if rank == 0:
-        tf = (fl_r + fl_u) / ((ms_r + ms_u) * 1e-3) / 1e12
+        (fl_r, by_r), (fl_u, by_u) = fl_r, fl_u
+        sec = (ms_r + ms_u) * 1e-3
+        tf, gbs = (fl_r + fl_u) / sec / 1e12, (by_r + by_u) / sec / 1e9
+        # which roof is lower for this mix of shapes: time at the HBM peak vs time at the tensor peak
+        t_hbm, t_tc = (by_r + by_u) / (hbm * 1e9), (fl_r + fl_u) / (tf_sus * 1e12)
+        mem_bound = t_hbm >= t_tc
         roof = {"kernel": "tc::gemm_bf16_kernel (tcgen05/TMA GEMM: every Linear / LSTM-gate forward, dgrad, wgrad of the step)",
-                "bound": "tensor", "achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus, "traffic": None,
-                "launches_per_step": int(n_r + n_u), "us_per_launch": (ms_r + ms_u) * 1e3 / max(n_r + n_u, 1),
-                "flops_per_step": fl_r + fl_u, "peak_source": peak_src + " (sustained bf16, kernel timed inside a long step)",
-                "rollout": {"launches": int(n_r), "ms": ms_r, "tflops": fl_r / (ms_r * 1e-3) / 1e12 if ms_r else None},
-                "update": {"launches": int(n_u), "ms": ms_u, "tflops": fl_u / (ms_u * 1e-3) / 1e12 if ms_u else None},
-                "note": "algorithmic flops 2*M*N*K counted once per GEMM (the split-bf16 scheme issues 3 MMAs per product); "
-                        "skinny shapes (K=48..512, N=1..512) make these GEMMs epilogue- and HBM-traffic-bound, see DESIGN.md"}
+                "bound": "hbm" if mem_bound else "tensor",
+                "achieved": gbs if mem_bound else tf, "peak": hbm if mem_bound else tf_sus,
+                "unit": "GB/s" if mem_bound else "TFLOP/s", "frac": (gbs / hbm) if mem_bound else (tf / tf_sus),
+                "traffic": None, "launches_per_step": int(n_r + n_u), "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
+                "alg_bytes_per_launch": (by_r + by_u) / max(n_r + n_u, 1), "alg_flops_per_launch": (fl_r + fl_u) / max(n_r + n_u, 1),
+                "tensor": {"achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus},
+                "hbm": {"achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm},
+                "arithmetic_intensity_flop_per_byte": (fl_r + fl_u) / (by_r + by_u),
+                "ridge_flop_per_byte": tf_sus * 1e12 / (hbm * 1e9), "peak_source": peak_src,
+                "rollout": {"launches": int(n_r), "ms": ms_r, "tflops": fl_r / (ms_r * 1e-3) / 1e12, "gbs": by_r / (ms_r * 1e-3) / 1e9},
+                "update": {"launches": int(n_u), "ms": ms_u, "tflops": fl_u / (ms_u * 1e-3) / 1e12, "gbs": by_u / (ms_u * 1e-3) / 1e9},
+                "note": "summed over every GEMM launch of one eager PPO iteration (CUDA events around each launch); algorithmic "
+                        "flops 2*M*N*K counted once (split-bf16 issues 3 MMAs per product), algorithmic bytes = every operand "
+                        "and output element once (bf16 hi+lo pairs, fp32 outputs); the shapes (K=48..512, N=1..512) sit far "
+                        "below the ridge point, so HBM is the roof"}
         iters = 200
 
         def time_call(fn, reps):

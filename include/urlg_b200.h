@@ -184,9 +184,10 @@ typedef struct urlg_gemm_desc {
 } urlg_gemm_desc;
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 /* Measurement hook (bench.py roofline): while enabled, every GEMM launch of this library is bracketed by CUDA events on
- * its stream (do not enable under graph capture); read returns the summed duration, launch count and 2*M*N*K flops. */
+ * its stream (do not enable under graph capture); read returns the summed duration, launch count, 2*M*N*K flops and the
+ * algorithmic HBM bytes (every operand and output element once). */
 int urlg_gemm_timing(int enable);
-int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops);
+int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops, double* bytes);
 
 /* ======================================================================================
  * PPO half: rsl_rl v1.0.2 [UPSTREAM, submodule absent from /root/reference] — reference call

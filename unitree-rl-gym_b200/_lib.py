@@ -130,7 +130,8 @@ SIGNATURES = {
                                      C.c_int64, C.c_void_p]),
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
     "urlg_gemm_timing": (C.c_int, [C.c_int]),
-    "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
+    "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double),
+                                       C.POINTER(C.c_double)]),
     "urlg_policy_workspace_bytes": (C.c_int64, [C.POINTER(PolicyDesc)]),
     "urlg_policy_create": (C.c_int, [C.POINTER(PolicyDesc), _P, _P, _P, _P, _P, _P, C.c_int64, C.POINTER(C.c_void_p)]),
     "urlg_policy_destroy": (None, [C.c_void_p]),

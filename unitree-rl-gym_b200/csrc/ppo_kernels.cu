@@ -201,7 +201,7 @@ int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStrea
 
 // ---------------------------------------------------------------- apply: norm, LR rule, clip, Adam
 __global__ void __launch_bounds__(256)
-grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ stats) {
+grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ partials) {
   float acc = 0.0f;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float x = g[i] * scale;
@@ -214,12 +214,17 @@ grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __
   if (threadIdx.x == 0) {
     float a = 0.0f;
     for (int k = 0; k < (int)(blockDim.x >> 5); ++k) a += sh[k];
-    atomicAdd(stats + URLG_STAT_GNORM_SQ, a);
+    partials[blockIdx.x] = a;      // summed in block order by ppo_scalars_kernel: the norm (hence the clip coefficient and the
+                                   // whole Adam step) is bit-reproducible, so data-parallel ranks stay bit-identical
   }
 }
 
 // One thread: the host-side scalar logic of PPO.update moved onto the device (no .item(), no KL branch sync).
-__global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hparams hp, float rows_total) {
+__global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hparams hp, float rows_total,
+                                   const float* __restrict__ partials, int num_partials) {
+  float gsq = 0.0f;
+  for (int k = 0; k < num_partials; ++k) gsq += partials[k];
+  stats[URLG_STAT_GNORM_SQ] = gsq;
   float lr = stats[URLG_STAT_LR];
   const float kl_mean = stats[URLG_STAT_KL_SUM] / rows_total;
   stats[URLG_STAT_KL_MEAN] = kl_mean;
@@ -319,8 +324,9 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   const int64_t n = p->desc.num_params;
   int blocks = (int)((n + 255) / 256);
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
-  grad_sumsq_kernel<<<blocks, 256, 0, st>>>(p->grads, n, h->grad_scale, p->stats);
-  ppo_scalars_kernel<<<1, 1, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale);
+  const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
+  grad_sumsq_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red);
+  ppo_scalars_kernel<<<1, 1, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale, p->red, nparts);
   adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
   URLG_LAUNCH_CHECK();
   return sync_weights(p, st);

@@ -46,7 +46,7 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
 // GEMM launch while enabled (never under graph capture), summed on read.
 static bool g_timing = false;
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
-static double g_flops = 0.0;
+static double g_flops = 0.0, g_bytes = 0.0;
 static size_t g_used = 0;
 
 int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st);
@@ -63,7 +63,13 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   const int rc = launch_gemm_impl(d, st);
   URLG_CUDA(cudaEventRecord(g_events[g_used].second, st));
   ++g_used;
-  if (d) g_flops += 2.0 * d->M * d->N * d->K;
+  if (d) {
+    g_flops += 2.0 * d->M * d->N * d->K;
+    // algorithmic HBM bytes: each operand element and each output element once (bf16, x2 when split into hi+lo)
+    const double parts = (d->A_lo && d->B_lo) ? 2.0 : 1.0, mn = (double)d->M * d->N;
+    g_bytes += 2.0 * parts * ((double)d->M * d->K + (double)d->N * d->K) + (d->out_f32 ? 4.0 * mn : 0.0) +
+               (d->out_bf16 ? 2.0 * parts * mn : 0.0) + (d->dact_ref ? 2.0 * parts * mn : 0.0);
+  }
   return rc;
 }
 
@@ -142,11 +148,11 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
 extern "C" int urlg_gemm_timing(int enable) {
   using namespace urlg::tc;
   g_timing = enable != 0;
-  if (g_timing) { g_used = 0; g_flops = 0.0; }
+  if (g_timing) { g_used = 0; g_flops = 0.0; g_bytes = 0.0; }
   return URLG_OK;
 }
 
-extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops) {
+extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops, double* bytes) {
   using namespace urlg::tc;
   double ms = 0.0;
   for (size_t i = 0; i < g_used; ++i) {
@@ -158,6 +164,7 @@ extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double
   if (total_ms) *total_ms = ms;
   if (launches) *launches = (int64_t)g_used;
   if (flops) *flops = g_flops;
+  if (bytes) *bytes = g_bytes;
   return URLG_OK;
 }
 
