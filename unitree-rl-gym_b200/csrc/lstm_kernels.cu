@@ -146,124 +146,189 @@ lstm_stage_x_kernel(const float* __restrict__ obs /* [T,N,in] */, int in, int in
   }
 }
 
-// Forward recurrence.  Thread (r, j): row r of the CTA, hidden unit j.  gates: in = x W_ih^T + b (pre-activation),
-// out = activated (i, f, g, o) kept for the backward pass.
+// W_hh [4H, H] (nn.LSTM layout) -> [k][j][gate] fp32 image for the forward recurrence.
+__global__ void __launch_bounds__(256)
+lstm_wt_image_kernel(const float* __restrict__ W_hh, int H, float* __restrict__ Wt) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 4 * H * H) return;
+  const int q = idx / H, k = idx % H, gate = q / H, jj = q % H;
+  Wt[((size_t)k * H + jj) * 4 + gate] = W_hh[idx];
+}
+
+// Forward recurrence.  Thread (rg, j): hidden unit j of RPT consecutive rows (row group rg of the CTA); the W_hh
+// column it needs is read from shared memory once per step and reused for its RPT rows.  gates: in = x W_ih^T + b
+// (pre-activation), out = activated (i, f, g, o) kept for the backward pass.  The next step's inputs are prefetched
+// into registers while the current step computes.
+template <int RPT>
 __global__ void __launch_bounds__(256)
 lstm_recur_fwd_kernel(float* __restrict__ gates, int T, int E, int H, int N, int env_begin,
                       const uint8_t* __restrict__ dones, const float* __restrict__ saved_h, const float* __restrict__ saved_c,
                       const float* __restrict__ W_hh, float* __restrict__ c_prev, float* __restrict__ c_new,
-                      bf16* __restrict__ xcat, int kcat, int in_pad, bf16* __restrict__ headx, int ld_headx, int64_t lo_off,
-                      int rows_per_cta) {
+                      bf16* __restrict__ xcat, int kcat, int in_pad, bf16* __restrict__ headx, int ld_headx, int64_t lo_off) {
   extern __shared__ __align__(16) float lsm[];
   float4* Wt = reinterpret_cast<float4*>(lsm);          // [k][j] -> (W[j][k], W[H+j][k], W[2H+j][k], W[3H+j][k])
-  float* hs = lsm + 4 * H * H;                          // [rows_per_cta][H]
-  for (int idx = threadIdx.x; idx < H * H; idx += blockDim.x) {
-    const int k = idx / H, jj = idx % H;
-    Wt[idx] = make_float4(W_hh[(size_t)jj * H + k], W_hh[(size_t)(H + jj) * H + k], W_hh[(size_t)(2 * H + jj) * H + k],
-                          W_hh[(size_t)(3 * H + jj) * H + k]);
+  float* hs = lsm + 4 * H * H;                          // [k][rows_per_cta]: a thread's RPT rows are contiguous
+  // W_hh arrives already in the [k][j][gate] layout (lstm_wt_image_kernel): coalesced 16-byte loads
+  for (int idx = threadIdx.x; idx < H * H; idx += blockDim.x) Wt[idx] = reinterpret_cast<const float4*>(W_hh)[idx];
+  const int RG = blockDim.x / H, rows_cta = RG * RPT;
+  const int rg = threadIdx.x / H, j = threadIdx.x % H;
+  const int e0 = blockIdx.x * rows_cta + rg * RPT;
+  float h[RPT], c[RPT];
+  float4 pre[RPT];                                      // prefetched projection of the current step
+  bool seed[RPT];
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    h[i] = 0.0f; c[i] = 0.0f; seed[i] = true;
+    pre[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (e0 + i < E) {
+      const float* g = gates + ((size_t)e0 + i) * 4 * H;
+      pre[i] = make_float4(g[j], g[H + j], g[2 * H + j], g[3 * H + j]);
+    }
   }
-  const int r = threadIdx.x / H, j = threadIdx.x % H;
-  const int e = blockIdx.x * rows_per_cta + r;
-  const bool valid = r < rows_per_cta && e < E;
-  const int env = env_begin + (valid ? e : 0);
-  float h = 0.0f, c = 0.0f;
   __syncthreads();
   for (int t = 0; t < T; ++t) {
-    const size_t row = (size_t)t * E + e;
-    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    if (valid) {
-      const float* g = gates + row * 4 * H;               // issue the projection loads first: latency hides under the dot
-      acc = make_float4(g[j], g[H + j], g[2 * H + j], g[3 * H + j]);
-      if (t == 0 || dones[(size_t)(t - 1) * N + env] != 0) {   // trajectory start: re-seed from the saved states
-        const size_t sv = ((size_t)t * N + env) * H + j;
-        h = saved_h[sv];
-        c = saved_c[sv];
+    float4 acc[RPT];
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int e = e0 + i;
+      acc[i] = pre[i];
+      if (e < E) {
+        const size_t row = (size_t)t * E + e;
+        if (seed[i]) {                                    // trajectory start: re-seed from the saved states
+          const size_t sv = ((size_t)t * N + env_begin + e) * H + j;
+          h[i] = saved_h[sv];
+          c[i] = saved_c[sv];
+        }
+        store_split(xcat, lo_off, row * kcat + in_pad + j, h[i]);    // h_prev operand image for dW_hh
+        c_prev[row * H + j] = c[i];
       }
-      hs[r * H + j] = h;
-      store_split(xcat, lo_off, row * kcat + in_pad + j, h);    // h_prev operand image for dW_hh
-      c_prev[row * H + j] = c;
+      hs[j * rows_cta + rg * RPT + i] = h[i];
     }
     __syncthreads();
-    if (valid) {
-      const float* hr = hs + r * H;
-#pragma unroll 8
-      for (int k = 0; k < H; ++k) {
-        const float hv = hr[k];
-        const float4 w = Wt[k * H + j];
-        acc.x += hv * w.x; acc.y += hv * w.y; acc.z += hv * w.z; acc.w += hv * w.w;
+    // prefetch step t+1 (projection + boundary flag) while this step's dot products run
+    if (t + 1 < T) {
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        const int e = e0 + i;
+        if (e < E) {
+          const float* g = gates + ((size_t)(t + 1) * E + e) * 4 * H;
+          pre[i] = make_float4(g[j], g[H + j], g[2 * H + j], g[3 * H + j]);
+          seed[i] = dones[(size_t)t * N + env_begin + e] != 0;
+        }
       }
-      const float i = sigmoidf_(acc.x), f = sigmoidf_(acc.y), gg = tanhf(acc.z), o = sigmoidf_(acc.w);
-      c = f * c + i * gg;
-      h = o * tanhf(c);
-      float* g = gates + row * 4 * H;
-      g[j] = i; g[H + j] = f; g[2 * H + j] = gg; g[3 * H + j] = o;
-      c_new[row * H + j] = c;
-      store_split(headx, lo_off, row * ld_headx + j, h);
+    }
+    const float* hk = hs + rg * RPT;
+#pragma unroll 4
+    for (int k = 0; k < H; ++k) {
+      const float4 w = Wt[k * H + j];
+      float hv[RPT];
+      if (RPT == 4) {
+        const float4 q = *reinterpret_cast<const float4*>(hk + k * rows_cta);
+        hv[0] = q.x; hv[1 % RPT] = q.y; hv[2 % RPT] = q.z; hv[3 % RPT] = q.w;
+      } else if (RPT == 2) {
+        const float2 q = *reinterpret_cast<const float2*>(hk + k * rows_cta);
+        hv[0] = q.x; hv[1 % RPT] = q.y;
+      } else {
+        hv[0] = hk[k * rows_cta];
+      }
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        acc[i].x += hv[i] * w.x; acc[i].y += hv[i] * w.y; acc[i].z += hv[i] * w.z; acc[i].w += hv[i] * w.w;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int e = e0 + i;
+      if (e < E) {
+        const size_t row = (size_t)t * E + e;
+        const float ig = sigmoidf_(acc[i].x), fg = sigmoidf_(acc[i].y), gg = tanhf(acc[i].z), og = sigmoidf_(acc[i].w);
+        c[i] = fg * c[i] + ig * gg;
+        h[i] = og * tanhf(c[i]);
+        float* g = gates + row * 4 * H;
+        g[j] = ig; g[H + j] = fg; g[2 * H + j] = gg; g[3 * H + j] = og;
+        c_new[row * H + j] = c[i];
+        store_split(headx, lo_off, row * ld_headx + j, h[i]);
+      }
     }
     __syncthreads();
   }
 }
 
-// Backward recurrence (BPTT).  Thread (r, j) carries dL/dc and the recurrent dL/dh of its unit in registers.
+// Backward recurrence (BPTT).  Thread (rg, j) carries dL/dc and the recurrent dL/dh of unit j for its RPT rows.
+template <int RPT>
 __global__ void __launch_bounds__(256)
 lstm_recur_bwd_kernel(const float* __restrict__ gates, int T, int E, int H, int N, int env_begin,
                       const uint8_t* __restrict__ dones, const float* __restrict__ c_prev, const float* __restrict__ c_new,
                       const bf16* __restrict__ dh_head, bf16* __restrict__ dgates, int64_t lo_off,
-                      const float* __restrict__ W_hh, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh,
-                      int rows_per_cta) {
+                      const float* __restrict__ W_hh, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh) {
   extern __shared__ __align__(16) float lsm[];
   float* Wb = lsm;                                      // [4H][H] as stored by nn.LSTM
-  float* dg = lsm + 4 * H * H;                          // [rows_per_cta][4H]
+  float* dg = lsm + 4 * H * H;                          // [4H][rows_per_cta]
   for (int idx = threadIdx.x; idx < 4 * H * H; idx += blockDim.x) Wb[idx] = W_hh[idx];
-  const int r = threadIdx.x / H, j = threadIdx.x % H;
-  const int e = blockIdx.x * rows_per_cta + r;
-  const bool valid = r < rows_per_cta && e < E;
-  const int env = env_begin + (valid ? e : 0);
-  float dh_rec = 0.0f, dc = 0.0f;
-  float bi = 0.0f, bf = 0.0f, bg = 0.0f, bo = 0.0f;
+  const int RG = blockDim.x / H, rows_cta = RG * RPT;
+  const int rg = threadIdx.x / H, j = threadIdx.x % H;
+  const int e0 = blockIdx.x * rows_cta + rg * RPT;
+  float dh_rec[RPT], dc[RPT], bsum[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) { dh_rec[i] = 0.0f; dc[i] = 0.0f; }
   __syncthreads();
   for (int t = T - 1; t >= 0; --t) {
-    const size_t row = (size_t)t * E + e;
-    if (valid) {
-      const size_t idx = row * H + j;
-      const bool carry = t < T - 1 && dones[(size_t)t * N + env] == 0;   // a done at t cuts the gradient from t+1
-      const float dh = load_split(dh_head, lo_off, idx) + (carry ? dh_rec : 0.0f);
-      const float dcn_in = carry ? dc : 0.0f;
-      const float* g = gates + row * 4 * H;
-      const float i = g[j], f = g[H + j], gg = g[2 * H + j], o = g[3 * H + j];
-      const float tc = tanhf(c_new[idx]);
-      const float d_o = dh * tc;
-      const float dcn = dcn_in + dh * o * (1.0f - tc * tc);
-      const float di = dcn * gg, dgg = dcn * i, df = dcn * c_prev[idx];
-      dc = dcn * f;
-      const float pi = di * i * (1.0f - i), pf = df * f * (1.0f - f), pg = dgg * (1.0f - gg * gg), po = d_o * o * (1.0f - o);
-      bf16* dgr = dgates + row * 4 * H;
-      store_split(dgr, lo_off, j, pi); store_split(dgr, lo_off, H + j, pf);
-      store_split(dgr, lo_off, 2 * H + j, pg); store_split(dgr, lo_off, 3 * H + j, po);
-      float* d4 = dg + r * 4 * H;
-      d4[j] = pi; d4[H + j] = pf; d4[2 * H + j] = pg; d4[3 * H + j] = po;
-      bi += pi; bf += pf; bg += pg; bo += po;
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int e = e0 + i;
+      float pi = 0.0f, pf = 0.0f, pg = 0.0f, po = 0.0f;
+      if (e < E) {
+        const size_t row = (size_t)t * E + e, idx = row * H + j;
+        const bool carry = t < T - 1 && dones[(size_t)t * N + env_begin + e] == 0;   // a done at t cuts the gradient from t+1
+        const float dh = load_split(dh_head, lo_off, idx) + (carry ? dh_rec[i] : 0.0f);
+        const float dcn_in = carry ? dc[i] : 0.0f;
+        const float* g = gates + row * 4 * H;
+        const float ig = g[j], fg = g[H + j], gg = g[2 * H + j], og = g[3 * H + j];
+        const float tc = tanhf(c_new[idx]);
+        const float d_o = dh * tc;
+        const float dcn = dcn_in + dh * og * (1.0f - tc * tc);
+        const float di = dcn * gg, dgg = dcn * ig, df = dcn * c_prev[idx];
+        dc[i] = dcn * fg;
+        pi = di * ig * (1.0f - ig); pf = df * fg * (1.0f - fg); pg = dgg * (1.0f - gg * gg); po = d_o * og * (1.0f - og);
+        bf16* dgr = dgates + row * 4 * H;
+        store_split(dgr, lo_off, j, pi); store_split(dgr, lo_off, H + j, pf);
+        store_split(dgr, lo_off, 2 * H + j, pg); store_split(dgr, lo_off, 3 * H + j, po);
+        bsum[0] += pi; bsum[1] += pf; bsum[2] += pg; bsum[3] += po;
+      }
+      const int col = rg * RPT + i;
+      dg[j * rows_cta + col] = pi; dg[(H + j) * rows_cta + col] = pf;
+      dg[(2 * H + j) * rows_cta + col] = pg; dg[(3 * H + j) * rows_cta + col] = po;
     }
     __syncthreads();
-    if (valid && t > 0) {                                 // dL/dh_{t-1} (recurrent part) = dgates_t W_hh
-      const float* d4 = dg + r * 4 * H;
-      float a = 0.0f;
-#pragma unroll 8
-      for (int q = 0; q < 4 * H; ++q) a += d4[q] * Wb[q * H + j];
-      dh_rec = a;
+    if (t > 0) {                                          // dL/dh_{t-1} (recurrent part) = dgates_t W_hh
+      float a[RPT];
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) a[i] = 0.0f;
+      const float* dq = dg + rg * RPT;
+#pragma unroll 4
+      for (int q = 0; q < 4 * H; ++q) {
+        const float w = Wb[q * H + j];
+        if (RPT == 4) {
+          const float4 d = *reinterpret_cast<const float4*>(dq + q * rows_cta);
+          a[0] += d.x * w; a[1 % RPT] += d.y * w; a[2 % RPT] += d.z * w; a[3 % RPT] += d.w * w;
+        } else if (RPT == 2) {
+          const float2 d = *reinterpret_cast<const float2*>(dq + q * rows_cta);
+          a[0] += d.x * w; a[1 % RPT] += d.y * w;
+        } else {
+          a[0] += dq[q * rows_cta] * w;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) dh_rec[i] = a[i];
     }
     __syncthreads();
   }
-  // bias gradients: sum over the CTA's rows, then one atomic per gate unit (b_ih and b_hh get the same gradient)
-  if (valid) {
-    float* d4 = dg + r * 4 * H;
-    d4[j] = bi; d4[H + j] = bf; d4[2 * H + j] = bg; d4[3 * H + j] = bo;
-  }
+  // bias gradients: per-thread sums over (t, own rows) -> per-CTA sums over row groups -> one atomic per gate unit
+  dg[j * RG + rg] = bsum[0]; dg[(H + j) * RG + rg] = bsum[1]; dg[(2 * H + j) * RG + rg] = bsum[2]; dg[(3 * H + j) * RG + rg] = bsum[3];
   __syncthreads();
-  const int live_rows = min(rows_per_cta, E - blockIdx.x * rows_per_cta);
   for (int q = threadIdx.x; q < 4 * H; q += blockDim.x) {
     float a = 0.0f;
-    for (int rr = 0; rr < live_rows; ++rr) a += dg[rr * 4 * H + q];
+    for (int rr = 0; rr < RG; ++rr) a += dg[q * RG + rr];
     if (a != 0.0f) { atomicAdd(g_b_ih + q, a); atomicAdd(g_b_hh + q, a); }
   }
 }
@@ -279,12 +344,24 @@ static int persistent_rows(int H) {
   const int r = 256 / H;
   return r < 1 ? 0 : (r > 8 ? 8 : r);
 }
+// Rows per thread: W_hh traffic from shared memory is per thread and per step, so more rows per thread amortise it;
+// keep at least ~one CTA per SM.
+static int rows_per_thread(int E, int rpc) {
+  if (E >= 4 * rpc * kNumSMs) return 4;
+  if (E >= 2 * rpc * kNumSMs) return 2;
+  return 1;
+}
 static int recur_smem_attr(int smem) {
   static int set_to = 0;
   if (smem > set_to) {
-    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    set_to = smem;
+    const int cap = 200 * 1024;
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_fwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    URLG_CUDA(cudaFuncSetAttribute(lstm_recur_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap));
+    set_to = cap;
   }
   return URLG_OK;
 }
@@ -345,11 +422,21 @@ int lstm_update_forward(urlg_policy* p, int k, const urlg_storage* s, int env_be
     g.out_f32 = w.gates; g.ld_f32 = 4 * H;
     with_lo(p, g);
     if (int rc = tc::launch_gemm(&g, st)) return rc;
-    const int smem = (4 * H * H + rpc * H) * (int)sizeof(float);
+    const int rpt = rows_per_thread(E, rpc);
+    const int rows_cta = rpc * rpt;
+    const int smem = (4 * H * H + rows_cta * H) * (int)sizeof(float);
     if (int rc = recur_smem_attr(smem)) return rc;
-    lstm_recur_fwd_kernel<<<(E + rpc - 1) / rpc, rpc * H, smem, st>>>(
-        w.gates, T, E, H, s->N, env_begin, s->dones, sh, sc, p->params + w.off[1], c_prev, c_new, w.xcat, w.kcat, w.in_pad,
-        n.x, n.kpad[0], p->lo_off, rpc);
+    const int grid = (E + rows_cta - 1) / rows_cta;
+    float* wt_img = w.dhrec;                   // [R, H] scratch of the per-step path, unused here (R*H >= 4H*H)
+    if ((int64_t)p->R * H < 4 * H * H) return fail(URLG_EINVAL, "lstm update: max_rows too small for the W_hh image");
+    lstm_wt_image_kernel<<<(4 * H * H + 255) / 256, 256, 0, st>>>(p->params + w.off[1], H, wt_img);
+    URLG_LAUNCH_CHECK();
+#define URLG_FWD(RPT)                                                                                                  \
+    lstm_recur_fwd_kernel<RPT><<<grid, rpc * H, smem, st>>>(w.gates, T, E, H, s->N, env_begin, s->dones, sh, sc,        \
+                                                           wt_img, c_prev, c_new, w.xcat, w.kcat,                       \
+                                                           w.in_pad, n.x, n.kpad[0], p->lo_off)
+    if (rpt == 4) URLG_FWD(4); else if (rpt == 2) URLG_FWD(2); else URLG_FWD(1);
+#undef URLG_FWD
     URLG_LAUNCH_CHECK();
     return URLG_OK;
   }
@@ -375,11 +462,17 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
   const int total = E * H;
   const int rpc = persistent_rows(H);
   if (rpc > 0) {
-    const int smem = (4 * H * H + rpc * 4 * H) * (int)sizeof(float);
+    const int rpt = rows_per_thread(E, rpc);
+    const int rows_cta = rpc * rpt;
+    const int smem = (4 * H * H + rows_cta * 4 * H) * (int)sizeof(float);
     if (int rc = recur_smem_attr(smem)) return rc;
-    lstm_recur_bwd_kernel<<<(E + rpc - 1) / rpc, rpc * H, smem, st>>>(
-        w.gates, T, E, H, s->N, env_begin, s->dones, c_prev, c_new, w.dx_head, w.dgates, p->lo_off, p->params + w.off[1],
-        p->grads + w.off[2], p->grads + w.off[3], rpc);
+    const int grid = (E + rows_cta - 1) / rows_cta;
+#define URLG_BWD(RPT)                                                                                                  \
+    lstm_recur_bwd_kernel<RPT><<<grid, rpc * H, smem, st>>>(w.gates, T, E, H, s->N, env_begin, s->dones, c_prev, c_new, \
+                                                           w.dx_head, w.dgates, p->lo_off, p->params + w.off[1],        \
+                                                           p->grads + w.off[2], p->grads + w.off[3])
+    if (rpt == 4) URLG_BWD(4); else if (rpt == 2) URLG_BWD(2); else URLG_BWD(1);
+#undef URLG_BWD
     URLG_LAUNCH_CHECK();
   }
   for (int t = rpc > 0 ? -1 : T - 1; t >= 0; --t) {

@@ -219,12 +219,19 @@ grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __
   }
 }
 
-// One thread: the host-side scalar logic of PPO.update moved onto the device (no .item(), no KL branch sync).
+// One block (thread 0 after the norm reduction): the host-side scalar logic of PPO.update moved onto the device (no .item(), no KL branch sync).
 __global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hparams hp, float rows_total,
                                    const float* __restrict__ partials, int num_partials) {
-  float gsq = 0.0f;
-  for (int k = 0; k < num_partials; ++k) gsq += partials[k];
-  stats[URLG_STAT_GNORM_SQ] = gsq;
+  // fixed-shape tree over the (<= 256) block partials: deterministic, and one load latency instead of 256 chained ones
+  __shared__ float sh[256];
+  sh[threadIdx.x] = (int)threadIdx.x < num_partials ? partials[threadIdx.x] : 0.0f;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x != 0) return;
+  stats[URLG_STAT_GNORM_SQ] = sh[0];
   float lr = stats[URLG_STAT_LR];
   const float kl_mean = stats[URLG_STAT_KL_SUM] / rows_total;
   stats[URLG_STAT_KL_MEAN] = kl_mean;
@@ -326,7 +333,7 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
   const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
   grad_sumsq_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red);
-  ppo_scalars_kernel<<<1, 1, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale, p->red, nparts);
+  ppo_scalars_kernel<<<1, 256, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale, p->red, nparts);
   adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
   URLG_LAUNCH_CHECK();
   return sync_weights(p, st);
