@@ -181,6 +181,7 @@ typedef struct urlg_gemm_desc {
   const void* A_lo; const void* B_lo;
   void* out_bf16_lo;              /* optional low part of out_bf16 */
   const void* dact_ref_lo;        /* optional low part of dact_ref */
+  int32_t max_ctas;               /* 0 = one persistent CTA per SM; else cap the grid (two GEMMs side by side on two streams) */
 } urlg_gemm_desc;
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 /* Measurement hook (bench.py roofline): while enabled, every GEMM launch of this library is bracketed by CUDA events on

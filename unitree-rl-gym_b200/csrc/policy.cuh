@@ -51,6 +51,10 @@ struct urlg_policy {
   float* red;                        // small fp32 scratch (head reductions)
   int64_t lo_off;                    // split precision: element offset from a bf16 slab to its low-part twin (0 = off)
   int64_t last_rows;                 // rows of the pending minibatch gradient (set by minibatch_grads)
+  // rollout: the actor and critic chains are independent until the sampling kernel, so the critic runs on a side
+  // stream forked from / joined to the caller's stream by events (capturable: the side stream joins the graph)
+  cudaStream_t side;
+  cudaEvent_t ev_fork, ev_join;
 };
 
 namespace urlg {
@@ -74,7 +78,7 @@ inline void with_lo(const urlg_policy* p, urlg_gemm_desc& g) {
   if (g.dact_ref) g.dact_ref_lo = static_cast<const bf16*>(g.dact_ref) + p->lo_off;
 }
 int sync_weights(urlg_policy* p, cudaStream_t st);
-int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st);
+int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas = 0);
 int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);
 int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld, cudaStream_t st);
 }

@@ -139,7 +139,7 @@ int sync_weights(urlg_policy* p, cudaStream_t st) {
 
 // ---------------------------------------------------------------- MLP forward (x already staged in n.x)
 // keep_hidden: activations stay in n.h[] (needed by the backward pass); the rollout reuses the same slabs.
-int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st) {
+int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas) {
   const int L = n.d.num_layers;
   for (int l = 0; l < L; ++l) {
     urlg_gemm_desc g = {};
@@ -150,6 +150,7 @@ int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st) {
     g.bias = p->params + n.d.b_off[l];
     if (l + 1 < L) { g.out_bf16 = n.h[l + 1]; g.ld_bf16 = n.d.dims[l + 1]; g.flags = URLG_GEMM_ELU; }
     else { g.out_f32 = n.out; g.ld_f32 = n.d.dims[L]; }
+    g.max_ctas = max_ctas;
     with_lo(p, g);
     if (int rc = tc::launch_gemm(&g, st)) return rc;
   }
@@ -246,11 +247,24 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
   if (!rc && total > workspace_bytes) rc = fail(URLG_EINVAL, "urlg_policy_create: workspace too small (%lld < %lld)",
                                                 (long long)workspace_bytes, (long long)total);
   if (rc) { delete p; return rc; }
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr;
+  if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    urlg_policy_destroy(p);
+    return fail(URLG_ECUDA, "urlg_policy_create: side stream / events: %s", cudaGetErrorString(cudaGetLastError()));
+  }
   *out = p;
   return URLG_OK;
 }
 
-extern "C" void urlg_policy_destroy(urlg_policy* p) { delete p; }
+extern "C" void urlg_policy_destroy(urlg_policy* p) {
+  if (!p) return;
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->side) cudaStreamDestroy(p->side);
+  delete p;
+}
 
 extern "C" int urlg_policy_sync_weights(urlg_policy* p, void* stream) {
   if (!p) return fail(URLG_EINVAL, "urlg_policy_sync_weights: null policy");
@@ -279,19 +293,33 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
   const float* cobs = critic_obs ? critic_obs : obs;
   float* store_o = s->observations + (size_t)t * N * s->num_obs;
   float* store_p = s->privileged_observations ? s->privileged_observations + (size_t)t * N * s->num_priv : nullptr;
-  if (!d.recurrent) {
-    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
-    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
-  } else {
+  if (d.recurrent) {
     if (!hidden) return fail(URLG_EINVAL, "urlg_policy_act: recurrent policy needs hidden state");
-    const size_t HS = (size_t)N * d.rnn_hidden, slab = (size_t)t * HS;
     if (!s->hid_a_h || !s->hid_a_c || !s->hid_c_h || !s->hid_c_c)
       return fail(URLG_EINVAL, "urlg_policy_act: recurrent storage lacks saved hidden states");
-    if (int rc = lstm_rollout_step(p, 0, obs, N, store_o, hidden, hidden + HS, s->hid_a_h + slab, s->hid_a_c + slab, st)) return rc;
-    if (int rc = lstm_rollout_step(p, 1, cobs, N, store_p, hidden + 2 * HS, hidden + 3 * HS, s->hid_c_h + slab, s->hid_c_c + slab, st)) return rc;
   }
-  if (int rc = mlp_forward(p, p->net[0], N, st)) return rc;
-  if (int rc = mlp_forward(p, p->net[1], N, st)) return rc;
+  // fork: critic chain on the side stream, actor chain on the caller's; when one GEMM cannot fill the GPU (rollout-sized
+  // M) each chain is capped to half the SMs so the two run side by side instead of back to back
+  cudaStream_t sc = p->side;
+  URLG_CUDA(cudaEventRecord(p->ev_fork, st));
+  URLG_CUDA(cudaStreamWaitEvent(sc, p->ev_fork, 0));
+  const int cap = N <= 8192 ? kNumSMs / 2 : 0;
+  int rc_a = URLG_OK, rc_c = URLG_OK;
+  if (!d.recurrent) {
+    rc_a = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st);
+    rc_c = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], sc);
+  } else {
+    const size_t HS = (size_t)N * d.rnn_hidden, slab = (size_t)t * HS;
+    rc_a = lstm_rollout_step(p, 0, obs, N, store_o, hidden, hidden + HS, s->hid_a_h + slab, s->hid_a_c + slab, st);
+    rc_c = lstm_rollout_step(p, 1, cobs, N, store_p, hidden + 2 * HS, hidden + 3 * HS, s->hid_c_h + slab, s->hid_c_c + slab, sc);
+  }
+  if (!rc_a) rc_a = mlp_forward(p, p->net[0], N, st, cap);
+  if (!rc_c) rc_c = mlp_forward(p, p->net[1], N, sc, cap);
+  // join (always, so a capture in progress is never left with an unjoined stream)
+  URLG_CUDA(cudaEventRecord(p->ev_join, sc));
+  URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+  if (rc_a) return rc_a;
+  if (rc_c) return rc_c;
   sample_store_kernel<<<(N + 127) / 128, 128, 0, st>>>(p->net[0].out, p->net[1].out, p->params + d.std_off, noise, *s, t,
                                                        actions_out, d.num_actions, d.seed_lo, d.seed_hi, d.env_offset,
                                                        step_base, step_offset);

@@ -136,7 +136,8 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   g.tiles_n = (d->N + bn - 1) / bn;
   g.splits = splits;
   const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
-  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);     // persistent: one CTA per SM walks the tiles
+  int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
+  if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;
   gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages), st>>>(ta, tb, tal, tbl, g);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
