@@ -314,7 +314,61 @@ def own_arm(a):
     t = torch.tensor([sum(e2e_ms) / len(e2e_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_roll_ms = t.item()
+    e2e_eager_ms = t.item()
+    e2e_roll_ms, e2e_mode = e2e_eager_ms, "eager"
+
+    # ---- e2e, per-step graphs (public API: rsl_rl.runners.rollout_graph.StepGraphs): one graph launch per env step; the
+    #      frame of step k+1 is copied from pinned host memory on a copy stream while step k computes; rewards / dones
+    #      of every step are read back to pinned host memory.  Same bytes per step as the eager loop.
+    if use_graph:
+        from unitree_rl_gym_b200.rsl_rl.runners.rollout_graph import StepGraphs
+        sg = StepGraphs(runner).capture()
+        copy_stream = torch.cuda.Stream(device=dev)
+        cur = torch.cuda.current_stream()
+        slot_free = [torch.cuda.Event() for _ in range(POOL_FRAMES)]
+        for e_ in slot_free:
+            e_.record(cur)
+        frame_ready = [torch.cuda.Event() for _ in range(T)]
+        step_no = {"k": (int(env.gym.calls_base.item()) + env.gym.sim_calls) // D}
+
+        def stage_frame(k, idx):
+            f = k % POOL_FRAMES
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(slot_free[f])          # the last step that read this pool slot has finished
+                for key, v in pin.items():
+                    pool[key][f].copy_(v[f], non_blocking=True)
+                frame_ready[idx].record(copy_stream)
+
+        def e2e_graph_rollout():
+            k0 = step_no["k"]
+            stage_frame(k0, 0)
+            with torch.inference_mode():
+                for i in range(T):
+                    if i + 1 < T:
+                        stage_frame(k0 + i + 1, i + 1)        # overlaps with the compute of step i
+                    cur.wait_event(frame_ready[i])
+                    obs, cobs, rew, dones = sg.replay(i)
+                    slot_free[(k0 + i) % POOL_FRAMES].record(cur)
+                    rew_h.copy_(rew, non_blocking=True)
+                    done_h.copy_(dones, non_blocking=True)
+            step_no["k"] = k0 + T
+            return obs, cobs
+
+        g_ms = []
+        for i in range(2 + min(a.steps, 5)):
+            barrier()
+            e0, e1 = ev(), ev()
+            e0.record()
+            _, cobs = e2e_graph_rollout()
+            e1.record()
+            e1.synchronize()
+            if i >= 2:
+                g_ms.append(e0.elapsed_time(e1))
+            finish(cobs)
+        t = torch.tensor([sum(g_ms) / len(g_ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_roll_ms, e2e_mode = t.item(), "one CUDA graph per env step (StepGraphs), next frame's H2D overlapped on a copy stream"
 
     # ---- roofline of the dominant kernel.  By the ncu launch list (profiles/) the tcgen05 GEMM is ~70% of the GPU time
     #      of a step, so `roofline` is the GEMM against the tensor peak: CUDA events around every GEMM launch of one
@@ -455,9 +509,12 @@ def own_arm(a):
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": n * T * world / (e2e_roll_ms * 1e-3), "unit": "env-steps/s",
                         "h2d_bytes_per_step": int(h2d * T), "d2h_bytes_per_step": int(d2h * T), "rollout_ms": e2e_roll_ms,
-                        "note": "eager public API (PPO.act / LeggedRobot.step / PPO.process_env_step); per env step the "
-                                "physics frame (root, dof x decimation, contact) is copied from pinned host memory and "
-                                "rewards + dones are read back to pinned host memory; bytes are per 24-step rollout"},
+                        "launch": e2e_mode,
+                        "eager": {"value": n * T * world / (e2e_eager_ms * 1e-3), "rollout_ms": e2e_eager_ms,
+                                  "launch": "eager PPO.act / LeggedRobot.step / PPO.process_env_step, ~40 launches per env step"},
+                        "note": "public API with HOST physics frames: per env step the frame (root, dof x decimation, contact) "
+                                "is copied from pinned host memory and rewards + dones are read back to pinned host memory; "
+                                "bytes are per 24-step rollout (one bench step)"},
                 "roofline": roof, "cpu_baseline": cpu}
         line.update(extra)
         print(json.dumps(line), flush=True)

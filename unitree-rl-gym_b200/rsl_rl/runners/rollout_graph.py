@@ -71,3 +71,56 @@ class RolloutGraph:
         self.graph.replay()
         self.runner.alg.storage.step = self.runner.num_steps_per_env
         return self.obs_out, self.critic_out
+
+
+class StepGraphs:
+    """One CUDA graph per rollout position t = 0..T-1 (PPO.act -> env.step -> PPO.process_env_step writing storage slab
+    t), for callers whose physics state arrives from outside between env steps (host-resident or a separate simulator):
+    they refresh the physics tensors, call `replay(t)`, and read rewards / dones, one launch per env step instead of ~25.
+    Positions must be replayed in order 0..T-1 (the obs ping-pong slot and the storage slab are baked per position)."""
+
+    def __init__(self, runner):
+        self.runner = runner
+        self.graphs = []
+        self.launches = 0
+
+    def capture(self):
+        from ... import _lib
+        r = self.runner
+        env, alg = r.env, r.alg
+        if not RolloutGraph.supported(r):
+            raise RuntimeError("StepGraphs: env / runner configuration is not capturable")
+        if alg.storage.step != 0:
+            raise RuntimeError("StepGraphs.capture: storage must be empty (call after update())")
+        slot0 = env._obs_slot
+        pool = torch.cuda.graph_pool_handle()
+        self.outs = []
+        n0 = _lib.lib().urlg_launch_count()
+        torch.cuda.synchronize()
+        for t in range(r.num_steps_per_env):
+            obs = env.get_observations()
+            priv = env.get_privileged_observations()
+            critic_obs = priv if priv is not None else obs
+            env.begin_relative()
+            alg.begin_relative()
+            g = torch.cuda.CUDAGraph()
+            with torch.inference_mode(), torch.cuda.graph(g, pool=pool):
+                actions = alg.act(obs, critic_obs)
+                obs2, priv2, rew, dones, infos = env.step(actions)
+                alg.process_env_step(rew, dones, infos)
+                env.advance_base()
+                alg.advance_base()
+            env.end_relative()
+            alg.end_relative()
+            self.graphs.append(g)
+            self.outs.append((obs2, priv2 if priv2 is not None else obs2, rew, dones))
+        self.launches = (_lib.lib().urlg_launch_count() - n0) // max(len(self.graphs), 1)
+        alg.storage.clear()
+        assert env._obs_slot == slot0
+        return self
+
+    def replay(self, t):
+        """Run env step t of the rollout; returns (obs, critic_obs, rewards, dones) device tensors of that step."""
+        self.graphs[t].replay()
+        self.runner.alg.storage.step = t + 1
+        return self.outs[t]
