@@ -116,23 +116,56 @@ __global__ void bias_sum_kernel(float* __restrict__ dst, const float* __restrict
   if (i < n) dst[i] = a[i] + b[i];
 }
 
+// All weight images of a policy in ONE launch (it runs after every Adam step): a table of up to 16 segments, each a
+// [rows, kpad] image of a [rows, cols] fp32 matrix, or (rows == 0) a bias sum b_ih + b_hh of `cols` elements.
+struct ImgSeg {
+  bf16* dst; float* fdst; const float* src; const float* src2;
+  int rows, cols, kpad, dst_col0, ld;
+  int64_t start;                       // first flat element of this segment
+};
+struct ImgTable { int n; int64_t total; ImgSeg seg[16]; };
+
+__global__ void __launch_bounds__(256) weight_images_kernel(const __grid_constant__ ImgTable tb, int64_t lo_off) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < tb.total; i += (int64_t)gridDim.x * blockDim.x) {
+    int k = 0;
+    while (k + 1 < tb.n && i >= tb.seg[k + 1].start) ++k;
+    const ImgSeg& sg = tb.seg[k];
+    const int64_t j = i - sg.start;
+    if (sg.rows == 0) {
+      sg.fdst[j] = sg.src[j] + sg.src2[j];
+    } else {
+      const int r = (int)(j / sg.kpad), c = (int)(j % sg.kpad);
+      store_split(sg.dst, lo_off, (size_t)r * sg.ld + sg.dst_col0 + c, c < sg.cols ? sg.src[(size_t)r * sg.cols + c] : 0.0f);
+    }
+  }
+}
+
 int sync_weights(urlg_policy* p, cudaStream_t st) {
+  ImgTable tb;
+  tb.n = 0; tb.total = 0;
+  auto add = [&](bf16* dst, float* fdst, const float* src, const float* src2, int rows, int cols, int kpad, int col0, int ld) {
+    ImgSeg& sg = tb.seg[tb.n++];
+    sg.dst = dst; sg.fdst = fdst; sg.src = src; sg.src2 = src2;
+    sg.rows = rows; sg.cols = cols; sg.kpad = kpad; sg.dst_col0 = col0; sg.ld = ld;
+    sg.start = tb.total;
+    tb.total += rows ? (int64_t)rows * kpad : cols;
+  };
   for (int k = 0; k < 2; ++k) {
     NetWs& n = p->net[k];
-    for (int l = 0; l < n.d.num_layers; ++l) {
-      const int rows = n.d.dims[l + 1], cols = n.d.dims[l];
-      const int64_t total = (int64_t)rows * n.kpad[l];
-      weight_image_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(n.w[l], p->lo_off, p->params + n.d.w_off[l], rows, cols,
-                                                                      n.kpad[l], 0, n.kpad[l]);
-    }
+    if (n.d.num_layers + (p->desc.recurrent ? 3 : 0) + tb.n > 16) return fail(URLG_EINVAL, "sync_weights: too many layers");
+    for (int l = 0; l < n.d.num_layers; ++l)
+      add(n.w[l], nullptr, p->params + n.d.w_off[l], nullptr, n.d.dims[l + 1], n.d.dims[l], n.kpad[l], 0, n.kpad[l]);
     if (p->desc.recurrent) {
       LstmWs& w = p->lstm[k];
       const int G = 4 * w.H;
-      weight_image_kernel<<<(G * w.in_pad + 255) / 256, 256, 0, st>>>(w.w, p->lo_off, p->params + w.off[0], G, w.in, w.in_pad, 0, w.kcat);
-      weight_image_kernel<<<(G * w.H + 255) / 256, 256, 0, st>>>(w.w, p->lo_off, p->params + w.off[1], G, w.H, w.H, w.in_pad, w.kcat);
-      bias_sum_kernel<<<(G + 255) / 256, 256, 0, st>>>(w.bias, p->params + w.off[2], p->params + w.off[3], G);
+      add(w.w, nullptr, p->params + w.off[0], nullptr, G, w.in, w.in_pad, 0, w.kcat);
+      add(w.w, nullptr, p->params + w.off[1], nullptr, G, w.H, w.H, w.in_pad, w.kcat);
+      add(nullptr, w.bias, p->params + w.off[2], p->params + w.off[3], 0, G, 0, 0, 0);
     }
   }
+  int blocks = (int)((tb.total + 255) / 256);
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  weight_images_kernel<<<blocks, 256, 0, st>>>(tb, p->lo_off);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

@@ -23,12 +23,15 @@ __device__ __forceinline__ int64_t row_index(const int64_t* __restrict__ indices
 // ---------------------------------------------------------------- K6: gather
 __global__ void __launch_bounds__(256)
 gather_obs_kernel(const float* __restrict__ src, int cols, const int64_t* __restrict__ indices, int64_t rows,
-                  bf16* __restrict__ dst, int64_t lo_off, int kpad) {
+                  bf16* __restrict__ dst, bf16* __restrict__ dst2 /* optional second consumer of the same rows */,
+                  int64_t lo_off, int kpad) {
   const int64_t total = rows * kpad;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / kpad;
     const int c = (int)(i % kpad);
-    store_split(dst, lo_off, (size_t)i, c < cols ? src[indices[r] * cols + c] : 0.0f);
+    const float v = c < cols ? src[indices[r] * cols + c] : 0.0f;
+    store_split(dst, lo_off, (size_t)i, v);
+    if (dst2) store_split(dst2, lo_off, (size_t)i, v);
   }
 }
 
@@ -299,10 +302,15 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   if (!d.recurrent) {
     const float* cobs = s->privileged_observations ? s->privileged_observations : s->observations;
     int blocks = (int)((rows * na.kpad[0] + 255) / 256);
-    gather_obs_kernel<<<blocks, 256, 0, st>>>(s->observations, d.num_actor_obs, indices, rows, na.x, p->lo_off, na.kpad[0]);
-    blocks = (int)((rows * nc.kpad[0] + 255) / 256);
-    gather_obs_kernel<<<blocks, 256, 0, st>>>(cobs, d.num_critic_obs, indices, rows, nc.x, p->lo_off, nc.kpad[0]);
+    const bool shared = cobs == s->observations && na.kpad[0] == nc.kpad[0];   // no privileged obs: one gather feeds both nets
+    gather_obs_kernel<<<blocks, 256, 0, st>>>(s->observations, d.num_actor_obs, indices, rows, na.x, shared ? nc.x : nullptr,
+                                              p->lo_off, na.kpad[0]);
     URLG_LAUNCH_CHECK();
+    if (!shared) {
+      blocks = (int)((rows * nc.kpad[0] + 255) / 256);
+      gather_obs_kernel<<<blocks, 256, 0, st>>>(cobs, d.num_critic_obs, indices, rows, nc.x, nullptr, p->lo_off, nc.kpad[0]);
+      URLG_LAUNCH_CHECK();
+    }
   } else {
     if (int rc = lstm_update_forward(p, 0, s, env_begin, env_count, st)) return rc;
     if (int rc = lstm_update_forward(p, 1, s, env_begin, env_count, st)) return rc;
