@@ -78,6 +78,24 @@ def measured_peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+def ncu_traffic_per_launch(path=os.path.join(REPO, "profiles", "r1_gemm_minibatch_ncu.csv")):
+    """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch, averaged over the 22 launches of one update minibatch,
+    from the committed `ncu --set full` capture (tools/ncu_summary.py output); None when the file is absent."""
+    try:
+        import csv
+        rows = {r[0]: r for r in csv.reader(open(path))}
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot, n = 0.0, 0
+        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            r = rows[key]
+            vals = [float(x) * scale[r[1]] for x in r[2:]]
+            tot += sum(vals)
+            n = len(vals)
+        return tot / n
+    except Exception:
+        return None
+
+
 def make_frames(task, n, frames, seed=1):
     import torch
     from unitree_rl_gym_b200 import synthetic
@@ -402,7 +420,8 @@ def own_arm(a):
                 "bound": "hbm" if mem_bound else "tensor",
                 "achieved": gbs if mem_bound else tf, "peak": hbm if mem_bound else tf_sus,
                 "unit": "GB/s" if mem_bound else "TFLOP/s", "frac": (gbs / hbm) if mem_bound else (tf / tf_sus),
-                "traffic": None, "launches_per_step": int(n_r + n_u), "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
+                "traffic": ncu_traffic_per_launch(), "launches_per_step": int(n_r + n_u),
+                "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
                 "alg_bytes_per_launch": (by_r + by_u) / max(n_r + n_u, 1), "alg_flops_per_launch": (fl_r + fl_u) / max(n_r + n_u, 1),
                 "tensor": {"achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus},
                 "hbm": {"achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm},

@@ -116,3 +116,143 @@ def test_unknown_controller_raises_nameerror():
     sp.dt = cfg.sim.dt
     with pytest.raises(NameError):
         LeggedRobot(cfg=cfg, sim_params=sp, physics_engine=None, sim_device="cuda:0", headless=True)
+
+
+# ------------------------------------------------------------------ size-independent properties
+def _sliced_frames(frames, lo, hi, A, B, n):
+    """Rows [lo, hi) of every env-major frame tensor (dof / contact / rigid_body are flattened over env)."""
+    out = {"root": frames["root"][:, lo:hi].contiguous()}
+    P, D = frames["dof"].shape[0], frames["dof"].shape[1]
+    out["dof"] = frames["dof"].view(P, D, n, A, 2)[:, :, lo:hi].reshape(P, D, (hi - lo) * A, 2).contiguous()
+    out["contact"] = frames["contact"].view(P, n, B, 3)[:, lo:hi].reshape(P, (hi - lo) * B, 3).contiguous()
+    out["rigid_body"] = frames["rigid_body"].view(P, n, B, 13)[:, lo:hi].reshape(P, (hi - lo) * B, 13).contiguous()
+    return out
+
+
+@pytest.mark.parametrize("task,n,cut", [("go2", 4096, 2048), ("g1", 600, 250)])
+def test_env_shards_reproduce_the_whole(task, n, cut):
+    """Multi-GPU sharding property at the BASELINE size: stepping envs [0,cut) and [cut,n) as two env
+    objects with env_offset 0 / cut gives bit-identical tensors to stepping all n envs as one object — every Philox
+    draw is keyed by the global env id, and nothing in K1/K2 couples envs except the any-push flag and the extras means,
+    which are compared after re-deriving them from the shards."""
+    from unitree_rl_gym_b200 import synthetic
+    from unitree_rl_gym_b200.legged_gym.envs import LeggedRobot, G1Robot
+    from unitree_rl_gym_b200.legged_gym.utils.helpers import SimParams
+    from unitree_rl_gym_b200.physics import SyntheticGym
+    from unitree_rl_gym_b200.robots import ROBOTS
+    H.ENV_CASES["tmp"] = (task, n, False)
+    try:
+        spec = H.make_spec("tmp")
+    finally:
+        del H.ENV_CASES["tmp"]
+    robot = ROBOTS[task]
+    frames = synthetic.make_frames(robot, None, n, 3, spec.decimation, seed=11, feet_idx=spec.feet_idx, pen_idx=spec.pen_idx,
+                                   term_idx=spec.term_idx, init_z=float(spec.base_init_state[2]),
+                                   default_dof_pos=torch.from_numpy(spec.default_dof_pos))
+
+    def build(lo, hi):
+        cfg = H.make_cfg(task, hi - lo, False)
+        cfg.seed = 1
+        cfg.env.env_offset = lo
+        sp = SimParams()
+        sp.dt = cfg.sim.dt
+        fr = frames if (lo, hi) == (0, n) else _sliced_frames(frames, lo, hi, robot.num_dof, robot.num_bodies, n)
+        gym = SyntheticGym(robot, hi - lo, cfg.control.decimation, "cuda:0", frames=fr)
+        cls = {"go2": LeggedRobot, "g1": G1Robot}[task]
+        return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device="cuda:0", headless=True)
+    whole, parts = build(0, n), [build(0, cut), build(cut, n)]
+    g = torch.Generator().manual_seed(4)
+    ep = torch.randint(0, 1001, (n,), generator=g)
+    for e, (lo, hi) in zip([whole] + parts, [(0, n), (0, cut), (cut, n)]):
+        e.reset()
+        e.episode_length_buf = ep[lo:hi].cuda()
+    names = ["obs_buf", "rew_buf", "reset_buf", "time_out_buf", "episode_length_buf", "torques", "commands", "actions",
+             "last_actions", "last_dof_vel", "feet_air_time", "last_contacts", "rpy", "base_lin_vel", "dof_state"]
+    for t in range(4):
+        a = torch.randn(n, spec.num_dof, generator=g).cuda()
+        whole.step(a)
+        parts[0].step(a[:cut].contiguous())
+        parts[1].step(a[cut:].contiguous())
+        torch.cuda.synchronize()
+        for k in names + (["privileged_obs_buf"] if whole.privileged_obs_buf is not None else []):
+            w = getattr(whole, k)
+            got = torch.cat([getattr(parts[0], k).reshape(cut, -1), getattr(parts[1], k).reshape(n - cut, -1)]).reshape(w.shape)
+            assert torch.equal(w, got), f"step{t}/{k}"
+        for k in whole.episode_sums:
+            got = torch.cat([parts[0].episode_sums[k], parts[1].episode_sums[k]])
+            assert torch.equal(whole.episode_sums[k], got), f"step{t}/episode_sums/{k}"
+
+
+def test_masks_at_thresholds():
+    """Adversarial inputs within +-2 ulp of every mask threshold: termination contact norm 1.0, penalised
+    contact 0.1, feet F_z 1.0, |roll| 0.8, |pitch| 1.0, command norm 0.2.  Contact / command thresholds are exact IEEE
+    sqrt / compare and must match bit for bit; roll / pitch go through atan2f / asinf (CUDA libm vs the CPU's SLEEF), so
+    an env whose oracle angle lies within 2 ulp of its threshold is excluded from the reset comparison."""
+    from oracle.env_port import EnvPort
+    from unitree_rl_gym_b200 import synthetic
+    from unitree_rl_gym_b200.robots import ROBOTS
+    task, n = "go2", 512
+    H.ENV_CASES["tmp"] = (task, n, False)
+    try:
+        spec = H.make_spec("tmp")
+        frames = synthetic.make_frames(ROBOTS[task], None, n, 2, spec.decimation, seed=21, feet_idx=spec.feet_idx,
+                                       pen_idx=spec.pen_idx, term_idx=spec.term_idx, init_z=float(spec.base_init_state[2]),
+                                       default_dof_pos=torch.from_numpy(spec.default_dof_pos))
+        B = ROBOTS[task].num_bodies
+
+        def near(x, i):          # x shifted by (i % 5) - 2 ulps
+            v = np.float32(x)
+            for _ in range(abs(i % 5 - 2)):
+                v = np.nextafter(v, np.float32(np.inf if i % 5 > 2 else -np.inf))
+            return float(v)
+        con = frames["contact"].view(2, n, B, 3)
+        root = frames["root"]
+        for f in range(2):
+            for e in range(n):
+                kind = e % 6
+                if kind == 0:      # termination body norm ~ 1.0 along one axis (exact sqrt of a square)
+                    con[f, e, spec.term_idx[0]] = torch.tensor([0.0, near(1.0, e // 6), 0.0])
+                elif kind == 1:    # penalised body norm ~ 0.1
+                    con[f, e, spec.pen_idx[e % len(spec.pen_idx)]] = torch.tensor([near(0.1, e // 6), 0.0, 0.0])
+                elif kind == 2:    # foot F_z ~ 1.0
+                    con[f, e, spec.feet_idx[e % len(spec.feet_idx)]] = torch.tensor([0.0, 0.0, near(1.0, e // 6)])
+                elif kind == 3:    # pure roll ~ 0.8
+                    th = near(0.8, e // 6) * (1 if e % 12 < 6 else -1)
+                    root[f, e, 3:7] = torch.tensor([np.sin(th / 2), 0.0, 0.0, np.cos(th / 2)], dtype=torch.float32)
+                elif kind == 4:    # pure pitch ~ 1.0
+                    th = near(1.0, e // 6) * (1 if e % 12 < 6 else -1)
+                    root[f, e, 3:7] = torch.tensor([0.0, np.sin(th / 2), 0.0, np.cos(th / 2)], dtype=torch.float32)
+        env = make_env("tmp", frames=frames)
+    finally:
+        H.ENV_CASES.pop("tmp", None)
+    port = EnvPort(spec)
+    calls = {"n": 0}
+
+    def physics(sub):
+        if sub is not None:
+            calls["n"] += 1
+        port.load_frame(frames, ((calls["n"] - 1) // spec.decimation) % 2, sub)
+    env.reset()
+    port.reset(physics)
+    g = torch.Generator().manual_seed(8)
+    checked = 0
+    for t in range(3):
+        a = torch.randn(n, spec.num_dof, generator=g)
+        env.step(a.cuda())
+        port.step(a, physics)
+        snap = env_snapshot(env)
+        rpy = port.rpy.numpy()
+        band = lambda v, th: np.abs(np.abs(v) - np.float32(th)) <= 2 * np.spacing(np.float32(th))
+        skip = band(rpy[:, 0], 0.8) | band(rpy[:, 1], 1.0)
+        keep = ~skip
+        checked += int(keep.sum())
+        assert np.array_equal(snap["reset_buf"][keep], port.reset_buf.numpy()[keep]), f"step{t}"
+        H.compare("time_out_buf", snap["time_out_buf"], port.time_out_buf.numpy(), f"step{t}/")
+        H.compare("last_contacts", snap["last_contacts"], port.last_contacts.numpy(), f"step{t}/")
+        # collision / feet_air_time terms flip by a whole unit when their mask flips: they must agree everywhere
+        for k in ("collision", "feet_air_time"):
+            H.compare("episode_sums/" + k, snap["episode_sums/" + k][keep], port.episode_sums[k].numpy()[keep], f"step{t}/")
+        # an excluded env may legitimately reset on one side only: re-align the port with the device for the next step
+        if skip.any():
+            break
+    assert checked >= n // 2
