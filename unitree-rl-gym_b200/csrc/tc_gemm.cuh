@@ -51,6 +51,25 @@ __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : __expf(x)
 __device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
+// Tile coordinates of a persistent CTA, advanced by gridDim.x tiles per step without divisions.
+struct TileWalk {
+  int tx, ty, tz, dx, dy, dz, tm, tn;
+  __device__ __forceinline__ void init(int tile, int step, int tiles_m, int tiles_n) {
+    tm = tiles_m; tn = tiles_n;
+    tx = tile % tm; const int r = tile / tm; ty = r % tn; tz = r / tn;
+    dx = step % tm; const int q = step / tm; dy = q % tn; dz = q / tn;
+  }
+  __device__ __forceinline__ void next() {
+    tx += dx;
+    int carry = 0;
+    if (tx >= tm) { tx -= tm; carry = 1; }
+    ty += dy + carry;
+    carry = 0;
+    if (ty >= tn) { ty -= tn; carry = 1; }
+    tz += dz + carry;
+  }
+};
+
 // Persistent kernel: each CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The accumulator is double
 // buffered in TMEM (2 x tmem_cols_for(block_n) columns), so the MMAs of tile i+1 run under the epilogue of tile i;
 // the epilogue (the expensive part for these skinny GEMMs: bias, ELU / ELU', hi+lo split, column sums) is spread
@@ -96,10 +115,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===== TMA producer =====
     if (lane == 0) {
       int kbt = 0;                                                       // k-blocks issued so far (all tiles)
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int tx = tile % g.tiles_m, ty = (tile / g.tiles_m) % g.tiles_n, tz = tile / (g.tiles_m * g.tiles_n);
-        const int m0 = tx * kBlockM, n0 = ty * g.block_n;
-        const int k_begin = tz * g.k_per_split;
+      TileWalk tw;
+      tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, tw.next()) {
+        const int m0 = tw.tx * kBlockM, n0 = tw.ty * g.block_n;
+        const int k_begin = tw.tz * g.k_per_split;
         const int k_end = min(g.K, k_begin + g.k_per_split);
         const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
         for (int kb = 0; kb < num_kb; ++kb, ++kbt) {
@@ -134,9 +154,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t a_lbo = g.a_mn ? 8192u : 16u, b_lbo = g.b_mn ? 8192u : 16u;
       const uint32_t a_kstep = g.a_mn ? 2048u : 32u, b_kstep = g.b_mn ? 2048u : 32u;
       int kbt = 0, it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int tz = tile / (g.tiles_m * g.tiles_n);
-        const int k_begin = tz * g.k_per_split;
+      TileWalk tw;
+      tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it, tw.next()) {
+        const int k_begin = tw.tz * g.k_per_split;
         const int k_end = min(g.K, k_begin + g.k_per_split);
         const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
         const int acc = it & 1;
@@ -172,9 +193,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int cg = (warp - 2) >> 2;                // column group 0..3: chunks cg, cg+4, ...
     const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int tx = tile % g.tiles_m, ty = (tile / g.tiles_m) % g.tiles_n;
-      const int m0 = tx * kBlockM, n0 = ty * g.block_n;
+    TileWalk tw;
+    tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it, tw.next()) {
+      const int m0 = tw.tx * kBlockM, n0 = tw.ty * g.block_n;
       const int acc = it & 1;
       mbar_wait(tfull0 + 8 * acc, (it >> 1) & 1);
       tc_fence_after();
@@ -230,7 +252,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         }
-        if (!row_ok || !full) {
+        if (!full || __any_sync(0xffffffffu, !row_ok)) {       // warp-uniform: interior tiles skip the 16 selects
 #pragma unroll
           for (int i = 0; i < 16; ++i) if (!row_ok || i >= ncol) v[i] = 0.0f;
         }
