@@ -26,7 +26,8 @@ static EncodeTiledFn encode_fn() {
 }
 
 // bf16 row-major matrix [outer, inner] with row pitch ld (elements); box {box_inner, box_outer}; zero OOB fill.
-int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer,
+                   CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn enc = encode_fn();
   if (!enc) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled entry point unavailable");
   if (((uintptr_t)ptr & 15) || ((ld * 2) & 15))
@@ -36,7 +37,7 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return URLG_OK;
@@ -106,11 +107,23 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   g.split = (d->A_lo && d->B_lo) ? 1 : 0;
   if ((d->A_lo != nullptr) != (d->B_lo != nullptr)) return fail(URLG_EINVAL, "urlg_tc_gemm: A_lo and B_lo go together");
   if (g.split && bn > 128) { bn = 128; g.block_n = bn; }       // two operand sets per stage: keep >= 3 stages in 227 KB
-  g.stages = gemm_stages_for(bn, g.split);
   g.out_lo = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_lo);
   g.dact_lo = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref_lo);
-  CUtensorMap ta, tb, tal, tbl;
+  // bf16 outputs go through shared staging + TMA tensor stores whenever a tensor map can describe them
+  g.tma_out = (g.out_bf16 && (((uintptr_t)g.out_bf16 | (uintptr_t)g.out_lo) & 15) == 0 && (g.ld_bf16 & 7) == 0) ? 1 : 0;
+  g.stages = gemm_stages_for(bn, g.split, g.tma_out);
+  CUtensorMap ta, tb, tal, tbl, to, tol;
   int rc;
+  if (g.tma_out) {
+    rc = make_tmap_bf16(&to, g.out_bf16, d->N, d->M, g.ld_bf16, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
+    if (rc) return rc;
+    if (g.out_lo) {
+      rc = make_tmap_bf16(&tol, g.out_lo, d->N, d->M, g.ld_bf16, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
+      if (rc) return rc;
+    } else {
+      tol = to;
+    }
+  }
   if (!g.a_mn) rc = make_tmap_bf16(&ta, d->A, d->K, d->M, d->lda, kBlockK, kBlockM);
   else rc = make_tmap_bf16(&ta, d->A, d->M, d->K, d->lda, 64, kBlockK);
   if (rc) return rc;
@@ -127,6 +140,7 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   } else {
     tal = ta; tbl = tb;
   }
+  if (!g.tma_out) { to = ta; tol = ta; }
   static bool attr_set = false;
   if (!attr_set) {
     URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -138,7 +152,7 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
   int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
   if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;
-  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages), st>>>(ta, tb, tal, tbl, g);
+  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages, g.tma_out), st>>>(ta, tb, tal, tbl, to, tol, g);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

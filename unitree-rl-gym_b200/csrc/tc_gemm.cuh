@@ -33,16 +33,22 @@ struct GemmArgs {
   int stages;            // smem pipeline depth (fits 227 KB)
   __nv_bfloat16* out_lo; // split: low part of the bf16 output (same ld as out_bf16)
   const __nv_bfloat16* dact_lo;   // split: low part of dact_ref
+  int tma_out;           // bf16 outputs leave through per-warp shared staging + TMA tensor stores (tmO / tmOlo valid)
 };
 
 __host__ __device__ inline int stage_bytes_a() { return kBlockM * kBlockK * 2; }
 __host__ __device__ inline int stage_bytes_b(int block_n) { return block_n * kBlockK * 2; }
 inline int gemm_stage_bytes(int block_n, int split) { return (split ? 2 : 1) * (stage_bytes_a() + stage_bytes_b(block_n)); }
-inline int gemm_stages_for(int block_n, int split) {
-  int s = (227 * 1024 - 1024 - 256) / gemm_stage_bytes(block_n, split);
+// Epilogue staging: per warp one 32-row x 16-column bf16 chunk for the high and one for the low part (1 KB each).
+constexpr int kEpiStageBytes = 2048;
+inline int gemm_epi_bytes(int tma_out) { return tma_out ? kEpiWarps * kEpiStageBytes : 0; }
+inline int gemm_stages_for(int block_n, int split, int tma_out) {
+  int s = (227 * 1024 - 1024 - 256 - gemm_epi_bytes(tma_out)) / gemm_stage_bytes(block_n, split);
   return s > kMaxStages ? kMaxStages : s;
 }
-inline int gemm_smem_bytes(int block_n, int split, int stages) { return stages * gemm_stage_bytes(block_n, split) + 1024 + 256; }
+inline int gemm_smem_bytes(int block_n, int split, int stages, int tma_out) {
+  return stages * gemm_stage_bytes(block_n, split) + gemm_epi_bytes(tma_out) + 1024 + 256;
+}
 
 // ELU(x) = x > 0 ? x : exp(x) - 1.  The epilogue is instruction-bound (ncu: IPC-limited, tensor pipe ~10% busy), and
 // expm1f is ~20 of its ~35 instructions per element; ex2.approx (2 ulp) - 1 has an absolute error <= 2.5e-7, far inside
@@ -76,16 +82,18 @@ struct TileWalk {
 // over 16 warps = 4 per scheduler.
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo, const GemmArgs g) {
+                 const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo,
+                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmOlo, const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int bytes_a = stage_bytes_a(), bytes_b = stage_bytes_b(g.block_n);
   const int kStages = g.stages;
-  // layout: A[stages] | B[stages] | (split) Alo[stages] | Blo[stages] | barriers
+  // layout: A[stages] | B[stages] | (split) Alo[stages] | Blo[stages] | (tma_out) epilogue staging | barriers
   const uint32_t sA = base, sB = base + kStages * bytes_a;
   const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (g.split ? kStages * bytes_a : 0);
-  const uint32_t bars = sBlo + (g.split ? kStages * bytes_b : 0);
+  const uint32_t sEpi = sBlo + (g.split ? kStages * bytes_b : 0);           // 1024-byte aligned (stage sizes are 8 KB multiples)
+  const uint32_t bars = sEpi + (g.tma_out ? kEpiWarps * kEpiStageBytes : 0);
   // full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2], tmem_ptr
   const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tfull0 = bars + 16 * kMaxStages;
   const uint32_t tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
@@ -101,6 +109,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (g.split) { tma_prefetch_desc(&tmAlo); tma_prefetch_desc(&tmBlo); }
+    if (g.tma_out) { tma_prefetch_desc(&tmO); if (g.out_lo) tma_prefetch_desc(&tmOlo); }
     for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, kEpiWarps); }
     fence_mbar_init();
@@ -192,6 +201,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int lg = warp & 3;                       // TMEM lane quarter this warp may access (warp id % 4)
     const int cg = (warp - 2) >> 2;                // column group 0..3: chunks cg, cg+4, ...
     const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
+    // this warp's staging chunk: row r (= lane) at 32 r bytes, its two 16-byte halves swapped when r & 4 (SWIZZLE_32B)
+    const uint32_t stage_hi = sEpi + (uint32_t)(warp - 2) * kEpiStageBytes, stage_lo = stage_hi + 1024;
+    const uint32_t st_row = (uint32_t)lane * 32u, st_sw = (uint32_t)((lane >> 2) & 1) << 4;
     int it = 0;
     TileWalk tw;
     tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
@@ -256,6 +268,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int i = 0; i < 16; ++i) if (!row_ok || i >= ncol) v[i] = 0.0f;
         }
+        if (g.out_bf16 && g.tma_out) {
+          // pack (hi, lo), stage the 32 x 16 chunk in shared memory and let TMA write full 32-byte row segments
+          // (a row-per-thread st.global touches 32 lines per instruction; rows >= M / columns >= N are clipped by TMA)
+          uint32_t p[8], q[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            p[i] = *reinterpret_cast<uint32_t*>(&h);
+            __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * i] - bf16lo(p[i]), v[2 * i + 1] - bf16hi(p[i]));
+            q[i] = *reinterpret_cast<uint32_t*>(&l);
+          }
+          if (lane == 0) bulk_wait_read0();          // the previous chunk's stores have finished reading the staging
+          __syncwarp();
+          st_shared_v4(stage_hi + st_row + st_sw, p[0], p[1], p[2], p[3]);
+          st_shared_v4(stage_hi + st_row + (16u ^ st_sw), p[4], p[5], p[6], p[7]);
+          if (g.out_lo) {
+            st_shared_v4(stage_lo + st_row + st_sw, q[0], q[1], q[2], q[3]);
+            st_shared_v4(stage_lo + st_row + (16u ^ st_sw), q[4], q[5], q[6], q[7]);
+          }
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmO, stage_hi, col0, m0 + lg * 32);
+            if (g.out_lo) tma_store_2d(&tmOlo, stage_lo, col0, m0 + lg * 32);
+            bulk_commit();
+          }
+        }
         if (row_ok) {
           if (g.out_f32) {
             float* o = g.out_f32 + (size_t)row * g.ld_f32 + col0;
@@ -277,7 +316,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int i = 0; i < 16; ++i) if (i < ncol) o[i] = v[i];
             }
           }
-          if (g.out_bf16) {
+          if (g.out_bf16 && !g.tma_out) {
             __nv_bfloat16* o = g.out_bf16 + (size_t)row * g.ld_bf16 + col0;
             __nv_bfloat16* ol = g.out_lo ? g.out_lo + (size_t)row * g.ld_bf16 + col0 : nullptr;
             if (full && vec_bf16 && (((uintptr_t)o | (uintptr_t)ol) & 15) == 0) {
@@ -341,6 +380,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);     // this warp is done reading accumulator `acc`
     }
+    if (g.tma_out && lane == 0) bulk_wait_read0();       // staging must outlive the last stores' reads
   }
   tc_fence_before();
   __syncthreads();
