@@ -20,6 +20,8 @@ def main():
     import bench
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=24576)
+    ap.add_argument("--only", default="", help="comma-separated shape names; with --profile: 3 eager launches each (for ncu)")
+    ap.add_argument("--profile", action="store_true")
     a = ap.parse_args()
     R = a.rows
     L = _lib.lib()
@@ -40,7 +42,10 @@ def main():
         tiles = ((nout + 127) // 128) * ((nin + bn - 1) // bn)
         splits = max(1, min((2 * 148 + tiles - 1) // tiles, ((R + 63) // 64) // 4))
         shapes.append((f"wgrad{l}", nout, nin, R, 1, 1, 2, splits, bn, "atomic f32"))
+    only = set(a.only.split(",")) if a.only else None
     for name, M, N, K, a_mn, b_mn, flags, splits, bn, epi in shapes:
+        if only and name not in only:
+            continue
         if not a_mn:
             lda = rup(K, 8); A, Al = bf(M, lda), bf(M, lda)
         else:
@@ -75,6 +80,8 @@ def main():
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
+        if a.profile:
+            continue
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             for _ in range(20):

@@ -111,8 +111,9 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   g.dact_lo = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref_lo);
   // bf16 outputs go through shared staging + TMA tensor stores whenever a tensor map can describe them
   g.tma_out = (g.out_bf16 && (((uintptr_t)g.out_bf16 | (uintptr_t)g.out_lo) & 15) == 0 && (g.ld_bf16 & 7) == 0) ? 1 : 0;
-  g.stages = gemm_stages_for(bn, g.split, g.tma_out);
-  CUtensorMap ta, tb, tal, tbl, to, tol;
+  g.tma_ref = (g.tma_out && g.dact_ref && (((uintptr_t)g.dact_ref | (uintptr_t)g.dact_lo) & 15) == 0 && (g.ld_ref & 7) == 0) ? 1 : 0;
+  g.stages = gemm_stages_for(bn, g.split, g.tma_out, g.tma_ref);
+  CUtensorMap ta, tb, tal, tbl, to, tol, tr, trl;
   int rc;
   if (g.tma_out) {
     rc = make_tmap_bf16(&to, g.out_bf16, d->N, d->M, g.ld_bf16, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
@@ -141,6 +142,18 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
     tal = ta; tbl = tb;
   }
   if (!g.tma_out) { to = ta; tol = ta; }
+  if (g.tma_ref) {
+    rc = make_tmap_bf16(&tr, g.dact_ref, d->N, d->M, g.ld_ref, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
+    if (rc) return rc;
+    if (g.dact_lo) {
+      rc = make_tmap_bf16(&trl, g.dact_lo, d->N, d->M, g.ld_ref, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
+      if (rc) return rc;
+    } else {
+      trl = tr;
+    }
+  } else {
+    tr = ta; trl = ta;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -152,7 +165,7 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
   int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
   if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;
-  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages, g.tma_out), st>>>(ta, tb, tal, tbl, to, tol, g);
+  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages, g.tma_out, g.tma_ref), st>>>(ta, tb, tal, tbl, to, tol, tr, trl, g);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

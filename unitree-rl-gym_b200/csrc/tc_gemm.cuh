@@ -33,6 +33,7 @@ struct GemmArgs {
   int stages;            // smem pipeline depth (fits 227 KB)
   __nv_bfloat16* out_lo; // split: low part of the bf16 output (same ld as out_bf16)
   const __nv_bfloat16* dact_lo;   // split: low part of dact_ref
+  int tma_ref;           // dact_ref chunks arrive by TMA tensor loads, one chunk ahead (tmR / tmRlo valid; needs tma_out)
   int tma_out;           // bf16 outputs leave through per-warp shared staging + TMA tensor stores (tmO / tmOlo valid)
 };
 
@@ -41,13 +42,13 @@ __host__ __device__ inline int stage_bytes_b(int block_n) { return block_n * kBl
 inline int gemm_stage_bytes(int block_n, int split) { return (split ? 2 : 1) * (stage_bytes_a() + stage_bytes_b(block_n)); }
 // Epilogue staging: per warp one 32-row x 16-column bf16 chunk for the high and one for the low part (1 KB each).
 constexpr int kEpiStageBytes = 2048;
-inline int gemm_epi_bytes(int tma_out) { return tma_out ? kEpiWarps * kEpiStageBytes : 0; }
-inline int gemm_stages_for(int block_n, int split, int tma_out) {
-  int s = (227 * 1024 - 1024 - 256 - gemm_epi_bytes(tma_out)) / gemm_stage_bytes(block_n, split);
+inline int gemm_epi_bytes(int tma_out, int tma_ref) { return tma_out ? kEpiWarps * kEpiStageBytes * (tma_ref ? 2 : 1) : 0; }
+inline int gemm_stages_for(int block_n, int split, int tma_out, int tma_ref) {
+  int s = (227 * 1024 - 1024 - 256 - gemm_epi_bytes(tma_out, tma_ref)) / gemm_stage_bytes(block_n, split);
   return s > kMaxStages ? kMaxStages : s;
 }
-inline int gemm_smem_bytes(int block_n, int split, int stages, int tma_out) {
-  return stages * gemm_stage_bytes(block_n, split) + gemm_epi_bytes(tma_out) + 1024 + 256;
+inline int gemm_smem_bytes(int block_n, int split, int stages, int tma_out, int tma_ref) {
+  return stages * gemm_stage_bytes(block_n, split) + gemm_epi_bytes(tma_out, tma_ref) + 1024 + 256;
 }
 
 // ELU(x) = x > 0 ? x : exp(x) - 1.  The epilogue is instruction-bound (ncu: IPC-limited, tensor pipe ~10% busy), and
@@ -83,7 +84,8 @@ struct TileWalk {
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo,
-                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmOlo, const GemmArgs g) {
+                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmOlo,
+                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmRlo, const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -93,10 +95,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t sA = base, sB = base + kStages * bytes_a;
   const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (g.split ? kStages * bytes_a : 0);
   const uint32_t sEpi = sBlo + (g.split ? kStages * bytes_b : 0);           // 1024-byte aligned (stage sizes are 8 KB multiples)
-  const uint32_t bars = sEpi + (g.tma_out ? kEpiWarps * kEpiStageBytes : 0);
+  const uint32_t epi_stride = g.tma_ref ? 2 * kEpiStageBytes : kEpiStageBytes;
+  const uint32_t bars = sEpi + (g.tma_out ? kEpiWarps * epi_stride : 0);
   // full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2], tmem_ptr
   const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tfull0 = bars + 16 * kMaxStages;
   const uint32_t tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+  const uint32_t rbar0 = bars + 128;                     // ref_full[kEpiWarps]: one per epilogue warp
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
@@ -110,6 +114,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmB);
     if (g.split) { tma_prefetch_desc(&tmAlo); tma_prefetch_desc(&tmBlo); }
     if (g.tma_out) { tma_prefetch_desc(&tmO); if (g.out_lo) tma_prefetch_desc(&tmOlo); }
+    if (g.tma_ref) { tma_prefetch_desc(&tmR); if (g.dact_lo) tma_prefetch_desc(&tmRlo); }
+    for (int w = 0; w < kEpiWarps; ++w) mbar_init(rbar0 + 8 * w, 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, kEpiWarps); }
     fence_mbar_init();
@@ -202,11 +208,30 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int cg = (warp - 2) >> 2;                // column group 0..3: chunks cg, cg+4, ...
     const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
     // this warp's staging chunk: row r (= lane) at 32 r bytes, its two 16-byte halves swapped when r & 4 (SWIZZLE_32B)
-    const uint32_t stage_hi = sEpi + (uint32_t)(warp - 2) * kEpiStageBytes, stage_lo = stage_hi + 1024;
+    const uint32_t stage_hi = sEpi + (uint32_t)(warp - 2) * epi_stride, stage_lo = stage_hi + 1024;
+    const uint32_t ref_hi = stage_hi + kEpiStageBytes, ref_lo = ref_hi + 1024, rbar = rbar0 + 8 * (warp - 2);
     const uint32_t st_row = (uint32_t)lane * 32u, st_sw = (uint32_t)((lane >> 2) & 1) << 4;
     int it = 0;
     TileWalk tw;
     tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
+    // dact_ref prefetch cursor: walks this warp's valid chunks in processing order, one chunk ahead of the consumer
+    TileWalk pw = tw;
+    int ptile = blockIdx.x, pc = 16 * cg - 64;
+    uint32_t ref_phase = 0;
+    auto prefetch_ref = [&]() {
+      for (pc += 64;; pc = 16 * cg) {
+        if (ptile >= num_tiles) return;
+        if (pc < g.block_n && pw.ty * g.block_n + pc < g.N) break;
+        ptile += gridDim.x;
+        pw.next();
+      }
+      if (lane == 0) {
+        mbar_arrive_expect_tx(rbar, g.dact_lo ? 2048u : 1024u);
+        tma_load_2d(ref_hi, &tmR, rbar, pw.ty * g.block_n + pc, pw.tx * kBlockM + lg * 32);
+        if (g.dact_lo) tma_load_2d(ref_lo, &tmRlo, rbar, pw.ty * g.block_n + pc, pw.tx * kBlockM + lg * 32);
+      }
+    };
+    if (g.tma_ref) prefetch_ref();
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it, tw.next()) {
       const int m0 = tw.tx * kBlockM, n0 = tw.ty * g.block_n;
       const int acc = it & 1;
@@ -218,6 +243,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int c0 = 16 * cg; c0 < g.block_n; c0 += 64) {
         const int col0 = n0 + c0;
         if (col0 >= g.N) break;                      // uniform across the warp
+        uint4 rh0, rh1, rl0 = make_uint4(0, 0, 0, 0), rl1 = rl0;
+        if (g.tma_ref) {
+          mbar_wait(rbar, ref_phase);
+          ref_phase ^= 1;
+          rh0 = ld_shared_v4(ref_hi + st_row + st_sw);
+          rh1 = ld_shared_v4(ref_hi + st_row + (16u ^ st_sw));
+          if (g.dact_lo) {
+            rl0 = ld_shared_v4(ref_lo + st_row + st_sw);
+            rl1 = ld_shared_v4(ref_lo + st_row + (16u ^ st_sw));
+          }
+          __syncwarp();
+          prefetch_ref();                          // the next chunk's reference lands while this one is processed
+        }
         float v[16];
         tmem_ld16(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
         const int ncol = min(16, g.N - col0);
@@ -238,7 +276,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = elu1(v[i]);
         }
-        if (g.dact_ref && row_ok) {
+        if (g.tma_ref) {
+          const uint32_t aw[8] = {rh0.x, rh0.y, rh0.z, rh0.w, rh1.x, rh1.y, rh1.z, rh1.w};
+          const uint32_t bw[8] = {rl0.x, rl0.y, rl0.z, rl0.w, rl1.x, rl1.y, rl1.z, rl1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {            // clipped rows / columns read zeros: factor 1, zeroed below
+            const float y0 = bf16lo(aw[i]) + bf16lo(bw[i]), y1 = bf16hi(aw[i]) + bf16hi(bw[i]);
+            v[2 * i] *= (y0 > 0.0f ? 1.0f : y0 + 1.0f);
+            v[2 * i + 1] *= (y1 > 0.0f ? 1.0f : y1 + 1.0f);
+          }
+        } else if (g.dact_ref && row_ok) {
           const __nv_bfloat16* rp = g.dact_ref + (size_t)row * g.ld_ref + col0;
           const __nv_bfloat16* rl = g.dact_lo ? g.dact_lo + (size_t)row * g.ld_ref + col0 : nullptr;
           if (full && vec_ref && (((uintptr_t)rp | (uintptr_t)rl) & 15) == 0) {
