@@ -106,7 +106,7 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   g.flags = d->flags;
   g.split = (d->A_lo && d->B_lo) ? 1 : 0;
   if ((d->A_lo != nullptr) != (d->B_lo != nullptr)) return fail(URLG_EINVAL, "urlg_tc_gemm: A_lo and B_lo go together");
-  if (g.split && bn > 128) { bn = 128; g.block_n = bn; }       // two operand sets per stage: keep >= 3 stages in 227 KB
+  if (g.split && bn > 128) { bn = 128; g.block_n = bn; }       // two operand sets per stage: keep >= 2-3 stages in 227 KB
   g.out_lo = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_lo);
   g.dact_lo = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref_lo);
   // bf16 outputs go through shared staging + TMA tensor stores whenever a tensor map can describe them

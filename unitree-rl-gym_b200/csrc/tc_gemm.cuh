@@ -54,7 +54,13 @@ inline int gemm_smem_bytes(int block_n, int split, int stages, int tma_out, int 
 // ELU(x) = x > 0 ? x : exp(x) - 1.  The epilogue is instruction-bound (ncu: IPC-limited, tensor pipe ~10% busy), and
 // expm1f is ~20 of its ~35 instructions per element; ex2.approx (2 ulp) - 1 has an absolute error <= 2.5e-7, far inside
 // the 1e-4 forward / 1e-3 update tolerances (the values feed bf16 hi+lo operands of ~2^-17 relative resolution).
-__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// one FMUL + one MUFU (no denormal range fix-up: exp(x) below 2^-126 flushes to 0, i.e. ELU = -1 exactly as fp32 rounds it)
+__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : ex2_ftz(x * 1.4426950408889634f) - 1.0f; }
 __device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
