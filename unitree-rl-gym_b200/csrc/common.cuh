@@ -1,5 +1,6 @@
 // Shared host/device plumbing for liburlg_b200.so (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -26,6 +27,32 @@ inline int fail(int code, const char* fmt, ...) {
       return urlg::fail(URLG_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr,         \
                         cudaGetErrorString(e__));                                        \
   } while (0)
+
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------------------
+// A kernel that starts with pdl_enter() and is launched through launch_pdl() lets the next such kernel in the stream
+// onto SMs the current grid has already left (launch latency and set-up overlap the tail); griddepcontrol.wait then
+// holds it until the previous grid has completed and flushed.  Used by the tcgen05 GEMM (8 back-to-back launches per
+// env step, 22 per minibatch per network): measured on B200, rollout 2.55 -> 2.26 ms, PPO iteration 12.4 -> 11.6 ms.
+// Extending it to the small elementwise kernels was measured too and is slower (12.4 ms), so they keep plain launches.
+// URLG_PDL=0 launches everything with plain stream order.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+inline bool pdl_enabled() {
+  static const bool on = []() { const char* e = getenv("URLG_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 #define URLG_LAUNCH_CHECK()          \
   do {                               \

@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "tc_gemm.cuh"
 #include <cudaTypedefs.h>
+#include <cstdlib>
 #include <utility>
 #include <vector>
 
@@ -165,7 +166,10 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
   int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
   if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;
-  gemm_bf16_kernel<<<grid, kGemmThreads, gemm_smem_bytes(bn, g.split, g.stages, g.tma_out, g.tma_ref), st>>>(ta, tb, tal, tbl, to, tol, tr, trl, g);
+  // launched with programmatic stream serialization (see the kernel): back-to-back kernels overlap launch + set-up
+  // of the next with the tail of the previous (common.cuh)
+  URLG_CUDA(launch_pdl(gemm_bf16_kernel, dim3(grid), dim3(kGemmThreads), gemm_smem_bytes(bn, g.split, g.stages, g.tma_out, g.tma_ref),
+                       st, ta, tb, tal, tbl, to, tol, tr, trl, g));
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

@@ -131,6 +131,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // Programmatic dependent launch: the next kernel in the stream may start its own set-up (barriers, TMEM, descriptor
+  // prefetch) on SMs this grid has already left; nothing above touches global memory, everything below waits for
+  // the previous grid to have completed and flushed.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp == 0) {
     // ===== TMA producer =====
