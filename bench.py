@@ -298,6 +298,16 @@ def own_arm(a):
     done_h = torch.empty(n, dtype=torch.bool, pin_memory=True)
     h2d = sum(v[0].numel() * 4 for v in pin.values())
     d2h = n * 4 + n
+    # the host link alone: the same pinned frames copied back to back (floor of the e2e rollout = 24 frames / this rate)
+    torch.cuda.synchronize()
+    c0, c1 = ev(), ev()
+    c0.record()
+    for r in range(2 * POOL_FRAMES):
+        for k, v in pin.items():
+            pool[k][r % POOL_FRAMES].copy_(v[r % POOL_FRAMES], non_blocking=True)
+    c1.record()
+    c1.synchronize()
+    h2d_gbs = h2d * 2 * POOL_FRAMES / (c0.elapsed_time(c1) * 1e-3) / 1e9
 
     def e2e_rollout():
         obs = env.get_observations()
@@ -347,18 +357,27 @@ def own_arm(a):
         for e_ in slot_free:
             e_.record(cur)
         frame_ready = [torch.cuda.Event() for _ in range(T)]
+        # rewards / dones of env step i are read back from their rollout-storage rows (written by that step's graph and
+        # not touched again during the rollout) on a third stream, so the read-back never stalls step i + 1
+        d2h_stream = torch.cuda.Stream(device=dev)
+        step_done = [torch.cuda.Event() for _ in range(T)]
+        st_ = alg.storage
+        rew_rows = torch.empty(T, n, dtype=torch.float, pin_memory=True)
+        done_rows = torch.empty(T, n, dtype=st_.dones.dtype, pin_memory=True)
         step_no = {"k": (int(env.gym.calls_base.item()) + env.gym.sim_calls) // D}
+
+        h2d_batch = [_lib.CopyBatch([(pool[key][f], v[f]) for key, v in pin.items()]) for f in range(POOL_FRAMES)]
+        d2h_batch = [_lib.CopyBatch([(rew_rows[i], st_.rewards[i]), (done_rows[i], st_.dones[i])]) for i in range(T)]
 
         def stage_frame(k, idx):
             f = k % POOL_FRAMES
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(slot_free[f])          # the last step that read this pool slot has finished
-                for key, v in pin.items():
-                    pool[key][f].copy_(v[f], non_blocking=True)
-                frame_ready[idx].record(copy_stream)
+            copy_stream.wait_event(slot_free[f])              # the last step that read this pool slot has finished
+            h2d_batch[f].enqueue(copy_stream)                 # one C call: root, dof x decimation, contact (, rigid body)
+            frame_ready[idx].record(copy_stream)
 
         def e2e_graph_rollout():
             k0 = step_no["k"]
+            cur.wait_stream(d2h_stream)                       # last rollout's read-backs are done with the storage rows
             stage_frame(k0, 0)
             with torch.inference_mode():
                 for i in range(T):
@@ -367,26 +386,75 @@ def own_arm(a):
                     cur.wait_event(frame_ready[i])
                     obs, cobs, rew, dones = sg.replay(i)
                     slot_free[(k0 + i) % POOL_FRAMES].record(cur)
-                    rew_h.copy_(rew, non_blocking=True)
-                    done_h.copy_(dones, non_blocking=True)
+                    step_done[i].record(cur)
+                    d2h_stream.wait_event(step_done[i])
+                    d2h_batch[i].enqueue(d2h_stream)
+            cur.wait_stream(d2h_stream)                       # the timed region ends after the last read-back
             step_no["k"] = k0 + T
             return obs, cobs
 
-        g_ms = []
-        for i in range(2 + min(a.steps, 5)):
-            barrier()
-            e0, e1 = ev(), ev()
-            e0.record()
-            _, cobs = e2e_graph_rollout()
-            e1.record()
-            e1.synchronize()
-            if i >= 2:
-                g_ms.append(e0.elapsed_time(e1))
-            finish(cobs)
-        t = torch.tensor([sum(g_ms) / len(g_ms)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_roll_ms, e2e_mode = t.item(), "one CUDA graph per env step (StepGraphs), next frame's H2D overlapped on a copy stream"
+        def timed(fn):
+            ms = []
+            for i in range(2 + min(a.steps, 5)):
+                barrier()
+                e0, e1 = ev(), ev()
+                e0.record()
+                _, cobs = fn()
+                e1.record()
+                e1.synchronize()
+                if i >= 2:
+                    ms.append(e0.elapsed_time(e1))
+                finish(cobs)
+            t = torch.tensor([sum(ms) / len(ms)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+
+        e2e_steps_ms = timed(e2e_graph_rollout)
+        e2e_roll_ms = e2e_steps_ms
+        e2e_mode = ("one CUDA graph per env step (StepGraphs), next frame's H2D overlapped on a copy stream, per-step "
+                    "reward/done read-back on a third stream")
+
+        # ---- e2e, whole rollout as ONE graph with the host traffic inside it (RolloutGraph.capture hooks): the upload
+        #      of frame t + 1 is a memcpy node on a forked branch beside the kernels of step t, the read-back of step t's
+        #      rewards / dones a node on a second branch.  Needs the frame ring to divide the rollout (24 % 8 == 0), so
+        #      that the slot a captured step reads is the same on every replay.
+        e2e_one_ms = None
+        if T % POOL_FRAMES == 0:
+            k0 = step_no["k"]
+            fr, sd = [torch.cuda.Event() for _ in range(T)], [torch.cuda.Event() for _ in range(T)]
+
+            def pre_step(i):
+                c = torch.cuda.current_stream()
+                if i == 0:
+                    copy_stream.wait_stream(c)                # fork
+                    d2h_stream.wait_stream(c)
+                    h2d_batch[k0 % POOL_FRAMES].enqueue(copy_stream)
+                    fr[0].record(copy_stream)
+                if i + 1 < T:
+                    if i + 1 >= POOL_FRAMES:                  # ring slot (i + 1) % 8 was last read by step i + 1 - 8:
+                        copy_stream.wait_event(sd[i + 1 - POOL_FRAMES])   # uploads run up to a ring ahead of the compute
+                    h2d_batch[(k0 + i + 1) % POOL_FRAMES].enqueue(copy_stream)
+                    fr[i + 1].record(copy_stream)
+                c.wait_event(fr[i])
+
+            def post_step(i):
+                c = torch.cuda.current_stream()
+                sd[i].record(c)
+                d2h_stream.wait_event(sd[i])
+                d2h_batch[i].enqueue(d2h_stream)
+
+            def join():
+                c = torch.cuda.current_stream()
+                c.wait_stream(copy_stream)
+                c.wait_stream(d2h_stream)
+
+            g1 = RolloutGraph(runner).capture(pre_step, post_step, join)
+            e2e_one_ms = timed(g1.replay)
+            if e2e_one_ms < e2e_roll_ms:
+                e2e_roll_ms = e2e_one_ms
+                e2e_mode = ("ONE CUDA graph per 24-step rollout (RolloutGraph with capture hooks): per-step H2D frame "
+                            "uploads and reward/done read-backs are memcpy nodes on forked branches of the same graph")
 
     # ---- roofline of the dominant kernel.  By the ncu launch list (profiles/) the tcgen05 GEMM is ~70% of the GPU time
     #      of a step, so `roofline` is the GEMM against the tensor peak: CUDA events around every GEMM launch of one
@@ -528,7 +596,8 @@ def own_arm(a):
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": n * T * world / (e2e_roll_ms * 1e-3), "unit": "env-steps/s",
                         "h2d_bytes_per_step": int(h2d * T), "d2h_bytes_per_step": int(d2h * T), "rollout_ms": e2e_roll_ms,
-                        "launch": e2e_mode,
+                        "launch": e2e_mode, "step_graphs_ms": e2e_steps_ms if use_graph else None,
+                        "one_graph_ms": e2e_one_ms if use_graph else None, "h2d_link_gbs": h2d_gbs, "h2d_floor_ms": h2d * T / h2d_gbs / 1e6,
                         "eager": {"value": n * T * world / (e2e_eager_ms * 1e-3), "rollout_ms": e2e_eager_ms,
                                   "launch": "eager PPO.act / LeggedRobot.step / PPO.process_env_step, ~40 launches per env step"},
                         "note": "public API with HOST physics frames: per env step the frame (root, dof x decimation, contact) "

@@ -151,6 +151,11 @@ int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const i
 int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num_frames, int64_t substeps,
                        int per_substep, const int64_t* calls_base, int64_t calls_offset, void* stream);
 
+/* n asynchronous copies (cudaMemcpyDefault) enqueued on `stream` in one call: the per-env-step host <-> device traffic
+ * of a physics engine that lives on the host (state frame in, rewards / dones out) without n trips through the caller's
+ * language runtime.  Host pointers should be pinned. */
+int urlg_copy_batch(void* const* dst, const void* const* src, const int64_t* bytes, int n, void* stream);
+
 /* Philox4x32-10 uniforms exactly as the kernels draw them (for tests): out[N,num_slots]. */
 int urlg_philox_uniform(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
                         uint32_t stream_id, int64_t env_offset, int64_t step, void* stream);

@@ -113,3 +113,62 @@ def test_update_graph_equals_eager(task):
             # split-K / bias-gradient atomics make the two runs differ in the last bits of a gradient sum
             np.testing.assert_allclose(p.detach().cpu().numpy(), q.detach().cpu().numpy(), rtol=0, atol=2e-4, err_msg=k)
     assert rb.alg._update_graph is not None
+
+
+def test_rollout_graph_with_host_traffic_hooks():
+    """RolloutGraph.capture(pre_step, post_step, epilogue): frame uploads from pinned host memory and per-step reward /
+    done read-backs recorded on forked streams inside the capture (one launch per rollout, bench.py's e2e path) leave
+    storage bit-identical to the eager loop, and the host rows equal the storage rows."""
+    from unitree_rl_gym_b200 import _lib
+    from unitree_rl_gym_b200.rsl_rl.runners.rollout_graph import RolloutGraph
+    n = 192
+    ra, rb = make_runner("go2", n), make_runner("go2", n)
+    T = ra.num_steps_per_env
+    perm = torch.randperm(n * T, generator=torch.Generator().manual_seed(9))
+    for r in (ra, rb):
+        finish(r, eager_rollout(r), perm)
+    rb.alg.engine.flat.copy_(ra.alg.engine.flat)
+    rb.alg.engine.sync_weights()
+    pool = rb.env.gym.frames
+    nf = rb.env.gym.num_frames
+    pin = {k: v.cpu().pin_memory() for k, v in pool.items() if v is not None}
+    up = [_lib.CopyBatch([(pool[k][f], pin[k][f]) for k in pin]) for f in range(nf)]
+    st = rb.alg.storage
+    rew_rows = torch.zeros(T, n, pin_memory=True)
+    done_rows = torch.zeros(T, n, dtype=st.dones.dtype, pin_memory=True)
+    down = [_lib.CopyBatch([(rew_rows[i], st.rewards[i]), (done_rows[i], st.dones[i])]) for i in range(T)]
+    side, back = torch.cuda.Stream(), torch.cuda.Stream()
+    done_ev = [torch.cuda.Event() for _ in range(T)]
+    up_ev = [torch.cuda.Event() for _ in range(T)]
+    k0 = (int(rb.env.gym.calls_base.item()) + rb.env.gym.sim_calls) // rb.env.cfg.control.decimation
+
+    def pre(i):
+        c = torch.cuda.current_stream()
+        if i == 0:
+            side.wait_stream(c)
+            back.wait_stream(c)
+        else:
+            side.wait_event(done_ev[i - 1])
+        up[(k0 + i) % nf].enqueue(side)                   # same bytes the pool already holds: only ordering is at stake
+        up_ev[i].record(side)
+        c.wait_event(up_ev[i])
+
+    def post(i):
+        c = torch.cuda.current_stream()
+        done_ev[i].record(c)
+        back.wait_event(done_ev[i])
+        down[i].enqueue(back)
+
+    def join():
+        c = torch.cuda.current_stream()
+        c.wait_stream(side)
+        c.wait_stream(back)
+
+    g = RolloutGraph(rb).capture(pre, post, join)
+    ca = eager_rollout(ra)
+    cb = g.replay()[1]
+    torch.cuda.synchronize()
+    storage_equal(ra.alg.storage, rb.alg.storage)
+    assert torch.equal(ca, cb)
+    assert torch.equal(rew_rows, ra.alg.storage.rewards.view(T, n).cpu())
+    assert torch.equal(done_rows, ra.alg.storage.dones.view(T, n).cpu())

@@ -126,6 +126,7 @@ SIGNATURES = {
     "urlg_pd_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "urlg_post_physics": (C.c_int, [C.c_void_p, _I64P, C.c_int64, C.c_int, C.c_void_p]),
     "urlg_env_reset_idx": (C.c_int, [C.c_void_p, _I64P, C.c_int64, _I64P, C.c_int64, C.c_void_p]),
+    "urlg_copy_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
                                      C.c_int64, C.c_void_p]),
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
@@ -197,6 +198,25 @@ def ptr(t):
     if not t.is_cuda:
         raise RuntimeError("urlg_b200: the hot path runs on CUDA tensors only (no CPU fallback)")
     return C.c_void_p(t.data_ptr())
+
+
+class CopyBatch:
+    """A fixed list of (dst, src) tensor copies enqueued on a stream by ONE urlg_copy_batch call (host tensors pinned):
+    the per-env-step frame upload / reward read-back of a host-side physics engine without a Python call per tensor."""
+
+    def __init__(self, pairs):
+        n = len(pairs)
+        for d, s_ in pairs:
+            if d.numel() * d.element_size() != s_.numel() * s_.element_size() or not (d.is_contiguous() and s_.is_contiguous()):
+                raise ValueError("CopyBatch: each pair must be two contiguous tensors of equal byte size")
+        self.n = n
+        self.dst = (C.c_void_p * n)(*[d.data_ptr() for d, _ in pairs])
+        self.src = (C.c_void_p * n)(*[s_.data_ptr() for _, s_ in pairs])
+        self.bytes = (C.c_int64 * n)(*[d.numel() * d.element_size() for d, _ in pairs])
+        self.keep = pairs
+
+    def enqueue(self, stream):
+        check(lib().urlg_copy_batch(self.dst, self.src, self.bytes, self.n, C.c_void_p(stream.cuda_stream)))
 
 
 def cur_stream():

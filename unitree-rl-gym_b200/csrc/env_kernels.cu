@@ -894,6 +894,15 @@ extern "C" int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t
   return URLG_OK;
 }
 
+extern "C" int urlg_copy_batch(void* const* dst, const void* const* src, const int64_t* bytes, int n, void* stream) {
+  if (n < 0 || (n > 0 && (!dst || !src || !bytes))) return fail(URLG_EINVAL, "urlg_copy_batch: bad argument");
+  for (int i = 0; i < n; ++i) {
+    if (bytes[i] < 0 || (bytes[i] > 0 && (!dst[i] || !src[i]))) return fail(URLG_EINVAL, "urlg_copy_batch: bad entry %d", i);
+    if (bytes[i]) URLG_CUDA(cudaMemcpyAsync(dst[i], src[i], (size_t)bytes[i], cudaMemcpyDefault, (cudaStream_t)stream));
+  }
+  return URLG_OK;
+}
+
 extern "C" int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num_frames, int64_t substeps,
                                   int per_substep, const int64_t* calls_base, int64_t calls_offset, void* stream) {
   if (!dst || !pool || elems <= 0 || num_frames <= 0 || substeps <= 0)

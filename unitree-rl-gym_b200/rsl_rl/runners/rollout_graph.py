@@ -27,16 +27,24 @@ class RolloutGraph:
         return (all(hasattr(env, m) for m in ("begin_relative", "advance_base", "end_relative"))
                 and runner.num_steps_per_env % 2 == 0 and torch.device(runner.device).type == "cuda")
 
-    def _loop(self, obs, critic_obs):
+    def _loop(self, obs, critic_obs, pre_step=None, post_step=None):
         env, alg = self.runner.env, self.runner.alg
-        for _ in range(self.runner.num_steps_per_env):
+        for t in range(self.runner.num_steps_per_env):
+            if pre_step is not None:
+                pre_step(t)
             actions = alg.act(obs, critic_obs)
             obs, privileged_obs, rewards, dones, infos = env.step(actions)
             critic_obs = privileged_obs if privileged_obs is not None else obs
             alg.process_env_step(rewards, dones, infos)
+            if post_step is not None:
+                post_step(t)
         return obs, critic_obs
 
-    def capture(self):
+    def capture(self, pre_step=None, post_step=None, epilogue=None):
+        """pre_step(t) / post_step(t) / epilogue() run INSIDE the capture, around env step t and after the last one: a
+        caller whose physics state lives elsewhere records its own stream-ordered work there (e.g. the upload of step
+        t + 1's state frame on a forked copy stream, the read-back of step t's rewards), so the whole rollout including
+        that traffic stays one graph launch.  Forked streams must be joined back (in `epilogue`) before capture ends."""
         from ... import _lib
         r = self.runner
         env, alg = r.env, r.alg
@@ -54,9 +62,11 @@ class RolloutGraph:
         g = torch.cuda.CUDAGraph()
         n0 = _lib.lib().urlg_launch_count()
         with torch.inference_mode(), torch.cuda.graph(g):
-            obs_out, critic_out = self._loop(obs, critic_obs)
+            obs_out, critic_out = self._loop(obs, critic_obs, pre_step, post_step)
             env.advance_base()
             alg.advance_base()
+            if epilogue is not None:
+                epilogue()
         self.launches = _lib.lib().urlg_launch_count() - n0
         env.end_relative()
         alg.end_relative()
