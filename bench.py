@@ -464,8 +464,10 @@ def own_arm(a):
     extra = {}
     import ctypes as C
 
+    GEMM_REPEAT = 8                        # launches per event bracket: see include/urlg_b200.h (results are discarded)
+
     def gemm_timed(fn):
-        _lib.check(L.urlg_gemm_timing(1))
+        _lib.check(L.urlg_gemm_timing(GEMM_REPEAT))
         out = fn()
         torch.cuda.synchronize()
         ms, cnt, fl, by = C.c_double(), C.c_int64(), C.c_double(), C.c_double()
@@ -497,7 +499,10 @@ def own_arm(a):
                 "ridge_flop_per_byte": tf_sus * 1e12 / (hbm * 1e9), "peak_source": peak_src,
                 "rollout": {"launches": int(n_r), "ms": ms_r, "tflops": fl_r / (ms_r * 1e-3) / 1e12, "gbs": by_r / (ms_r * 1e-3) / 1e9},
                 "update": {"launches": int(n_u), "ms": ms_u, "tflops": fl_u / (ms_u * 1e-3) / 1e12, "gbs": by_u / (ms_u * 1e-3) / 1e9},
-                "note": "summed over every GEMM launch of one eager PPO iteration (CUDA events around each launch); algorithmic "
+                "launches_per_event_bracket": GEMM_REPEAT,
+                "note": "summed over every GEMM launch of one eager PPO iteration; each launch is issued 8 times back to back between "
+                        "two CUDA events on its stream and the bracket divided by 8 (one launch on an idle GPU would add event + "
+                        "launch latency to a 10-20 us kernel); algorithmic "
                         "flops 2*M*N*K counted once (split-bf16 issues 3 MMAs per product), algorithmic bytes = every operand "
                         "and output element once (bf16 hi+lo pairs, fp32 outputs); the shapes (K=48..512, N=1..512) sit far "
                         "below the ridge point, so HBM is the roof"}

@@ -191,7 +191,10 @@ typedef struct urlg_gemm_desc {
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 /* Measurement hook (bench.py roofline): while enabled, every GEMM launch of this library is bracketed by CUDA events on
  * its stream (do not enable under graph capture); read returns the summed duration, launch count, 2*M*N*K flops and the
- * algorithmic HBM bytes (every operand and output element once). */
+ * algorithmic HBM bytes (every operand and output element once).  enable = R > 1 issues every GEMM R times back to back
+ * inside its bracket and divides the bracket by R: the per-launch duration of a busy stream instead of one launch on an
+ * idle GPU (event + launch latency would otherwise be a third of a 10-20 us kernel); accumulating (atomic) outputs are
+ * then R times too large, so the results of such a pass are for timing only. */
 int urlg_gemm_timing(int enable);
 int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops, double* bytes);
 

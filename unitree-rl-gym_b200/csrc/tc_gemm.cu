@@ -47,6 +47,7 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
 // Optional per-launch timing (bench.py's roofline leg): CUDA events recorded on the launching stream around every
 // GEMM launch while enabled (never under graph capture), summed on read.
 static bool g_timing = false;
+static int g_repeat = 1;        // launches per event bracket (urlg_gemm_timing(R)); the bracket's time is divided by R
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
 static double g_flops = 0.0, g_bytes = 0.0;
 static size_t g_used = 0;
@@ -62,7 +63,8 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
     g_events.emplace_back(a, b);
   }
   URLG_CUDA(cudaEventRecord(g_events[g_used].first, st));
-  const int rc = launch_gemm_impl(d, st);
+  int rc = URLG_OK;
+  for (int r = 0; r < g_repeat && rc == URLG_OK; ++r) rc = launch_gemm_impl(d, st);
   URLG_CUDA(cudaEventRecord(g_events[g_used].second, st));
   ++g_used;
   if (d) {
@@ -180,6 +182,7 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
 extern "C" int urlg_gemm_timing(int enable) {
   using namespace urlg::tc;
   g_timing = enable != 0;
+  g_repeat = enable > 1 ? enable : 1;
   if (g_timing) { g_used = 0; g_flops = 0.0; g_bytes = 0.0; }
   return URLG_OK;
 }
@@ -191,7 +194,7 @@ extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double
     URLG_CUDA(cudaEventSynchronize(g_events[i].second));
     float t = 0.0f;
     URLG_CUDA(cudaEventElapsedTime(&t, g_events[i].first, g_events[i].second));
-    ms += t;
+    ms += t / g_repeat;
   }
   if (total_ms) *total_ms = ms;
   if (launches) *launches = (int64_t)g_used;
