@@ -55,10 +55,13 @@ class ActorCriticRecurrent(ActorCritic):
         H = self.memory_a.rnn.hidden_size
         dev = self.std.device
         if self._hidden is None or self._hidden.shape[1] != num_rows or self._hidden.device != dev:
-            self._hidden = torch.zeros(4, num_rows, H, device=dev)
-            h = self._hidden
-            self.memory_a.hidden_states = (h[0].unsqueeze(0), h[1].unsqueeze(0))
-            self.memory_c.hidden_states = (h[2].unsqueeze(0), h[3].unsqueeze(0))
+            # a normal tensor even when the first call comes from inside torch.inference_mode() (the runner's rollout):
+            # reset(dones) is also called from plain code (play.py-style loops) and must be able to write in place
+            with torch.inference_mode(False):
+                self._hidden = torch.zeros(4, num_rows, H, device=dev)
+                h = self._hidden
+                self.memory_a.hidden_states = (h[0].unsqueeze(0), h[1].unsqueeze(0))
+                self.memory_c.hidden_states = (h[2].unsqueeze(0), h[3].unsqueeze(0))
         return self._hidden
 
     def reset(self, dones=None):
