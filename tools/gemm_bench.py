@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--rows", type=int, default=24576)
     ap.add_argument("--only", default="", help="comma-separated shape names; with --profile: 3 eager launches each (for ncu)")
     ap.add_argument("--profile", action="store_true")
+    ap.add_argument("--waves", type=int, default=1, help="split-K weight gradients: tiles x splits <= waves x 148")
     a = ap.parse_args()
     R = a.rows
     L = _lib.lib()
@@ -39,8 +40,9 @@ def main():
     for l in (3, 2, 1, 0):
         nout, nin = dims[l + 1], dims[l]
         bn = min(256, rup(nin, 64))
-        tiles = ((nout + 127) // 128) * ((nin + bn - 1) // bn)
-        splits = max(1, min((2 * 148 + tiles - 1) // tiles, ((R + 63) // 64) // 4))
+        bn_eff = min(bn, 128)                                   # split-bf16 tiles are at most 128 wide
+        tiles = ((nout + 127) // 128) * ((nin + bn_eff - 1) // bn_eff)
+        splits = max(1, min((a.waves * 148) // tiles, ((R + 63) // 64) // 4))
         shapes.append((f"wgrad{l}", nout, nin, R, 1, 1, 2, splits, bn, "atomic f32"))
     only = set(a.only.split(",")) if a.only else None
     for name, M, N, K, a_mn, b_mn, flags, splits, bn, epi in shapes:
