@@ -44,6 +44,8 @@ def main():
         tiles = ((nout + 127) // 128) * ((nin + bn_eff - 1) // bn_eff)
         splits = max(1, min((a.waves * 148) // tiles, ((R + 63) // 64) // 4))
         shapes.append((f"wgrad{l}", nout, nin, R, 1, 1, 2, splits, bn, "atomic f32"))
+    # launch floor: one tile, one k-block
+    shapes.append(("floor", 128, 64, 64, 0, 0, 1, 1, 0, "bias+elu+bf16"))
     only = set(a.only.split(",")) if a.only else None
     for name, M, N, K, a_mn, b_mn, flags, splits, bn, epi in shapes:
         if only and name not in only:

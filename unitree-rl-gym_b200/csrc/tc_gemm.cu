@@ -52,10 +52,11 @@ static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
 static double g_flops = 0.0, g_bytes = 0.0;
 static size_t g_used = 0;
 
-int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st);
+int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
 
-int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
-  if (!g_timing) return launch_gemm_impl(d, st);
+// n independent problems in one launch (n <= kMaxGroup); see GroupArgs in tc_gemm.cuh.
+int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
+  if (!g_timing) return launch_group_impl(ds, n, st);
   if (g_used == g_events.size()) {
     cudaEvent_t a, b;
     URLG_CUDA(cudaEventCreate(&a));
@@ -64,10 +65,12 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   }
   URLG_CUDA(cudaEventRecord(g_events[g_used].first, st));
   int rc = URLG_OK;
-  for (int r = 0; r < g_repeat && rc == URLG_OK; ++r) rc = launch_gemm_impl(d, st);
+  for (int r = 0; r < g_repeat && rc == URLG_OK; ++r) rc = launch_group_impl(ds, n, st);
   URLG_CUDA(cudaEventRecord(g_events[g_used].second, st));
   ++g_used;
-  if (d) {
+  for (int i = 0; ds && i < n; ++i) {
+    const urlg_gemm_desc* d = ds[i];
+    if (!d) continue;
     g_flops += 2.0 * d->M * d->N * d->K;
     // algorithmic HBM bytes: each operand element and each output element once (bf16, x2 when split into hi+lo)
     const double parts = (d->A_lo && d->B_lo) ? 2.0 : 1.0, mn = (double)d->M * d->N;
@@ -77,9 +80,13 @@ int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) {
   return rc;
 }
 
-int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
+int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) { return launch_gemm_group(&d, 1, st); }
+
+// Fills one problem's kernel arguments and its 8 tensor maps.
+static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm) {
   if (!d || !d->A || !d->B || d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(URLG_EINVAL, "urlg_tc_gemm: bad argument");
-  GemmArgs g;
+  CUtensorMap &ta = tm[kTmA], &tb = tm[kTmB], &tal = tm[kTmAlo], &tbl = tm[kTmBlo], &to = tm[kTmO], &tol = tm[kTmOlo],
+              &tr = tm[kTmR], &trl = tm[kTmRlo];
   g.M = d->M; g.N = d->N; g.K = d->K;
   g.a_mn = d->a_mn ? 1 : 0; g.b_mn = d->b_mn ? 1 : 0;
   int bn = d->block_n;
@@ -116,7 +123,6 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   g.tma_out = (g.out_bf16 && (((uintptr_t)g.out_bf16 | (uintptr_t)g.out_lo) & 15) == 0 && (g.ld_bf16 & 7) == 0) ? 1 : 0;
   g.tma_ref = (g.tma_out && g.dact_ref && (((uintptr_t)g.dact_ref | (uintptr_t)g.dact_lo) & 15) == 0 && (g.ld_ref & 7) == 0) ? 1 : 0;
   g.stages = gemm_stages_for(bn, g.split, g.tma_out, g.tma_ref);
-  CUtensorMap ta, tb, tal, tbl, to, tol, tr, trl;
   int rc;
   if (g.tma_out) {
     rc = make_tmap_bf16(&to, g.out_bf16, d->N, d->M, g.ld_bf16, 16, 32, CU_TENSOR_MAP_SWIZZLE_32B);
@@ -157,21 +163,47 @@ int launch_gemm_impl(const urlg_gemm_desc* d, cudaStream_t st) {
   } else {
     tr = ta; trl = ta;
   }
+  g.tiles_m = (d->M + kBlockM - 1) / kBlockM;
+  g.tiles_n = (d->N + bn - 1) / bn;
+  g.splits = splits;
+  return URLG_OK;
+}
+
+int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
+  if (!ds || n < 1 || n > kMaxGroup) return fail(URLG_EINVAL, "urlg_tc_gemm: 1..%d problems per launch", kMaxGroup);
+  static GroupArgs P;                       // ~5 KB of kernel parameters, copied at launch
+  P.num = n;
+  int64_t tiles = 0;
+  int bn_max = 0, max_ctas = 0;
+  P.any_tma_out = P.any_tma_ref = 0;
+  for (int i = 0; i < n; ++i) {
+    if (int rc = build_problem(ds[i], P.g[i], P.tm[i])) return rc;
+    const GemmArgs& g = P.g[i];
+    if (i && g.split != P.g[0].split) return fail(URLG_EINVAL, "urlg_tc_gemm: grouped problems must share the operand mode (hi+lo or plain)");
+    tiles += (int64_t)g.tiles_m * g.tiles_n * g.splits;
+    if (tiles > 0x7fffffff) return fail(URLG_EINVAL, "urlg_tc_gemm: too many tiles");
+    P.tile_end[i] = (int)tiles;
+    bn_max = g.block_n > bn_max ? g.block_n : bn_max;
+    P.any_tma_out |= g.tma_out;
+    P.any_tma_ref |= g.tma_ref;
+    if (ds[i]->max_ctas > 0 && (max_ctas == 0 || ds[i]->max_ctas < max_ctas)) max_ctas = ds[i]->max_ctas;
+  }
+  for (int i = n; i < kMaxGroup; ++i) P.tile_end[i] = (int)tiles;
+  P.split = P.g[0].split;
+  P.stages = gemm_stages_for(bn_max, P.split, P.any_tma_out, P.any_tma_ref);
+  P.bytes_b_max = stage_bytes_b(bn_max);
+  P.acc_cols = (int)tmem_cols_for(bn_max);
   static bool attr_set = false;
   if (!attr_set) {
     URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  g.tiles_m = (d->M + kBlockM - 1) / kBlockM;
-  g.tiles_n = (d->N + bn - 1) / bn;
-  g.splits = splits;
-  const int64_t tiles = (int64_t)g.tiles_m * g.tiles_n * splits;
   int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
-  if (d->max_ctas > 0 && grid > d->max_ctas) grid = d->max_ctas;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   // launched with programmatic stream serialization (see the kernel): back-to-back kernels overlap launch + set-up
   // of the next with the tail of the previous (common.cuh)
-  URLG_CUDA(launch_pdl(gemm_bf16_kernel, dim3(grid), dim3(kGemmThreads), gemm_smem_bytes(bn, g.split, g.stages, g.tma_out, g.tma_ref),
-                       st, ta, tb, tal, tbl, to, tol, tr, trl, g));
+  URLG_CUDA(launch_pdl(gemm_bf16_kernel, dim3(grid), dim3(kGemmThreads),
+                       gemm_smem_bytes(bn_max, P.split, P.stages, P.any_tma_out, P.any_tma_ref), st, P));
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

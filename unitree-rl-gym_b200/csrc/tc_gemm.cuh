@@ -64,45 +64,52 @@ __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : ex2_ftz(x
 __device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
-// Tile coordinates of a persistent CTA, advanced by gridDim.x tiles per step without divisions.
-struct TileWalk {
-  int tx, ty, tz, dx, dy, dz, tm, tn;
-  __device__ __forceinline__ void init(int tile, int step, int tiles_m, int tiles_n) {
-    tm = tiles_m; tn = tiles_n;
-    tx = tile % tm; const int r = tile / tm; ty = r % tn; tz = r / tn;
-    dx = step % tm; const int q = step / tm; dy = q % tn; dz = q / tn;
-  }
-  __device__ __forceinline__ void next() {
-    tx += dx;
-    int carry = 0;
-    if (tx >= tm) { tx -= tm; carry = 1; }
-    ty += dy + carry;
-    carry = 0;
-    if (ty >= tn) { ty -= tn; carry = 1; }
-    tz += dz + carry;
-  }
+// A launch carries up to kMaxGroup independent problems (e.g. the same layer of the actor and of the critic, or a
+// layer's dgrad and wgrad): their tiles form one persistent tile space, so small problems share a launch's fixed cost
+// (~4 us: launch, TMEM allocation, descriptor fetch, pipeline fill and drain) and fill each other's wave tails.
+constexpr int kMaxGroup = 4;
+enum { kTmA = 0, kTmB, kTmAlo, kTmBlo, kTmO, kTmOlo, kTmR, kTmRlo, kTmCount };
+struct GroupArgs {
+  CUtensorMap tm[kMaxGroup][kTmCount];
+  GemmArgs g[kMaxGroup];
+  int tile_end[kMaxGroup];   // exclusive prefix sums of the problems' tile counts
+  int num;
+  int stages, split;         // common smem pipeline depth / operand mode
+  int bytes_b_max;           // stage stride of the B ring (largest block_n of the group)
+  int acc_cols;              // TMEM columns per accumulator buffer (largest block_n of the group)
+  int any_tma_out, any_tma_ref;
 };
+struct TileRef { int p, tx, ty, tz; };
+__device__ __forceinline__ TileRef locate(const GroupArgs& P, int tile) {
+  TileRef t;
+  t.p = 0;
+  while (t.p + 1 < P.num && tile >= P.tile_end[t.p]) ++t.p;
+  const int local = tile - (t.p ? P.tile_end[t.p - 1] : 0);
+  const GemmArgs& g = P.g[t.p];
+  t.tx = local % g.tiles_m;
+  const int r = local / g.tiles_m;
+  t.ty = r % g.tiles_n;
+  t.tz = r / g.tiles_n;
+  return t;
+}
 
 // Persistent kernel: each CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The accumulator is double
 // buffered in TMEM (2 x tmem_cols_for(block_n) columns), so the MMAs of tile i+1 run under the epilogue of tile i;
 // the epilogue (the expensive part for these skinny GEMMs: bias, ELU / ELU', hi+lo split, column sums) is spread
 // over 16 warps = 4 per scheduler.
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmAlo, const __grid_constant__ CUtensorMap tmBlo,
-                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmOlo,
-                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmRlo, const GemmArgs g) {
+gemm_bf16_kernel(const __grid_constant__ GroupArgs P) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int bytes_a = stage_bytes_a(), bytes_b = stage_bytes_b(g.block_n);
-  const int kStages = g.stages;
+  const int bytes_a = stage_bytes_a(), bytes_b = P.bytes_b_max;         // ring strides; a tile loads its own block_n rows
+  const int kStages = P.stages;
   // layout: A[stages] | B[stages] | (split) Alo[stages] | Blo[stages] | (tma_out) epilogue staging | barriers
   const uint32_t sA = base, sB = base + kStages * bytes_a;
-  const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (g.split ? kStages * bytes_a : 0);
-  const uint32_t sEpi = sBlo + (g.split ? kStages * bytes_b : 0);           // 1024-byte aligned (stage sizes are 8 KB multiples)
-  const uint32_t epi_stride = g.tma_ref ? 2 * kEpiStageBytes : kEpiStageBytes;
-  const uint32_t bars = sEpi + (g.tma_out ? kEpiWarps * epi_stride : 0);
+  const uint32_t sAlo = sB + kStages * bytes_b, sBlo = sAlo + (P.split ? kStages * bytes_a : 0);
+  const uint32_t sEpi = sBlo + (P.split ? kStages * bytes_b : 0);           // 1024-byte aligned (stage sizes are 8 KB multiples)
+  const uint32_t epi_stride = P.any_tma_ref ? 2 * kEpiStageBytes : kEpiStageBytes;
+  const uint32_t bars = sEpi + (P.any_tma_out ? kEpiWarps * epi_stride : 0);
   // full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2], tmem_ptr
   const uint32_t full0 = bars, empty0 = bars + 8 * kMaxStages, tfull0 = bars + 16 * kMaxStages;
   const uint32_t tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
@@ -111,16 +118,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t acc_stride = tmem_cols_for(g.block_n);
+  const uint32_t acc_stride = (uint32_t)P.acc_cols;
   const uint32_t ncols = 2 * acc_stride;
-  const int num_tiles = g.tiles_m * g.tiles_n * g.splits;
+  const int num_tiles = P.tile_end[P.num - 1];
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    if (g.split) { tma_prefetch_desc(&tmAlo); tma_prefetch_desc(&tmBlo); }
-    if (g.tma_out) { tma_prefetch_desc(&tmO); if (g.out_lo) tma_prefetch_desc(&tmOlo); }
-    if (g.tma_ref) { tma_prefetch_desc(&tmR); if (g.dact_lo) tma_prefetch_desc(&tmRlo); }
+    for (int q = 0; q < P.num; ++q) {
+      const GemmArgs& g = P.g[q];
+      tma_prefetch_desc(&P.tm[q][kTmA]);
+      tma_prefetch_desc(&P.tm[q][kTmB]);
+      if (P.split) { tma_prefetch_desc(&P.tm[q][kTmAlo]); tma_prefetch_desc(&P.tm[q][kTmBlo]); }
+      if (g.tma_out) { tma_prefetch_desc(&P.tm[q][kTmO]); if (g.out_lo) tma_prefetch_desc(&P.tm[q][kTmOlo]); }
+      if (g.tma_ref) { tma_prefetch_desc(&P.tm[q][kTmR]); if (g.dact_lo) tma_prefetch_desc(&P.tm[q][kTmRlo]); }
+    }
     for (int w = 0; w < kEpiWarps; ++w) mbar_init(rbar0 + 8 * w, 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, kEpiWarps); }
@@ -141,9 +151,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===== TMA producer =====
     if (lane == 0) {
       int kbt = 0;                                                       // k-blocks issued so far (all tiles)
-      TileWalk tw;
-      tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, tw.next()) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const TileRef tw = locate(P, tile);
+        const GemmArgs& g = P.g[tw.p];
         const int m0 = tw.tx * kBlockM, n0 = tw.ty * g.block_n;
         const int k_begin = tw.tz * g.k_per_split;
         const int k_end = min(g.K, k_begin + g.k_per_split);
@@ -152,11 +162,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int s = kbt % kStages, ph = (kbt / kStages) & 1;
           mbar_wait(empty0 + 8 * s, ph ^ 1);
           const uint32_t full = full0 + 8 * s;
-          mbar_arrive_expect_tx(full, (g.split ? 2 : 1) * (bytes_a + bytes_b));
+          mbar_arrive_expect_tx(full, (P.split ? 2 : 1) * (bytes_a + stage_bytes_b(g.block_n)));
           const int k0 = k_begin + kb * kBlockK;
-          for (int part = 0; part <= g.split; ++part) {
-            const CUtensorMap* ta = part ? &tmAlo : &tmA;
-            const CUtensorMap* tb = part ? &tmBlo : &tmB;
+          for (int part = 0; part <= P.split; ++part) {
+            const CUtensorMap* ta = &P.tm[tw.p][part ? kTmAlo : kTmA];
+            const CUtensorMap* tb = &P.tm[tw.p][part ? kTmBlo : kTmB];
             const uint32_t a_dst = (part ? sAlo : sA) + s * bytes_a, b_dst = (part ? sBlo : sB) + s * bytes_b;
             if (!g.a_mn) {
               tma_load_2d(a_dst, ta, full, k0, m0);                        // box {64 k, 128 m}
@@ -176,13 +186,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(kBlockM, g.block_n, g.a_mn, g.b_mn);
-      const uint32_t a_lbo = g.a_mn ? 8192u : 16u, b_lbo = g.b_mn ? 8192u : 16u;
-      const uint32_t a_kstep = g.a_mn ? 2048u : 32u, b_kstep = g.b_mn ? 2048u : 32u;
       int kbt = 0, it = 0;
-      TileWalk tw;
-      tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it, tw.next()) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const TileRef tw = locate(P, tile);
+        const GemmArgs& g = P.g[tw.p];
+        const uint32_t idesc = make_idesc_bf16(kBlockM, g.block_n, g.a_mn, g.b_mn);
+        const uint32_t a_lbo = g.a_mn ? 8192u : 16u, b_lbo = g.b_mn ? 8192u : 16u;
+        const uint32_t a_kstep = g.a_mn ? 2048u : 32u, b_kstep = g.b_mn ? 2048u : 32u;
         const int k_begin = tw.tz * g.k_per_split;
         const int k_end = min(g.K, k_begin + g.k_per_split);
         const int num_kb = (k_end - k_begin + kBlockK - 1) / kBlockK;
@@ -201,7 +211,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint64_t ad = make_sdesc_sw128(a_src + k * a_kstep, a_lbo, 1024);
             const uint64_t bd = make_sdesc_sw128(b_src + k * b_kstep, b_lbo, 1024);
             umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
-            if (g.split) {
+            if (P.split) {
               const uint64_t ald = make_sdesc_sw128(al_src + k * a_kstep, a_lbo, 1024);
               const uint64_t bld = make_sdesc_sw128(bl_src + k * b_kstep, b_lbo, 1024);
               umma_bf16(tmem_d, ald, bd, idesc, 1u);
@@ -217,33 +227,40 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===== epilogue: TMEM -> registers -> global =====
     const int lg = warp & 3;                       // TMEM lane quarter this warp may access (warp id % 4)
     const int cg = (warp - 2) >> 2;                // column group 0..3: chunks cg, cg+4, ...
-    const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
     // this warp's staging chunk: row r (= lane) at 32 r bytes, its two 16-byte halves swapped when r & 4 (SWIZZLE_32B)
     const uint32_t stage_hi = sEpi + (uint32_t)(warp - 2) * epi_stride, stage_lo = stage_hi + 1024;
     const uint32_t ref_hi = stage_hi + kEpiStageBytes, ref_lo = ref_hi + 1024, rbar = rbar0 + 8 * (warp - 2);
     const uint32_t st_row = (uint32_t)lane * 32u, st_sw = (uint32_t)((lane >> 2) & 1) << 4;
     int it = 0;
-    TileWalk tw;
-    tw.init(blockIdx.x, gridDim.x, g.tiles_m, g.tiles_n);
-    // dact_ref prefetch cursor: walks this warp's valid chunks in processing order, one chunk ahead of the consumer
-    TileWalk pw = tw;
-    int ptile = blockIdx.x, pc = 16 * cg - 64;
+    // dact_ref prefetch cursor: walks this warp's valid chunks (of the problems that read a reference) in processing
+    // order, one chunk ahead of the consumer
+    int ptile = blockIdx.x, pc = -1;
     uint32_t ref_phase = 0;
     auto prefetch_ref = [&]() {
-      for (pc += 64;; pc = 16 * cg) {
+      for (;;) {
         if (ptile >= num_tiles) return;
-        if (pc < g.block_n && pw.ty * g.block_n + pc < g.N) break;
+        const TileRef pw = locate(P, ptile);
+        const GemmArgs& q = P.g[pw.p];
+        pc = pc < 0 ? 16 * cg : pc + 64;
+        if (q.tma_ref && pc < q.block_n && pw.ty * q.block_n + pc < q.N) {
+          if (lane == 0) {
+            mbar_arrive_expect_tx(rbar, q.dact_lo ? 2048u : 1024u);
+            tma_load_2d(ref_hi, &P.tm[pw.p][kTmR], rbar, pw.ty * q.block_n + pc, pw.tx * kBlockM + lg * 32);
+            if (q.dact_lo) tma_load_2d(ref_lo, &P.tm[pw.p][kTmRlo], rbar, pw.ty * q.block_n + pc, pw.tx * kBlockM + lg * 32);
+          }
+          return;
+        }
         ptile += gridDim.x;
-        pw.next();
-      }
-      if (lane == 0) {
-        mbar_arrive_expect_tx(rbar, g.dact_lo ? 2048u : 1024u);
-        tma_load_2d(ref_hi, &tmR, rbar, pw.ty * g.block_n + pc, pw.tx * kBlockM + lg * 32);
-        if (g.dact_lo) tma_load_2d(ref_lo, &tmRlo, rbar, pw.ty * g.block_n + pc, pw.tx * kBlockM + lg * 32);
+        pc = -1;
       }
     };
-    if (g.tma_ref) prefetch_ref();
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it, tw.next()) {
+    if (P.any_tma_ref) prefetch_ref();
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const TileRef tw = locate(P, tile);
+      const GemmArgs& g = P.g[tw.p];
+      const CUtensorMap* tmO = &P.tm[tw.p][kTmO];
+      const CUtensorMap* tmOlo = &P.tm[tw.p][kTmOlo];
+      const bool vec_bf16 = (g.ld_bf16 & 7) == 0, vec_f32 = (g.ld_f32 & 3) == 0, vec_ref = (g.ld_ref & 7) == 0;
       const int m0 = tw.tx * kBlockM, n0 = tw.ty * g.block_n;
       const int acc = it & 1;
       mbar_wait(tfull0 + 8 * acc, (it >> 1) & 1);
@@ -348,8 +365,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           fence_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmO, stage_hi, col0, m0 + lg * 32);
-            if (g.out_lo) tma_store_2d(&tmOlo, stage_lo, col0, m0 + lg * 32);
+            tma_store_2d(tmO, stage_hi, col0, m0 + lg * 32);
+            if (g.out_lo) tma_store_2d(tmOlo, stage_lo, col0, m0 + lg * 32);
             bulk_commit();
           }
         }
@@ -438,7 +455,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);     // this warp is done reading accumulator `acc`
     }
-    if (g.tma_out && lane == 0) bulk_wait_read0();       // staging must outlive the last stores' reads
+    if (P.any_tma_out && lane == 0) bulk_wait_read0();   // staging must outlive the last stores' reads
   }
   tc_fence_before();
   __syncthreads();
