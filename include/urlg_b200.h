@@ -189,6 +189,11 @@ typedef struct urlg_gemm_desc {
   int32_t max_ctas;               /* 0 = one persistent CTA per SM; else cap the grid (two GEMMs side by side on two streams) */
 } urlg_gemm_desc;
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
+/* n (1..4) independent problems in ONE launch: their tiles form one persistent tile space, so e.g. the same layer of the
+ * actor and of the critic, or a layer's data and weight gradients, share a launch's fixed cost (~4 us) and fill each
+ * other's wave tails.  All problems must use the same operand mode (hi+lo pairs or plain bf16); results are those of n
+ * separate urlg_tc_gemm calls. */
+int urlg_tc_gemm_group(const urlg_gemm_desc* descs, int n, void* stream);
 /* Measurement hook (bench.py roofline): while enabled, every GEMM launch of this library is bracketed by CUDA events on
  * its stream (do not enable under graph capture); read returns the summed duration, launch count, 2*M*N*K flops and the
  * algorithmic HBM bytes (every operand and output element once).  enable = R > 1 issues every GEMM R times back to back

@@ -130,6 +130,7 @@ SIGNATURES = {
     "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
                                      C.c_int64, C.c_void_p]),
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
+    "urlg_tc_gemm_group": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_void_p]),
     "urlg_gemm_timing": (C.c_int, [C.c_int]),
     "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                        C.POINTER(C.c_double)]),

@@ -80,5 +80,7 @@ inline void with_lo(const urlg_policy* p, urlg_gemm_desc& g) {
 int sync_weights(urlg_policy* p, cudaStream_t st);
 int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas = 0);
 int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);
+int mlp_forward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, cudaStream_t st);
+int mlp_backward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, bf16* dxa, bf16* dxc, cudaStream_t st);
 int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld, cudaStream_t st);
 }

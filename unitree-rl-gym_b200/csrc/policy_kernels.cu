@@ -7,7 +7,10 @@
 #include <new>
 
 namespace urlg {
-namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
+namespace tc {
+int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st);
+int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
+}
 
 // ---------------------------------------------------------------- workspace carving
 // bf16 slabs come from their own region so that, in split precision, the whole region can be duplicated
@@ -172,20 +175,40 @@ int sync_weights(urlg_policy* p, cudaStream_t st) {
 
 // ---------------------------------------------------------------- MLP forward (x already staged in n.x)
 // keep_hidden: activations stay in n.h[] (needed by the backward pass); the rollout reuses the same slabs.
-int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas) {
+static urlg_gemm_desc forward_desc(urlg_policy* p, NetWs& n, int l, int64_t rows, int max_ctas) {
   const int L = n.d.num_layers;
-  for (int l = 0; l < L; ++l) {
-    urlg_gemm_desc g = {};
-    g.A = l == 0 ? (const void*)n.x : (const void*)n.h[l];
-    g.lda = l == 0 ? n.kpad[0] : n.d.dims[l];
-    g.B = n.w[l]; g.ldb = n.kpad[l];
-    g.M = (int)rows; g.N = n.d.dims[l + 1]; g.K = n.kpad[l];
-    g.bias = p->params + n.d.b_off[l];
-    if (l + 1 < L) { g.out_bf16 = n.h[l + 1]; g.ld_bf16 = n.d.dims[l + 1]; g.flags = URLG_GEMM_ELU; }
-    else { g.out_f32 = n.out; g.ld_f32 = n.d.dims[L]; }
-    g.max_ctas = max_ctas;
-    with_lo(p, g);
+  urlg_gemm_desc g = {};
+  g.A = l == 0 ? (const void*)n.x : (const void*)n.h[l];
+  g.lda = l == 0 ? n.kpad[0] : n.d.dims[l];
+  g.B = n.w[l]; g.ldb = n.kpad[l];
+  g.M = (int)rows; g.N = n.d.dims[l + 1]; g.K = n.kpad[l];
+  g.bias = p->params + n.d.b_off[l];
+  if (l + 1 < L) { g.out_bf16 = n.h[l + 1]; g.ld_bf16 = n.d.dims[l + 1]; g.flags = URLG_GEMM_ELU; }
+  else { g.out_f32 = n.out; g.ld_f32 = n.d.dims[L]; }
+  g.max_ctas = max_ctas;
+  with_lo(p, g);
+  return g;
+}
+
+int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas) {
+  for (int l = 0; l < n.d.num_layers; ++l) {
+    const urlg_gemm_desc g = forward_desc(p, n, l, rows, max_ctas);
     if (int rc = tc::launch_gemm(&g, st)) return rc;
+  }
+  return URLG_OK;
+}
+
+// Actor and critic side by side: layer l of both networks is ONE launch (two problems in the GEMM's tile space), so
+// a forward of both is max(La, Lc) launches instead of La + Lc; the ~4 us fixed cost of a launch is paid once per layer.
+int mlp_forward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, cudaStream_t st) {
+  const int La = a.d.num_layers, Lc = c.d.num_layers;
+  for (int l = 0; l < (La > Lc ? La : Lc); ++l) {
+    urlg_gemm_desc g[2];
+    const urlg_gemm_desc* ptr[2];
+    int n = 0;
+    if (l < La) { g[n] = forward_desc(p, a, l, rows, 0); ptr[n] = &g[n]; ++n; }
+    if (l < Lc) { g[n] = forward_desc(p, c, l, rows, 0); ptr[n] = &g[n]; ++n; }
+    if (int rc = tc::launch_gemm_group(ptr, n, st)) return rc;
   }
   return URLG_OK;
 }
@@ -331,28 +354,26 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
     if (!s->hid_a_h || !s->hid_a_c || !s->hid_c_h || !s->hid_c_c)
       return fail(URLG_EINVAL, "urlg_policy_act: recurrent storage lacks saved hidden states");
   }
-  // fork: critic chain on the side stream, actor chain on the caller's; when one GEMM cannot fill the GPU (rollout-sized
-  // M) each chain is capped to half the SMs so the two run side by side instead of back to back
-  cudaStream_t sc = p->side;
-  URLG_CUDA(cudaEventRecord(p->ev_fork, st));
-  URLG_CUDA(cudaStreamWaitEvent(sc, p->ev_fork, 0));
-  const int cap = N <= 8192 ? kNumSMs / 2 : 0;
-  int rc_a = URLG_OK, rc_c = URLG_OK;
   if (!d.recurrent) {
-    rc_a = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st);
-    rc_c = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], sc);
+    // both observation stagings, then 4 paired GEMM launches on the caller's stream
+    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
+    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
   } else {
+    // fork: the critic's LSTM step on the side stream, the actor's on the caller's (each a short chain of small
+    // launches), joined before the paired heads
+    cudaStream_t sc = p->side;
+    URLG_CUDA(cudaEventRecord(p->ev_fork, st));
+    URLG_CUDA(cudaStreamWaitEvent(sc, p->ev_fork, 0));
     const size_t HS = (size_t)N * d.rnn_hidden, slab = (size_t)t * HS;
-    rc_a = lstm_rollout_step(p, 0, obs, N, store_o, hidden, hidden + HS, s->hid_a_h + slab, s->hid_a_c + slab, st);
-    rc_c = lstm_rollout_step(p, 1, cobs, N, store_p, hidden + 2 * HS, hidden + 3 * HS, s->hid_c_h + slab, s->hid_c_c + slab, sc);
+    const int rc_a = lstm_rollout_step(p, 0, obs, N, store_o, hidden, hidden + HS, s->hid_a_h + slab, s->hid_a_c + slab, st);
+    const int rc_c = lstm_rollout_step(p, 1, cobs, N, store_p, hidden + 2 * HS, hidden + 3 * HS, s->hid_c_h + slab, s->hid_c_c + slab, sc);
+    // join (always, so a capture in progress is never left with an unjoined stream)
+    URLG_CUDA(cudaEventRecord(p->ev_join, sc));
+    URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+    if (rc_a) return rc_a;
+    if (rc_c) return rc_c;
   }
-  if (!rc_a) rc_a = mlp_forward(p, p->net[0], N, st, cap);
-  if (!rc_c) rc_c = mlp_forward(p, p->net[1], N, sc, cap);
-  // join (always, so a capture in progress is never left with an unjoined stream)
-  URLG_CUDA(cudaEventRecord(p->ev_join, sc));
-  URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
-  if (rc_a) return rc_a;
-  if (rc_c) return rc_c;
+  if (int rc = mlp_forward_pair(p, p->net[0], p->net[1], N, st)) return rc;
   sample_store_kernel<<<(N + 127) / 128, 128, 0, st>>>(p->net[0].out, p->net[1].out, p->params + d.std_off, noise, *s, t,
                                                        actions_out, d.num_actions, d.seed_lo, d.seed_hi, d.env_offset,
                                                        step_base, step_offset);

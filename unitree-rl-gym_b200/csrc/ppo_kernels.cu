@@ -10,7 +10,10 @@
 #include "policy.cuh"
 
 namespace urlg {
-namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
+namespace tc {
+int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st);
+int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
+}
 
 int lstm_update_forward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int env_count, cudaStream_t st);
 int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int env_count, cudaStream_t st);
@@ -166,51 +169,86 @@ namespace urlg {
 //   wgrad  dW_l[out,in] += G_l^T a_l          (A = G_l MN-major, B = a_l MN-major, split-K atomics)
 //   dgrad  dz[l] = (G_l W_l) * ELU'(h[l])     (B = W_l image MN-major), column sums -> db_{l-1}
 // dx_out (optional, bf16 [rows, dims[0]]): gradient wrt the network input (recurrent heads), no activation.
-int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st) {
+static urlg_gemm_desc wgrad_desc(urlg_policy* p, NetWs& n, int l, int64_t rows) {
   const int L = n.d.num_layers;
-  for (int l = L - 1; l >= 0; --l) {
-    const bf16* G = l == L - 1 ? n.dout : n.dz[l + 1];
-    const int ldG = l == L - 1 ? n.opad : n.d.dims[l + 1];
-    const int nout = n.d.dims[l + 1], nin = n.d.dims[l];
-    {
-      urlg_gemm_desc g = {};
-      g.A = G; g.lda = ldG; g.a_mn = 1;
-      g.B = l == 0 ? (const void*)n.x : (const void*)n.h[l];
-      g.ldb = l == 0 ? n.kpad[0] : nin; g.b_mn = 1;
-      g.M = nout; g.N = nin; g.K = (int)rows;
-      g.out_f32 = p->grads + n.d.w_off[l]; g.ld_f32 = nin;
-      g.flags = URLG_GEMM_ATOMIC;
-      const int bn = nin > 256 ? 256 : round_up(nin, 64);
-      g.block_n = bn;
-      // split K so that tiles x splits fills ONE wave of the persistent grid (split-bf16 tiles are at most 128 wide):
-      // measured on B200, one wave beats two (wgrad1 23.0 vs 25.8 us, wgrad0 12.1 vs 13.6): half the fp32 atomics
-      // and twice the k-blocks per tile to pipeline
-      const int bn_eff = bn > 128 ? 128 : bn;
-      const int tiles = ((nout + 127) / 128) * ((nin + bn_eff - 1) / bn_eff);
-      int splits = kNumSMs / tiles;
-      const int kblocks = (int)((rows + 63) / 64);
-      if (splits > kblocks / 4) splits = kblocks / 4;
-      if (splits < 1) splits = 1;
-      g.k_splits = splits;
-      with_lo(p, g);
-      if (int rc = tc::launch_gemm(&g, st)) return rc;
-    }
-    if (l >= 1 || dx_out) {
-      urlg_gemm_desc g = {};
-      g.A = G; g.lda = ldG;
-      g.B = n.w[l]; g.ldb = n.kpad[l]; g.b_mn = 1;
-      g.M = (int)rows; g.N = nin; g.K = nout;
-      g.block_n = nin > 256 ? 256 : round_up(nin, 64);
-      if (l >= 1) {
-        g.out_bf16 = n.dz[l]; g.ld_bf16 = nin;
-        g.dact_ref = n.h[l]; g.ld_ref = nin;
-        g.colsum = p->grads + n.d.b_off[l - 1];
-      } else {
-        g.out_bf16 = dx_out; g.ld_bf16 = nin;
-      }
-      with_lo(p, g);
-      if (int rc = tc::launch_gemm(&g, st)) return rc;
-    }
+  const bf16* G = l == L - 1 ? n.dout : n.dz[l + 1];
+  const int ldG = l == L - 1 ? n.opad : n.d.dims[l + 1];
+  const int nout = n.d.dims[l + 1], nin = n.d.dims[l];
+  urlg_gemm_desc g = {};
+  g.A = G; g.lda = ldG; g.a_mn = 1;
+  g.B = l == 0 ? (const void*)n.x : (const void*)n.h[l];
+  g.ldb = l == 0 ? n.kpad[0] : nin; g.b_mn = 1;
+  g.M = nout; g.N = nin; g.K = (int)rows;
+  g.out_f32 = p->grads + n.d.w_off[l]; g.ld_f32 = nin;
+  g.flags = URLG_GEMM_ATOMIC;
+  const int bn = nin > 256 ? 256 : round_up(nin, 64);
+  g.block_n = bn;
+  // split K so that tiles x splits fills ONE wave of the persistent grid (split-bf16 tiles are at most 128 wide):
+  // measured on B200, one wave beats two (wgrad1 23.0 vs 25.8 us, wgrad0 12.1 vs 13.6): half the fp32 atomics
+  // and twice the k-blocks per tile to pipeline
+  const int bn_eff = bn > 128 ? 128 : bn;
+  const int tiles = ((nout + 127) / 128) * ((nin + bn_eff - 1) / bn_eff);
+  int splits = kNumSMs / tiles;
+  const int kblocks = (int)((rows + 63) / 64);
+  if (splits > kblocks / 4) splits = kblocks / 4;
+  if (splits < 1) splits = 1;
+  g.k_splits = splits;
+  with_lo(p, g);
+  return g;
+}
+
+// false when layer l has no data gradient to produce (l == 0 without dx_out)
+static bool dgrad_desc(urlg_policy* p, NetWs& n, int l, int64_t rows, bf16* dx_out, urlg_gemm_desc& g) {
+  if (!(l >= 1 || dx_out)) return false;
+  const int L = n.d.num_layers;
+  const bf16* G = l == L - 1 ? n.dout : n.dz[l + 1];
+  const int ldG = l == L - 1 ? n.opad : n.d.dims[l + 1];
+  const int nout = n.d.dims[l + 1], nin = n.d.dims[l];
+  g = urlg_gemm_desc{};
+  g.A = G; g.lda = ldG;
+  g.B = n.w[l]; g.ldb = n.kpad[l]; g.b_mn = 1;
+  g.M = (int)rows; g.N = nin; g.K = nout;
+  g.block_n = nin > 256 ? 256 : round_up(nin, 64);
+  if (l >= 1) {
+    g.out_bf16 = n.dz[l]; g.ld_bf16 = nin;
+    g.dact_ref = n.h[l]; g.ld_ref = nin;
+    g.colsum = p->grads + n.d.b_off[l - 1];
+  } else {
+    g.out_bf16 = dx_out; g.ld_bf16 = nin;
+  }
+  with_lo(p, g);
+  return true;
+}
+
+int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st) {
+  for (int l = n.d.num_layers - 1; l >= 0; --l) {
+    urlg_gemm_desc g[2];
+    const urlg_gemm_desc* ptr[2];
+    int k = 0;
+    g[k] = wgrad_desc(p, n, l, rows); ptr[k] = &g[k]; ++k;
+    if (dgrad_desc(p, n, l, rows, dx_out, g[k])) { ptr[k] = &g[k]; ++k; }
+    if (int rc = tc::launch_gemm_group(ptr, k, st)) return rc;
+  }
+  return URLG_OK;
+}
+
+// Both networks, top layer down: level k = layer La-1-k of the actor and Lc-1-k of the critic.  A level's weight
+// gradients and data gradients of both networks only READ that level's incoming gradient (written by the previous
+// launch) and forward activations, and write disjoint outputs, so they are one launch of up to 4 problems: a
+// backward of both networks is max(La, Lc) launches instead of 2 (La + Lc) - 2.  Long tiles (split-K weight
+// gradients) first.
+int mlp_backward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, bf16* dxa, bf16* dxc, cudaStream_t st) {
+  const int La = a.d.num_layers, Lc = c.d.num_layers;
+  for (int k = 0; k < (La > Lc ? La : Lc); ++k) {
+    const int la = La - 1 - k, lc = Lc - 1 - k;
+    urlg_gemm_desc g[4];
+    const urlg_gemm_desc* ptr[4];
+    int n = 0;
+    if (la >= 0) { g[n] = wgrad_desc(p, a, la, rows); ptr[n] = &g[n]; ++n; }
+    if (lc >= 0) { g[n] = wgrad_desc(p, c, lc, rows); ptr[n] = &g[n]; ++n; }
+    if (la >= 0 && dgrad_desc(p, a, la, rows, dxa, g[n])) { ptr[n] = &g[n]; ++n; }
+    if (lc >= 0 && dgrad_desc(p, c, lc, rows, dxc, g[n])) { ptr[n] = &g[n]; ++n; }
+    if (int rc = tc::launch_gemm_group(ptr, n, st)) return rc;
   }
   return URLG_OK;
 }
@@ -328,15 +366,14 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     if (int rc = lstm_update_forward(p, 0, s, env_begin, env_count, st)) return rc;
     if (int rc = lstm_update_forward(p, 1, s, env_begin, env_count, st)) return rc;
   }
-  if (int rc = mlp_forward(p, na, rows, st)) return rc;
-  if (int rc = mlp_forward(p, nc, rows, st)) return rc;
+  if (int rc = mlp_forward_pair(p, na, nc, rows, st)) return rc;
   ppo_head_kernel<<<(int)((rows + kHeadThreads - 1) / kHeadThreads), kHeadThreads, 0, st>>>(
       na.out, nc.out, p->params + d.std_off, *s, indices, rows, env_begin, env_count, *h, na.dout, na.opad, nc.dout,
       nc.opad, p->lo_off, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
       p->grads + nc.d.b_off[nc.d.num_layers - 1], p->stats);
   URLG_LAUNCH_CHECK();
-  if (int rc = mlp_backward(p, na, rows, d.recurrent ? p->lstm[0].dx_head : nullptr, st)) return rc;
-  if (int rc = mlp_backward(p, nc, rows, d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
+  if (int rc = mlp_backward_pair(p, na, nc, rows, d.recurrent ? p->lstm[0].dx_head : nullptr,
+                                 d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
   if (d.recurrent) {
     if (int rc = lstm_update_backward(p, 0, s, env_begin, env_count, st)) return rc;
     if (int rc = lstm_update_backward(p, 1, s, env_begin, env_count, st)) return rc;

@@ -83,7 +83,7 @@ int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
 int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) { return launch_gemm_group(&d, 1, st); }
 
 // Fills one problem's kernel arguments and its 8 tensor maps.
-static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm) {
+static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, int group_n) {
   if (!d || !d->A || !d->B || d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(URLG_EINVAL, "urlg_tc_gemm: bad argument");
   CUtensorMap &ta = tm[kTmA], &tb = tm[kTmB], &tal = tm[kTmAlo], &tbl = tm[kTmBlo], &to = tm[kTmO], &tol = tm[kTmOlo],
               &tr = tm[kTmR], &trl = tm[kTmRlo];
@@ -97,7 +97,7 @@ static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm) 
     const int tm = (d->M + kBlockM - 1) / kBlockM;
     const int min_bn = g.b_mn ? 64 : 32;
     while (bn > min_bn && (bn % 2 == 0) && ((bn / 2) % (g.b_mn ? 64 : 16) == 0) &&
-           tm * ((d->N + bn - 1) / bn) < (kNumSMs * 3) / 4)
+           tm * ((d->N + bn - 1) / bn) * group_n < (kNumSMs * 3) / 4)     // the group's problems share the SMs
       bn /= 2;
   }
   if (bn > 256) bn = 256;
@@ -177,7 +177,7 @@ int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
   int bn_max = 0, max_ctas = 0;
   P.any_tma_out = P.any_tma_ref = 0;
   for (int i = 0; i < n; ++i) {
-    if (int rc = build_problem(ds[i], P.g[i], P.tm[i])) return rc;
+    if (int rc = build_problem(ds[i], P.g[i], P.tm[i], n)) return rc;
     const GemmArgs& g = P.g[i];
     if (i && g.split != P.g[0].split) return fail(URLG_EINVAL, "urlg_tc_gemm: grouped problems must share the operand mode (hi+lo or plain)");
     tiles += (int64_t)g.tiles_m * g.tiles_n * g.splits;
@@ -237,4 +237,12 @@ extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double
 
 extern "C" int urlg_tc_gemm(const urlg_gemm_desc* d, void* stream) {
   return urlg::tc::launch_gemm(d, (cudaStream_t)stream);
+}
+
+extern "C" int urlg_tc_gemm_group(const urlg_gemm_desc* descs, int n, void* stream) {
+  if (!descs || n < 1 || n > urlg::tc::kMaxGroup)
+    return urlg::fail(URLG_EINVAL, "urlg_tc_gemm_group: 1..%d problems per launch", urlg::tc::kMaxGroup);
+  const urlg_gemm_desc* ptr[urlg::tc::kMaxGroup];
+  for (int i = 0; i < n; ++i) ptr[i] = descs + i;
+  return urlg::tc::launch_gemm_group(ptr, n, (cudaStream_t)stream);
 }
