@@ -363,8 +363,16 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
       URLG_LAUNCH_CHECK();
     }
   } else {
-    if (int rc = lstm_update_forward(p, 0, s, env_begin, env_count, st)) return rc;
-    if (int rc = lstm_update_forward(p, 1, s, env_begin, env_count, st)) return rc;
+    // the two memories are independent chains of latency-bound kernels (staging, projection GEMM, one persistent
+    // recurrence of ~100 us on a fraction of the SMs): the critic's runs on the side stream beside the actor's
+    URLG_CUDA(cudaEventRecord(p->ev_fork, st));
+    URLG_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    const int rc_a = lstm_update_forward(p, 0, s, env_begin, env_count, st);
+    const int rc_c = lstm_update_forward(p, 1, s, env_begin, env_count, p->side);
+    URLG_CUDA(cudaEventRecord(p->ev_join, p->side));       // join always: a capture must not end with a forked stream
+    URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+    if (rc_a) return rc_a;
+    if (rc_c) return rc_c;
   }
   if (int rc = mlp_forward_pair(p, na, nc, rows, st)) return rc;
   ppo_head_kernel<<<(int)((rows + kHeadThreads - 1) / kHeadThreads), kHeadThreads, 0, st>>>(
@@ -375,8 +383,14 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   if (int rc = mlp_backward_pair(p, na, nc, rows, d.recurrent ? p->lstm[0].dx_head : nullptr,
                                  d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
   if (d.recurrent) {
-    if (int rc = lstm_update_backward(p, 0, s, env_begin, env_count, st)) return rc;
-    if (int rc = lstm_update_backward(p, 1, s, env_begin, env_count, st)) return rc;
+    URLG_CUDA(cudaEventRecord(p->ev_fork, st));
+    URLG_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    const int rc_a = lstm_update_backward(p, 0, s, env_begin, env_count, st);
+    const int rc_c = lstm_update_backward(p, 1, s, env_begin, env_count, p->side);
+    URLG_CUDA(cudaEventRecord(p->ev_join, p->side));
+    URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+    if (rc_a) return rc_a;
+    if (rc_c) return rc_c;
   }
   p->last_rows = rows;
   return URLG_OK;

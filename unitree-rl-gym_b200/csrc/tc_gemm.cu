@@ -169,9 +169,9 @@ static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, 
   return URLG_OK;
 }
 
-int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
-  if (!ds || n < 1 || n > kMaxGroup) return fail(URLG_EINVAL, "urlg_tc_gemm: 1..%d problems per launch", kMaxGroup);
-  static GroupArgs P;                       // ~5 KB of kernel parameters, copied at launch
+template <int G>
+static int launch_group_g(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
+  static GroupArgs<G> P;                    // 1.2 KB of kernel parameters per problem, copied at launch
   P.num = n;
   int64_t tiles = 0;
   int bn_max = 0, max_ctas = 0;
@@ -188,24 +188,31 @@ int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
     P.any_tma_ref |= g.tma_ref;
     if (ds[i]->max_ctas > 0 && (max_ctas == 0 || ds[i]->max_ctas < max_ctas)) max_ctas = ds[i]->max_ctas;
   }
-  for (int i = n; i < kMaxGroup; ++i) P.tile_end[i] = (int)tiles;
+  for (int i = n; i < G; ++i) P.tile_end[i] = (int)tiles;
   P.split = P.g[0].split;
   P.stages = gemm_stages_for(bn_max, P.split, P.any_tma_out, P.any_tma_ref);
   P.bytes_b_max = stage_bytes_b(bn_max);
   P.acc_cols = (int)tmem_cols_for(bn_max);
   static bool attr_set = false;
   if (!attr_set) {
-    URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    URLG_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
   int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);           // persistent: one CTA per SM walks the tiles
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   // launched with programmatic stream serialization (see the kernel): back-to-back kernels overlap launch + set-up
   // of the next with the tail of the previous (common.cuh)
-  URLG_CUDA(launch_pdl(gemm_bf16_kernel, dim3(grid), dim3(kGemmThreads),
+  URLG_CUDA(launch_pdl(gemm_bf16_kernel<G>, dim3(grid), dim3(kGemmThreads),
                        gemm_smem_bytes(bn_max, P.split, P.stages, P.any_tma_out, P.any_tma_ref), st, P));
   URLG_LAUNCH_CHECK();
   return URLG_OK;
+}
+
+int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
+  if (!ds || n < 1 || n > kMaxGroup) return fail(URLG_EINVAL, "urlg_tc_gemm: 1..%d problems per launch", kMaxGroup);
+  if (n == 1) return launch_group_g<1>(ds, n, st);
+  if (n == 2) return launch_group_g<2>(ds, n, st);
+  return launch_group_g<4>(ds, n, st);
 }
 
 }  // namespace tc

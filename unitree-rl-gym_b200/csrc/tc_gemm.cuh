@@ -69,10 +69,13 @@ __device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w &
 // (~4 us: launch, TMEM allocation, descriptor fetch, pipeline fill and drain) and fill each other's wave tails.
 constexpr int kMaxGroup = 4;
 enum { kTmA = 0, kTmB, kTmAlo, kTmBlo, kTmO, kTmOlo, kTmR, kTmRlo, kTmCount };
+// G = capacity (1, 2 or 4): the parameter block is 1.2 KB per problem and is fetched at every launch, so a single
+// problem is launched through the G = 1 instantiation (measured: +0.7 us per launch with the 4-problem block).
+template <int G>
 struct GroupArgs {
-  CUtensorMap tm[kMaxGroup][kTmCount];
-  GemmArgs g[kMaxGroup];
-  int tile_end[kMaxGroup];   // exclusive prefix sums of the problems' tile counts
+  CUtensorMap tm[G][kTmCount];
+  GemmArgs g[G];
+  int tile_end[G];           // exclusive prefix sums of the problems' tile counts
   int num;
   int stages, split;         // common smem pipeline depth / operand mode
   int bytes_b_max;           // stage stride of the B ring (largest block_n of the group)
@@ -80,10 +83,13 @@ struct GroupArgs {
   int any_tma_out, any_tma_ref;
 };
 struct TileRef { int p, tx, ty, tz; };
-__device__ __forceinline__ TileRef locate(const GroupArgs& P, int tile) {
+template <int G>
+__device__ __forceinline__ TileRef locate(const GroupArgs<G>& P, int tile) {
   TileRef t;
   t.p = 0;
-  while (t.p + 1 < P.num && tile >= P.tile_end[t.p]) ++t.p;
+  if (G > 1) {
+    while (t.p + 1 < P.num && tile >= P.tile_end[t.p]) ++t.p;
+  }
   const int local = tile - (t.p ? P.tile_end[t.p - 1] : 0);
   const GemmArgs& g = P.g[t.p];
   t.tx = local % g.tiles_m;
@@ -97,8 +103,9 @@ __device__ __forceinline__ TileRef locate(const GroupArgs& P, int tile) {
 // buffered in TMEM (2 x tmem_cols_for(block_n) columns), so the MMAs of tile i+1 run under the epilogue of tile i;
 // the epilogue (the expensive part for these skinny GEMMs: bias, ELU / ELU', hi+lo split, column sums) is spread
 // over 16 warps = 4 per scheduler.
+template <int G>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ GroupArgs P) {
+gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
