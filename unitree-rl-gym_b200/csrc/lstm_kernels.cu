@@ -9,7 +9,10 @@
 #include "policy.cuh"
 
 namespace urlg {
-namespace tc { int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st); }
+namespace tc {
+int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st);
+int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
+}
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
@@ -494,22 +497,26 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
     }
   }
   // weight gradients over the whole sequence: dW_ih = dgates^T x, dW_hh = dgates^T h_prev (K = T*E)
+  // (both parts in ONE launch: they read the same dgates and write disjoint gradient slices)
+  urlg_gemm_desc gs[2];
+  const urlg_gemm_desc* ptr[2] = {&gs[0], &gs[1]};
   for (int part = 0; part < 2; ++part) {
-    urlg_gemm_desc g = {};
+    urlg_gemm_desc& g = gs[part];
+    g = urlg_gemm_desc{};
     g.A = w.dgates; g.lda = 4 * H; g.a_mn = 1;
     g.B = part == 0 ? w.xcat : w.xcat + w.in_pad; g.ldb = w.kcat; g.b_mn = 1;
     g.M = 4 * H; g.N = part == 0 ? w.in : H; g.K = T * E;
     g.block_n = round_up(g.N, 64);
     g.out_f32 = p->grads + w.off[part]; g.ld_f32 = g.N;
     g.flags = URLG_GEMM_ATOMIC;
-    const int tiles = (4 * H + 127) / 128;
-    int splits = (kNumSMs + tiles - 1) / tiles;
+    const int tiles = 2 * ((4 * H + 127) / 128);          // both parts share the wave
+    int splits = kNumSMs / tiles;
     const int kblocks = (T * E + 63) / 64;
     if (splits > kblocks / 4) splits = kblocks / 4;
     g.k_splits = splits < 1 ? 1 : splits;
     with_lo(p, g);
-    if (int rc = tc::launch_gemm(&g, st)) return rc;
   }
+  if (int rc = tc::launch_gemm_group(ptr, 2, st)) return rc;
   return URLG_OK;
 }
 
