@@ -230,6 +230,29 @@ stage_obs_kernel(const float* __restrict__ src, int64_t rows, int cols, float* _
   }
 }
 
+// Actor and critic observations in one launch (rollout: saves a launch per env step); same element mapping as above.
+__global__ void __launch_bounds__(256)
+stage_obs_pair_kernel(const float* __restrict__ src_a, int cols_a, float* __restrict__ store_a, bf16* __restrict__ dst_a, int kpad_a,
+                      const float* __restrict__ src_c, int cols_c, float* __restrict__ store_c, bf16* __restrict__ dst_c, int kpad_c,
+                      int64_t rows, int64_t lo_off) {
+  const int64_t total_a = rows * kpad_a, total = total_a + rows * kpad_c;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const bool crit = i >= total_a;
+    const int64_t k = crit ? i - total_a : i;
+    const int kpad = crit ? kpad_c : kpad_a, cols = crit ? cols_c : cols_a;
+    const float* src = crit ? src_c : src_a;
+    float* store = crit ? store_c : store_a;
+    const int64_t r = k / kpad;
+    const int c = (int)(k % kpad);
+    float v = 0.0f;
+    if (c < cols) {
+      v = src[r * cols + c];
+      if (store) store[r * cols + c] = v;
+    }
+    store_split(crit ? dst_c : dst_a, lo_off, (size_t)(r * kpad + c), v);
+  }
+}
+
 int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld,
               cudaStream_t st) {
   const int64_t total = rows * kpad;
@@ -243,36 +266,45 @@ int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst,
 // ---------------------------------------------------------------- sample + log-prob + transition store
 // Normal(mu, std).sample(): eps from Philox (Box-Muller on slots 2j, 2j+1 of stream kStreamPolicy, counter
 // (global env, step)) or injected.  log_prob follows torch.distributions.Normal.log_prob term by term.
-__global__ void __launch_bounds__(128)
+// One thread per (env, action): 32 envs x A threads per block, all loads / stores contiguous; the per-action log-prob
+// terms meet in shared memory and are summed in action order by the env's first thread (the order a per-env loop uses).
+constexpr int kSampleEnvs = 32;
+__global__ void __launch_bounds__(1024)
 sample_store_kernel(const float* __restrict__ mu_in, const float* __restrict__ val_in, const float* __restrict__ std_param,
                     const float* __restrict__ noise, urlg_storage s, int t, float* __restrict__ actions_out, int A,
                     uint32_t seed_lo, uint32_t seed_hi, int64_t env_offset, const int64_t* step_base, int64_t step_off) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= s.N) return;
-  SlotRng rng;
-  rng.init(seed_lo, seed_hi, kStreamPolicy, env_offset + i, eff_step(step_base, step_off), nullptr);
-  const size_t row = (size_t)t * s.N + i;
-  float lp = 0.0f;
-  for (int j = 0; j < A; ++j) {
+  extern __shared__ float terms[];                       // [kSampleEnvs * A]
+  const int e = threadIdx.x / A, j = threadIdx.x - e * A;
+  const int i = blockIdx.x * kSampleEnvs + e;
+  if (i < s.N) {
+    const size_t row = (size_t)t * s.N + i;
     const float mu = mu_in[(size_t)i * A + j];
     const float sd = mu * 0.0f + std_param[j];
     float eps;
     if (noise) {
       eps = noise[(size_t)i * A + j];
     } else {
+      SlotRng rng;
+      rng.init(seed_lo, seed_hi, kStreamPolicy, env_offset + i, eff_step(step_base, step_off), nullptr);
       const float u1 = 1.0f - rng.uniform(2 * j), u2 = rng.uniform(2 * j + 1);   // u1 in (0,1]
       eps = sqrtf(-2.0f * logf(u1)) * cosf(6.28318530717958647692f * u2);
     }
     const float a = mu + sd * eps;
     const float d = a - mu;
-    lp += -(d * d) / (2.0f * (sd * sd)) - logf(sd) - 0.918938533204672741780f;
+    terms[threadIdx.x] = -(d * d) / (2.0f * (sd * sd)) - logf(sd) - 0.918938533204672741780f;
     s.actions[row * A + j] = a;
     s.mu[row * A + j] = mu;
     s.sigma[row * A + j] = sd;
     actions_out[(size_t)i * A + j] = a;
   }
-  s.actions_log_prob[row] = lp;
-  s.values[row] = val_in[i];
+  __syncthreads();
+  if (i < s.N && j == 0) {
+    const size_t row = (size_t)t * s.N + i;
+    float lp = 0.0f;
+    for (int k = 0; k < A; ++k) lp += terms[e * A + k];
+    s.actions_log_prob[row] = lp;
+    s.values[row] = val_in[i];
+  }
 }
 
 }  // namespace urlg
@@ -356,8 +388,15 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
   }
   if (!d.recurrent) {
     // both observation stagings, then one paired GEMM launch per layer on the caller's stream
-    if (int rc = stage_obs(obs, N, d.num_actor_obs, store_o, p->net[0].x, p->lo_off, p->net[0].kpad[0], p->net[0].kpad[0], st)) return rc;
-    if (int rc = stage_obs(cobs, N, d.num_critic_obs, store_p, p->net[1].x, p->lo_off, p->net[1].kpad[0], p->net[1].kpad[0], st)) return rc;
+    {
+      const int ka = p->net[0].kpad[0], kc = p->net[1].kpad[0];
+      const int64_t total = (int64_t)N * (ka + kc);
+      int blocks = (int)((total + 255) / 256);
+      if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+      stage_obs_pair_kernel<<<blocks, 256, 0, st>>>(obs, d.num_actor_obs, store_o, p->net[0].x, ka, cobs, d.num_critic_obs,
+                                                    store_p, p->net[1].x, kc, N, p->lo_off);
+      URLG_LAUNCH_CHECK();
+    }
     if (int rc = mlp_forward_pair(p, p->net[0], p->net[1], N, st)) return rc;
   } else {
     // fork: the critic's LSTM step + head on the side stream, the actor's on the caller's.  Each chain is a handful of
@@ -378,7 +417,9 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
     if (rc_a) return rc_a;
     if (rc_c) return rc_c;
   }
-  sample_store_kernel<<<(N + 127) / 128, 128, 0, st>>>(p->net[0].out, p->net[1].out, p->params + d.std_off, noise, *s, t,
+  if (d.num_actions > 32) return fail(URLG_EINVAL, "urlg_policy_act: more than 32 actions");
+  sample_store_kernel<<<(N + kSampleEnvs - 1) / kSampleEnvs, kSampleEnvs * d.num_actions,
+                        kSampleEnvs * d.num_actions * sizeof(float), st>>>(p->net[0].out, p->net[1].out, p->params + d.std_off, noise, *s, t,
                                                        actions_out, d.num_actions, d.seed_lo, d.seed_hi, d.env_offset,
                                                        step_base, step_offset);
   URLG_LAUNCH_CHECK();
