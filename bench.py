@@ -490,7 +490,12 @@ def own_arm(a):
                 "bound": "hbm" if mem_bound else "tensor",
                 "achieved": gbs if mem_bound else tf, "peak": hbm if mem_bound else tf_sus,
                 "unit": "GB/s" if mem_bound else "TFLOP/s", "frac": (gbs / hbm) if mem_bound else (tf / tf_sus),
-                "traffic": ncu_traffic_per_launch(), "launches_per_step": int(n_r + n_u),
+                "traffic": ncu_traffic_per_launch(),
+                "traffic_scope": "ncu --set full capture of the 8 grouped GEMM launches of one update minibatch "
+                                 "(profiles/r1_gemm_minibatch_ncu.csv): DRAM read + write per launch; compare with "
+                                 "traffic_alg_bytes_per_launch = algorithmic bytes per update-phase launch",
+                "traffic_alg_bytes_per_launch": by_u / max(n_u, 1),
+                "launches_per_step": int(n_r + n_u),
                 "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
                 "alg_bytes_per_launch": (by_r + by_u) / max(n_r + n_u, 1), "alg_flops_per_launch": (fl_r + fl_u) / max(n_r + n_u, 1),
                 "tensor": {"achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus},
