@@ -28,6 +28,31 @@ __global__ void __launch_bounds__(256)
 gather_obs_kernel(const float* __restrict__ src, int cols, const int64_t* __restrict__ indices, int64_t rows,
                   bf16* __restrict__ dst, bf16* __restrict__ dst2 /* optional second consumer of the same rows */,
                   int64_t lo_off, int kpad) {
+  if (((cols | kpad) & 3) == 0 && (lo_off & 3) == 0 && ((uintptr_t)src & 15) == 0 &&
+      (((uintptr_t)dst | (uintptr_t)dst2) & 7) == 0 && rows * (kpad >> 2) < 0x7fffffff) {
+    // 4 columns per thread: one float4 load, packed bf16x4 stores of the high and the low parts, 32-bit index math
+    const int k4 = kpad >> 2, c4n = cols >> 2;
+    const int total = (int)rows * k4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      const int r = i / k4, c = i - r * k4;
+      float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      if (c < c4n) v = __ldg(reinterpret_cast<const float4*>(src + indices[r] * cols) + c);
+      const __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+      const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+      const __nv_bfloat162 l0 = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
+      uint2 hi, lo;
+      hi.x = *reinterpret_cast<const uint32_t*>(&h0); hi.y = *reinterpret_cast<const uint32_t*>(&h1);
+      lo.x = *reinterpret_cast<const uint32_t*>(&l0); lo.y = *reinterpret_cast<const uint32_t*>(&l1);
+      const size_t o = (size_t)i * 4;
+      *reinterpret_cast<uint2*>(dst + o) = hi;
+      if (lo_off) *reinterpret_cast<uint2*>(dst + o + lo_off) = lo;
+      if (dst2) {
+        *reinterpret_cast<uint2*>(dst2 + o) = hi;
+        if (lo_off) *reinterpret_cast<uint2*>(dst2 + o + lo_off) = lo;
+      }
+    }
+    return;
+  }
   const int64_t total = rows * kpad;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / kpad;
