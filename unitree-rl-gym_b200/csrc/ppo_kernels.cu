@@ -142,12 +142,43 @@ ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_
       dv = 2.0f * (v - ret);
     }
     dv *= hp.value_loss_coef * inv_rows;
+    if ((ld_dmu & 7) == 0 && ld_dmu <= kMaxA && (lo_off & 7) == 0 && ((uintptr_t)dmu & 15) == 0) {
+      // 8 columns per 16-byte store (packed bf16 high parts, then low parts) instead of 2-byte scalar stores
 #pragma unroll
-    for (int j = 0; j < kMaxA; ++j)
-      if (j < A) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), dm[j]);
-    for (int j = A; j < ld_dmu; ++j) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), 0.0f);
-    store_split(dval, lo_off, (size_t)(r * ld_dval), dv);
-    for (int j = 1; j < ld_dval; ++j) store_split(dval, lo_off, (size_t)(r * ld_dval + j), 0.0f);
+      for (int g8 = 0; g8 < kMaxA / 8; ++g8) {
+        if (g8 * 8 < ld_dmu) {
+          uint32_t hi[4], lo[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int j = g8 * 8 + 2 * k;
+            const float x0 = j < A ? dm[j] : 0.0f, x1 = j + 1 < A ? dm[j + 1] : 0.0f;
+            const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+            const float2 f = __bfloat1622float2(h);
+            const __nv_bfloat162 l = __floats2bfloat162_rn(x0 - f.x, x1 - f.y);
+            hi[k] = *reinterpret_cast<const uint32_t*>(&h);
+            lo[k] = *reinterpret_cast<const uint32_t*>(&l);
+          }
+          bf16* o = dmu + (size_t)r * ld_dmu + g8 * 8;
+          *reinterpret_cast<uint4*>(o) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          if (lo_off) *reinterpret_cast<uint4*>(o + lo_off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kMaxA; ++j)
+        if (j < A) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), dm[j]);
+      for (int j = A; j < ld_dmu; ++j) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), 0.0f);
+    }
+    if (ld_dval == 8 && (lo_off & 7) == 0 && ((uintptr_t)dval & 15) == 0) {
+      const bf16 h = __float2bfloat16(dv);
+      const bf16 l = __float2bfloat16(dv - __bfloat162float(h));
+      bf16* o = dval + (size_t)r * 8;
+      *reinterpret_cast<uint4*>(o) = make_uint4((uint32_t)__bfloat16_as_ushort(h), 0u, 0u, 0u);
+      if (lo_off) *reinterpret_cast<uint4*>(o + lo_off) = make_uint4((uint32_t)__bfloat16_as_ushort(l), 0u, 0u, 0u);
+    } else {
+      store_split(dval, lo_off, (size_t)(r * ld_dval), dv);
+      for (int j = 1; j < ld_dval; ++j) store_split(dval, lo_off, (size_t)(r * ld_dval + j), 0.0f);
+    }
   }
   // block reductions -> atomics
   __shared__ float red[kHeadThreads / 32][2 * kMaxA + 5];
