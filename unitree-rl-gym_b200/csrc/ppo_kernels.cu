@@ -64,7 +64,14 @@ gather_obs_kernel(const float* __restrict__ src, int cols, const int64_t* __rest
 }
 
 // ---------------------------------------------------------------- loss head
-constexpr int kHeadThreads = 64;   // 24576-row minibatch -> 384 blocks: every SM gets 2-3 (one thread per row, long chain)
+// One thread per (row, action), 32 rows per block: ~60 warps per SM and a few hundred SASS instructions.  (The first
+// version ran one thread per row with the action loops unrolled 32-wide: 7.8k SASS instructions executed once per warp
+// at 5 warps per SM -- ncu: 8.6 % issue-active, `no_instruction` the top stall, 25 us per launch.)
+//   phase 1  per (row, j): log-prob and KL terms -> shared memory
+//   leader   (j == 0): sums them in action order (bit-identical to a per-row loop), ratio, surrogate, value loss,
+//            d loss / d log-prob and d loss / d value of the row
+//   phase 2  per (row, j): d loss / d mu_j, d loss / d sigma_j; column sums over the block's rows -> atomics
+constexpr int kHeadRows = 32;
 constexpr int kMaxA = 32;
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -73,146 +80,117 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-__global__ void __launch_bounds__(kHeadThreads)
+__global__ void __launch_bounds__(kHeadRows * kMaxA)
 ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_new, const float* __restrict__ std_param,
                 const urlg_storage s, const int64_t* __restrict__ indices, int64_t rows, int env_begin, int env_count,
                 const urlg_ppo_hparams hp, bf16* __restrict__ dmu, int ld_dmu, bf16* __restrict__ dval, int ld_dval,
                 int64_t lo_off,
                 float* __restrict__ g_std, float* __restrict__ g_bias_mu, float* __restrict__ g_bias_val,
                 float* __restrict__ stats) {
+  extern __shared__ float sh[];
   const int A = s.num_actions;
-  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  float* t_a = sh;                         // [rows][A]  log-prob terms, then d loss / d mu
+  float* t_b = t_a + kHeadRows * A;        // [rows][A]  KL terms, then d loss / d sigma
+  float* row_dlp = t_b + kHeadRows * A;    // [rows]
+  float* row_s = row_dlp + kHeadRows;      // [rows][5]  kl, surrogate, value loss, entropy, d loss / d value
+  float* c_log = row_s + 5 * kHeadRows;    // [A]        log sigma_j
+  const int tid = threadIdx.x;
+  const int e = tid / A, j = tid - e * A;
+  const int64_t r = blockIdx.x * (int64_t)kHeadRows + e;
   const bool ok = r < rows;
   const float inv_rows = 1.0f / (float)rows;
-  float kl = 0.0f, surr = 0.0f, vloss = 0.0f, ent = 0.0f, dv = 0.0f;
-  float dm[kMaxA], ds[kMaxA];
-#pragma unroll
-  for (int j = 0; j < kMaxA; ++j) { dm[j] = 0.0f; ds[j] = 0.0f; }
-  // row-invariant per-action constants once per block: sigma, log sigma, 1 / (2 sigma^2)
-  __shared__ float c_sd[kMaxA], c_log[kMaxA], c_i2v[kMaxA];
-  if (threadIdx.x < A) {
-    const float sd = std_param[threadIdx.x];
-    c_sd[threadIdx.x] = sd;
-    c_log[threadIdx.x] = logf(sd);
-    c_i2v[threadIdx.x] = 2.0f * (sd * sd);
-  }
+  if (tid < A) c_log[tid] = logf(std_param[tid]);
   __syncthreads();
+  int64_t q = 0;
+  float d = 0.0f, var = 1.0f, sd = 1.0f;
   if (ok) {
-    const int64_t q = row_index(indices, r, s.N, env_begin, env_count);
-    float lp = 0.0f;
-#pragma unroll
-    for (int j = 0; j < kMaxA; ++j) {
-      if (j < A) {
-        const float mu = mu_new[r * A + j], sd = c_sd[j], lsd = c_log[j], var2 = c_i2v[j];
-        const float a = s.actions[q * A + j], mo = s.mu[q * A + j], so = s.sigma[q * A + j];
-        const float d = a - mu, var = sd * sd;
-        lp += -(d * d) / var2 - lsd - 0.918938533204672741780f;
-        ent += 0.5f + 0.918938533204672741780f + lsd;
-        kl += logf(sd / so + 1.e-5f) + (so * so + (mo - mu) * (mo - mu)) / var2 - 0.5f;
-        dm[j] = d / var;                         // d logp / d mu
-        ds[j] = d * d / (var * sd) - 1.0f / sd;  // d logp / d sigma
-      }
-    }
-    const float adv = s.advantages[q], old_lp = s.actions_log_prob[q];
-    const float ratio = expf(lp - old_lp);
-    const float lo = 1.0f - hp.clip_param, hi = 1.0f + hp.clip_param;
-    const float rc = fminf(fmaxf(ratio, lo), hi);
-    const float s1 = -adv * ratio, s2 = -adv * rc;
-    surr = fmaxf(s1, s2);
-    // d max(s1,s2)/d ratio (torch.max splits ties evenly; clamp passes gradient on [lo,hi] inclusive)
-    const float in_rng = (ratio >= lo && ratio <= hi) ? 1.0f : 0.0f;
-    float dr;
-    if (s1 > s2) dr = -adv;
-    else if (s1 < s2) dr = -adv * in_rng;
-    else dr = 0.5f * (-adv) + 0.5f * (-adv) * in_rng;
-    const float dlp = dr * ratio * inv_rows;
-#pragma unroll
-    for (int j = 0; j < kMaxA; ++j) { dm[j] *= dlp; ds[j] *= dlp; }
-    const float v = val_new[r], ret = s.returns[q], vo = s.values[q];
-    if (hp.use_clipped_value_loss) {
-      const float dvv = v - vo;
-      const float vc = vo + fminf(fmaxf(dvv, -hp.clip_param), hp.clip_param);
-      const float l1 = (v - ret) * (v - ret), l2 = (vc - ret) * (vc - ret);
-      vloss = fmaxf(l1, l2);
-      const float in_v = (dvv >= -hp.clip_param && dvv <= hp.clip_param) ? 1.0f : 0.0f;
-      const float g1 = 2.0f * (v - ret), g2 = 2.0f * (vc - ret) * in_v;
-      dv = l1 > l2 ? g1 : (l1 < l2 ? g2 : 0.5f * g1 + 0.5f * g2);
-    } else {
-      vloss = (ret - v) * (ret - v);
-      dv = 2.0f * (v - ret);
-    }
-    dv *= hp.value_loss_coef * inv_rows;
-    if ((ld_dmu & 7) == 0 && ld_dmu <= kMaxA && (lo_off & 7) == 0 && ((uintptr_t)dmu & 15) == 0) {
-      // 8 columns per 16-byte store (packed bf16 high parts, then low parts) instead of 2-byte scalar stores
-#pragma unroll
-      for (int g8 = 0; g8 < kMaxA / 8; ++g8) {
-        if (g8 * 8 < ld_dmu) {
-          uint32_t hi[4], lo[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int j = g8 * 8 + 2 * k;
-            const float x0 = j < A ? dm[j] : 0.0f, x1 = j + 1 < A ? dm[j + 1] : 0.0f;
-            const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
-            const float2 f = __bfloat1622float2(h);
-            const __nv_bfloat162 l = __floats2bfloat162_rn(x0 - f.x, x1 - f.y);
-            hi[k] = *reinterpret_cast<const uint32_t*>(&h);
-            lo[k] = *reinterpret_cast<const uint32_t*>(&l);
-          }
-          bf16* o = dmu + (size_t)r * ld_dmu + g8 * 8;
-          *reinterpret_cast<uint4*>(o) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          if (lo_off) *reinterpret_cast<uint4*>(o + lo_off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-        }
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < kMaxA; ++j)
-        if (j < A) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), dm[j]);
-      for (int j = A; j < ld_dmu; ++j) store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), 0.0f);
-    }
-    if (ld_dval == 8 && (lo_off & 7) == 0 && ((uintptr_t)dval & 15) == 0) {
-      const bf16 h = __float2bfloat16(dv);
-      const bf16 l = __float2bfloat16(dv - __bfloat162float(h));
-      bf16* o = dval + (size_t)r * 8;
-      *reinterpret_cast<uint4*>(o) = make_uint4((uint32_t)__bfloat16_as_ushort(h), 0u, 0u, 0u);
-      if (lo_off) *reinterpret_cast<uint4*>(o + lo_off) = make_uint4((uint32_t)__bfloat16_as_ushort(l), 0u, 0u, 0u);
-    } else {
-      store_split(dval, lo_off, (size_t)(r * ld_dval), dv);
-      for (int j = 1; j < ld_dval; ++j) store_split(dval, lo_off, (size_t)(r * ld_dval + j), 0.0f);
-    }
-  }
-  // block reductions -> atomics
-  __shared__ float red[kHeadThreads / 32][2 * kMaxA + 5];
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  float t;
-  t = warp_sum(kl); if (l == 0) red[w][0] = t;
-  t = warp_sum(surr); if (l == 0) red[w][1] = t;
-  t = warp_sum(vloss); if (l == 0) red[w][2] = t;
-  t = warp_sum(ent); if (l == 0) red[w][3] = t;
-  t = warp_sum(dv); if (l == 0) red[w][4] = t;
-#pragma unroll
-  for (int j = 0; j < kMaxA; ++j) {
-    if (j < A) {
-      t = warp_sum(dm[j]); if (l == 0) red[w][5 + j] = t;
-      t = warp_sum(ds[j]); if (l == 0) red[w][5 + kMaxA + j] = t;
-    }
+    q = row_index(indices, r, s.N, env_begin, env_count);
+    const float mu = mu_new[r * A + j];
+    sd = std_param[j];
+    const float a = s.actions[q * A + j], mo = s.mu[q * A + j], so = s.sigma[q * A + j];
+    d = a - mu;
+    var = sd * sd;
+    t_a[tid] = -(d * d) / (2.0f * var) - c_log[j] - 0.918938533204672741780f;
+    t_b[tid] = logf(sd / so + 1.e-5f) + (so * so + (mo - mu) * (mo - mu)) / (2.0f * var) - 0.5f;
   }
   __syncthreads();
-  const int nslots = 5 + 2 * kMaxA;
-  for (int k = threadIdx.x; k < nslots; k += blockDim.x) {
-    if (k >= 5) { const int j = (k - 5) % kMaxA; if (j >= A) continue; }
-    float a = 0.0f;
-    for (int ww = 0; ww < kHeadThreads / 32; ++ww) a += red[ww][k];
-    if (k == 0) atomicAdd(stats + URLG_STAT_KL_SUM, a);
-    else if (k == 1) atomicAdd(stats + URLG_STAT_SURR_SUM, a);
-    else if (k == 2) atomicAdd(stats + URLG_STAT_VLOSS_SUM, a);
-    else if (k == 3) atomicAdd(stats + URLG_STAT_ENT_SUM, a);
-    else if (k == 4) atomicAdd(g_bias_val, a);
-    else if (k < 5 + kMaxA) atomicAdd(g_bias_mu + (k - 5), a);
-    else {
-      const int j = k - 5 - kMaxA;
-      if (blockIdx.x == 0) a += -hp.entropy_coef / std_param[j];   // d(-c_ent * mean entropy)/d sigma_j
-      atomicAdd(g_std + j, a);
+  if (j == 0) {
+    float kl = 0.0f, surr = 0.0f, vloss = 0.0f, ent = 0.0f, dv = 0.0f, dlp = 0.0f;
+    if (ok) {
+      float lp = 0.0f;
+      for (int k = 0; k < A; ++k) {
+        lp += t_a[e * A + k];
+        kl += t_b[e * A + k];
+        ent += 0.5f + 0.918938533204672741780f + c_log[k];
+      }
+      const float adv = s.advantages[q], old_lp = s.actions_log_prob[q];
+      const float ratio = expf(lp - old_lp);
+      const float lo = 1.0f - hp.clip_param, hi = 1.0f + hp.clip_param;
+      const float rc = fminf(fmaxf(ratio, lo), hi);
+      const float s1 = -adv * ratio, s2 = -adv * rc;
+      surr = fmaxf(s1, s2);
+      // d max(s1,s2)/d ratio (torch.max splits ties evenly; clamp passes gradient on [lo,hi] inclusive)
+      const float in_rng = (ratio >= lo && ratio <= hi) ? 1.0f : 0.0f;
+      float dr;
+      if (s1 > s2) dr = -adv;
+      else if (s1 < s2) dr = -adv * in_rng;
+      else dr = 0.5f * (-adv) + 0.5f * (-adv) * in_rng;
+      dlp = dr * ratio * inv_rows;
+      const float v = val_new[r], ret = s.returns[q], vo = s.values[q];
+      if (hp.use_clipped_value_loss) {
+        const float dvv = v - vo;
+        const float vc = vo + fminf(fmaxf(dvv, -hp.clip_param), hp.clip_param);
+        const float l1 = (v - ret) * (v - ret), l2 = (vc - ret) * (vc - ret);
+        vloss = fmaxf(l1, l2);
+        const float in_v = (dvv >= -hp.clip_param && dvv <= hp.clip_param) ? 1.0f : 0.0f;
+        const float g1 = 2.0f * (v - ret), g2 = 2.0f * (vc - ret) * in_v;
+        dv = l1 > l2 ? g1 : (l1 < l2 ? g2 : 0.5f * g1 + 0.5f * g2);
+      } else {
+        vloss = (ret - v) * (ret - v);
+        dv = 2.0f * (v - ret);
+      }
+      dv *= hp.value_loss_coef * inv_rows;
+      if (ld_dval == 8 && (lo_off & 7) == 0 && ((uintptr_t)dval & 15) == 0) {
+        const bf16 h = __float2bfloat16(dv);
+        const bf16 l = __float2bfloat16(dv - __bfloat162float(h));
+        bf16* o = dval + (size_t)r * 8;
+        *reinterpret_cast<uint4*>(o) = make_uint4((uint32_t)__bfloat16_as_ushort(h), 0u, 0u, 0u);
+        if (lo_off) *reinterpret_cast<uint4*>(o + lo_off) = make_uint4((uint32_t)__bfloat16_as_ushort(l), 0u, 0u, 0u);
+      } else {
+        store_split(dval, lo_off, (size_t)(r * ld_dval), dv);
+        for (int k = 1; k < ld_dval; ++k) store_split(dval, lo_off, (size_t)(r * ld_dval + k), 0.0f);
+      }
+      for (int k = A; k < ld_dmu; ++k) store_split(dmu, lo_off, (size_t)(r * ld_dmu + k), 0.0f);   // pad columns
     }
+    row_dlp[e] = dlp;
+    row_s[e * 5 + 0] = kl; row_s[e * 5 + 1] = surr; row_s[e * 5 + 2] = vloss; row_s[e * 5 + 3] = ent; row_s[e * 5 + 4] = dv;
+  }
+  __syncthreads();
+  float dmv = 0.0f, dsv = 0.0f;
+  if (ok) {
+    const float dlp = row_dlp[e];
+    dmv = (d / var) * dlp;                                   // d logp / d mu    * d loss / d logp
+    dsv = (d * d / (var * sd) - 1.0f / sd) * dlp;            // d logp / d sigma * d loss / d logp
+    store_split(dmu, lo_off, (size_t)(r * ld_dmu + j), dmv);
+  }
+  if (e < kHeadRows) { t_a[tid] = dmv; t_b[tid] = dsv; }
+  __syncthreads();
+  // column sums over the block's rows (fixed order), then one atomic per column and block
+  if (tid < A) {
+    float sm = 0.0f, ss = 0.0f;
+    for (int k = 0; k < kHeadRows; ++k) { sm += t_a[k * A + tid]; ss += t_b[k * A + tid]; }
+    atomicAdd(g_bias_mu + tid, sm);
+    if (blockIdx.x == 0) ss += -hp.entropy_coef / std_param[tid];   // d(-c_ent * mean entropy)/d sigma_j
+    atomicAdd(g_std + tid, ss);
+  } else if (tid >= 32 && tid < 37) {
+    const int k5 = tid - 32;
+    float a = 0.0f;
+    for (int k = 0; k < kHeadRows; ++k) a += row_s[k * 5 + k5];
+    if (k5 == 0) atomicAdd(stats + URLG_STAT_KL_SUM, a);
+    else if (k5 == 1) atomicAdd(stats + URLG_STAT_SURR_SUM, a);
+    else if (k5 == 2) atomicAdd(stats + URLG_STAT_VLOSS_SUM, a);
+    else if (k5 == 3) atomicAdd(stats + URLG_STAT_ENT_SUM, a);
+    else atomicAdd(g_bias_val, a);
   }
 }
 
@@ -431,7 +409,9 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     if (rc_c) return rc_c;
   }
   if (int rc = mlp_forward_pair(p, na, nc, rows, st)) return rc;
-  ppo_head_kernel<<<(int)((rows + kHeadThreads - 1) / kHeadThreads), kHeadThreads, 0, st>>>(
+  if (d.num_actions < 2 || d.num_actions > kMaxA) return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: 2..%d actions", kMaxA);
+  const int head_smem = (2 * kHeadRows * d.num_actions + 6 * kHeadRows + d.num_actions) * (int)sizeof(float);
+  ppo_head_kernel<<<(int)((rows + kHeadRows - 1) / kHeadRows), kHeadRows * d.num_actions, head_smem, st>>>(
       na.out, nc.out, p->params + d.std_off, *s, indices, rows, env_begin, env_count, *h, na.dout, na.opad, nc.dout,
       nc.opad, p->lo_off, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
       p->grads + nc.d.b_off[nc.d.num_layers - 1], p->stats);
