@@ -257,10 +257,12 @@ typedef struct urlg_ppo_hparams {
 
 /* Device-resident scalars of the update (float[URLG_STAT_COUNT]); nothing is read back per step. */
 enum {
-  URLG_STAT_LR = 0,        /* current learning rate (adaptive schedule runs on the device) */
-  URLG_STAT_STEP,          /* Adam step count */
-  URLG_STAT_KL_SUM,        /* this minibatch: sum over rows of KL */
+  /* the four per-minibatch sums come first: a data-parallel caller that lays the stats block directly behind the flat
+   * gradient buffer all-reduces [grads | these four] in ONE collective per minibatch */
+  URLG_STAT_KL_SUM = 0,    /* this minibatch: sum over rows of KL */
   URLG_STAT_SURR_SUM, URLG_STAT_VLOSS_SUM, URLG_STAT_ENT_SUM,   /* this minibatch: sums over rows */
+  URLG_STAT_LR,            /* current learning rate (adaptive schedule runs on the device) */
+  URLG_STAT_STEP,          /* Adam step count */
   URLG_STAT_GNORM_SQ,      /* this minibatch: squared gradient norm (after grad_scale) */
   URLG_STAT_CLIP_COEF,
   URLG_STAT_ACC_VLOSS, URLG_STAT_ACC_SURR, URLG_STAT_ACC_N,      /* accumulated minibatch means since last reset */

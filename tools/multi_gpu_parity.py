@@ -77,17 +77,38 @@ def main():
     oppo.perm, pppo.perm = torch.cat(glob), perms[rank]
     before = {n: p.detach().clone() for n, p in oac.named_parameters()}
     ov, osur = oppo.update()
+    eng = pppo.engine
+    pppo.cuda_graph_update = True                  # update 1 runs eagerly (warm-up), 2 captures + replays, 3 replays
+    snap = [t.clone() for t in (eng.flat, eng.exp_avg, eng.exp_avg_sq, eng.stats)]
+
+    def against_oracle():
+        worst_rel, worst_abs, n_in, n_tot = 0.0, 0.0, 0, 0
+        for (n, p), (_, q) in zip(pac.named_parameters(), oac.named_parameters()):
+            a, b = p.detach().cpu().numpy(), q.detach().numpy()
+            worst_rel = max(worst_rel, T.rel_l2(a, b))
+            d = np.abs(a - b)
+            worst_abs = max(worst_abs, float(d.max()))
+            n_in += int((d <= 1e-3).sum())
+            n_tot += d.size
+        return worst_rel, worst_abs, n_in, n_tot
+
     pv, psur = pppo.update()
     torch.cuda.synchronize()
-
-    worst_rel, worst_abs, n_in, n_tot = 0.0, 0.0, 0, 0
-    for (n, p), (_, q) in zip(pac.named_parameters(), oac.named_parameters()):
-        a, b = p.detach().cpu().numpy(), q.detach().numpy()
-        worst_rel = max(worst_rel, T.rel_l2(a, b))
-        d = np.abs(a - b)
-        worst_abs = max(worst_abs, float(d.max()))
-        n_in += int((d <= 1e-3).sum())
-        n_tot += d.size
+    worst_rel, worst_abs, n_in, n_tot = against_oracle()
+    eager_flat = eng.flat.clone()
+    # the same update again from the same state, now with the 20 minibatch steps AND their NCCL all-reduces as one graph
+    graph_rounds = []
+    for mode in ("capture+replay", "replay"):
+        for t, c in zip((eng.flat, eng.exp_avg, eng.exp_avg_sq, eng.stats), snap):
+            t.copy_(c)
+        eng.sync_weights()
+        sp.step = steps
+        gv, gsur = pppo.update()
+        torch.cuda.synchronize()
+        g_rel, g_abs, g_in, g_tot = against_oracle()
+        graph_rounds.append({"mode": mode, "graph": pppo._update_graph is not None, "update_param_rel_l2_worst": g_rel,
+                             "update_param_max_abs": g_abs, "update_frac_within_1e-3": g_in / g_tot,
+                             "vs_eager_max_abs": float((eng.flat - eager_flat).abs().max()), "losses": [gv, gsur]})
     moved = max(float((q.detach() - before[n]).abs().max()) for n, q in oac.named_parameters())
     # every rank must hold identical parameters
     flat = pppo.engine.flat.clone()
@@ -99,12 +120,16 @@ def main():
     res = {"world": world, "n_loc": n_loc, "steps": steps, "returns_max_abs_err": ret_err, "advantages_max_abs_err": adv_err,
            "update_param_rel_l2_worst": worst_rel, "update_param_max_abs": worst_abs, "update_frac_within_1e-3": n_in / n_tot,
            "oracle_param_moved_max": moved, "lr": [oppo.learning_rate, pppo.learning_rate],
-           "losses": [ov, pv, osur, psur], "ranks_bit_identical": bool(flags.item())}
-    ok = (adv_err < 1e-4 and ret_err < 1e-4 and worst_rel < 1e-3 and n_in / n_tot >= 0.9999 and worst_abs <= 3e-3 and
+           "losses": [ov, pv, osur, psur], "ranks_bit_identical": bool(flags.item()),
+           "update_graph_with_nccl": graph_rounds, "update_graph_launches": pppo.update_graph_launches}
+    graph_ok = all(g["graph"] and g["update_param_rel_l2_worst"] < 1e-3 and g["update_frac_within_1e-3"] >= 0.9999 and
+                   g["update_param_max_abs"] <= 3e-3 for g in graph_rounds) or not pppo._graph_nccl
+    ok = (graph_ok and adv_err < 1e-4 and ret_err < 1e-4 and worst_rel < 1e-3 and n_in / n_tot >= 0.9999 and worst_abs <= 3e-3 and
           abs(oppo.learning_rate - pppo.learning_rate) < 1e-6 * oppo.learning_rate + 1e-9 and res["ranks_bit_identical"])
     res["pass"] = bool(ok)
     if rank == 0:
         print(json.dumps(res), flush=True)
+    pppo.release_graphs()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)

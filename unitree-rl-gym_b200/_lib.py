@@ -107,7 +107,7 @@ class PpoHparams(C.Structure):
                 ("grad_scale", C.c_float), ("kl_count_scale", C.c_float)]
 
 
-(STAT_LR, STAT_STEP, STAT_KL_SUM, STAT_SURR_SUM, STAT_VLOSS_SUM, STAT_ENT_SUM, STAT_GNORM_SQ, STAT_CLIP_COEF,
+(STAT_KL_SUM, STAT_SURR_SUM, STAT_VLOSS_SUM, STAT_ENT_SUM, STAT_LR, STAT_STEP, STAT_GNORM_SQ, STAT_CLIP_COEF,
  STAT_ACC_VLOSS, STAT_ACC_SURR, STAT_ACC_N, STAT_KL_MEAN, STAT_BC1, STAT_BC2) = range(14)
 STAT_COUNT = 16
 

@@ -381,8 +381,13 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: indices/rows are required for a feed-forward policy");
   }
   if (rows > p->R) return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: rows %lld exceed max_rows %d", (long long)rows, p->R);
-  URLG_CUDA(cudaMemsetAsync(p->grads, 0, (size_t)d.num_params * sizeof(float), st));
-  zero_minibatch_stats_kernel<<<1, 32, 0, st>>>(p->stats);
+  // when the caller laid the stats block directly behind the flat gradients (the data-parallel layout, one all-reduce over
+  // [grads | KL, surrogate, value, entropy sums]) the same memset clears the four sums; GNORM_SQ is overwritten by
+  // urlg_ppo_apply before anything reads it
+  static_assert(URLG_STAT_KL_SUM == 0 && URLG_STAT_ENT_SUM == 3, "the four per-minibatch sums lead the stats block");
+  const bool sums_behind_grads = p->stats == p->grads + d.num_params;
+  URLG_CUDA(cudaMemsetAsync(p->grads, 0, ((size_t)d.num_params + (sums_behind_grads ? 4 : 0)) * sizeof(float), st));
+  if (!sums_behind_grads) zero_minibatch_stats_kernel<<<1, 32, 0, st>>>(p->stats);
   NetWs &na = p->net[0], &nc = p->net[1];
   if (!d.recurrent) {
     const float* cobs = s->privileged_observations ? s->privileged_observations : s->observations;

@@ -10,7 +10,11 @@ legged_robot_config.py:257-270).  Same constructor and methods; what each does o
                       learning-rate rule runs on the device, so there is ONE host read per update (the returned
                       mean losses) instead of the reference's 40.
 """
+import atexit
 import ctypes as C
+import gc
+import os
+import weakref
 
 import torch
 import torch.distributed as dist
@@ -112,9 +116,12 @@ class PPO:
         self.update_graph_launches = 0
         self._idx_buf = None
         self._update_graph = None
+        self._atexit_hooked = False
         self._update_warm = None
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank() if self.world > 1 else 0
+        self._graph_nccl = os.environ.get("URLG_GRAPH_NCCL", "0") == "1" and (
+            self.world > 1 and dist.get_backend() == "nccl")
 
     # ---- learning rate lives on the device (adaptive schedule); the attribute stays readable / writable
     @property
@@ -262,9 +269,18 @@ class PPO:
                 _lib.check(L.urlg_ppo_minibatch_grads(eng.handle, C.byref(sd), _lib.ptr(ind), rows, e0, ec,
                                                       C.byref(h), st))
                 if self.world > 1:
-                    dist.all_reduce(eng.grads)
-                    dist.all_reduce(eng.stats[_lib.STAT_KL_SUM:_lib.STAT_ENT_SUM + 1])
+                    dist.all_reduce(eng.grads_and_sums)     # flat gradients + (KL, surrogate, value, entropy) sums
                 _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), st))
+
+    def release_graphs(self):
+        """Destroy the captured update graph.  With several ranks it holds NCCL kernels: NCCL keeps the communicator
+        alive until every graph that captured its collectives is destroyed, so this must run before
+        `dist.destroy_process_group()` (also registered with atexit when such a graph is captured)."""
+        if self._update_graph is not None:
+            torch.cuda.synchronize()
+            self._update_graph = None
+            gc.collect()
+            torch.cuda.synchronize()
 
     def update(self):
         eng, s = self._check_engine(), self.storage
@@ -283,11 +299,13 @@ class PPO:
             self._idx_buf.copy_(idx)           # static buffer: the captured graph gathers through it
             idx = self._indices = self._idx_buf
         # opt-in (`cuda_graph_update`, set by the runner's `cuda_graph` cfg key): the 20 minibatch steps (~800 launches
-        # for the MLP, ~8000 for the LSTM's per-step BPTT) replayed as one graph; single process only (NCCL calls are
-        # left eager), and invalidated when the engine / storage it captured is replaced
+        # for the MLP, ~8000 for the LSTM's per-step BPTT) replayed as one graph, invalidated when the engine / storage
+        # it captured is replaced.  With several ranks the per-minibatch NCCL all-reduces (flat gradients + KL / loss
+        # sums) are captured as nodes of the same graph (NCCL >= 2.9.6 enqueues capturable kernels; every rank captures
+        # and replays the same sequence) when URLG_GRAPH_NCCL=1; by default the multi-rank update stays eager.
         key = (id(eng), s.desc().observations, self.clip_param, self.value_loss_coef, self.entropy_coef, self.max_grad_norm,
                self.desired_kl, self.schedule, self.num_learning_epochs, self.num_mini_batches, self.use_clipped_value_loss)
-        if self.cuda_graph_update and self.world == 1:
+        if self.cuda_graph_update and (self.world == 1 or self._graph_nccl):
             if self._update_graph is None or self._update_graph[0] != key:
                 if self._update_warm != key:
                     self._minibatch_loop(idx)          # first update runs eagerly (lazy init, warm-up), capture on the next
@@ -296,10 +314,15 @@ class PPO:
                     torch.cuda.synchronize()
                     g = torch.cuda.CUDAGraph()
                     n0 = _lib.lib().urlg_launch_count()
-                    with torch.cuda.graph(g):
+                    # thread-local capture mode: the NCCL watchdog thread may poll events of earlier collectives
+                    with torch.cuda.graph(g, capture_error_mode="thread_local" if self.world > 1 else "global"):
                         self._minibatch_loop(idx)
                     self.update_graph_launches = _lib.lib().urlg_launch_count() - n0
                     self._update_graph = (key, g)
+                    if self.world > 1 and not self._atexit_hooked:
+                        self._atexit_hooked = True
+                        ref = weakref.ref(self)
+                        atexit.register(lambda: ref() is not None and ref().release_graphs())
                     g.replay()
             else:
                 self._update_graph[1].replay()

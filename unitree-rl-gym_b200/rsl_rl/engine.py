@@ -32,10 +32,14 @@ class PolicyEngine:
         n = sum(p.numel() for p in params)
         self.num_params = n
         self.flat = torch.zeros(n, device=dev)
-        self.grads = torch.zeros(n, device=dev)
+        # flat gradients and the stats block share one allocation: [grads (n) | stats (STAT_COUNT)], so that the
+        # data-parallel update all-reduces the gradients and the four per-minibatch sums (stats[0:4]) in one collective
+        self._grads_stats = torch.zeros(n + _lib.STAT_COUNT, device=dev)
+        self.grads = self._grads_stats[:n]
         self.exp_avg = torch.zeros(n, device=dev)
         self.exp_avg_sq = torch.zeros(n, device=dev)
-        self.stats = torch.zeros(_lib.STAT_COUNT, device=dev)
+        self.stats = self._grads_stats[n:]
+        self.grads_and_sums = self._grads_stats[:n + _lib.STAT_ENT_SUM + 1]
         self.offsets = {}
         off = 0
         with torch.no_grad():
