@@ -120,6 +120,27 @@ def test_update_graph_equals_eager(task):
     assert rb.alg._update_graph is not None
 
 
+def test_release_graphs_drops_and_recaptures():
+    """PPO.release_graphs() (run before dist.destroy_process_group when the graph holds NCCL kernels) destroys the captured
+    update graph; the next updates warm up / capture again and keep training."""
+    n = 128
+    r = make_runner("go2", n)
+    r.alg.cuda_graph_update = True
+    T = r.num_steps_per_env
+    perm = torch.randperm(n * T, generator=torch.Generator().manual_seed(5))
+    for _ in range(2):
+        finish(r, eager_rollout(r), perm)
+    assert r.alg._update_graph is not None
+    r.alg.release_graphs()
+    assert r.alg._update_graph is None
+    before = r.alg.engine.flat.clone()
+    finish(r, eager_rollout(r), perm)                    # same key: captures again
+    torch.cuda.synchronize()
+    assert r.alg._update_graph is not None
+    assert not torch.equal(before, r.alg.engine.flat)
+    assert torch.isfinite(r.alg.engine.flat).all()
+
+
 def test_rollout_graph_with_host_traffic_hooks():
     """RolloutGraph.capture(pre_step, post_step, epilogue): frame uploads from pinned host memory and per-step reward /
     done read-backs recorded on forked streams inside the capture (one launch per rollout, bench.py's e2e path) leave
