@@ -145,7 +145,7 @@ def config_dict(task, n, world, graph):
             "task": task, "envs_per_gpu": n, "rollout_steps": ROLLOUT, "epochs": 5, "mini_batches": 4,
             "parallelism": f"dp{world} (env shards, flat-gradient all-reduce)" if world > 1 else "single GPU",
             "rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph; the 20 minibatch steps of "
-                              "the update as a second graph when single-process; N>1: eager update, or graph incl. the NCCL all-reduces with URLG_GRAPH_NCCL=1)" if graph else "eager",
+                              "the update as a second graph, N>1: with its per-minibatch NCCL all-reduce as graph nodes unless URLG_GRAPH_NCCL=0)" if graph else "eager",
             "l2_policy": "working set per iteration (35 MB rollout storage + 8-frame physics pool) is cycled; every timed "
                          "iteration additionally starts after a 256 MiB L2 flush write outside the event bracket"}
 
@@ -218,7 +218,7 @@ def own_arm(a):
     env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     use_graph = (not a.no_graph) and RolloutGraph.supported(runner)
-    alg.cuda_graph_update = use_graph      # PPO.update replays its 20 minibatch steps as one graph (N>1: only with URLG_GRAPH_NCCL=1)
+    alg.cuda_graph_update = use_graph      # PPO.update replays its 20 minibatch steps as one graph (N>1: NCCL all-reduces captured too unless URLG_GRAPH_NCCL=0)
 
     def eager_rollout():
         obs = env.get_observations()

@@ -120,7 +120,7 @@ class PPO:
         self._update_warm = None
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank() if self.world > 1 else 0
-        self._graph_nccl = os.environ.get("URLG_GRAPH_NCCL", "0") == "1" and (
+        self._graph_nccl = os.environ.get("URLG_GRAPH_NCCL", "1") != "0" and (
             self.world > 1 and dist.get_backend() == "nccl")
 
     # ---- learning rate lives on the device (adaptive schedule); the attribute stays readable / writable
@@ -302,7 +302,7 @@ class PPO:
         # for the MLP, ~8000 for the LSTM's per-step BPTT) replayed as one graph, invalidated when the engine / storage
         # it captured is replaced.  With several ranks the per-minibatch NCCL all-reduces (flat gradients + KL / loss
         # sums) are captured as nodes of the same graph (NCCL >= 2.9.6 enqueues capturable kernels; every rank captures
-        # and replays the same sequence) when URLG_GRAPH_NCCL=1; by default the multi-rank update stays eager.
+        # and replays the same sequence; measured clean at 2, 4 and 8 ranks); URLG_GRAPH_NCCL=0 keeps the multi-rank update eager.
         key = (id(eng), s.desc().observations, self.clip_param, self.value_loss_coef, self.entropy_coef, self.max_grad_norm,
                self.desired_kl, self.schedule, self.num_learning_epochs, self.num_mini_batches, self.use_clipped_value_loss)
         if self.cuda_graph_update and (self.world == 1 or self._graph_nccl):
