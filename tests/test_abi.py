@@ -49,3 +49,38 @@ def test_no_cpu_fallback():
     from unitree_rl_gym_b200 import _lib
     with pytest.raises(RuntimeError):
         _lib.ptr(torch.zeros(4))
+
+
+def _probe(body):
+    import subprocess
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "p.c")
+        open(c, "w").write('#include <stdio.h>\n#include "urlg_b200.h"\nint main(){' + body + 'return 0;}\n')
+        exe = os.path.join(d, "p")
+        subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), c, "-o", exe])
+        return subprocess.check_output([exe]).split()
+
+
+def test_policy_side_struct_sizes_match_header():
+    """The ctypes mirrors of the policy / storage / PPO structs have the size gcc gives the header's."""
+    from unitree_rl_gym_b200 import _lib
+    names = [("urlg_gemm_desc", _lib.GemmDesc), ("urlg_mlp_desc", _lib.MlpDesc), ("urlg_policy_desc", _lib.PolicyDesc),
+             ("urlg_storage", _lib.Storage), ("urlg_ppo_hparams", _lib.PpoHparams)]
+    body = 'printf("' + " ".join("%zu" for _ in names) + '\\n",' + ",".join(f"sizeof({n})" for n, _ in names) + ");"
+    sizes = list(map(int, _probe(body)))
+    for (n, cls), sz in zip(names, sizes):
+        assert ctypes.sizeof(cls) == sz, n
+
+
+def test_stat_slots_match_header_and_lead_with_the_minibatch_sums():
+    """_lib.STAT_* equal the header's enum; the four per-minibatch sums are slots 0..3 so that a data-parallel caller
+    all-reduces [flat gradients | sums] as one contiguous range."""
+    from unitree_rl_gym_b200 import _lib
+    names = ["KL_SUM", "SURR_SUM", "VLOSS_SUM", "ENT_SUM", "LR", "STEP", "GNORM_SQ", "CLIP_COEF", "ACC_VLOSS", "ACC_SURR",
+             "ACC_N", "KL_MEAN", "BC1", "BC2", "COUNT"]
+    body = 'printf("' + " ".join("%d" for _ in names) + '\\n",' + ",".join("URLG_STAT_" + n for n in names) + ");"
+    vals = list(map(int, _probe(body)))
+    for n, v in zip(names, vals):
+        assert getattr(_lib, "STAT_" + n) == v, n
+    assert [_lib.STAT_KL_SUM, _lib.STAT_SURR_SUM, _lib.STAT_VLOSS_SUM, _lib.STAT_ENT_SUM] == [0, 1, 2, 3]
