@@ -100,7 +100,7 @@ static int carve_pass(urlg_policy* p, Carver& c) {
   } else if (d.actor.dims[0] != d.num_actor_obs || d.critic.dims[0] != d.num_critic_obs) {
     return fail(URLG_EINVAL, "policy: MLP input widths must equal the observation widths");
   }
-  p->red = c.take<float>(256);
+  p->red = c.take<float>(256 + 8);   // 256 block partials of the gradient norm + the last-block ticket (red[256], as uint)
   return URLG_OK;
 }
 
@@ -335,6 +335,10 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
   if (!rc && total > workspace_bytes) rc = fail(URLG_EINVAL, "urlg_policy_create: workspace too small (%lld < %lld)",
                                                 (long long)workspace_bytes, (long long)total);
   if (rc) { delete p; return rc; }
+  if (cudaMemset(p->red + 256, 0, 8 * sizeof(float)) != cudaSuccess) {       // ticket of grad_norm_scalars_kernel starts at 0
+    delete p;
+    return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
+  }
   p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||

@@ -288,31 +288,35 @@ int mlp_backward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, bf16* dx
 }
 
 // ---------------------------------------------------------------- apply: norm, LR rule, clip, Adam
+// Gradient norm + the host-side scalar logic of PPO.update in ONE launch: every block writes its partial sum of squares,
+// the block that draws the last ticket sums the (<= 256) partials in block order (fixed-shape tree: the norm, hence the
+// clip coefficient and the whole Adam step, is bit-reproducible, so data-parallel ranks stay bit-identical) and then
+// runs the LR rule / Adam bias corrections / loss accumulators as one thread -- no .item(), no KL branch sync.
 __global__ void __launch_bounds__(256)
-grad_sumsq_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ partials) {
+grad_norm_scalars_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ partials,
+                         unsigned int* __restrict__ ticket, float* __restrict__ stats, const urlg_ppo_hparams hp,
+                         float rows_total) {
   float acc = 0.0f;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float x = g[i] * scale;
     acc += x * x;
   }
   acc = warp_sum(acc);
-  __shared__ float sh[8];
+  __shared__ float sh[256];
+  __shared__ bool last;
   if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
   __syncthreads();
   if (threadIdx.x == 0) {
     float a = 0.0f;
     for (int k = 0; k < (int)(blockDim.x >> 5); ++k) a += sh[k];
-    partials[blockIdx.x] = a;      // summed in block order by ppo_scalars_kernel: the norm (hence the clip coefficient and the
-                                   // whole Adam step) is bit-reproducible, so data-parallel ranks stay bit-identical
+    partials[blockIdx.x] = a;
+    __threadfence();                                              // partial visible before the ticket is drawn
+    last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;     // wraps to 0 on the last draw: ready for the next launch
   }
-}
-
-// One block (thread 0 after the norm reduction): the host-side scalar logic of PPO.update moved onto the device (no .item(), no KL branch sync).
-__global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hparams hp, float rows_total,
-                                   const float* __restrict__ partials, int num_partials) {
-  // fixed-shape tree over the (<= 256) block partials: deterministic, and one load latency instead of 256 chained ones
-  __shared__ float sh[256];
-  sh[threadIdx.x] = (int)threadIdx.x < num_partials ? partials[threadIdx.x] : 0.0f;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  sh[threadIdx.x] = threadIdx.x < gridDim.x ? __ldcg(partials + threadIdx.x) : 0.0f;
   __syncthreads();
   for (int w = 128; w > 0; w >>= 1) {
     if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
@@ -332,7 +336,7 @@ __global__ void ppo_scalars_kernel(float* __restrict__ stats, const urlg_ppo_hpa
   stats[URLG_STAT_STEP] = step;
   stats[URLG_STAT_BC1] = 1.0f - powf(hp.beta1, step);
   stats[URLG_STAT_BC2] = 1.0f - powf(hp.beta2, step);
-  const float total_norm = sqrtf(stats[URLG_STAT_GNORM_SQ]);
+  const float total_norm = sqrtf(sh[0]);
   stats[URLG_STAT_CLIP_COEF] = hp.max_grad_norm > 0.0f ? fminf(hp.max_grad_norm / (total_norm + 1e-6f), 1.0f) : 1.0f;
   stats[URLG_STAT_ACC_VLOSS] += stats[URLG_STAT_VLOSS_SUM] / rows_total;
   stats[URLG_STAT_ACC_SURR] += stats[URLG_STAT_SURR_SUM] / rows_total;
@@ -445,8 +449,10 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   int blocks = (int)((n + 255) / 256);
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
   const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
-  grad_sumsq_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red);
-  ppo_scalars_kernel<<<1, 256, 0, st>>>(p->stats, *h, (float)p->last_rows * h->kl_count_scale, p->red, nparts);
+  grad_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red,
+                                                   reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                   (float)p->last_rows * h->kl_count_scale);
+  URLG_LAUNCH_CHECK();
   adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
   URLG_LAUNCH_CHECK();
   return sync_weights(p, st);
