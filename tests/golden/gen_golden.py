@@ -26,6 +26,10 @@ CASES = {
     "h1_n40": ("h1", 40, False, 6),
     "g1_n64": ("g1", 64, True, 6),
     "h1_2_n33": ("h1_2", 33, False, 5),
+    # SURVEY.md 8(f) row 1 ("next"): the unmodified GO2HandstandEnv on the same synthetic frames.  Reference vectors for
+    # the round that ports the task (46-dim obs with contact flags, gravity-based termination, 13 extra reward terms,
+    # termination = -5); no product code consumes this fixture yet (tests only check it is well-formed).
+    "go2_handstand_n64": ("go2_handstand", 64, False, 6),
 }
 SEED = 1
 NUM_FRAMES = 4
@@ -114,6 +118,9 @@ def motion_pt():
 
 
 if __name__ == "__main__":
+    only = sys.argv[1:]                    # optional: case names (and/or "motion_pt") to (re)generate
     for c in CASES:
-        run_case(c)
-    motion_pt()
+        if not only or c in only:
+            run_case(c)
+    if not only or "motion_pt" in only:
+        motion_pt()

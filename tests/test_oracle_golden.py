@@ -1,5 +1,7 @@
 """The oracle's env port (oracle/env_port.py) against fixtures produced by the unmodified
 reference classes (tests/golden/gen_golden.py).  CPU only."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -78,3 +80,35 @@ def test_env_port_matches_reference_fixture(case):
         snap = port_snapshot(port)
         for k in H.snapshot_keys(fx, f"step{t}"):
             H.compare(k, snap[k], fx[f"step{t}/{k}"], f"step{t}/")
+
+
+def test_handstand_reference_fixture_frame_transforms():
+    """SURVEY.md 8(f) row 1 groundwork: the fixture recorded from the UNMODIFIED GO2HandstandEnv (46-dim obs, 17 active
+    reward terms + termination) is well-formed, and the oracle's frame-transform restatements (the part of the path the
+    handstand task shares, E4) reproduce its rpy / base_ang_vel / projected_gravity on every env that was not reset
+    in the step (a reset rewrites root_states after the transforms were taken)."""
+    from oracle.env_port import quat_rotate_inverse, euler_xyz
+    fx = np.load(os.path.join(H.GOLDEN, "env_go2_handstand_n64.npz"))
+    names = [str(x) for x in fx["const/reward_names"]]
+    for n in ("front_feet_contact", "front_feet_together", "front_hip_neutral", "hind_feet_no_contact", "pose",
+              "stability", "stay_still", "orientation", "base_height"):
+        assert n in names
+    steps = int(fx["const/scalars"][4])
+    assert fx["step0/obs_buf"].shape == (64, 46)
+    checked = 0
+    for t in range(steps):
+        keep = ~fx[f"step{t}/reset_buf"].astype(bool)
+        assert keep.sum() > 32 and (~keep).sum() > 0          # resets fire in every recorded step
+        root = torch.from_numpy(fx[f"step{t}/root_states"])[torch.from_numpy(keep)]
+        q = root[:, 3:7]
+        grav = torch.tensor([[0.0, 0.0, -1.0]]).repeat(q.shape[0], 1)
+        np.testing.assert_allclose(quat_rotate_inverse(q, grav).numpy(), fx[f"step{t}/projected_gravity"][keep],
+                                   rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(quat_rotate_inverse(q, root[:, 10:13]).numpy(), fx[f"step{t}/base_ang_vel"][keep],
+                                   rtol=1e-5, atol=1e-6)
+        rpy = euler_xyz(q)
+        rpy = torch.stack(list(rpy), dim=1) if isinstance(rpy, (tuple, list)) else rpy
+        np.testing.assert_allclose(rpy.numpy(), fx[f"step{t}/rpy"][keep], rtol=1e-5, atol=1e-6)
+        assert np.isfinite(fx[f"step{t}/rew_buf"]).all() and np.isfinite(fx[f"step{t}/obs_buf"]).all()
+        checked += int(keep.sum())
+    assert checked > 300
