@@ -112,3 +112,28 @@ def test_handstand_reference_fixture_frame_transforms():
         assert np.isfinite(fx[f"step{t}/rew_buf"]).all() and np.isfinite(fx[f"step{t}/obs_buf"]).all()
         checked += int(keep.sum())
     assert checked > 300
+
+
+def test_handstand_termination_restatement_is_bit_exact():
+    """oracle/handstand_port.handstand_termination against the reference's reset / time-out masks, step by step.  The
+    snapshot's episode_length_buf is already zeroed for reset envs, so the pre-reset counter is rebuilt from the planted
+    lengths (+1 per step, 0 after a reset) exactly as post_physics_step does (legged_robot.py:681)."""
+    from oracle.handstand_port import handstand_termination
+    fx = np.load(os.path.join(H.GOLDEN, "env_go2_handstand_n64.npz"))
+    steps, P = int(fx["const/scalars"][4]), int(fx["const/scalars"][5])
+    max_len = int(fx["const/scalars"][1])
+    n = fx["step0/obs_buf"].shape[0]
+    term_idx = torch.from_numpy(fx["const/termination_contact_indices"]).long()
+    contact = torch.from_numpy(fx["frames/contact"]).reshape(P, n, -1, 3)
+    ep = torch.from_numpy(fx["planted_episode_length"]).long()
+    fired = 0
+    for t in range(steps):
+        ep = ep + 1
+        reset, time_out = handstand_termination(contact[(t + 1) % P], term_idx,   # frame 0 went to reset()
+                                                torch.from_numpy(fx[f"step{t}/projected_gravity"]), ep, max_len)
+        assert np.array_equal(reset.numpy(), fx[f"step{t}/reset_buf"].astype(bool)), t
+        assert np.array_equal(time_out.numpy(), fx[f"step{t}/time_out_buf"].astype(bool)), t
+        fired += int(reset.sum())
+        ep = torch.where(reset, torch.zeros_like(ep), ep)
+        assert np.array_equal(ep.numpy(), fx[f"step{t}/episode_length_buf"])
+    assert fired >= 10
