@@ -2,7 +2,7 @@
 
 First pieces of a CPU restatement of the reference's go2_handstand task ("next"), pinned to
 tests/golden/env_go2_handstand_n64.npz (recorded from the unmodified GO2HandstandEnv under oracle/refharness).
-Only the termination rule is restated so far; the observation layout, the PD variant and the 13 extra reward terms
+Restated so far: the termination rule and the PD variant; the observation layout and the 13 extra reward terms
 follow when the task is ported.
 """
 import torch
@@ -28,3 +28,20 @@ def handstand_termination(contact_forces, termination_contact_indices, projected
     fallen = (cos_up > -0.2) & (cos_up < 0.2)
     time_out = episode_length_buf > max_episode_length
     return illegal | fallen | time_out, time_out
+
+
+def handstand_pd_torques(actions, dof_pos, dof_vel, p_gains, d_gains, default_dof_pos, action_scale, rear_dof_idx,
+                         rear_center, rear_limit):
+    """reference: legged_gym/envs/go2/go2_handstand_env.py:326-350 (_compute_torques override; `actions` already
+    clipped to +-clip_actions by LeggedRobot.step, legged_robot.py:623-624).
+
+      target = default_dof_pos + action_scale * actions                                   (:333)
+      target[:, rear] = clamp(target[:, rear], rear_center - rear_limit, rear_center + rear_limit)   (:336-346)
+      torque = kp * (target - q) - kd * qd        -- no torque-limit clip, unlike the base class   (:349-350)
+    rear = the six RL_/RR_ hip, thigh, calf joints (:27-39), rear_center = handstand pose of those joints (:41),
+    rear_limit = 0.15 rad (:42).
+    """
+    targets = default_dof_pos + action_scale * actions
+    if rear_dof_idx.numel() > 0:
+        targets[:, rear_dof_idx] = torch.clamp(targets[:, rear_dof_idx], rear_center - rear_limit, rear_center + rear_limit)
+    return p_gains * (targets - dof_pos) - d_gains * dof_vel

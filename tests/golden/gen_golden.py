@@ -81,6 +81,13 @@ def run_case(name):
     out["const/termination_contact_indices"] = env.termination_contact_indices.numpy()
     out["const/env_origins"] = env.env_origins.numpy()
     out["const/base_init_state"] = env.base_init_state.numpy()
+    if hasattr(env, "rear_dof_idx"):          # go2_handstand: constants of its PD / pose overrides
+        out["const/handstand/rear_dof_idx"] = env.rear_dof_idx.numpy()
+        out["const/handstand/rear_center"] = env.rear_center.numpy()
+        out["const/handstand/rear_limit"] = np.array(env.rear_limit, dtype=np.float64)
+        out["const/handstand/pose_targets"] = env.pose_targets[0].numpy()
+        out["const/handstand/action_scale_clip"] = np.array([env.cfg.control.action_scale,
+                                                             env.cfg.normalization.clip_actions], dtype=np.float64)
     out["const/reward_names"] = np.array(env.reward_names)
     out["const/reward_scales"] = np.array([env.reward_scales[k] for k in env.reward_names], dtype=np.float64)
     out["const/scalars"] = np.array([env.dt, env.max_episode_length, env.cfg.domain_rand.push_interval,

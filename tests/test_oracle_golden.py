@@ -137,3 +137,27 @@ def test_handstand_termination_restatement_is_bit_exact():
         ep = torch.where(reset, torch.zeros_like(ep), ep)
         assert np.array_equal(ep.numpy(), fx[f"step{t}/episode_length_buf"])
     assert fired >= 10
+
+
+def test_handstand_pd_restatement_matches_reference_torques():
+    """oracle/handstand_port.handstand_pd_torques against the reference's `torques` buffer (the last decimation substep
+    of each recorded step: dof frame (t+1) % P, substep decimation-1; frame 0 went to reset()) to 1e-5."""
+    from oracle.handstand_port import handstand_pd_torques
+    fx = np.load(os.path.join(H.GOLDEN, "env_go2_handstand_n64.npz"))
+    steps, P = int(fx["const/scalars"][4]), int(fx["const/scalars"][5])
+    n, A = fx["step0/torques"].shape
+    scale, clip = fx["const/handstand/action_scale_clip"]
+    t_ = torch.from_numpy
+    idx = t_(fx["const/handstand/rear_dof_idx"]).long()
+    assert idx.tolist() == [6, 7, 8, 9, 10, 11]                   # RL_*, RR_* in the go2 DOF order of SURVEY 8(a).4
+    clamped = 0
+    for t in range(steps):
+        a = t_(fx[f"actions/{t}"]).clamp(-clip, clip)
+        d = t_(fx["frames/dof"][(t + 1) % P, 3]).view(n, A, 2)
+        tq = handstand_pd_torques(a, d[..., 0], d[..., 1], t_(fx["const/p_gains"]), t_(fx["const/d_gains"]),
+                                  t_(fx["const/default_dof_pos"]), float(scale), idx,
+                                  t_(fx["const/handstand/rear_center"]), float(fx["const/handstand/rear_limit"]))
+        np.testing.assert_allclose(tq.numpy(), fx[f"step{t}/torques"], rtol=1e-5, atol=1e-5)
+        lim = t_(fx["const/torque_limits"])
+        clamped += int((tq.abs() > lim).sum())
+    assert clamped > 0            # the override really leaves torques beyond the URDF effort limits unclipped
