@@ -2,8 +2,8 @@
 
 First pieces of a CPU restatement of the reference's go2_handstand task ("next"), pinned to
 tests/golden/env_go2_handstand_n64.npz (recorded from the unmodified GO2HandstandEnv under oracle/refharness).
-Restated so far: the termination rule and the PD variant; the observation layout and the 13 extra reward terms
-follow when the task is ported.
+Restated so far: the termination rule, the PD variant and the 46-dim observation; the 13 extra reward terms follow
+when the task is ported.
 """
 import torch
 
@@ -45,3 +45,28 @@ def handstand_pd_torques(actions, dof_pos, dof_vel, p_gains, d_gains, default_do
     if rear_dof_idx.numel() > 0:
         targets[:, rear_dof_idx] = torch.clamp(targets[:, rear_dof_idx], rear_center - rear_limit, rear_center + rear_limit)
     return p_gains * (targets - dof_pos) - d_gains * dof_vel
+
+
+def handstand_observations(base_ang_vel, projected_gravity, dof_pos, dof_vel, default_dof_pos, actions, contact_forces,
+                           front_feet_indices, hind_feet_indices, ang_vel_scale, dof_pos_scale, dof_vel_scale,
+                           noise_uniforms=None, noise_scale_vec=None, flips=None):
+    """reference: legged_gym/envs/go2/go2_handstand_env.py:140-176 (the second, effective compute_observations).
+
+    46 = [base_ang_vel*s (3), projected_gravity (3), (q - q_default)*s (12), qd*s (12), actions (12),
+          1[F_z(front feet) > 5] (2), 1[F_z(hind feet) > 5] (2)]                                   (:141-155)
+    noise: obs += (2u - 1) * noise_scale_vec, u uniform per element                                (:157-158)
+    then the four contact flags are re-binarised and flipped with probability 0.01:
+      flag = (flag > 0.5) xor flip                                                                 (:160-169)
+    `flips` (bool [N, 4]) are the Bernoulli draws; None = no flip.  No command and no base linear velocity in this
+    observation; privileged_obs_buf is a clone (:172).
+    """
+    front = (contact_forces[:, front_feet_indices, 2] > 5.0).float()
+    hind = (contact_forces[:, hind_feet_indices, 2] > 5.0).float()
+    n = base_ang_vel.shape[0]
+    obs = torch.cat((base_ang_vel * ang_vel_scale, projected_gravity, (dof_pos - default_dof_pos) * dof_pos_scale,
+                     dof_vel * dof_vel_scale, actions, front.view(n, -1), hind.view(n, -1)), dim=-1)
+    if noise_uniforms is not None:
+        obs = obs + (2.0 * noise_uniforms - 1.0) * noise_scale_vec
+        f = flips if flips is not None else torch.zeros(n, 4, dtype=torch.bool)
+        obs[:, -4:] = torch.logical_xor(obs[:, -4:] > 0.5, f).float()
+    return obs

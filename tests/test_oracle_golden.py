@@ -161,3 +161,33 @@ def test_handstand_pd_restatement_matches_reference_torques():
         lim = t_(fx["const/torque_limits"])
         clamped += int((tq.abs() > lim).sum())
     assert clamped > 0            # the override really leaves torques beyond the URDF effort limits unclipped
+
+
+def test_handstand_observation_restatement_matches_reference():
+    """oracle/handstand_port.handstand_observations against the reference obs_buf: the 42 continuous columns (incl. the
+    noise, drawn from the shared Philox table at step t+2 — reset() took steps 0 and 1) to 1e-5; the four contact flags
+    are exact up to the reference's 1 % Bernoulli flips, which come from torch's global generator (not replayable)."""
+    from oracle import philox
+    from oracle.handstand_port import handstand_observations
+    fx = np.load(os.path.join(H.GOLDEN, "env_go2_handstand_n64.npz"))
+    steps, P, seed = int(fx["const/scalars"][4]), int(fx["const/scalars"][5]), int(fx["const/scalars"][6])
+    n, A = fx["step0/torques"].shape
+    O = fx["step0/obs_buf"].shape[1]
+    t_ = torch.from_numpy
+    feet = t_(fx["const/feet_indices"]).long()
+    nsv = t_(fx["const/noise_scale_vec"])
+    flipped = total = 0
+    for t in range(steps):
+        d = t_(fx[f"step{t}/dof_state"]).view(n, A, 2)
+        u = philox.uniform_table(seed, philox.STREAM_ENV, np.arange(n), t + 2, 14 + A + O)[:, 14 + A:14 + A + O]
+        obs = handstand_observations(t_(fx[f"step{t}/base_ang_vel"]), t_(fx[f"step{t}/projected_gravity"]), d[..., 0],
+                                     d[..., 1], t_(fx["const/default_dof_pos"]), t_(fx[f"step{t}/actions"]),
+                                     t_(fx["frames/contact"][(t + 1) % P]).view(n, -1, 3), feet[[0, 1]], feet[[2, 3]],
+                                     0.25, 1.0, 0.05, t_(u.astype(np.float32)), nsv)
+        ref = fx[f"step{t}/obs_buf"]
+        np.testing.assert_allclose(obs[:, :-4].numpy(), ref[:, :-4], rtol=1e-5, atol=1e-6)
+        assert set(np.unique(ref[:, -4:])) <= {0.0, 1.0}
+        flipped += int((obs[:, -4:].numpy() != ref[:, -4:]).sum())
+        total += 4 * n
+        np.testing.assert_array_equal(fx[f"step{t}/privileged_obs_buf"], ref)
+    assert flipped <= 0.04 * total          # p = 0.01 flips; 1536 draws
