@@ -70,3 +70,44 @@ def handstand_observations(base_ang_vel, projected_gravity, dof_pos, dof_vel, de
         f = flips if flips is not None else torch.zeros(n, 4, dtype=torch.bool)
         obs[:, -4:] = torch.logical_xor(obs[:, -4:] > 0.5, f).float()
     return obs
+
+
+# ---- reward terms of the handstand task that read only base-frame velocities, gravity, feet contact and hip angles.
+#      Each returns [N] f32 BEFORE the scale*dt factor (legged_robot.py:770-787 applies it).  Still to restate:
+#      base_height (:237-246), pose (:277-307), front_feet_together (:360-373, needs feet_pos), energy (:319-324).
+def reward_orientation(projected_gravity):
+    """go2_handstand_env.py:224-235: exp(-3 (1 - clamp(g_z, -1, 1))^2)."""
+    err = 1.0 - projected_gravity[:, 2].clamp(-1.0, 1.0)
+    return torch.exp(-3.0 * err * err)
+
+
+def reward_front_feet_contact(contact_forces, front_feet_indices):
+    """go2_handstand_env.py:248-256: mean over the two front feet of 1[F_z > 5]."""
+    return (contact_forces[:, front_feet_indices, 2] > 5.0).float().mean(dim=1)
+
+
+def reward_hind_feet_no_contact(contact_forces, hind_feet_indices):
+    """go2_handstand_env.py:258-265: 1 - mean over the two hind feet of 1[F_z > 5]."""
+    return 1.0 - (contact_forces[:, hind_feet_indices, 2] > 5.0).float().mean(dim=1)
+
+
+def reward_stability(base_lin_vel, base_ang_vel):
+    """go2_handstand_env.py:309-317: exp(-2 (|v_xy| + 0.5 |w_xy|))."""
+    return torch.exp(-2.0 * (torch.norm(base_lin_vel[:, :2], dim=1) + 0.5 * torch.norm(base_ang_vel[:, :2], dim=1)))
+
+
+def reward_front_hip_neutral(dof_pos, fl_hip, fr_hip):
+    """go2_handstand_env.py:352-358: exp(-4 (q_FLhip^2 + q_FRhip^2))."""
+    hip = dof_pos[:, [fl_hip, fr_hip]]
+    return torch.exp(-4.0 * (hip ** 2).sum(dim=1))
+
+
+def reward_stay_still(base_lin_vel, base_ang_vel):
+    """go2_handstand_env.py:375-380: exp(-(|v_xy| / 0.05)^2 - (|w_z| / 0.2)^2)."""
+    lin_xy = torch.norm(base_lin_vel[:, :2], dim=1)
+    return torch.exp(-(lin_xy / 0.05) ** 2 - (torch.abs(base_ang_vel[:, 2]) / 0.2) ** 2)
+
+
+def reward_lin_vel_xy(base_lin_vel):
+    """go2_handstand_env.py:382-383: |v_xy|."""
+    return torch.norm(base_lin_vel[:, :2], dim=1)

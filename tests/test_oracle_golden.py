@@ -191,3 +191,33 @@ def test_handstand_observation_restatement_matches_reference():
         total += 4 * n
         np.testing.assert_array_equal(fx[f"step{t}/privileged_obs_buf"], ref)
     assert flipped <= 0.04 * total          # p = 0.01 flips; 1536 draws
+
+
+def test_handstand_reward_terms_match_reference_episode_sums():
+    """Seven handstand reward terms (oracle/handstand_port.reward_*) against the reference: on envs that were not reset
+    in the step, episode_sums[name] grows by term * (scale * dt) (legged_robot.py:778-781; const/reward_scales already
+    carry the dt factor, :824-826)."""
+    from oracle import handstand_port as HP
+    fx = np.load(os.path.join(H.GOLDEN, "env_go2_handstand_n64.npz"))
+    steps, P = int(fx["const/scalars"][4]), int(fx["const/scalars"][5])
+    n, A = fx["step0/torques"].shape
+    t_ = torch.from_numpy
+    feet = t_(fx["const/feet_indices"]).long()
+    scales = dict(zip([str(x) for x in fx["const/reward_names"]], fx["const/reward_scales"]))
+    for t in range(steps):
+        keep = ~fx[f"step{t}/reset_buf"].astype(bool)
+        con = t_(fx["frames/contact"][(t + 1) % P]).view(n, -1, 3)
+        lin, ang = t_(fx[f"step{t}/base_lin_vel"]), t_(fx[f"step{t}/base_ang_vel"])
+        q = t_(fx[f"step{t}/dof_state"]).view(n, A, 2)[..., 0]          # unchanged by the step on non-reset envs
+        terms = {"orientation": HP.reward_orientation(t_(fx[f"step{t}/projected_gravity"])),
+                 "front_feet_contact": HP.reward_front_feet_contact(con, feet[[0, 1]]),
+                 "hind_feet_no_contact": HP.reward_hind_feet_no_contact(con, feet[[2, 3]]),
+                 "stability": HP.reward_stability(lin, ang),
+                 "front_hip_neutral": HP.reward_front_hip_neutral(q, 0, 3),     # FL_hip, FR_hip in the go2 DOF order
+                 "stay_still": HP.reward_stay_still(lin, ang),
+                 "lin_vel_xy": HP.reward_lin_vel_xy(lin)}
+        prev = "reset" if t == 0 else f"step{t - 1}"
+        for name, r in terms.items():
+            delta = fx[f"step{t}/episode_sums/{name}"] - fx[f"{prev}/episode_sums/{name}"]
+            want = (r.numpy() * np.float32(scales[name]))
+            np.testing.assert_allclose(delta[keep], want[keep], rtol=2e-4, atol=2e-6, err_msg=f"{name} step {t}")
