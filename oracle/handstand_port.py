@@ -2,8 +2,8 @@
 
 First pieces of a CPU restatement of the reference's go2_handstand task ("next"), pinned to
 tests/golden/env_go2_handstand_n64.npz (recorded from the unmodified GO2HandstandEnv under oracle/refharness).
-Restated so far: the termination rule, the PD variant and the 46-dim observation; the 13 extra reward terms follow
-when the task is ported.
+Restated so far: the termination rule, the PD variant, the 46-dim observation and the ten task-specific reward terms
+that are active in the shipped config; wiring them into an EnvPort subclass (and the kernel side) is the next step.
 """
 import torch
 
@@ -73,8 +73,8 @@ def handstand_observations(base_ang_vel, projected_gravity, dof_pos, dof_vel, de
 
 
 # ---- reward terms of the handstand task that read only base-frame velocities, gravity, feet contact and hip angles.
-#      Each returns [N] f32 BEFORE the scale*dt factor (legged_robot.py:770-787 applies it).  Still to restate:
-#      base_height (:237-246), pose (:277-307), front_feet_together (:360-373, needs feet_pos), energy (:319-324).
+#      Each returns [N] f32 BEFORE the scale*dt factor (legged_robot.py:770-787 applies it).  The task's remaining active terms (action_rate,
+#      ang_vel_xy, collision, dof_pos_limits, dof_vel, lin_vel_z, torques) are the base class's, already in env_port.py.
 def reward_orientation(projected_gravity):
     """go2_handstand_env.py:224-235: exp(-3 (1 - clamp(g_z, -1, 1))^2)."""
     err = 1.0 - projected_gravity[:, 2].clamp(-1.0, 1.0)
@@ -111,3 +111,27 @@ def reward_stay_still(base_lin_vel, base_ang_vel):
 def reward_lin_vel_xy(base_lin_vel):
     """go2_handstand_env.py:382-383: |v_xy|."""
     return torch.norm(base_lin_vel[:, :2], dim=1)
+
+
+def reward_base_height(root_z, base_height_target):
+    """go2_handstand_env.py:237-246: exp(-8 max(target - z, 0)^2) — only heights BELOW the target are penalised."""
+    err = (base_height_target - root_z).clamp(min=0.0)
+    return torch.exp(-8.0 * err * err)
+
+
+def reward_pose(dof_pos, pose_targets, front_ids=(0, 1, 2, 3, 4, 5), hind_ids=(6, 7, 8, 9, 10, 11)):
+    """go2_handstand_env.py:277-307 (the second, effective _reward_pose): exp(-4 (sum_front e^2 + 0.3 sum_hind e^2)),
+    e = q - handstand pose; front = FL/FR hip, thigh, calf, hind = RL/RR hip, thigh, calf."""
+    err = dof_pos - pose_targets
+    sq = (err[:, list(front_ids)] ** 2).sum(dim=1) + 0.3 * (err[:, list(hind_ids)] ** 2).sum(dim=1)
+    return torch.exp(-4.0 * sq)
+
+
+def reward_front_feet_together(feet_pos):
+    """go2_handstand_env.py:360-373: exp(-20 max(|p_FL.xy - p_FR.xy| - 0.12, 0)^2); feet_pos [N, F, 3] are the feet rows
+    of the rigid-body state tensor, refreshed in the task's _post_physics_step_callback (:84-96).  That override does
+    NOT call the base class's callback, so this task never resamples commands, recomputes the heading command or pushes
+    robots (legged_robot.py:488-517 is skipped)."""
+    dist = torch.norm(feet_pos[:, 0, :2] - feet_pos[:, 1, :2], dim=1)
+    err = (dist - 0.12).clamp(min=0.0)
+    return torch.exp(-20.0 * err * err)

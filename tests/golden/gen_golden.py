@@ -86,6 +86,7 @@ def run_case(name):
         out["const/handstand/rear_center"] = env.rear_center.numpy()
         out["const/handstand/rear_limit"] = np.array(env.rear_limit, dtype=np.float64)
         out["const/handstand/pose_targets"] = env.pose_targets[0].numpy()
+        out["const/handstand/base_height_target"] = np.array(env.cfg.rewards.base_height_target, dtype=np.float64)
         out["const/handstand/action_scale_clip"] = np.array([env.cfg.control.action_scale,
                                                              env.cfg.normalization.clip_actions], dtype=np.float64)
     out["const/reward_names"] = np.array(env.reward_names)

@@ -194,7 +194,7 @@ def test_handstand_observation_restatement_matches_reference():
 
 
 def test_handstand_reward_terms_match_reference_episode_sums():
-    """Seven handstand reward terms (oracle/handstand_port.reward_*) against the reference: on envs that were not reset
+    """Ten handstand reward terms (oracle/handstand_port.reward_*) against the reference: on envs that were not reset
     in the step, episode_sums[name] grows by term * (scale * dt) (legged_robot.py:778-781; const/reward_scales already
     carry the dt factor, :824-826)."""
     from oracle import handstand_port as HP
@@ -215,7 +215,12 @@ def test_handstand_reward_terms_match_reference_episode_sums():
                  "stability": HP.reward_stability(lin, ang),
                  "front_hip_neutral": HP.reward_front_hip_neutral(q, 0, 3),     # FL_hip, FR_hip in the go2 DOF order
                  "stay_still": HP.reward_stay_still(lin, ang),
-                 "lin_vel_xy": HP.reward_lin_vel_xy(lin)}
+                 "lin_vel_xy": HP.reward_lin_vel_xy(lin),
+                 "base_height": HP.reward_base_height(t_(fx[f"step{t}/root_states"])[:, 2],
+                                                      float(fx["const/handstand/base_height_target"])),
+                 "pose": HP.reward_pose(q, t_(fx["const/handstand/pose_targets"])),
+                 "front_feet_together": HP.reward_front_feet_together(
+                     t_(fx["frames/rigid_body"][(t + 1) % P]).view(n, -1, 13)[:, feet, :3])}
         prev = "reset" if t == 0 else f"step{t - 1}"
         for name, r in terms.items():
             delta = fx[f"step{t}/episode_sums/{name}"] - fx[f"{prev}/episode_sums/{name}"]
