@@ -322,7 +322,14 @@ class PPO:
                     if self.world > 1 and not self._atexit_hooked:
                         self._atexit_hooked = True
                         ref = weakref.ref(self)
-                        atexit.register(lambda: ref() is not None and ref().release_graphs())
+                        def _at_exit():
+                            alg = ref()
+                            if alg is not None:
+                                try:
+                                    alg.release_graphs()
+                                except Exception:      # interpreter / CUDA context already going down
+                                    pass
+                        atexit.register(_at_exit)
                     g.replay()
             else:
                 self._update_graph[1].replay()
