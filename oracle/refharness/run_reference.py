@@ -57,7 +57,7 @@ class RefRun:
     """One reference env instance + its fake gym + RNG plumbing."""
 
     def __init__(self, task, num_envs, seed=1, env_offset=0, num_frames=4, frames=None, frame_seed=1,
-                 add_noise=True, push=True):
+                 add_noise=True, push=True, cfg_hook=None):
         from oracle import philox
         envs = import_reference()
         from isaacgym import gymapi, torch_utils
@@ -70,9 +70,13 @@ class RefRun:
         self.task = task
         self.torch_utils = torch_utils
         env_cfg, train_cfg = task_registry.get_cfgs(task)
+        import copy
+        env_cfg = copy.deepcopy(env_cfg)      # the registry hands out one shared instance per task; overrides stay local
         env_cfg.env.num_envs = num_envs
         env_cfg.noise.add_noise = add_noise
         env_cfg.domain_rand.push_robots = push
+        if cfg_hook is not None:          # config overrides applied before construction (same hook as tests/helpers.py)
+            cfg_hook(env_cfg)
         self.env_cfg, self.train_cfg = env_cfg, train_cfg
         robot = robot_for_asset(env_cfg.asset.file)
         self.robot = robot

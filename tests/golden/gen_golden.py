@@ -18,6 +18,7 @@ REPO = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, REPO)
 
 from oracle.refharness.run_reference import RefRun  # noqa: E402
+from tests.helpers import TWEAKS  # noqa: E402
 
 CASES = {
     # name: (task, num_envs, only_positive_rewards, steps)
@@ -26,6 +27,11 @@ CASES = {
     "h1_n40": ("h1", 40, False, 6),
     "g1_n64": ("g1", 64, True, 6),
     "h1_2_n33": ("h1_2", 33, False, 5),
+    # reward terms / control types no shipped task enables (config overrides in tests/helpers.py TWEAKS)
+    "go2_n48_allterms": ("go2", 48, False, 6),
+    "h1_2_n35_allterms": ("h1_2", 35, True, 5),
+    "go2_n40_ctrlV": ("go2", 40, True, 4),
+    "go2_n40_ctrlT": ("go2", 40, True, 4),
     # SURVEY.md 8(f) row 1 ("next"): the unmodified GO2HandstandEnv on the same synthetic frames.  Reference vectors for
     # the round that ports the task (46-dim obs with contact flags, gravity-based termination, 13 extra reward terms,
     # termination = -5); no product code consumes this fixture yet (tests only check it is well-formed).
@@ -46,9 +52,12 @@ def plant_episode_lengths(n, max_len, resample, push, gen):
 
 def run_case(name):
     task, n, only_pos, steps = CASES[name]
-    r = RefRun(task, n, seed=SEED, num_frames=NUM_FRAMES)
+    def hook(cfg):
+        cfg.rewards.only_positive_rewards = only_pos
+        if name in TWEAKS:
+            TWEAKS[name](cfg)
+    r = RefRun(task, n, seed=SEED, num_frames=NUM_FRAMES, cfg_hook=hook)
     env = r.env
-    env.cfg.rewards.only_positive_rewards = only_pos
     out = {}
     for k, v in r.frames.items():
         out["frames/" + k] = v.numpy()

@@ -6,7 +6,41 @@ import torch
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 ENV_CASES = {"go2_n64": ("go2", 64, True), "go2_n64_signed": ("go2", 64, False), "h1_n40": ("h1", 40, False),
-             "g1_n64": ("g1", 64, True), "h1_2_n33": ("h1_2", 33, False)}
+             "g1_n64": ("g1", 64, True), "h1_2_n33": ("h1_2", 33, False),
+             "go2_n48_allterms": ("go2", 48, False), "h1_2_n35_allterms": ("h1_2", 35, True),
+             "go2_n40_ctrlV": ("go2", 40, True), "go2_n40_ctrlT": ("go2", 40, True)}
+
+
+
+# Config overrides of a case, applied identically to the reference's config object (tests/golden/gen_golden.py, before the
+# unmodified reference env is constructed) and to this repo's config (make_cfg): the reward terms / control types that
+# no shipped task switches on (legged_robot.py:882-884, 892-899, 925-939; :656-668).
+def _tweak_allterms(cfg):
+    sc = cfg.rewards.scales
+    sc.dof_vel_limits = -1.0
+    sc.torque_limits = -0.01
+    sc.stumble = -0.5              # the config key `feet_stumble` has no function (quirk 7); `_reward_stumble` does
+    sc.stand_still = -0.2
+    sc.feet_contact_forces = -0.01
+    sc.termination = -5.0
+    cfg.rewards.soft_dof_vel_limit = 0.1       # 3.0 rad/s: a third of the synthetic dof_vel ~ N(0, 3^2) exceeds it
+    cfg.rewards.soft_torque_limit = 0.5
+    cfg.rewards.max_contact_force = 100.0
+    cfg.commands.ranges.lin_vel_x = [-0.3, 0.3]   # a third of the resampled commands fall under the 0.2 norm cut
+    cfg.commands.ranges.lin_vel_y = [-0.3, 0.3]   # -> zero command -> stand_still is active
+
+
+def _tweak_ctrl_v(cfg):
+    cfg.control.control_type = "V"
+
+
+def _tweak_ctrl_t(cfg):
+    cfg.control.control_type = "T"
+    cfg.control.action_scale = 9.0             # scaled actions on both sides of the +-23.7 / 35.55 torque limits
+
+
+TWEAKS = {"go2_n48_allterms": _tweak_allterms, "h1_2_n35_allterms": _tweak_allterms, "go2_n40_ctrlV": _tweak_ctrl_v,
+          "go2_n40_ctrlT": _tweak_ctrl_t}
 
 # north_star tolerances: masks / indices bit-exact; obs, rewards, torques 1e-5 relative (fp32)
 RTOL = 1e-5
@@ -19,12 +53,14 @@ def load_case(name):
     return {k: z[k] for k in z.files}
 
 
-def make_cfg(task, num_envs, only_positive):
+def make_cfg(task, num_envs, only_positive, tweak=None):
     from unitree_rl_gym_b200.legged_gym.envs import robot_configs as rc
     cls = {"go2": rc.GO2RoughCfg, "h1": rc.H1RoughCfg, "g1": rc.G1RoughCfg, "h1_2": rc.H1_2RoughCfg}[task]
     cfg = cls()
     cfg.env.num_envs = num_envs
     cfg.rewards.only_positive_rewards = only_positive
+    if tweak is not None:
+        tweak(cfg)
     return cfg
 
 
@@ -32,7 +68,7 @@ def make_spec(case):
     from unitree_rl_gym_b200.envspec import build_env_spec
     from unitree_rl_gym_b200.robots import ROBOTS
     task, n, pos = ENV_CASES[case]
-    cfg = make_cfg(task, n, pos)
+    cfg = make_cfg(task, n, pos, TWEAKS.get(case))
     return build_env_spec(task, cfg, ROBOTS[task], cfg.sim.dt, seed=1)
 
 

@@ -15,7 +15,7 @@ def make_env(case, fx=None, frames=None, seed=1):
     from unitree_rl_gym_b200.physics import SyntheticGym
     from unitree_rl_gym_b200.robots import ROBOTS
     task, n, pos = H.ENV_CASES[case]
-    cfg = H.make_cfg(task, n, pos)
+    cfg = H.make_cfg(task, n, pos, H.TWEAKS.get(case))
     cfg.seed = seed
     sp = SimParams()
     sp.dt = cfg.sim.dt

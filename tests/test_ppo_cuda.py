@@ -266,43 +266,135 @@ def test_minibatch_gradients_match_oracle(recurrent, n_obs, n_priv, n_act, hidde
 
 
 # ------------------------------------------------------------------ one full PPO update (north_star: 1e-3)
-@pytest.mark.parametrize("recurrent,n_obs,n_priv,n_act,hidden,N,T", [
-    (False, 48, None, 12, [512, 256, 128], 256, 24),
-    (True, 47, 50, 12, [32], 128, 24),
-])
-def test_one_update_matches_oracle(recurrent, n_obs, n_priv, n_act, hidden, N, T):
-    oppo, pppo = make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, init_noise_std=0.8)
+def _to_double(oppo):
+    """fp64 twin of an oracle PPO after its rollout: same parameters, same storage, update arithmetic in double.  The
+    distance fp32-oracle <-> fp64-oracle is the floor any fp32 evaluation order of the update can reach."""
+    from oracle import rsl_rl_port as O
+    twin = copy.deepcopy(oppo)
+    twin.actor_critic.double()
+    twin.optimizer = torch.optim.Adam(twin.actor_critic.parameters(), lr=oppo.learning_rate)
+    st = twin.storage
+    for k, v in list(vars(st).items()):
+        if torch.is_tensor(v) and v.dtype == torch.float32:
+            setattr(st, k, v.double())
+        elif isinstance(v, (list, tuple)) and v and torch.is_tensor(v[0]) and v[0].dtype == torch.float32:
+            setattr(st, k, type(v)(x.double() for x in v))
+    return twin
+
+
+def one_update_report(recurrent, n_obs, n_priv, n_act, hidden, N, T, kl_target=None, with_fp64=False, seed=0):
+    """Runs ONE PPO.update (num_learning_epochs x num_mini_batches Adam steps) on the oracle and on the CUDA path from
+    identical parameters / storage / permutation and returns the distances, measured on the UPDATE DELTA
+    (theta_after - theta_before), not on the parameter vector (which is dominated by the unchanged initial values).
+
+    kl_target: if given, the stored old means are shifted by a constant d so that the first minibatch's mean KL equals
+    kl_target (KL = A d^2 / (2 sigma^2) for identical sigma), which steers the adaptive-KL rule into a chosen branch."""
+    oppo, pppo = make_pair(recurrent, n_obs, n_priv, n_act, hidden, N, T, init_noise_std=0.8, seed=seed)
     last = rollout(oppo, pppo, N, T, n_obs, n_priv, n_act, done_p=0.05)
     with torch.no_grad():
         oppo.compute_returns(last)
+    if kl_target is not None:
+        d = float(np.sqrt(2.0 * kl_target * 0.8 ** 2 / n_act))
+        oppo.storage.mu += d
     copy_storage(oppo.storage, pppo.storage)
     before = {n: p.detach().clone() for n, p in oppo.actor_critic.named_parameters()}
     mini = (N * T) // oppo.num_mini_batches
     perm = torch.randperm(oppo.num_mini_batches * mini, generator=torch.Generator().manual_seed(2))
     oppo.perm, pppo.perm = perm, perm
+    twin = _to_double(oppo) if with_fp64 else None
+    pppo.lr_trace = []
     ov, osur = oppo.update()
     pv, psur = pppo.update()
     torch.cuda.synchronize()
-    assert abs(pv - ov) < 1e-4 * abs(ov) + 1e-5 and abs(psur - osur) < 1e-4
-    # the device-side adaptive-KL rule took the same LR decisions as the oracle's host branch
-    assert abs(pppo.learning_rate - oppo.learning_rate) < 1e-9 + 1e-6 * oppo.learning_rate, \
-        (pppo.learning_rate, oppo.learning_rate, oppo.lr_trace)
-    worst, n_tot, n_in = 0.0, 0, 0
-    for n, p in pppo.actor_critic.named_parameters():
-        a, b = p.detach().cpu().numpy(), dict(oppo.actor_critic.named_parameters())[n].detach().numpy()
-        assert rel_l2(a, b) < 1e-3, (n, rel_l2(a, b))                       # parameter vector, relative L2
-        d = np.abs(a - b)
-        worst = max(worst, d.max())
-        n_tot += d.size
-        n_in += int((d <= 1e-3).sum())
-        moved = np.abs(b - before[n].numpy()).max()
-        assert moved > 1e-4, (n, moved)                                     # the update did move this tensor
-    # north_star: parameters within 1e-3 after one update (= 20 Adam steps).  Adam's step m/(sqrt(v)+eps) is
-    # sign-like for a parameter whose gradient is at the rounding-noise level (|g| ~ eps = 1e-8), so a handful of the
-    # 380k parameters can differ by one step (lr ~ 1e-3) between ANY two fp32 evaluation orders (the oracle itself
-    # moves with the host's thread count); bound that tail instead of letting it decide the test.
-    assert n_in / n_tot >= 0.9999, (n_in, n_tot)
-    assert worst <= 3e-3, worst
+    rep = {"recurrent": recurrent, "N": N, "T": T, "kl_target": kl_target,
+           "losses": {"oracle": [ov, osur], "cuda": [pv, psur]},
+           "lr_final": {"oracle": oppo.learning_rate, "cuda": pppo.learning_rate},
+           "lr_trace_oracle": [(round(k, 8), lr) for k, lr in oppo.lr_trace],
+           "lr_trace_cuda": [(round(k, 8), lr) for k, lr in pppo.lr_trace]}
+    op = dict(oppo.actor_critic.named_parameters())
+    names = [n for n, _ in pppo.actor_critic.named_parameters()]
+    cat = lambda f: np.concatenate([f(n).reshape(-1) for n in names]).astype(np.float64)
+    th0 = cat(lambda n: before[n].numpy())
+    d_o = cat(lambda n: op[n].detach().numpy()) - th0
+    d_p = cat(lambda n: dict(pppo.actor_critic.named_parameters())[n].detach().cpu().numpy()) - th0
+
+    def dist(d_x, d_ref):
+        err = np.abs(d_x - d_ref)
+        return {"delta_rel_l2": float(np.linalg.norm(d_x - d_ref) / np.linalg.norm(d_ref)),
+                "param_max_abs": float(err.max()), "param_frac_within_1e-3": float(np.mean(err <= 1e-3)),
+                "n_beyond_1e-3": int((err > 1e-3).sum()), "param_rel_l2": float(np.linalg.norm(d_x - d_ref) / np.linalg.norm(th0 + d_ref))}
+    rep["delta_scale"] = {"l2": float(np.linalg.norm(d_o)), "max_abs": float(np.abs(d_o).max()),
+                          "n_params": int(d_o.size), "moved_min_per_tensor": float(min(
+                              np.abs(op[n].detach().numpy() - before[n].numpy()).max() for n in names))}
+    rep["cuda_vs_oracle32"] = dist(d_p, d_o)
+    rep["per_tensor_delta_rel_l2"] = {}
+    off = 0
+    for n in names:
+        k = before[n].numel()
+        rep["per_tensor_delta_rel_l2"][n] = float(np.linalg.norm(d_p[off:off + k] - d_o[off:off + k]) /
+                                                  max(np.linalg.norm(d_o[off:off + k]), 1e-30))
+        off += k
+    if twin is not None:
+        twin.perm = perm
+        twin.update()
+        d_64 = cat(lambda n: dict(twin.actor_critic.named_parameters())[n].detach().numpy()) - th0
+        rep["oracle32_vs_oracle64"] = dist(d_o, d_64)
+        rep["cuda_vs_oracle64"] = dist(d_p, d_64)
+        rep["lr_final"]["oracle64"] = twin.learning_rate
+    return rep
+
+
+def _check_update(rep):
+    ov, osur = rep["losses"]["oracle"]
+    pv, psur = rep["losses"]["cuda"]
+    assert abs(pv - ov) < 1e-4 * abs(ov) + 1e-5 and abs(psur - osur) < 1e-4, rep["losses"]
+    # the device-side adaptive-KL rule took the same LR decision as the oracle's host branch at every minibatch
+    lo, lc = rep["lr_trace_oracle"], rep["lr_trace_cuda"]
+    assert len(lo) == len(lc) and len(lo) > 0
+    for i, ((ko, lro), (kc, lrc)) in enumerate(zip(lo, lc)):
+        assert abs(lrc - lro) <= 1e-6 * lro, (i, lo, lc)
+        assert abs(kc - ko) <= 1e-3 * abs(ko) + 1e-7, (i, ko, kc)
+    assert rep["delta_scale"]["moved_min_per_tensor"] > 1e-4, rep["delta_scale"]     # every tensor really moved
+    d = rep["cuda_vs_oracle32"]
+    # north_star: parameters after one update agree to 1e-3 -- every parameter, no looser ceiling for a tail
+    assert d["param_max_abs"] <= 1e-3, d
+    assert d["param_rel_l2"] <= 1e-3, d
+    return d
+
+
+@pytest.mark.parametrize("recurrent,n_obs,n_priv,n_act,hidden,N,T", [
+    (False, 48, None, 12, [512, 256, 128], 256, 24),
+    (True, 47, 50, 12, [32], 128, 24),
+    (False, 48, None, 12, [512, 256, 128], 4096, 24),      # BASELINE configs[1]: 24 576-row minibatches
+    (True, 47, 50, 12, [32], 4096, 24),                    # BASELINE configs[3] (G1 LSTM)
+])
+def test_one_update_matches_oracle(recurrent, n_obs, n_priv, n_act, hidden, N, T):
+    rep = one_update_report(recurrent, n_obs, n_priv, n_act, hidden, N, T)
+    d = _check_update(rep)
+    # the update delta itself (theta_after - theta_before), relative to its own scale.  Adam turns a gradient into
+    # lr * m / (sqrt(v) + eps): the fp32 oracle evaluated in another summation order (or in fp64) moves by the same
+    # amount (tools/ppo_update_parity.py reports both distances side by side: profiles/r2_ppo_parity_4096.json).
+    assert d["delta_rel_l2"] <= DELTA_REL_L2, d
+
+
+DELTA_REL_L2 = 2e-2
+
+
+@pytest.mark.parametrize("kl_target,first", [(0.0202, "down"), (0.00495, "up")])
+def test_adaptive_lr_takes_both_branches(kl_target, first):
+    """Crafted rollouts whose first-minibatch KL lands just above 2 * desired_kl (lr / 1.5) and just below
+    desired_kl / 2 (lr * 1.5): both branches of the device-side rule fire and every one of the 20 LR decisions equals
+    the oracle's ([UPSTREAM] ppo.py update: adaptive schedule)."""
+    rep = one_update_report(False, 48, None, 12, [512, 256, 128], 1024, 24, kl_target=kl_target)
+    lr0 = ALG["learning_rate"]
+    k0, l0 = rep["lr_trace_cuda"][0]
+    assert abs(k0 - kl_target) < 2e-3 * kl_target, (k0, kl_target)
+    assert abs(l0 - (lr0 / 1.5 if first == "down" else lr0 * 1.5)) < 1e-9, rep["lr_trace_cuda"][:3]
+    lrs = [lr for _, lr in rep["lr_trace_cuda"]]
+    ups = sum(1 for a, b in zip([lr0] + lrs[:-1], lrs) if b > a * 1.0001)
+    downs = sum(1 for a, b in zip([lr0] + lrs[:-1], lrs) if b < a * 0.9999)
+    assert (ups if first == "up" else downs) >= 1
+    _check_update(rep)
 
 
 # ------------------------------------------------------------------ drop-in runner end to end

@@ -112,6 +112,7 @@ class PPO:
         self._act_base = None
         self.sample_noise = None     # parity hook: N(0,1) [N, A] used instead of Philox for the next act()
         self.perm = None             # parity hook: minibatch permutation [T*N] used instead of randperm
+        self.lr_trace = None         # parity hook: a list -> (kl_mean, lr) read back after every minibatch (eager update)
         self.cuda_graph_update = False
         self.update_graph_launches = 0
         self._idx_buf = None
@@ -271,6 +272,9 @@ class PPO:
                 if self.world > 1:
                     dist.all_reduce(eng.grads_and_sums)     # flat gradients + (KL, surrogate, value, entropy) sums
                 _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), st))
+                if self.lr_trace is not None:
+                    v = eng.stats.tolist()
+                    self.lr_trace.append((v[_lib.STAT_KL_MEAN], v[_lib.STAT_LR]))
 
     def release_graphs(self):
         """Destroy the captured update graph.  With several ranks it holds NCCL kernels: NCCL keeps the communicator
@@ -305,7 +309,7 @@ class PPO:
         # and replays the same sequence; measured clean at 2, 4 and 8 ranks); URLG_GRAPH_NCCL=0 keeps the multi-rank update eager.
         key = (id(eng), s.desc().observations, self.clip_param, self.value_loss_coef, self.entropy_coef, self.max_grad_norm,
                self.desired_kl, self.schedule, self.num_learning_epochs, self.num_mini_batches, self.use_clipped_value_loss)
-        if self.cuda_graph_update and (self.world == 1 or self._graph_nccl):
+        if self.cuda_graph_update and self.lr_trace is None and (self.world == 1 or self._graph_nccl):
             if self._update_graph is None or self._update_graph[0] != key:
                 if self._update_warm != key:
                     self._minibatch_loop(idx)          # first update runs eagerly (lazy init, warm-up), capture on the next
