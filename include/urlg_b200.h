@@ -26,11 +26,12 @@
 extern "C" {
 #endif
 
-#define URLG_ABI_VERSION 1
+#define URLG_ABI_VERSION 2
 #define URLG_MAX_DOF 16
 #define URLG_MAX_IDX 16
 #define URLG_MAX_TERMS 32
 #define URLG_MAX_OBS 128
+#define URLG_MAX_FEET 4
 
 typedef enum {
   URLG_OK = 0,
@@ -39,21 +40,33 @@ typedef enum {
   URLG_ENOMEM = -3
 } urlg_status;
 
-/* Reward-term ids: alphabetical = the reference's execution order (helpers.py:15 dir()). */
+/* Reward-term ids: alphabetical by reward NAME = the reference's execution order (helpers.py:15 dir()).  A name whose
+ * formula a subclass overrides has two ids (base / _HS = go2_handstand_env.py); a config activates at most one of them. */
 typedef enum {
-  URLG_T_ACTION_RATE = 0, URLG_T_ALIVE, URLG_T_ANG_VEL_XY, URLG_T_BASE_HEIGHT, URLG_T_COLLISION,
-  URLG_T_CONTACT, URLG_T_CONTACT_NO_VEL, URLG_T_DOF_ACC, URLG_T_DOF_POS_LIMITS, URLG_T_DOF_VEL,
-  URLG_T_DOF_VEL_LIMITS, URLG_T_FEET_AIR_TIME, URLG_T_FEET_CONTACT_FORCES, URLG_T_FEET_SWING_HEIGHT,
-  URLG_T_HIP_POS, URLG_T_LIN_VEL_Z, URLG_T_ORIENTATION, URLG_T_STAND_STILL, URLG_T_STUMBLE,
-  URLG_T_TORQUE_LIMITS, URLG_T_TORQUES, URLG_T_TRACKING_ANG_VEL, URLG_T_TRACKING_LIN_VEL,
+  URLG_T_ACTION_RATE = 0, URLG_T_ALIVE, URLG_T_ANG_VEL_XY, URLG_T_BASE_HEIGHT, URLG_T_BASE_HEIGHT_HS, URLG_T_COLLISION,
+  URLG_T_CONTACT, URLG_T_CONTACT_NO_VEL, URLG_T_DOF_ACC, URLG_T_DOF_POS_LIMITS, URLG_T_DOF_VEL, URLG_T_DOF_VEL_LIMITS,
+  URLG_T_ENERGY, URLG_T_FEET_AIR_TIME, URLG_T_FEET_CONTACT_FORCES, URLG_T_FEET_SWING_HEIGHT, URLG_T_FRONT_FEET_CONTACT,
+  URLG_T_FRONT_FEET_TOGETHER, URLG_T_FRONT_HIP_NEUTRAL, URLG_T_HIND_FEET_NO_CONTACT, URLG_T_HIP_POS, URLG_T_LIN_VEL_XY,
+  URLG_T_LIN_VEL_Z, URLG_T_ORIENTATION, URLG_T_ORIENTATION_HS, URLG_T_POSE, URLG_T_STABILITY, URLG_T_STAND_STILL,
+  URLG_T_STAY_STILL, URLG_T_STUMBLE, URLG_T_TORQUE_LIMITS, URLG_T_TORQUES, URLG_T_TRACKING_ANG_VEL,
+  URLG_T_TRACKING_LIN_VEL,
   URLG_T_COUNT
 } urlg_reward_term;
+
+/* Env class variants (what the reference expresses by subclassing LeggedRobot). */
+enum { URLG_FAMILY_BASE = 0,        /* LeggedRobot: 12+3A obs (legged_robot.py:789-811) */
+       URLG_FAMILY_H1 = 1,          /* H1Robot / H1_2Robot / G1Robot: gait phase, 9+3A+2 obs + privileged obs (h1_env.py) */
+       URLG_FAMILY_HANDSTAND = 2 }; /* GO2HandstandEnv: 6+3A+4 obs with contact flags (go2_handstand_env.py:140-176) */
+enum { URLG_TERMINATION_RPY = 0,      /* contact | |pitch|>1 | |roll|>0.8 | time-out  (legged_robot.py:711-721) */
+       URLG_TERMINATION_GRAVITY = 1 };/* contact | -0.2 < projected_gravity.z < 0.2 | time-out (go2_handstand_env.py:178-219) */
+enum { URLG_CALLBACK_BASE = 0,      /* resample commands + heading command (legged_robot.py:488-517) */
+       URLG_CALLBACK_NONE = 1 };    /* an override that never calls the base callback (go2_handstand_env.py:84-96) */
 
 /* Init-time constants of one env instance: what LeggedRobot._parse_cfg / _init_buffers /
  * _process_dof_props / _prepare_reward_function / _get_noise_scale_vec compute once
  * (legged_robot.py:52-67, 69-186, 442-470, 817-840, 188-219; h1_env.py:10-32). */
 typedef struct urlg_env_desc {
-  int32_t family;            /* 0 = LeggedRobot obs layout, 1 = H1-family (gait phase + privileged obs) */
+  int32_t family;            /* URLG_FAMILY_* */
   int32_t num_envs, num_dof, num_bodies, num_obs, num_priv;
   int32_t num_feet, num_pen, num_term_bodies, num_hip;
   int32_t decimation, control_type;          /* control_type: 'P','V','T' as ASCII */
@@ -79,6 +92,14 @@ typedef struct urlg_env_desc {
   float base_init_state[13];
   uint32_t seed_lo, seed_hi;
   int64_t env_offset;                         /* global id of local env 0 (multi-GPU shard) */
+  /* ---- variant tables (ABI v2): what go2_handstand_env.py changes by overriding methods ---- */
+  int32_t termination_mode;                   /* URLG_TERMINATION_* */
+  int32_t callback_mode;                      /* URLG_CALLBACK_* */
+  int32_t clip_torques;                       /* 1: clip to +-torque_limits (legged_robot.py:671); 0: none (go2_handstand_env.py:349-350) */
+  int32_t num_front_dof;                      /* handstand pose term: DOFs [0, num_front_dof) weigh 1.0, the rest 0.3 (:277-307) */
+  float pd_target_lo[URLG_MAX_DOF];           /* P control: target = clamp(action*scale + default, lo, hi); +-inf = no clamp */
+  float pd_target_hi[URLG_MAX_DOF];           /*   (rear-leg clamp of go2_handstand_env.py:336-346) */
+  float pose_targets[URLG_MAX_DOF];           /* handstand pose (go2_handstand_config.py handstand_pose) */
 } urlg_env_desc;
 
 /* Device pointers of every public tensor of the env (legged_robot.py:104-186, base_task.py:41-49,
@@ -112,8 +133,12 @@ typedef struct urlg_env_buffers {
   const float* env_origins;        /* [N,3] */
   float* extras_episode;           /* [num_sums] extras["episode"]["rew_*"], refreshed only when >=1 env reset */
   uint8_t* extras_time_outs;       /* [N] bool, extras["time_outs"], same staleness rule (legged_robot.py:742,767) */
-  int32_t* reset_ids;              /* [N] compacted ids of envs reset this step (for set_*_tensor_indexed), may be NULL */
+  int32_t* reset_ids;              /* [N] compacted ids of envs reset this step: argument of set_dof_state_tensor_indexed
+                                      (legged_robot.py:569-572); order is not defined; may be NULL */
   int32_t* reset_count;            /* [1] */
+  int32_t* root_ids;               /* [N] envs whose root state was rewritten this step = reset envs + push-due envs:
+                                      argument of set_actor_root_state_tensor_indexed (:552-555, 591-594); may be NULL */
+  int32_t* root_count;             /* [1] */
   const float* rng_override;       /* optional [N,num_rng_slots] uniforms replacing Philox (debug), else NULL */
 } urlg_env_buffers;
 
@@ -140,6 +165,26 @@ int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream);
  * ping-pong buffer written. */
 int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot, void* stream);
 
+/* ---- pool-indexed physics seam (bench / rollout graphs) ----
+ * Instead of copying the next synthetic frame into root_states / dof_state / contact_forces / rigid_body_states before
+ * every kernel (urlg_synth_refresh = the stand-in for PhysX filling its tensors), the kernels can read the current frame
+ * straight out of a device-resident pool: frame index = ((*calls_base + calls_offset - 1) / substeps) % num_frames,
+ * dof substep = (*calls_base + calls_offset - 1) % substeps, calls = number of simulate() calls so far (<= 0: the bound
+ * tensors are read).  Resets / pushes are still written to the bound root_states / dof_state tensors.  Results are
+ * identical to the copy path (tests/test_env_cuda.py::test_pool_seam_matches_copy_seam). */
+typedef struct urlg_frame_pool {
+  const float* root;          /* [P, N, 13] */
+  const float* dof;           /* [P, substeps, N*A, 2] */
+  const float* contact;       /* [P, N*B, 3] */
+  const float* rigid_body;    /* [P, N*B, 13] or NULL */
+  int64_t num_frames, substeps;
+  const int64_t* calls_base;  /* device int64 [1] */
+} urlg_frame_pool;
+int urlg_env_bind_frame_pool(urlg_env* env, const urlg_frame_pool* pool /* NULL: unbind */);
+int urlg_pd_torques_at(urlg_env* env, const float* raw_actions, int64_t calls_offset, void* stream);
+int urlg_post_physics_at(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot,
+                         int64_t calls_offset, void* stream);
+
 /* reset_idx(env_ids) called from outside step() (base_task.py:82-86, legged_robot.py:723-768).
  * env_ids: device int64 [n], or NULL for "all envs". */
 int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const int64_t* step_base,
@@ -150,6 +195,12 @@ int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const i
  * i.e. refresh_*_tensor (legged_robot.py:639,678-679; h1_env.py:49) served from a device-resident pool. */
 int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, int64_t num_frames, int64_t substeps,
                        int per_substep, const int64_t* calls_base, int64_t calls_offset, void* stream);
+
+/* dst rows ids[0 .. *count) <- the same rows of src (row_floats floats each; *count read on the device, at most max_rows):
+ * what set_dof_state_tensor_indexed / set_actor_root_state_tensor_indexed do inside a simulator whose state lives apart
+ * from the exposed tensors (legged_robot.py:552-555, 569-572, 591-594), without a host read of the count. */
+int urlg_scatter_rows(float* dst, const float* src, const int32_t* ids, const int32_t* count, int row_floats,
+                      int max_rows, void* stream);
 
 /* n asynchronous copies (cudaMemcpyDefault) enqueued on `stream` in one call: the per-env-step host <-> device traffic
  * of a physics engine that lives on the host (state frame in, rewards / dones out) without n trips through the caller's

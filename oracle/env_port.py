@@ -275,21 +275,8 @@ class EnvPort:
         self.base_lin_vel = quat_rotate_inverse(q, self.root_states[:, 7:10])
         self.base_ang_vel = quat_rotate_inverse(q, self.root_states[:, 10:13])
         self.projected_gravity = quat_rotate_inverse(q, self.gravity_vec)
-        # E5 callback: h1_env.py:55-65 then :511-516
-        if s.family == 1:
-            self.phase = (self.episode_length_buf * s.dt) % 0.8 / 0.8
-            self.leg_phase = torch.stack([self.phase, (self.phase + 0.5) % 1], dim=-1)
-        due = self.episode_length_buf % s.resample_steps == 0
-        self._resample(due, U, 0)
-        if s.heading_command:
-            fwd = quat_apply(q, self.forward_vec)
-            heading = torch.atan2(fwd[:, 1], fwd[:, 0])
-            self.commands[:, 2] = torch.clip(0.5 * wrap_to_pi(self.commands[:, 3] - heading), -1., 1.)
-        # E7 :715-721
-        self.reset_buf = torch.any(torch.norm(self.contact_forces[:, s.term_idx, :], dim=-1) > 1., dim=1)
-        self.reset_buf = self.reset_buf | torch.logical_or(torch.abs(self.rpy[:, 1]) > 1.0, torch.abs(self.rpy[:, 0]) > 0.8)
-        self.time_out_buf = self.episode_length_buf > s.max_episode_length
-        self.reset_buf = self.reset_buf | self.time_out_buf
+        self._post_physics_step_callback(U)
+        self.check_termination()
         # E8 :775-787
         self.rew_buf = torch.zeros(s.num_envs)
         for name, scale in zip(s.reward_names, s.reward_scales):
@@ -304,15 +291,43 @@ class EnvPort:
             self.episode_sums["termination"] = self.episode_sums["termination"] + r
         # :697-698
         self.reset_idx(self.reset_buf.clone(), U)
-        # E11 :540-555 (quirk: any due env => all envs rewritten)
-        if s.push_robots and bool((self.episode_length_buf % s.push_interval == 0).any()):
-            m = s.max_push_vel
-            self.root_states[:, 7:9] = (m - (-m)) * U[:, 12 + A:14 + A] + (-m)
+        self._push_robots(U)
         # E12 :789-811 / h1_env.py:68-95
         self.compute_observations(U)
         self.last_actions = self.actions.clone()
         self.last_dof_vel = self.dof_vel.clone()
         self.last_root_vel = self.root_states[:, 7:13].clone()
+
+    # E5 callback: h1_env.py:55-65 then :511-516
+    def _post_physics_step_callback(self, U):
+        s = self.spec
+        q = self.root_states[:, 3:7]
+        if s.family == 1:
+            self.phase = (self.episode_length_buf * s.dt) % 0.8 / 0.8
+            self.leg_phase = torch.stack([self.phase, (self.phase + 0.5) % 1], dim=-1)
+        due = self.episode_length_buf % s.resample_steps == 0
+        self._resample(due, U, 0)
+        if s.heading_command:
+            fwd = quat_apply(q, self.forward_vec)
+            heading = torch.atan2(fwd[:, 1], fwd[:, 0])
+            self.commands[:, 2] = torch.clip(0.5 * wrap_to_pi(self.commands[:, 3] - heading), -1., 1.)
+
+    # E7 :715-721
+    def check_termination(self):
+        s = self.spec
+        self.reset_buf = torch.any(torch.norm(self.contact_forces[:, s.term_idx, :], dim=-1) > 1., dim=1)
+        self.reset_buf = self.reset_buf | torch.logical_or(torch.abs(self.rpy[:, 1]) > 1.0, torch.abs(self.rpy[:, 0]) > 0.8)
+        self.time_out_buf = self.episode_length_buf > s.max_episode_length
+        self.reset_buf = self.reset_buf | self.time_out_buf
+
+    # E11 :540-555 (quirk: any due env => all envs rewritten).  Called from post_physics_step itself (:700-701), after
+    # reset_idx — not from the callback — so a subclass that overrides the callback still pushes.
+    def _push_robots(self, U):
+        s = self.spec
+        A = s.num_dof
+        if s.push_robots and bool((self.episode_length_buf % s.push_interval == 0).any()):
+            m = s.max_push_vel
+            self.root_states[:, 7:9] = (m - (-m)) * U[:, 12 + A:14 + A] + (-m)
 
     def compute_observations(self, U):
         s = self.spec

@@ -1,11 +1,13 @@
 """TEST INFRASTRUCTURE ONLY (never imported by the product path).
 
-First pieces of a CPU restatement of the reference's go2_handstand task ("next"), pinned to
-tests/golden/env_go2_handstand_n64.npz (recorded from the unmodified GO2HandstandEnv under oracle/refharness).
-Restated so far: the termination rule, the PD variant, the 46-dim observation and the ten task-specific reward terms
-that are active in the shipped config; wiring them into an EnvPort subclass (and the kernel side) is the next step.
+CPU restatement of the reference's go2_handstand task, pinned to
+tests/golden/env_go2_handstand_n64.npz (recorded from the unmodified GO2HandstandEnv under oracle/refharness):
+the termination rule, the PD variant, the 46-dim observation, the eleven task-specific reward terms, and
+`HandstandPort`, the EnvPort subclass that wires them into a steppable env (tests/test_oracle_golden.py).
 """
 import torch
+
+from .env_port import EnvPort
 
 
 def handstand_termination(contact_forces, termination_contact_indices, projected_gravity, episode_length_buf,
@@ -130,8 +132,84 @@ def reward_pose(dof_pos, pose_targets, front_ids=(0, 1, 2, 3, 4, 5), hind_ids=(6
 def reward_front_feet_together(feet_pos):
     """go2_handstand_env.py:360-373: exp(-20 max(|p_FL.xy - p_FR.xy| - 0.12, 0)^2); feet_pos [N, F, 3] are the feet rows
     of the rigid-body state tensor, refreshed in the task's _post_physics_step_callback (:84-96).  That override does
-    NOT call the base class's callback, so this task never resamples commands, recomputes the heading command or pushes
-    robots (legged_robot.py:488-517 is skipped)."""
+    NOT call the base class's callback, so this task never resamples commands in the callback nor recomputes the heading
+    command (legged_robot.py:488-517 is skipped); pushes remain (post_physics_step calls _push_robots itself, :700-701)."""
     dist = torch.norm(feet_pos[:, 0, :2] - feet_pos[:, 1, :2], dim=1)
     err = (dist - 0.12).clamp(min=0.0)
     return torch.exp(-20.0 * err * err)
+
+
+def reward_energy(torques, dof_vel):
+    """go2_handstand_env.py:319-324: sum |tau| |qd| (scale 0 in the shipped config)."""
+    return torch.sum(torch.abs(torques) * torch.abs(dof_vel), dim=1)
+
+
+class HandstandPort(EnvPort):
+    """GO2HandstandEnv as overrides of the base port, mirroring which methods the reference subclass overrides."""
+
+    def __init__(self, spec, threads=None):
+        super().__init__(spec, threads)
+        s = spec
+        self.pose_targets = torch.as_tensor(s.pose_targets, dtype=torch.float32).view(1, -1).repeat(s.num_envs, 1)
+        idx = {n: i for i, n in enumerate(s.dof_names)}
+        self.rear_dof_idx = torch.tensor([idx[n] for n in ("RL_hip_joint", "RL_thigh_joint", "RL_calf_joint",
+                                                            "RR_hip_joint", "RR_thigh_joint", "RR_calf_joint")])
+        self.rear_center = self.pose_targets[0, self.rear_dof_idx].clone()
+        self.rear_limit = 0.15
+        self.front_feet = torch.tensor(s.feet_idx[:2])
+        self.hind_feet = torch.tensor(s.feet_idx[2:4])
+        self.fl_hip, self.fr_hip = idx["FL_hip_joint"], idx["FR_hip_joint"]
+        self.privileged_obs_buf = torch.zeros(s.num_envs, s.num_obs)
+
+    def compute_torques(self):                                   # :326-350
+        s = self.spec
+        self.torques = handstand_pd_torques(self.actions, self.dof_pos, self.dof_vel, self.p_gains, self.d_gains,
+                                            self.default_dof_pos, s.action_scale, self.rear_dof_idx, self.rear_center,
+                                            self.rear_limit)
+        return self.torques
+
+    def _post_physics_step_callback(self, U):                    # :92-96: feet states only
+        pass
+
+    def check_termination(self):                                 # :178-219
+        s = self.spec
+        self.reset_buf, self.time_out_buf = handstand_termination(
+            self.contact_forces, torch.tensor(s.term_idx), self.projected_gravity, self.episode_length_buf,
+            s.max_episode_length)
+
+    def _term(self, name):
+        s = self.spec
+        if name == "orientation":
+            return reward_orientation(self.projected_gravity)
+        if name == "base_height":
+            return reward_base_height(self.root_states[:, 2], s.base_height_target)
+        if name == "front_feet_contact":
+            return reward_front_feet_contact(self.contact_forces, self.front_feet)
+        if name == "hind_feet_no_contact":
+            return reward_hind_feet_no_contact(self.contact_forces, self.hind_feet)
+        if name == "pose":
+            return reward_pose(self.dof_pos, self.pose_targets, range(s.num_front_dof), range(s.num_front_dof, s.num_dof))
+        if name == "stability":
+            return reward_stability(self.base_lin_vel, self.base_ang_vel)
+        if name == "energy":
+            return reward_energy(self.torques, self.dof_vel)
+        if name == "front_hip_neutral":
+            return reward_front_hip_neutral(self.dof_pos, self.fl_hip, self.fr_hip)
+        if name == "front_feet_together":
+            return reward_front_feet_together(self.rigid_body_states[:, s.feet_idx, :3])
+        if name == "stay_still":
+            return reward_stay_still(self.base_lin_vel, self.base_ang_vel)
+        if name == "lin_vel_xy":
+            return reward_lin_vel_xy(self.base_lin_vel)
+        return super()._term(name)
+
+    def compute_observations(self, U):                           # :140-176; flips from slots 14+A+O .. +3
+        s = self.spec
+        A, O = s.num_dof, s.num_obs
+        noise = U[:, 14 + A:14 + A + O] if s.add_noise else None
+        flips = (U[:, 14 + A + O:14 + A + O + 4] < 0.01) if s.add_noise else None
+        self.obs_buf = handstand_observations(
+            self.base_ang_vel, self.projected_gravity, self.dof_pos, self.dof_vel, self.default_dof_pos, self.actions,
+            self.contact_forces, self.front_feet, self.hind_feet, s.obs_scale_ang_vel, s.obs_scale_dof_pos,
+            s.obs_scale_dof_vel, noise, self.noise_scale_vec, flips)
+        self.privileged_obs_buf = self.obs_buf.clone()

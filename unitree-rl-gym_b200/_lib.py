@@ -11,7 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "liburlg_b200.so")
 
-MAX_DOF, MAX_IDX, MAX_TERMS, MAX_OBS = 16, 16, 32, 128
+MAX_DOF, MAX_IDX, MAX_TERMS, MAX_OBS, MAX_FEET = 16, 16, 32, 128, 4
+ABI_VERSION = 2
 
 
 class EnvDesc(C.Structure):
@@ -41,6 +42,10 @@ class EnvDesc(C.Structure):
         ("hip_idx", C.c_int32 * MAX_IDX),
         ("noise_scale_vec", C.c_float * MAX_OBS), ("base_init_state", C.c_float * 13),
         ("seed_lo", C.c_uint32), ("seed_hi", C.c_uint32), ("env_offset", C.c_int64),
+        ("termination_mode", C.c_int32), ("callback_mode", C.c_int32), ("clip_torques", C.c_int32),
+        ("num_front_dof", C.c_int32),
+        ("pd_target_lo", C.c_float * MAX_DOF), ("pd_target_hi", C.c_float * MAX_DOF),
+        ("pose_targets", C.c_float * MAX_DOF),
     ]
 
 
@@ -57,8 +62,13 @@ class EnvBuffers(C.Structure):
         ("rpy", _P), ("base_lin_vel", _P), ("base_ang_vel", _P), ("projected_gravity", _P),
         ("phase", _P), ("leg_phase", _P), ("episode_sums", _P), ("env_origins", _P),
         ("extras_episode", _P), ("extras_time_outs", _P), ("reset_ids", _P), ("reset_count", _P),
-        ("rng_override", _P),
+        ("root_ids", _P), ("root_count", _P), ("rng_override", _P),
     ]
+
+
+class FramePool(C.Structure):
+    _fields_ = [("root", _P), ("dof", _P), ("contact", _P), ("rigid_body", _P),
+                ("num_frames", C.c_int64), ("substeps", C.c_int64), ("calls_base", _P)]
 
 
 class GemmDesc(C.Structure):
@@ -125,6 +135,10 @@ SIGNATURES = {
     "urlg_env_num_rng_slots": (C.c_int, [C.c_void_p]),
     "urlg_pd_torques": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "urlg_post_physics": (C.c_int, [C.c_void_p, _I64P, C.c_int64, C.c_int, C.c_void_p]),
+    "urlg_env_bind_frame_pool": (C.c_int, [C.c_void_p, C.POINTER(FramePool)]),
+    "urlg_pd_torques_at": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "urlg_post_physics_at": (C.c_int, [C.c_void_p, _I64P, C.c_int64, C.c_int, C.c_int64, C.c_void_p]),
+    "urlg_scatter_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "urlg_env_reset_idx": (C.c_int, [C.c_void_p, _I64P, C.c_int64, _I64P, C.c_int64, C.c_void_p]),
     "urlg_copy_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "urlg_synth_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, _I64P,
@@ -174,7 +188,7 @@ def lib():
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
-        if L.urlg_version() != 1:
+        if L.urlg_version() != ABI_VERSION:
             raise RuntimeError("liburlg_b200 ABI version mismatch")
         _lib = L
     return _lib
@@ -188,6 +202,8 @@ def check(code):
                 raise AssertionError(msg)  # same as [UPSTREAM] RolloutStorage.add_transitions
             if msg.startswith("Unknown controller type"):
                 raise NameError(msg)       # same exception type as legged_robot.py:670
+            if msg.startswith("Expected at least 4 feet"):
+                raise AssertionError(msg)  # go2_handstand_env.py:19
             raise ValueError(msg)
         raise RuntimeError(f"urlg error {code}: {msg}")
 

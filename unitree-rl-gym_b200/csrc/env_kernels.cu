@@ -1,30 +1,51 @@
 // Env half of the hot path: LeggedRobot.step minus the PhysX call, as three kernels.
-//   K1  pd_torques_kernel      _compute_torques                 legged_robot.py:649-671 (+ :623-624)
-//   K2  post_physics_kernel    post_physics_step + obs clips    legged_robot.py:673-709, 643-646; h1_env.py:55-123
+//   K1  pd_torques_kernel      _compute_torques                 legged_robot.py:649-671 (+ :623-624), go2_handstand_env.py:326-350
+//   K2  post_physics_kernel    post_physics_step + obs clips    legged_robot.py:673-709, 643-646; h1_env.py:55-123;
+//                                                               go2_handstand_env.py:84-96, 140-219, 224-383
 //   K2b finalize_step_kernel   _push_robots' all-env rewrite, last_root_vel, extras publication
 //                                                               legged_robot.py:540-555, 709, 742-768
-// Data layout: one warp owns 32 consecutive envs.  Row tensors ([N,13] root, [N,2A] dof_state,
-// [N,3B] contacts, [N,A] action-like) are staged through shared memory with coalesced loads and
-// odd row strides (bank-conflict-free thread-per-env access); [N] and [N,<=4] tensors are accessed
-// directly (already coalesced).  Compiled with -fmad=false: expressions evaluate as written.
+// K2 layout (v4): ONE THREAD PER ENV, one warp (32 consecutive envs) per block.  Every per-env quantity is computed once
+// (v3 split an env over 4 lanes and recomputed the frame transforms / termination / scalar terms on all four: 394
+// warp-instructions per env, instruction-bound at 0.24 of HBM).  Rows whose width is a multiple of 16 bytes (actions,
+// last_actions, last_dof_vel, torques, dof_state) are read with vector loads straight into registers; the odd-width
+// rows (root_states 13, contact_forces 3B floats) are staged by 1-D bulk TMA into shared memory, where the odd row
+// stride makes thread-per-row access bank-conflict-free; observations are assembled in registers, written to a shared
+// row image (noise is added there by a rolled loop over Philox blocks so the instruction footprint stays small) and
+// leave as one bulk-TMA store.  The rare reset path (2-3 % of envs) runs warp-cooperatively: one lane per random draw.
+// Compiled with -fmad=false: expressions evaluate as written (mask-deciding comparisons are bit-exact).
 #include "common.cuh"
 #include "philox.cuh"
 #include <new>
+#include <cmath>
 
 namespace urlg {
 
 thread_local char g_err[512] = "";
 long long g_launches = 0;
 
-constexpr int kMaxFeet = 8;
 constexpr float kPi = 3.14159274101257324f;      // float32(np.pi)
 constexpr float kTwoPi = 6.28318548202636719f;   // float32(2*np.pi)
 constexpr float kHalfPi = 1.57079637050628662f;  // float32(np.pi/2)
+constexpr int kAccCopies = 16;                   // episode-sum accumulators are spread over 16 copies (atomic contention)
 
 struct StepScratch {   // library-owned device scratch (zeroed at create)
-  float ep_acc[3][URLG_MAX_TERMS + 1];   // [slot][row] sums over reset envs, [slot][URLG_MAX_TERMS] = count
+  float ep_acc[3][kAccCopies][URLG_MAX_TERMS + 1];   // [slot][copy][row] sums over reset envs, [..][URLG_MAX_TERMS] = count
   int push_flag[3];
   int reset_cnt[3];
+  int root_cnt[3];
+};
+
+// Reward table by term id (built from the desc's active list at create): kernels test `mask >> id & 1`.
+struct TermTable {
+  unsigned long long mask;
+  float scale[URLG_T_COUNT];
+  int row[URLG_T_COUNT];
+};
+
+struct PoolArgs {
+  urlg_frame_pool pool;
+  int64_t calls_off;
+  int enabled;
 };
 
 }  // namespace urlg
@@ -32,45 +53,47 @@ struct StepScratch {   // library-owned device scratch (zeroed at create)
 struct urlg_env {
   urlg_env_desc desc;
   urlg_env_buffers bufs;
+  urlg::TermTable tt;
+  urlg::PoolArgs pool;
   urlg::StepScratch* scratch;
   int bound;
   int smem_bytes;
-  int vec_ok;      // every row tensor K2 stages / stores in bulk is 16-byte aligned (set at bind)
 };
 
 namespace urlg {
 
-// ---------------------------------------------------------------- shared-memory layout (K2)
-// One block = 32 consecutive envs x 4 lanes per env (128 threads).  The row tensors of those 32 envs are
-// contiguous in global memory, so each is ONE 1-D bulk-TMA copy (cp.async.bulk) into an unpadded shared image;
-// outputs with row structure (obs, privileged obs, last_actions, last_dof_vel) are assembled in shared memory and
-// leave as flat 16-byte vector stores.
-constexpr int kEnvsPerBlock = 32, kLanesPerEnv = 4, kK2Threads = kEnvsPerBlock * kLanesPerEnv;
-
-struct Layout {
-  int oRoot, oDof, oCon, oAct, oLact, oLdv, oTq, oRb, oObs, oPriv, oTerm, oBar, total;   // float offsets
+struct Seam {
+  const float* root;
+  const float* dof;
+  const float* contact;
+  const float* rigid;
 };
 
-__host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
-  Layout L;
-  const int A = c.num_dof, R = kEnvsPerBlock;
-  int o = 0;
-  L.oRoot = o; o += R * 13;
-  L.oDof = o; o += R * 2 * A;
-  L.oCon = o; o += R * 3 * c.num_bodies;
-  L.oAct = o; o += R * A;
-  L.oLact = o; o += R * A;
-  L.oLdv = o; o += R * A;
-  L.oTq = o; o += R * A;
-  L.oRb = o; o += c.family == 1 ? R * c.num_feet * 13 : 0;
-  o = (o + 3) & ~3;
-  L.oObs = o; o += R * c.num_obs;
-  L.oPriv = o; o += R * c.num_priv;
-  o = (o + 3) & ~3;
-  L.oTerm = o; o += R * URLG_MAX_TERMS;      // this step's scaled term values per env (episode_sums increments)
-  L.oBar = o; o += 4;
-  L.total = o;
-  return L;
+// Physics tensors of the current (sub)step: the bound tensors, or a frame of the bound pool (include/urlg_b200.h).
+__device__ __forceinline__ Seam resolve_seam(const urlg_env_desc& c, const urlg_env_buffers& b, const PoolArgs& pa) {
+  Seam s{b.root_states, b.dof_state, b.contact_forces, b.rigid_body_states};
+  if (pa.enabled) {
+    const int64_t calls = *pa.pool.calls_base + pa.calls_off;
+    if (calls > 0) {
+      const uint64_t cidx = (uint64_t)(calls - 1);
+      uint64_t frame, sub;
+      const uint32_t D = (uint32_t)pa.pool.substeps, P = (uint32_t)pa.pool.num_frames;
+      if (cidx <= 0xffffffffull) {
+        const uint32_t q = (uint32_t)cidx / D;
+        sub = (uint32_t)cidx - q * D;
+        frame = q % P;
+      } else {
+        frame = (cidx / D) % P;
+        sub = cidx % D;
+      }
+      const size_t N = (size_t)c.num_envs;
+      s.root = pa.pool.root + frame * N * 13;
+      s.dof = pa.pool.dof + (frame * D + sub) * N * (size_t)c.num_dof * 2;
+      s.contact = pa.pool.contact + frame * N * (size_t)c.num_bodies * 3;
+      if (pa.pool.rigid_body) s.rigid = pa.pool.rigid_body + frame * N * (size_t)c.num_bodies * 13;
+    }
+  }
+  return s;
 }
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -82,38 +105,38 @@ __device__ __forceinline__ void bulk_s2g(float* dst, const float* src, uint32_t 
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                ::"l"(reinterpret_cast<uint64_t>(dst)), "r"(smem_addr(src)), "r"(bytes) : "memory");
 }
-// Flat copy of `n` floats (tail / unaligned fallback).
-static __device__ __noinline__ void flat_in(float* __restrict__ s, const float* __restrict__ g, int n, int n_pad, int tid) {
-#pragma unroll 1
-  for (int i = tid; i < n_pad; i += kK2Threads) s[i] = i < n ? g[i] : 0.0f;
-}
-static __device__ __noinline__ void flat_out(float* __restrict__ g, const float* __restrict__ s, int n, int tid) {
-#pragma unroll 1
-  for (int i = tid; i < n; i += kK2Threads) g[i] = s[i];
-}
-// Sum over the 4 lanes of an env; every lane gets the same bits (commutative pairwise adds).
-__device__ __forceinline__ float qsum(float x) {
-  x += __shfl_xor_sync(0xffffffffu, x, 1);
-  x += __shfl_xor_sync(0xffffffffu, x, 2);
-  return x;
-}
 // episode_length_buf % period (period > 0); the counters are small, so avoid the 64-bit division.
 __device__ __forceinline__ bool divisible(int64_t len, int period) {
   if ((uint64_t)len <= 0x7fffffffull) return ((uint32_t)len % (uint32_t)period) == 0u;
   return (len % period) == 0;
 }
 
-// torch.remainder for floats: fmod then fix the sign (ATen BinaryOpsKernel remainder_kernel).
+// torch.remainder(a, b) for b > 0 (ATen: fmod, then += b if the sign differs).  fmod is exact; for |a| < 2b it is a or
+// a -+ b (exact by Sterbenz), for 0 <= a/b < 2^22 it is fma(-trunc(a/b), b, a) with a one-step correction (the exact
+// remainder is representable, so the fma is exact); anything else takes libm's fmodf.
 static __device__ __noinline__ float py_remainder(float a, float b) {
-  float m = fmodf(a, b);
-  if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m += b;
+  float m;
+  const float aa = fabsf(a);
+  if (aa < b) {
+    m = a;
+  } else if (aa < 2.0f * b) {
+    m = a < 0.0f ? a + b : a - b;
+  } else if (a > 0.0f && a < b * 4194304.0f) {
+    const float q = truncf(a / b);
+    m = fmaf(-q, b, a);
+    if (m < 0.0f) m += b;
+    else if (m >= b) m -= b;
+  } else {
+    m = fmodf(a, b);
+  }
+  if (m != 0.0f && m < 0.0f) m += b;
   return m;
 }
 
-// One out-of-line copy each of the libm-heavy helpers: K2 is latency-bound at 4096 envs and an I-cache miss costs more
-// than a call (ncu: 45% of stall samples were no_instructions with everything inlined, 10k SASS instructions).
+// One out-of-line copy of atan2f: K2 is latency-bound at 4096 envs and a cold instruction fetch costs more than a call.
 static __device__ __noinline__ float atan2_ni(float y, float x) { return atan2f(y, x); }
 __device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
 // [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw
 __device__ __forceinline__ void rot_inv(float qx, float qy, float qz, float qw, float vx, float vy, float vz,
@@ -126,18 +149,32 @@ __device__ __forceinline__ void rot_inv(float qx, float qy, float qz, float qw, 
   oz = vz * s - cz * qw * 2.0f + qz * d * 2.0f;
 }
 
+// Uniform of (global env, step, slot): Philox word slot%4 of block slot/4, or the injected table.
+__device__ __forceinline__ float slot_uniform(const urlg_env_desc& c, const float* ovr, int64_t genv, int64_t step,
+                                              int slot, int num_slots, int local_env) {
+  if (ovr) return ovr[(size_t)local_env * num_slots + slot];
+  const uint4 r = philox4x32_10(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff), (uint32_t)((uint64_t)step >> 32),
+                                           (uint32_t)(slot >> 2)), c.seed_lo, c.seed_hi ^ kStreamEnv);
+  const int l = slot & 3;
+  return u01(l == 0 ? r.x : l == 1 ? r.y : l == 2 ? r.z : r.w);
+}
+
 // ---------------------------------------------------------------- K1: PD torques
-// One element: clip + store the action (first substep), PD law, torque-limit clip (legged_robot.py:649-671).
+// One element: PD law (legged_robot.py:649-671).  P control clamps the target to [pd_target_lo, pd_target_hi]
+// (+-inf unless a task narrows it: go2_handstand_env.py:336-346); the torque clip is skipped when the task's override
+// has none (:349-350).
 __device__ __forceinline__ float pd_one(const urlg_env_desc& c, int j, float a, float q, float qd, float last_qd) {
   const float as = a * c.action_scale;
   float tq;
   if (c.control_type == 'P') {
-    tq = c.p_gains[j] * (as + c.default_dof_pos[j] - q) - c.d_gains[j] * qd;
+    const float target = clampf(as + c.default_dof_pos[j], c.pd_target_lo[j], c.pd_target_hi[j]);
+    tq = c.p_gains[j] * (target - q) - c.d_gains[j] * qd;
   } else if (c.control_type == 'V') {
     tq = c.p_gains[j] * (as - qd) - c.d_gains[j] * (qd - last_qd) / c.sim_dt;
   } else {
     tq = as;
   }
+  if (!c.clip_torques) return tq;
   const float lim = c.torque_limits[j];
   return fminf(fmaxf(tq, -lim), lim);
 }
@@ -147,9 +184,11 @@ __device__ __forceinline__ float pd_one(const urlg_env_desc& c, int j, float a, 
 // so every load of the grid is in flight at once.
 __global__ void __launch_bounds__(256) pd_torques_vec4_kernel(const __grid_constant__ urlg_env_desc c,
                                                               const __grid_constant__ urlg_env_buffers b,
+                                                              const __grid_constant__ PoolArgs pa,
                                                               const float* __restrict__ raw_actions, uint32_t total4) {
   const uint32_t i = blockIdx.x * 256u + threadIdx.x;
   if (i >= total4) return;
+  const Seam seam = resolve_seam(c, b, pa);
   const uint32_t quads = (uint32_t)c.num_dof >> 2;
   const int j0 = (int)(i % quads) * 4;
   float4 a;
@@ -162,8 +201,8 @@ __global__ void __launch_bounds__(256) pd_torques_vec4_kernel(const __grid_const
   } else {
     a = reinterpret_cast<const float4*>(b.actions)[i];
   }
-  const float4 s0 = reinterpret_cast<const float4*>(b.dof_state)[2 * (size_t)i];
-  const float4 s1 = reinterpret_cast<const float4*>(b.dof_state)[2 * (size_t)i + 1];
+  const float4 s0 = reinterpret_cast<const float4*>(seam.dof)[2 * (size_t)i];
+  const float4 s1 = reinterpret_cast<const float4*>(seam.dof)[2 * (size_t)i + 1];
   float4 l = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
   if (c.control_type == 'V') l = reinterpret_cast<const float4*>(b.last_dof_vel)[i];
   float4 t;
@@ -177,7 +216,9 @@ __global__ void __launch_bounds__(256) pd_torques_vec4_kernel(const __grid_const
 // Scalar form: one thread per (env, dof); actions / torques coalesced, dof_state read as float2.
 __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__ urlg_env_desc c,
                                                          const __grid_constant__ urlg_env_buffers b,
+                                                         const __grid_constant__ PoolArgs pa,
                                                          const float* __restrict__ raw_actions) {
+  const Seam seam = resolve_seam(c, b, pa);
   const uint32_t total = (uint32_t)c.num_envs * (uint32_t)c.num_dof;      // host checks num_envs * num_dof < 2^31
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int j = (int)(i % (uint32_t)c.num_dof);
@@ -188,131 +229,199 @@ __global__ void __launch_bounds__(256) pd_torques_kernel(const __grid_constant__
     } else {
       a = b.actions[i];
     }
-    const float2 pv = reinterpret_cast<const float2*>(b.dof_state)[i];
+    const float2 pv = reinterpret_cast<const float2*>(seam.dof)[i];
     b.torques[i] = pd_one(c, j, a, pv.x, pv.y, c.control_type == 'V' ? b.last_dof_vel[i] : 0.0f);
   }
 }
 
-// ---------------------------------------------------------------- command resampling (E6)
-static __device__ __noinline__ void resample_commands(const urlg_env_desc& c, SlotRng& rng, int slot, float* cmd) {
-  cmd[0] = (c.cmd_x[1] - c.cmd_x[0]) * rng.uniform(slot) + c.cmd_x[0];
-  cmd[1] = (c.cmd_y[1] - c.cmd_y[0]) * rng.uniform(slot + 1) + c.cmd_y[0];
+// ---------------------------------------------------------------- row helpers (thread per env)
+// W floats of one row into registers.  Rows of a multiple of 16 / 8 bytes use 128- / 64-bit loads (the tensors are
+// 16-byte aligned, checked at bind).
+template <int W>
+__device__ __forceinline__ void ld_row(float (&dst)[W], const float* __restrict__ src) {
+  if constexpr (W % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < W / 4; ++i) {
+      const float4 v = reinterpret_cast<const float4*>(src)[i];
+      dst[4 * i] = v.x; dst[4 * i + 1] = v.y; dst[4 * i + 2] = v.z; dst[4 * i + 3] = v.w;
+    }
+  } else if constexpr (W % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < W / 2; ++i) {
+      const float2 v = reinterpret_cast<const float2*>(src)[i];
+      dst[2 * i] = v.x; dst[2 * i + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < W; ++i) dst[i] = src[i];
+  }
+}
+template <int W>
+__device__ __forceinline__ void st_row(float* __restrict__ dst, const float (&src)[W]) {
+  if constexpr (W % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < W / 4; ++i)
+      reinterpret_cast<float4*>(dst)[i] = make_float4(src[4 * i], src[4 * i + 1], src[4 * i + 2], src[4 * i + 3]);
+  } else if constexpr (W % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < W / 2; ++i) reinterpret_cast<float2*>(dst)[i] = make_float2(src[2 * i], src[2 * i + 1]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < W; ++i) dst[i] = src[i];
+  }
+}
+
+// ---------------------------------------------------------------- shared-memory layout (K2): 32 envs per block
+// Row stride of the shared observation image: a stride that is a multiple of 8 floats would put the 32 rows of a warp
+// on 4 banks (48-dim Go2 obs: 16-way conflicts), so such rows are padded by one float and leave through a
+// warp-cooperative float4 copy; every other width is stored densely and leaves as one bulk-TMA store.
+__host__ __device__ constexpr int obs_stride(int num_obs) { return num_obs % 8 == 0 ? num_obs + 1 : num_obs; }
+
+struct Layout {
+  int oRoot, oCon, oObs, oPriv, oTerm, oBar, total;   // float offsets
+};
+__host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
+  Layout L;
+  int o = 0;
+  L.oRoot = o; o += 32 * 13;
+  L.oCon = o; o += 32 * 3 * c.num_bodies;
+  L.oObs = o; o += 32 * obs_stride(c.num_obs);
+  o = (o + 3) & ~3;
+  L.oPriv = o; o += c.family == URLG_FAMILY_H1 ? 32 * c.num_priv : 0;
+  o = (o + 3) & ~3;
+  L.oTerm = o; o += 32 * (c.num_sums > 0 ? c.num_sums : 1);
+  o = (o + 3) & ~3;
+  L.oBar = o; o += 4;
+  L.total = o;
+  return L;
+}
+
+template <int A, int FAM>
+struct ObsDims {
+  static constexpr int kObs = FAM == URLG_FAMILY_BASE ? 12 + 3 * A : FAM == URLG_FAMILY_H1 ? 11 + 3 * A : 10 + 3 * A;
+  static constexpr int kPriv = FAM == URLG_FAMILY_H1 ? kObs + 3 : 0;
+};
+
+// command resampling (E6, legged_robot.py:519-538) from three uniforms
+__device__ __forceinline__ void resample_commands(const urlg_env_desc& c, float ux, float uy, float uh, float (&cmd)[4]) {
+  cmd[0] = (c.cmd_x[1] - c.cmd_x[0]) * ux + c.cmd_x[0];
+  cmd[1] = (c.cmd_y[1] - c.cmd_y[0]) * uy + c.cmd_y[0];
   if (c.heading_command)
-    cmd[3] = (c.cmd_heading[1] - c.cmd_heading[0]) * rng.uniform(slot + 2) + c.cmd_heading[0];
+    cmd[3] = (c.cmd_heading[1] - c.cmd_heading[0]) * uh + c.cmd_heading[0];
   else
-    cmd[2] = (c.cmd_yaw[1] - c.cmd_yaw[0]) * rng.uniform(slot + 2) + c.cmd_yaw[0];
+    cmd[2] = (c.cmd_yaw[1] - c.cmd_yaw[0]) * uh + c.cmd_yaw[0];
   const float keep = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) > 0.2f ? 1.0f : 0.0f;
   cmd[0] *= keep;
   cmd[1] *= keep;
 }
 
-}  // namespace urlg
-
-namespace urlg {
-
 // ---------------------------------------------------------------- K2: fused post-physics step
-// Thread layout: tid = 4 * local_env + g.  Lane g of an env owns DOFs / bodies / feet / episode-sum rows
-// g, g+4, g+8, ... and the observation columns [g*ceil(num_obs/4), ...); per-env scalars (frame transforms,
-// commands, termination) are computed by all four lanes on identical inputs, so every lane holds identical bits
-// and the quad never diverges on an env-level decision.
-__global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
-                                                                 const __grid_constant__ urlg_env_buffers b,
-                                                                 StepScratch* __restrict__ scratch,
-                                                                 const int64_t* __restrict__ step_base, int64_t step_off,
-                                                                 int obs_slot, int num_slots, int vec_ok) {
+// RNG slot map per (env, step) (shared with oracle/refharness/run_reference.py):
+//   0..2 callback resample | 3..3+A-1 _reset_dofs | 3+A..8+A root velocities | 9+A..11+A reset resample |
+//   12+A,13+A push | 14+A..14+A+O-1 observation noise | handstand: 14+A+O..+3 contact-flag flips
+template <int A, int FAM>
+__global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+                                                          const __grid_constant__ urlg_env_buffers b,
+                                                          const __grid_constant__ TermTable tt,
+                                                          const __grid_constant__ PoolArgs pa,
+                                                          StepScratch* __restrict__ scratch,
+                                                          const int64_t* __restrict__ step_base, int64_t step_off,
+                                                          int obs_slot, int num_slots) {
+  constexpr int O = ObsDims<A, FAM>::kObs, PV = ObsDims<A, FAM>::kPriv, OS = obs_stride(O);
+  constexpr bool kPadObs = OS != O;
+  constexpr unsigned kFull = 0xffffffffu;
   extern __shared__ __align__(128) float sm[];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets K2b's blocks start their Philox draws early
   const Layout L = make_layout(c);
-  const int tid = threadIdx.x;
-  const int env0 = blockIdx.x * kEnvsPerBlock;
-  const int nrows = min(kEnvsPerBlock, c.num_envs - env0);
-  const int A = c.num_dof, B = c.num_bodies, F = c.num_feet, N = c.num_envs;
+  const int lane = threadIdx.x;
+  const int env0 = blockIdx.x * 32;
+  const int N = c.num_envs, B = c.num_bodies, F = c.num_feet;
+  const int nrows = min(32, N - env0);
+  const bool live = lane < nrows;
+  const int e = live ? env0 + lane : env0;       // dead lanes of the tail block shadow env0 and store nothing
   const int64_t step = eff_step(step_base, step_off);
   const int acc = (int)(step & 1);
-  const bool bulk = vec_ok && nrows == kEnvsPerBlock;
+  const bool bulk = nrows == 32;
+  const Seam seam = resolve_seam(c, b, pa);
+  const uint64_t mask = tt.mask;
+#define HAS(ID) ((mask >> (ID)) & 1ull)
 
-  // ---- stage the row tensors of this block's 32 envs ----
+  // ---- stage the odd-width rows (root 13, contacts 3B floats per env) ----
   const uint32_t bar = smem_addr(sm + L.oBar);
   if (bulk) {
-    if (tid == 0) {
+    if (lane == 0) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      const uint32_t bytes = (uint32_t)(kEnvsPerBlock * (13 + 2 * A + 3 * B + 4 * A) * sizeof(float));
+      const uint32_t bytes = (uint32_t)(32 * (13 + 3 * B) * sizeof(float));
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-      const uint32_t rA = kEnvsPerBlock * A * sizeof(float);
-      bulk_g2s(sm + L.oRoot, b.root_states + (size_t)env0 * 13, kEnvsPerBlock * 13 * sizeof(float), bar);
-      bulk_g2s(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, 2 * rA, bar);
-      bulk_g2s(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, kEnvsPerBlock * 3 * B * sizeof(float), bar);
-      bulk_g2s(sm + L.oAct, b.actions + (size_t)env0 * A, rA, bar);
-      bulk_g2s(sm + L.oLact, b.last_actions + (size_t)env0 * A, rA, bar);
-      bulk_g2s(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, rA, bar);
-      bulk_g2s(sm + L.oTq, b.torques + (size_t)env0 * A, rA, bar);
+      bulk_g2s(sm + L.oRoot, seam.root + (size_t)env0 * 13, 32 * 13 * sizeof(float), bar);
+      bulk_g2s(sm + L.oCon, seam.contact + (size_t)env0 * 3 * B, 32 * 3 * B * sizeof(float), bar);
     }
   } else {
-    flat_in(sm + L.oRoot, b.root_states + (size_t)env0 * 13, nrows * 13, kEnvsPerBlock * 13, tid);
-    flat_in(sm + L.oDof, b.dof_state + (size_t)env0 * 2 * A, nrows * 2 * A, kEnvsPerBlock * 2 * A, tid);
-    flat_in(sm + L.oCon, b.contact_forces + (size_t)env0 * 3 * B, nrows * 3 * B, kEnvsPerBlock * 3 * B, tid);
-    flat_in(sm + L.oAct, b.actions + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
-    flat_in(sm + L.oLact, b.last_actions + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
-    flat_in(sm + L.oLdv, b.last_dof_vel + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
-    flat_in(sm + L.oTq, b.torques + (size_t)env0 * A, nrows * A, kEnvsPerBlock * A, tid);
+    for (int i = lane; i < 32 * 13; i += 32) sm[L.oRoot + i] = i < nrows * 13 ? seam.root[(size_t)env0 * 13 + i] : 0.0f;
+    for (int i = lane; i < 32 * 3 * B; i += 32)
+      sm[L.oCon + i] = i < nrows * 3 * B ? seam.contact[(size_t)env0 * 3 * B + i] : 0.0f;
   }
-  if (c.family == 1) {   // only the feet rows of rigid_body_states (h1_env.py:51-53): 52-byte rows, plain loads
-    const int w = F * 13;
-    for (int i = tid; i < kEnvsPerBlock * w; i += kK2Threads) {
-      const int r = i / w, rem = i - r * w, f = rem / 13, k = rem - f * 13;
-      sm[L.oRb + i] = r < nrows ? b.rigid_body_states[((size_t)(env0 + r) * B + c.feet_idx[f]) * 13 + k] : 0.0f;
-    }
-  }
-  const int le = tid >> 2, g = tid & 3;
-  const int e = env0 + le;
-  const bool live = le < nrows;            // tail block: dead quads compute on zeros and store nothing
-  // ---- per-env scalars straight from global, issued before the wait so their latency hides under the bulk copy ----
-  int64_t len = (live ? b.episode_length_buf[e] : 0) + 1;              // :681
-  float cmd[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-  if (live) {
+
+  // ---- everything else straight into registers, issued before the wait ----
+  int64_t len = b.episode_length_buf[e] + 1;                             // :681
+  float cmd[4];
+  {
     const float4 v = reinterpret_cast<const float4*>(b.commands)[e];
     cmd[0] = v.x; cmd[1] = v.y; cmd[2] = v.z; cmd[3] = v.w;
   }
-  float air[2] = {0.0f, 0.0f};
-  uint8_t lastc[2] = {0, 0};
+  float act[A], lact[A], ldv[A], tq[A], dofs[2 * A];
+  ld_row<A>(act, b.actions + (size_t)e * A);
+  ld_row<A>(lact, b.last_actions + (size_t)e * A);
+  ld_row<A>(ldv, b.last_dof_vel + (size_t)e * A);
+  ld_row<A>(tq, b.torques + (size_t)e * A);
+  ld_row<2 * A>(dofs, seam.dof + (size_t)e * 2 * A);
+  float air[URLG_MAX_FEET];
+  uint8_t lastc[URLG_MAX_FEET];
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int f = g + 4 * q;
-    if (f < F && live) {
-      air[q] = b.feet_air_time[(size_t)e * F + f];
-      lastc[q] = b.last_contacts[(size_t)e * F + f];
+  for (int f = 0; f < URLG_MAX_FEET; ++f) {
+    air[f] = f < F ? b.feet_air_time[(size_t)e * F + f] : 0.0f;
+    lastc[f] = f < F ? b.last_contacts[(size_t)e * F + f] : (uint8_t)0;
+  }
+  // feet rows of rigid_body_states (h1_env.py:51-53; go2_handstand_env.py:73-76): only the columns the terms read
+  float foot_z[2] = {0.0f, 0.0f}, foot_v[2][3] = {{0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}}, foot_xy[2][2] = {{0.0f, 0.0f}, {0.0f, 0.0f}};
+  if constexpr (FAM == URLG_FAMILY_H1) {
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      if (f < F) {
+        const float* rb = seam.rigid + ((size_t)e * B + c.feet_idx[f]) * 13;
+        foot_z[f] = rb[2];
+        foot_v[f][0] = rb[7]; foot_v[f][1] = rb[8]; foot_v[f][2] = rb[9];
+      }
     }
   }
-  float sums[URLG_MAX_TERMS / kLanesPerEnv];      // episode_sums rows g, g+4, ... of this env
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    if (HAS(URLG_T_FRONT_FEET_TOGETHER)) {
 #pragma unroll
-  for (int q = 0; q < URLG_MAX_TERMS / kLanesPerEnv; ++q) {
-    const int k = g + kLanesPerEnv * q;
-    sums[q] = (live && k < c.num_sums) ? b.episode_sums[(size_t)k * N + e] : 0.0f;
+      for (int f = 0; f < 2; ++f) {
+        const float* rb = seam.rigid + ((size_t)e * B + c.feet_idx[f]) * 13;
+        foot_xy[f][0] = rb[0]; foot_xy[f][1] = rb[1];
+      }
+    }
   }
-  __syncthreads();
+  const float* ovr = b.rng_override;
+  const int64_t genv = c.env_offset + e;
+
   if (bulk) {
     uint32_t ok = 0;
     while (!ok) {
       asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                    : "=r"(ok) : "r"(bar) : "memory");
     }
+  } else {
+    __syncwarp();
   }
 
-  float* root = sm + L.oRoot + le * 13;
-  float* dof = sm + L.oDof + le * 2 * A;
-  const float* con = sm + L.oCon + le * 3 * B;
-  float* act = sm + L.oAct + le * A;
-  float* lact = sm + L.oLact + le * A;
-  float* ldv = sm + L.oLdv + le * A;
-  const float* tq = sm + L.oTq + le * A;
-  const float* rb = sm + L.oRb + le * F * 13;
-  float* obs = sm + L.oObs + le * c.num_obs;
-  float* priv = sm + L.oPriv + le * c.num_priv;
-  float* term = sm + L.oTerm + le * URLG_MAX_TERMS;
-
-  SlotRng rng;
-  rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
-           (b.rng_override && live) ? b.rng_override + (size_t)e * num_slots : nullptr);
+  float root[13];
+#pragma unroll
+  for (int k = 0; k < 13; ++k) root[k] = sm[L.oRoot + lane * 13 + k];
+  const float* con = sm + L.oCon + lane * 3 * B;
+  float* term = sm + L.oTerm + lane;           // term[row * 32]
   const float flen = (float)len;
 
   // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
@@ -329,347 +438,549 @@ __global__ void __launch_bounds__(kK2Threads, 6) post_physics_kernel(const __gri
 
   // ---- E5 callback: gait phase (h1_env.py:58-63), resample (:511-512), heading (:513-516) ----
   float phase = 0.0f, leg_phase[2] = {0.0f, 0.0f};
-  if (c.family == 1) {
+  if constexpr (FAM == URLG_FAMILY_H1) {
     phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
     leg_phase[0] = phase;
     leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
   }
-  if (divisible(len, c.resample_steps)) resample_commands(c, rng, 0, cmd);
-  if (c.heading_command) {
-    // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
-    const float ty = qz * 2.0f, tz = -qy * 2.0f;
-    const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
-    const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
-    const float heading = atan2_ni(fy, fx);
-    float a = py_remainder(cmd[3] - heading, kTwoPi);
-    a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
-    cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
+  if (c.callback_mode == URLG_CALLBACK_BASE) {
+    if (divisible(len, c.resample_steps)) {
+      const float ux = slot_uniform(c, ovr, genv, step, 0, num_slots, e);
+      const float uy = slot_uniform(c, ovr, genv, step, 1, num_slots, e);
+      const float uh = slot_uniform(c, ovr, genv, step, 2, num_slots, e);
+      resample_commands(c, ux, uy, uh, cmd);
+    }
+    if (c.heading_command) {
+      // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
+      const float ty = qz * 2.0f, tz = -qy * 2.0f;
+      const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
+      const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
+      const float heading = atan2_ni(fy, fx);
+      float a = py_remainder(cmd[3] - heading, kTwoPi);
+      a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
+      cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
+    }
   }
 
-  // ---- E7 termination :715-721 ----
-  float hits = 0.0f;
-  _Pragma("unroll 1") for (int k = g; k < c.num_term_bodies; k += kLanesPerEnv) {
+  // ---- E7 termination :715-721 / go2_handstand_env.py:178-219 ----
+  bool reset = false;
+  _Pragma("unroll 1") for (int k = 0; k < c.num_term_bodies; ++k) {
     const float* f3 = con + 3 * c.term_idx[k];
-    hits += norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
+    reset |= norm3(f3[0], f3[1], f3[2]) > 1.0f;
   }
-  bool reset = qsum(hits) > 0.0f;
-  reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
+  if (c.termination_mode == URLG_TERMINATION_RPY)
+    reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
+  else
+    reset |= (gz > -0.2f) && (gz < 0.2f);
   const bool time_out = flen > c.max_episode_length;
   reset |= time_out;
 
-  // ---- E8/E9 rewards, alphabetical, :775-787.  Lane g owns feet g and g+4. ----
+  // ---- feet contact state shared by several terms ----
+  float foot_fz[URLG_MAX_FEET], foot_fn[URLG_MAX_FEET], foot_fxy[URLG_MAX_FEET];
+#pragma unroll
+  for (int f = 0; f < URLG_MAX_FEET; ++f) {
+    foot_fz[f] = 0.0f; foot_fn[f] = 0.0f; foot_fxy[f] = 0.0f;
+    if (f < F) {
+      const float* f3 = con + 3 * c.feet_idx[f];
+      const float x = f3[0], y = f3[1], z = f3[2];
+      foot_fz[f] = z;
+      foot_fn[f] = norm3(x, y, z);
+      foot_fxy[f] = sqrtf(x * x + y * y);
+    }
+  }
+
+  // ---- E8/E9 rewards in alphabetical order of the reward names (:775-787) ----
+  // tensor / python-scalar: ATen's CUDA kernel multiplies by the reciprocal (BinaryDivTrueKernel.cu, CPU-scalar divisor),
+  // i.e. what the reference computes on its own device; the CPU fixtures (true division) agree to 1.2e-7 relative
+  const float inv_dt = 1.0f / c.dt, inv_sigma = 1.0f / c.tracking_sigma;
   const float cmd_xy = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]);
   float rew = 0.0f;
-  for (int t = 0; t < c.num_terms; ++t) {
-    float r = 0.0f;
-    switch (c.term_ids[t]) {
-      case URLG_T_ACTION_RATE:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float d = lact[j] - act[j]; r += d * d; }
-        r = qsum(r);
-        break;
-      case URLG_T_ALIVE: r = 1.0f; break;
-      case URLG_T_ANG_VEL_XY: r = avx * avx + avy * avy; break;
-      case URLG_T_BASE_HEIGHT: { const float d = root_z - c.base_height_target; r = d * d; } break;
-      case URLG_T_COLLISION:
-        _Pragma("unroll 1") for (int k = g; k < c.num_pen; k += kLanesPerEnv) {
-          const float* f3 = con + 3 * c.pen_idx[k];
-          r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
-        }
-        r = qsum(r);
-        break;
-      case URLG_T_CONTACT:
-        if (g < F && g < 2) {
-          const bool stance = leg_phase[g] < 0.55f;
-          const bool contact = con[3 * c.feet_idx[g] + 2] > 1.0f;
-          r = (contact != stance) ? 0.0f : 1.0f;
-        }
-        r = qsum(r);
-        break;
-      case URLG_T_CONTACT_NO_VEL:
-        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
-          const float* f3 = con + 3 * c.feet_idx[f];
-          const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 1.0f : 0.0f;
-          for (int k = 0; k < 3; ++k) { const float v = rb[f * 13 + 7 + k] * m; r += v * v; }
-        }
-        r = qsum(r);
-        break;
-      case URLG_T_DOF_ACC:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float d = (ldv[j] - dof[2 * j + 1]) / c.dt; r += d * d; }
-        r = qsum(r);
-        break;
-      case URLG_T_DOF_POS_LIMITS:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {
-          const float q = dof[2 * j];
-          r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
-        }
-        r = qsum(r);
-        break;
-      case URLG_T_DOF_VEL:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) { const float v = dof[2 * j + 1]; r += v * v; }
-        r = qsum(r);
-        break;
-      case URLG_T_DOF_VEL_LIMITS:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv)
-          r += fminf(fmaxf(fabsf(dof[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
-        r = qsum(r);
-        break;
-      case URLG_T_FEET_AIR_TIME: {   // stateful, :912-923
+#define TERM_END(ID) r *= tt.scale[ID]; rew += r; term[tt.row[ID] * 32] = r; }
+#define TERM_BEGIN(ID) if (HAS(ID)) { float r = 0.0f;
+  TERM_BEGIN(URLG_T_ACTION_RATE)
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const int f = g + 4 * q;
-          if (f < F) {
-            const bool contact = con[3 * c.feet_idx[f] + 2] > 1.0f;
-            const bool filt = contact || lastc[q];
-            lastc[q] = contact;
-            const float first = (air[q] > 0.0f && filt) ? 1.0f : 0.0f;
-            air[q] += c.dt;
-            r += (air[q] - 0.5f) * first;
-            air[q] *= filt ? 0.0f : 1.0f;
-          }
+    for (int j = 0; j < A; ++j) { const float d = lact[j] - act[j]; r += d * d; }
+  TERM_END(URLG_T_ACTION_RATE)
+  TERM_BEGIN(URLG_T_ALIVE) r = 1.0f; TERM_END(URLG_T_ALIVE)
+  TERM_BEGIN(URLG_T_ANG_VEL_XY) r = avx * avx + avy * avy; TERM_END(URLG_T_ANG_VEL_XY)
+  TERM_BEGIN(URLG_T_BASE_HEIGHT) { const float d = root_z - c.base_height_target; r = d * d; } TERM_END(URLG_T_BASE_HEIGHT)
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_BASE_HEIGHT_HS)           // go2_handstand_env.py:237-246
+      const float err = fmaxf(c.base_height_target - root_z, 0.0f);
+      r = expf(-8.0f * err * err);
+    TERM_END(URLG_T_BASE_HEIGHT_HS)
+  }
+  TERM_BEGIN(URLG_T_COLLISION)
+    _Pragma("unroll 1") for (int k = 0; k < c.num_pen; ++k) {
+      const float* f3 = con + 3 * c.pen_idx[k];
+      r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
+    }
+  TERM_END(URLG_T_COLLISION)
+  if constexpr (FAM == URLG_FAMILY_H1) {
+    TERM_BEGIN(URLG_T_CONTACT)                  // h1_env.py:98-104
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        if (f < F) {
+          const bool stance = leg_phase[f] < 0.55f;
+          const bool contact = foot_fz[f] > 1.0f;
+          r += (contact != stance) ? 0.0f : 1.0f;
         }
-        r = qsum(r);
-        r *= cmd_xy > 0.1f ? 1.0f : 0.0f;
-      } break;
-      case URLG_T_FEET_CONTACT_FORCES:
-        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
-          const float* f3 = con + 3 * c.feet_idx[f];
-          r += fmaxf(norm3(f3[0], f3[1], f3[2]) - c.max_contact_force, 0.0f);
-        }
-        r = qsum(r);
-        break;
-      case URLG_T_FEET_SWING_HEIGHT:
-        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
-          const float* f3 = con + 3 * c.feet_idx[f];
-          const float m = norm3(f3[0], f3[1], f3[2]) > 1.0f ? 0.0f : 1.0f;
-          const float d = rb[f * 13 + 2] - 0.08f;
+      }
+    TERM_END(URLG_T_CONTACT)
+    TERM_BEGIN(URLG_T_CONTACT_NO_VEL)           // h1_env.py:115-120
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        const float m = foot_fn[f] > 1.0f ? 1.0f : 0.0f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const float v = foot_v[f][k] * m; r += v * v; }
+      }
+    TERM_END(URLG_T_CONTACT_NO_VEL)
+  }
+  TERM_BEGIN(URLG_T_DOF_ACC)
+#pragma unroll
+    for (int j = 0; j < A; ++j) { const float d = (ldv[j] - dofs[2 * j + 1]) * inv_dt; r += d * d; }
+  TERM_END(URLG_T_DOF_ACC)
+  TERM_BEGIN(URLG_T_DOF_POS_LIMITS)
+#pragma unroll
+    for (int j = 0; j < A; ++j) {
+      const float q = dofs[2 * j];
+      r += -fminf(q - c.dof_pos_lo[j], 0.0f) + fmaxf(q - c.dof_pos_hi[j], 0.0f);
+    }
+  TERM_END(URLG_T_DOF_POS_LIMITS)
+  TERM_BEGIN(URLG_T_DOF_VEL)
+#pragma unroll
+    for (int j = 0; j < A; ++j) { const float v = dofs[2 * j + 1]; r += v * v; }
+  TERM_END(URLG_T_DOF_VEL)
+  TERM_BEGIN(URLG_T_DOF_VEL_LIMITS)
+#pragma unroll
+    for (int j = 0; j < A; ++j)
+      r += fminf(fmaxf(fabsf(dofs[2 * j + 1]) - c.dof_vel_limits[j] * c.soft_dof_vel_limit, 0.0f), 1.0f);
+  TERM_END(URLG_T_DOF_VEL_LIMITS)
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_ENERGY)                   // go2_handstand_env.py:319-324
+#pragma unroll
+      for (int j = 0; j < A; ++j) r += fabsf(tq[j]) * fabsf(dofs[2 * j + 1]);
+    TERM_END(URLG_T_ENERGY)
+  }
+  TERM_BEGIN(URLG_T_FEET_AIR_TIME)              // stateful, :912-923
+#pragma unroll
+    for (int f = 0; f < URLG_MAX_FEET; ++f) {
+      if (f < F) {
+        const bool contact = foot_fz[f] > 1.0f;
+        const bool filt = contact || lastc[f];
+        lastc[f] = contact;
+        const float first = (air[f] > 0.0f && filt) ? 1.0f : 0.0f;
+        air[f] += c.dt;
+        r += (air[f] - 0.5f) * first;
+        air[f] *= filt ? 0.0f : 1.0f;
+      }
+    }
+    r *= cmd_xy > 0.1f ? 1.0f : 0.0f;
+  TERM_END(URLG_T_FEET_AIR_TIME)
+  TERM_BEGIN(URLG_T_FEET_CONTACT_FORCES)
+#pragma unroll
+    for (int f = 0; f < URLG_MAX_FEET; ++f)
+      if (f < F) r += fmaxf(foot_fn[f] - c.max_contact_force, 0.0f);
+  TERM_END(URLG_T_FEET_CONTACT_FORCES)
+  if constexpr (FAM == URLG_FAMILY_H1) {
+    TERM_BEGIN(URLG_T_FEET_SWING_HEIGHT)        // h1_env.py:106-109
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        if (f < F) {
+          const float m = foot_fn[f] > 1.0f ? 0.0f : 1.0f;
+          const float d = foot_z[f] - 0.08f;
           r += d * d * m;
         }
-        r = qsum(r);
-        break;
-      case URLG_T_HIP_POS:
-        _Pragma("unroll 1") for (int k = g; k < c.num_hip; k += kLanesPerEnv) { const float q = dof[2 * c.hip_idx[k]]; r += q * q; }
-        r = qsum(r);
-        break;
-      case URLG_T_LIN_VEL_Z: r = lvz * lvz; break;
-      case URLG_T_ORIENTATION: r = gx * gx + gy * gy; break;
-      case URLG_T_STAND_STILL:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += fabsf(dof[2 * j] - c.default_dof_pos[j]);
-        r = qsum(r);
-        r *= cmd_xy < 0.1f ? 1.0f : 0.0f;
-        break;
-      case URLG_T_STUMBLE: {
-        _Pragma("unroll 1") for (int f = g; f < F; f += kLanesPerEnv) {
-          const float* f3 = con + 3 * c.feet_idx[f];
-          r += sqrtf(f3[0] * f3[0] + f3[1] * f3[1]) > 5.0f * fabsf(f3[2]) ? 1.0f : 0.0f;
-        }
-        r = qsum(r) > 0.0f ? 1.0f : 0.0f;
-      } break;
-      case URLG_T_TORQUE_LIMITS:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
-        r = qsum(r);
-        break;
-      case URLG_T_TORQUES:
-        _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) r += tq[j] * tq[j];
-        r = qsum(r);
-        break;
-      case URLG_T_TRACKING_ANG_VEL: { const float d = cmd[2] - avz; r = expf(-(d * d) / c.tracking_sigma); } break;
-      case URLG_T_TRACKING_LIN_VEL: {
-        const float dx = cmd[0] - lvx, dy = cmd[1] - lvy;
-        r = expf(-(dx * dx + dy * dy) / c.tracking_sigma);
-      } break;
-      default: break;
-    }
-    r *= c.term_scales[t];
-    rew += r;
-    if (g == 0) term[c.term_sum_row[t]] = r;
+      }
+    TERM_END(URLG_T_FEET_SWING_HEIGHT)
   }
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_FRONT_FEET_CONTACT)       // :248-256, feet 0,1 = front
+      r = ((foot_fz[0] > 5.0f ? 1.0f : 0.0f) + (foot_fz[1] > 5.0f ? 1.0f : 0.0f)) / 2.0f;
+    TERM_END(URLG_T_FRONT_FEET_CONTACT)
+    TERM_BEGIN(URLG_T_FRONT_FEET_TOGETHER)      // :360-373
+      const float dx = foot_xy[0][0] - foot_xy[1][0], dy = foot_xy[0][1] - foot_xy[1][1];
+      const float err = fmaxf(sqrtf(dx * dx + dy * dy) - 0.12f, 0.0f);
+      r = expf(-20.0f * err * err);
+    TERM_END(URLG_T_FRONT_FEET_TOGETHER)
+    TERM_BEGIN(URLG_T_FRONT_HIP_NEUTRAL)        // :352-358, hip_idx = (FL_hip, FR_hip)
+      float s = 0.0f;
+      _Pragma("unroll 1") for (int k = 0; k < c.num_hip; ++k) {
+        float q = 0.0f;
+#pragma unroll
+        for (int j = 0; j < A; ++j) q = c.hip_idx[k] == j ? dofs[2 * j] : q;
+        s += q * q;
+      }
+      r = expf(-4.0f * s);
+    TERM_END(URLG_T_FRONT_HIP_NEUTRAL)
+    TERM_BEGIN(URLG_T_HIND_FEET_NO_CONTACT)     // :258-265, feet 2,3 = hind
+      r = 1.0f - ((foot_fz[2] > 5.0f ? 1.0f : 0.0f) + (foot_fz[3] > 5.0f ? 1.0f : 0.0f)) / 2.0f;
+    TERM_END(URLG_T_HIND_FEET_NO_CONTACT)
+  }
+  if constexpr (FAM == URLG_FAMILY_H1) {
+    TERM_BEGIN(URLG_T_HIP_POS)                  // h1_env.py:122-123
+      _Pragma("unroll 1") for (int k = 0; k < c.num_hip; ++k) {
+        float q = 0.0f;
+#pragma unroll
+        for (int j = 0; j < A; ++j) q = c.hip_idx[k] == j ? dofs[2 * j] : q;
+        r += q * q;
+      }
+    TERM_END(URLG_T_HIP_POS)
+  }
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_LIN_VEL_XY) r = sqrtf(lvx * lvx + lvy * lvy); TERM_END(URLG_T_LIN_VEL_XY)   // :382-383
+  }
+  TERM_BEGIN(URLG_T_LIN_VEL_Z) r = lvz * lvz; TERM_END(URLG_T_LIN_VEL_Z)
+  TERM_BEGIN(URLG_T_ORIENTATION) r = gx * gx + gy * gy; TERM_END(URLG_T_ORIENTATION)
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_ORIENTATION_HS)           // :224-235
+      const float err = 1.0f - clampf(gz, -1.0f, 1.0f);
+      r = expf(-3.0f * err * err);
+    TERM_END(URLG_T_ORIENTATION_HS)
+    TERM_BEGIN(URLG_T_POSE)                     // :277-307
+      float sf = 0.0f, sh = 0.0f;
+#pragma unroll
+      for (int j = 0; j < A; ++j) {
+        const float d = dofs[2 * j] - c.pose_targets[j];
+        if (j < c.num_front_dof) sf += d * d; else sh += d * d;
+      }
+      r = expf(-4.0f * (sf + 0.3f * sh));
+    TERM_END(URLG_T_POSE)
+    TERM_BEGIN(URLG_T_STABILITY)                // :309-317
+      r = expf(-2.0f * (sqrtf(lvx * lvx + lvy * lvy) + 0.5f * sqrtf(avx * avx + avy * avy)));
+    TERM_END(URLG_T_STABILITY)
+  }
+  TERM_BEGIN(URLG_T_STAND_STILL)
+#pragma unroll
+    for (int j = 0; j < A; ++j) r += fabsf(dofs[2 * j] - c.default_dof_pos[j]);
+    r *= cmd_xy < 0.1f ? 1.0f : 0.0f;
+  TERM_END(URLG_T_STAND_STILL)
+  if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+    TERM_BEGIN(URLG_T_STAY_STILL)               // :375-380
+      const float a = sqrtf(lvx * lvx + lvy * lvy) * (1.0f / 0.05f), w = fabsf(avz) * (1.0f / 0.2f);
+      r = expf(-(a * a) - w * w);
+    TERM_END(URLG_T_STAY_STILL)
+  }
+  TERM_BEGIN(URLG_T_STUMBLE)
+    bool any = false;
+#pragma unroll
+    for (int f = 0; f < URLG_MAX_FEET; ++f)
+      if (f < F) any |= foot_fxy[f] > 5.0f * fabsf(foot_fz[f]);
+    r = any ? 1.0f : 0.0f;
+  TERM_END(URLG_T_STUMBLE)
+  TERM_BEGIN(URLG_T_TORQUE_LIMITS)
+#pragma unroll
+    for (int j = 0; j < A; ++j) r += fmaxf(fabsf(tq[j]) - c.torque_limits[j] * c.soft_torque_limit, 0.0f);
+  TERM_END(URLG_T_TORQUE_LIMITS)
+  TERM_BEGIN(URLG_T_TORQUES)
+#pragma unroll
+    for (int j = 0; j < A; ++j) r += tq[j] * tq[j];
+  TERM_END(URLG_T_TORQUES)
+  TERM_BEGIN(URLG_T_TRACKING_ANG_VEL) { const float d = cmd[2] - avz; r = expf(-(d * d) * inv_sigma); } TERM_END(URLG_T_TRACKING_ANG_VEL)
+  TERM_BEGIN(URLG_T_TRACKING_LIN_VEL)
+    const float dx = cmd[0] - lvx, dy = cmd[1] - lvy;
+    r = expf(-(dx * dx + dy * dy) * inv_sigma);
+  TERM_END(URLG_T_TRACKING_LIN_VEL)
+#undef TERM_BEGIN
+#undef TERM_END
   if (c.only_positive) rew = fmaxf(rew, 0.0f);
   if (c.has_termination) {
     const float r = ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale;
     rew += r;
-    if (g == 0) term[c.termination_sum_row] = r;
+    term[c.termination_sum_row * 32] = r;
   }
 
-  // ---- E10 reset_idx for this env :723-768 (quad-uniform branch) ----
-  if (reset) {
-    if (live) {
-      if (g == 0) {
-        atomicAdd(&scratch->ep_acc[acc][URLG_MAX_TERMS], 1.0f);
-        const int pos = atomicAdd(&scratch->reset_cnt[acc], 1);
-        if (b.reset_ids) b.reset_ids[pos] = e;
+  // ---- episode_sums += this step's terms (:779-780, 786); reset envs publish their sums and clear (:759-763) ----
+  {
+    const bool pub = reset && live;
+    float* accp = scratch->ep_acc[acc][blockIdx.x & (kAccCopies - 1)];
+    _Pragma("unroll 4") for (int k = 0; k < c.num_sums; ++k) {
+      float v = b.episode_sums[(size_t)k * N + e] + term[k * 32];
+      if (pub) { atomicAdd(accp + k, v); v = 0.0f; }
+      if (live) b.episode_sums[(size_t)k * N + e] = v;
+    }
+    if (pub) atomicAdd(accp + URLG_MAX_TERMS, 1.0f);
+  }
+
+  // ---- E10 reset_idx :723-768, warp-cooperative: for every reset env of the warp, lane l draws slot 3 + l
+  //      (l < A: _reset_dofs :566-567; A <= l < A+6: root velocities :590; A+6 <= l < A+9: _resample_commands :749)
+  //      and writes its element of the physics tensors; the owner lane picks the new values up by shuffle ----
+  {
+    unsigned rmask = __ballot_sync(kFull, reset && live);
+    while (rmask) {
+      const int src = __ffs(rmask) - 1;
+      rmask &= rmask - 1;
+      const int er = env0 + src;
+      float u = 0.0f;
+      if (lane < A + 9) u = slot_uniform(c, ovr, c.env_offset + er, step, 3 + lane, num_slots, er);
+      float p = 0.0f;
+      if (lane < A) {
+        p = c.default_dof_pos[lane] * ((1.5f - 0.5f) * u + 0.5f);
+        reinterpret_cast<float2*>(b.dof_state)[(size_t)er * A + lane] = make_float2(p, 0.0f);
+        b.actions[(size_t)er * A + lane] = 0.0f;                             // :752
+      }
+      const float uv = __shfl_sync(kFull, u, (lane >= 7 && lane < 13) ? A + (lane - 7) : 0);
+      if (lane < 13) {                                                      // _reset_root_states :587-590
+        float v = c.base_init_state[lane];
+        if (lane < 3) v += b.env_origins[(size_t)er * 3 + lane];
+        if (lane >= 7) v = (0.5f - (-0.5f)) * uv + (-0.5f);
+        b.root_states[(size_t)er * 13 + lane] = v;
+      }
+      const float ux = __shfl_sync(kFull, u, A + 6), uy = __shfl_sync(kFull, u, A + 7), uh = __shfl_sync(kFull, u, A + 8);
+      const bool mine = lane == src;
+#pragma unroll
+      for (int j = 0; j < A; ++j) {
+        const float pj = __shfl_sync(kFull, p, j);
+        if (mine) { dofs[2 * j] = pj; dofs[2 * j + 1] = 0.0f; act[j] = 0.0f; }
+      }
+      if (mine) {
+        resample_commands(c, ux, uy, uh, cmd);
+#pragma unroll
+        for (int f = 0; f < URLG_MAX_FEET; ++f) air[f] = 0.0f;              // :755
+        len = 0;                                                             // :756
       }
     }
-    float* gdof = b.dof_state + (size_t)e * 2 * A;
-    float* gact = b.actions + (size_t)e * A;
-    _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {                        // _reset_dofs :566-567, actions :752
-      const float p = c.default_dof_pos[j] * ((1.5f - 0.5f) * rng.uniform(3 + j) + 0.5f);
-      dof[2 * j] = p; dof[2 * j + 1] = 0.0f;
-      act[j] = 0.0f;
-      if (live) { gdof[2 * j] = p; gdof[2 * j + 1] = 0.0f; gact[j] = 0.0f; }
-    }
-    float* groot = b.root_states + (size_t)e * 13;                     // _reset_root_states :587-590
-    _Pragma("unroll 1") for (int k = g; k < 13; k += kLanesPerEnv) {
-      float v = c.base_init_state[k];
-      if (k < 3 && live) v += b.env_origins[(size_t)e * 3 + k];
-      if (k >= 7) v = (0.5f - (-0.5f)) * rng.uniform(3 + A + (k - 7)) + (-0.5f);
-      if (live) groot[k] = v;
-    }
-    resample_commands(c, rng, 9 + A, cmd);                             // :749
-    air[0] = 0.0f; air[1] = 0.0f;                                      // :755
-    len = 0;                                                            // :756
   }
   const bool push_due = live && c.push_robots && divisible(len, c.push_interval);   // :545, evaluated after the reset
 
-  // ---- episode_sums rows g, g+4, ...: += this step's term (:779-780, 786); reset envs publish and clear (:759-763) ----
-  __syncwarp();
-#pragma unroll
-  for (int q = 0; q < URLG_MAX_TERMS / kLanesPerEnv; ++q) {
-    const int k = g + kLanesPerEnv * q;
-    if (live && k < c.num_sums) {
-      float v = sums[q] + term[k];
-      if (reset) { atomicAdd(&scratch->ep_acc[acc][k], v); v = 0.0f; }
-      b.episode_sums[(size_t)k * N + e] = v;
+  // ---- compacted id lists for the indexed setters of the physics seam (:552-555, 569-572, 591-594) ----
+  {
+    const unsigned rm = __ballot_sync(kFull, reset && live);
+    const unsigned pm = __ballot_sync(kFull, (reset && live) || push_due);
+    const unsigned dm = __ballot_sync(kFull, push_due);
+    int rbase = 0, pbase = 0;
+    if (lane == 0) {
+      if (rm) rbase = atomicAdd(&scratch->reset_cnt[acc], __popc(rm));
+      if (pm) pbase = atomicAdd(&scratch->root_cnt[acc], __popc(pm));
+      if (dm) atomicOr(&scratch->push_flag[acc], 1);
     }
+    rbase = __shfl_sync(kFull, rbase, 0);
+    pbase = __shfl_sync(kFull, pbase, 0);
+    const unsigned below = (1u << lane) - 1u;
+    if (reset && live && b.reset_ids) b.reset_ids[rbase + __popc(rm & below)] = e;
+    if (((reset && live) || push_due) && b.root_ids) b.root_ids[pbase + __popc(pm & below)] = e;
   }
 
-  // ---- E12 observations :789-811 / h1_env.py:68-95 into the shared rows (raw), then noise + the clips of
-  //      step() :643-646 over this lane's contiguous column range ----
+  // ---- E12 observations :789-811 / h1_env.py:68-95 / go2_handstand_env.py:140-176, assembled in registers ----
+  float* obs_s = sm + L.oObs + lane * OS;
   {
-    const int o0 = c.family == 1 ? 0 : 3;          // column of ang_vel
-    if (g == 0) {
-      if (c.family == 0) {
-        obs[0] = lvx * c.obs_scale_lin_vel; obs[1] = lvy * c.obs_scale_lin_vel; obs[2] = lvz * c.obs_scale_lin_vel;
-      }
-      obs[o0 + 0] = avx * c.obs_scale_ang_vel; obs[o0 + 1] = avy * c.obs_scale_ang_vel; obs[o0 + 2] = avz * c.obs_scale_ang_vel;
-      obs[o0 + 3] = gx; obs[o0 + 4] = gy; obs[o0 + 5] = gz;
+    float obs[O];
+    const float cl = c.clip_obs;
+    constexpr int o0 = FAM == URLG_FAMILY_BASE ? 3 : 0;          // column of ang_vel
+    constexpr int oq = FAM == URLG_FAMILY_HANDSTAND ? o0 + 6 : o0 + 9;   // column of dof_pos (handstand has no commands)
+    if constexpr (FAM == URLG_FAMILY_BASE) {
+      obs[0] = lvx * c.obs_scale_lin_vel; obs[1] = lvy * c.obs_scale_lin_vel; obs[2] = lvz * c.obs_scale_lin_vel;
+    }
+    obs[o0 + 0] = avx * c.obs_scale_ang_vel; obs[o0 + 1] = avy * c.obs_scale_ang_vel; obs[o0 + 2] = avz * c.obs_scale_ang_vel;
+    obs[o0 + 3] = gx; obs[o0 + 4] = gy; obs[o0 + 5] = gz;
+    if constexpr (FAM != URLG_FAMILY_HANDSTAND) {
       obs[o0 + 6] = cmd[0] * c.obs_scale_lin_vel; obs[o0 + 7] = cmd[1] * c.obs_scale_lin_vel;
       obs[o0 + 8] = cmd[2] * c.obs_scale_ang_vel;
-      if (c.family == 1) {
-        obs[9 + 3 * A] = sinf(kTwoPi * phase);
-        obs[10 + 3 * A] = cosf(kTwoPi * phase);
-        const float cl = c.clip_obs;
-        priv[0] = fminf(fmaxf(lvx * c.obs_scale_lin_vel, -cl), cl);
-        priv[1] = fminf(fmaxf(lvy * c.obs_scale_lin_vel, -cl), cl);
-        priv[2] = fminf(fmaxf(lvz * c.obs_scale_lin_vel, -cl), cl);
-      }
     }
-    _Pragma("unroll 1") for (int j = g; j < A; j += kLanesPerEnv) {
-      const float qv = dof[2 * j + 1];
-      obs[o0 + 9 + j] = (dof[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
-      obs[o0 + 9 + A + j] = qv * c.obs_scale_dof_vel;
-      obs[o0 + 9 + 2 * A + j] = act[j];
-      lact[j] = act[j];                                                 // tail copies :707-708
-      ldv[j] = qv;
+#pragma unroll
+    for (int j = 0; j < A; ++j) {
+      obs[oq + j] = (dofs[2 * j] - c.default_dof_pos[j]) * c.obs_scale_dof_pos;
+      obs[oq + A + j] = dofs[2 * j + 1] * c.obs_scale_dof_vel;
+      obs[oq + 2 * A + j] = act[j];
     }
-    __syncwarp();
-    const int chunk = (c.num_obs + kLanesPerEnv - 1) / kLanesPerEnv;
-    const int i1 = min(c.num_obs, (g + 1) * chunk);
-    const float cl = c.clip_obs;
-    for (int i = g * chunk; i < i1; ++i) {
-      float v = obs[i];
-      if (c.family == 1) priv[3 + i] = fminf(fmaxf(v, -cl), cl);       // privileged obs carry no noise
-      const float ns = c.noise_scale_vec[i];
-      if (c.add_noise && ns != 0.0f) v += (2.0f * rng.uniform(14 + A + i) - 1.0f) * ns;
-      obs[i] = fminf(fmaxf(v, -cl), cl);
+    if constexpr (FAM == URLG_FAMILY_H1) {
+      obs[9 + 3 * A] = sinf(kTwoPi * phase);
+      obs[10 + 3 * A] = cosf(kTwoPi * phase);
+      float* priv_s = sm + L.oPriv + lane * PV;                  // privileged obs carry no noise
+      priv_s[0] = clampf(lvx * c.obs_scale_lin_vel, -cl, cl);
+      priv_s[1] = clampf(lvy * c.obs_scale_lin_vel, -cl, cl);
+      priv_s[2] = clampf(lvz * c.obs_scale_lin_vel, -cl, cl);
+#pragma unroll
+      for (int i = 0; i < O; ++i) priv_s[3 + i] = clampf(obs[i], -cl, cl);
     }
-  }
-
-  // ---- per-env scalars and short rows ----
-  if (live) {
-    if (g == 0) {
-      b.episode_length_buf[e] = len;
-      b.rew_buf[e] = rew;
-      b.reset_buf[e] = reset ? 1 : 0;
-      b.time_out_buf[e] = time_out ? 1 : 0;
-      reinterpret_cast<float4*>(b.commands)[e] = make_float4(cmd[0], cmd[1], cmd[2], cmd[3]);
-      if (c.family == 1) {
-        b.phase[e] = phase;
-        b.leg_phase[(size_t)e * 2] = leg_phase[0];
-        b.leg_phase[(size_t)e * 2 + 1] = leg_phase[1];
+    if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
+      // contact flags of the front (feet 0,1) and hind (feet 2,3) feet; with noise on, re-binarised and flipped with
+      // probability 0.01 (:160-169) -- their noise scale is 0, so the flip can be applied here
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        bool flag = foot_fz[k] > 5.0f;
+        if (c.add_noise) flag = flag != (slot_uniform(c, ovr, genv, step, 14 + A + O + k, num_slots, e) < 0.01f);
+        obs[oq + 3 * A + k] = flag ? 1.0f : 0.0f;
       }
     }
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int f = g + 4 * q;
-      if (f < F) {
-        b.feet_air_time[(size_t)e * F + f] = air[q];
-        b.last_contacts[(size_t)e * F + f] = lastc[q];
+    for (int i = 0; i < O; ++i) obs[i] = clampf(obs[i], -cl, cl);        // the clips of step() :643-646
+    if constexpr (kPadObs) {
+#pragma unroll
+      for (int i = 0; i < O; ++i) obs_s[i] = obs[i];
+    } else {
+      st_row<O>(obs_s, obs);
+    }
+  }
+  // ---- observation noise :811: obs += (2u - 1) * noise_scale_vec, one Philox block (4 uniforms) per iteration ----
+  if (c.add_noise) {
+    const float cl = c.clip_obs;
+    const int s0 = 14 + A, b0 = s0 >> 2, b1 = (s0 + O - 1) >> 2;
+    _Pragma("unroll 1") for (int blk = b0; blk <= b1; ++blk) {
+      const int i0 = 4 * blk - s0;                 // obs column of this block's word 0 (may be < 0 / run past O)
+      float ns[4];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = i0 + k;
+        ns[k] = (i >= 0 && i < O) ? c.noise_scale_vec[i] : 0.0f;
+        any |= ns[k] != 0.0f;
+      }
+      if (!any) continue;
+      float u[4];
+      if (ovr) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k;
+          u[k] = (i >= 0 && i < O) ? ovr[(size_t)e * num_slots + s0 + i] : 0.0f;
+        }
+      } else {
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
+                                                 (uint32_t)((uint64_t)step >> 32), (uint32_t)blk), c.seed_lo,
+                                      c.seed_hi ^ kStreamEnv);
+        u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = i0 + k;
+        if (ns[k] != 0.0f) obs_s[i] = clampf(obs_s[i] + (2.0f * u[k] - 1.0f) * ns[k], -cl, cl);
       }
     }
-    // lane g stores the g-th of (rpy, base_lin_vel, base_ang_vel, projected_gravity)
-    float* o3 = (g == 0 ? b.rpy : g == 1 ? b.base_lin_vel : g == 2 ? b.base_ang_vel : b.projected_gravity) + (size_t)e * 3;
-    o3[0] = g == 0 ? roll : g == 1 ? lvx : g == 2 ? avx : gx;
-    o3[1] = g == 0 ? pitch : g == 1 ? lvy : g == 2 ? avy : gy;
-    o3[2] = g == 0 ? yaw : g == 1 ? lvz : g == 2 ? avz : gz;
   }
-  if (__any_sync(0xffffffffu, push_due) && (tid & 31) == 0) atomicOr(&scratch->push_flag[acc], 1);
-  if (bulk) {
-    // ---- row outputs leave as 1-D bulk-TMA stores (shared -> global), issued by one thread ----
+
+  // ---- per-env stores ----
+  if (live) {
+    b.episode_length_buf[e] = len;
+    b.rew_buf[e] = rew;
+    b.reset_buf[e] = reset ? 1 : 0;
+    b.time_out_buf[e] = time_out ? 1 : 0;
+    reinterpret_cast<float4*>(b.commands)[e] = make_float4(cmd[0], cmd[1], cmd[2], cmd[3]);
+    if constexpr (FAM == URLG_FAMILY_H1) {
+      b.phase[e] = phase;
+      reinterpret_cast<float2*>(b.leg_phase)[e] = make_float2(leg_phase[0], leg_phase[1]);
+    }
+#pragma unroll
+    for (int f = 0; f < URLG_MAX_FEET; ++f) {
+      if (f < F) {
+        b.feet_air_time[(size_t)e * F + f] = air[f];
+        b.last_contacts[(size_t)e * F + f] = lastc[f];
+      }
+    }
+    float* o3 = b.rpy + (size_t)e * 3;
+    o3[0] = roll; o3[1] = pitch; o3[2] = yaw;
+    o3 = b.base_lin_vel + (size_t)e * 3;
+    o3[0] = lvx; o3[1] = lvy; o3[2] = lvz;
+    o3 = b.base_ang_vel + (size_t)e * 3;
+    o3[0] = avx; o3[1] = avy; o3[2] = avz;
+    o3 = b.projected_gravity + (size_t)e * 3;
+    o3[0] = gx; o3[1] = gy; o3[2] = gz;
+    // tail copies :707-708 (after a reset: zeros)
+    float dv[A];
+#pragma unroll
+    for (int j = 0; j < A; ++j) dv[j] = dofs[2 * j + 1];
+    st_row<A>(b.last_actions + (size_t)e * A, act);
+    st_row<A>(b.last_dof_vel + (size_t)e * A, dv);
+  }
+
+  // ---- observation rows leave as one bulk-TMA store per tensor (flat stores for the tail block) ----
+  float* gobs = b.obs_buf[obs_slot] + (size_t)env0 * O;
+  float* gpriv = c.num_priv ? b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv : nullptr;
+  if constexpr (kPadObs) {
+    static_assert(!kPadObs || (O % 4 == 0 && PV == 0), "padded observation rows leave as float4");
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < O / 4; ++it) {
+      const int q = it * 32 + lane, row = q / (O / 4), c4 = q - row * (O / 4);
+      const float* sp = sm + L.oObs + row * OS + 4 * c4;
+      const float4 v = make_float4(sp[0], sp[1], sp[2], sp[3]);
+      if (row < nrows) reinterpret_cast<float4*>(gobs)[q] = v;
+    }
+  } else if (bulk) {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
-    if (tid == 0) {
-      bulk_s2g(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, kEnvsPerBlock * c.num_obs * sizeof(float));
-      if (c.num_priv)
-        bulk_s2g(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, kEnvsPerBlock * c.num_priv * sizeof(float));
-      bulk_s2g(b.last_actions + (size_t)env0 * A, sm + L.oLact, kEnvsPerBlock * A * sizeof(float));
-      bulk_s2g(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, kEnvsPerBlock * A * sizeof(float));
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(gobs, sm + L.oObs, 32 * O * sizeof(float));
+      if constexpr (FAM == URLG_FAMILY_H1) bulk_s2g(gpriv, sm + L.oPriv, 32 * PV * sizeof(float));
+      if constexpr (FAM == URLG_FAMILY_HANDSTAND)                         // privileged_obs_buf = obs.clone() (:172)
+        if (gpriv) bulk_s2g(gpriv, sm + L.oObs, 32 * O * sizeof(float));
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
-    return;
+  } else {
+    __syncwarp();
+    for (int i = lane; i < nrows * O; i += 32) gobs[i] = sm[L.oObs + i];
+    if constexpr (FAM == URLG_FAMILY_H1)
+      for (int i = lane; i < nrows * PV; i += 32) gpriv[i] = sm[L.oPriv + i];
+    if constexpr (FAM == URLG_FAMILY_HANDSTAND)
+      if (gpriv) for (int i = lane; i < nrows * O; i += 32) gpriv[i] = sm[L.oObs + i];
   }
-  __syncthreads();
-
-  // ---- tail block / unaligned fallback: flat stores of the row outputs ----
-  flat_out(b.obs_buf[obs_slot] + (size_t)env0 * c.num_obs, sm + L.oObs, nrows * c.num_obs, tid);
-  if (c.num_priv)
-    flat_out(b.priv_obs_buf[obs_slot] + (size_t)env0 * c.num_priv, sm + L.oPriv, nrows * c.num_priv, tid);
-  flat_out(b.last_actions + (size_t)env0 * A, sm + L.oLact, nrows * A, tid);
-  flat_out(b.last_dof_vel + (size_t)env0 * A, sm + L.oLdv, nrows * A, tid);
+#undef HAS
 }
 
 // ---------------------------------------------------------------- K2b: finalize
-// Runs after K2 of the same step (stream order).  Reads this step's accumulators, applies the
-// all-env push (quirk: any due env => every env's xy velocity is redrawn, :544-550), copies
-// last_root_vel (:709), publishes extras only if >= 1 env reset (:742-743, 759-768), and clears the
-// other parity's accumulators for the next step.
-__global__ void __launch_bounds__(256) finalize_step_kernel(const __grid_constant__ urlg_env_desc c,
+// Launched behind K2 with programmatic stream serialization: its blocks draw the push velocities of their envs (a
+// Philox block each, independent of K2) while K2 drains, then wait for K2's completion.  Reads this step's accumulators,
+// applies the all-env push (quirk: any due env => every env's xy velocity is redrawn, :544-550), copies last_root_vel
+// (:709), publishes extras only if >= 1 env reset (:742-743, 759-768), and clears the other parity's accumulators.
+__global__ void __launch_bounds__(128) finalize_step_kernel(const __grid_constant__ urlg_env_desc c,
                                                             const __grid_constant__ urlg_env_buffers b,
+                                                            const __grid_constant__ PoolArgs pa,
                                                             StepScratch* __restrict__ scratch,
                                                             const int64_t* __restrict__ step_base, int64_t step_off,
                                                             int num_slots) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int A = c.num_dof;
+  const bool live = e < c.num_envs;
+  float px = 0.0f, py = 0.0f;
+  const bool may_push = c.push_robots != 0;    // post_physics_step calls _push_robots itself (:700-701), not the callback
+  // ---- independent of K2: step counter (advanced by an earlier graph node), push draws ----
   const int64_t step = eff_step(step_base, step_off);
+  if (live && may_push) {
+    const float m = c.max_push_vel;
+    const float* ovr = b.rng_override;
+    px = (m - (-m)) * slot_uniform(c, ovr, c.env_offset + e, step, 12 + A, num_slots, e) + (-m);
+    py = (m - (-m)) * slot_uniform(c, ovr, c.env_offset + e, step, 13 + A, num_slots, e) + (-m);
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");       // K2 of this step has completed and flushed
   const int acc = (int)(step & 1);
   const bool push = scratch->push_flag[acc] != 0;
-  const float cnt = scratch->ep_acc[acc][URLG_MAX_TERMS];
-  const int A = c.num_dof;
-  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < c.num_envs; e += gridDim.x * blockDim.x) {
+  float cnt = 0.0f;
+#pragma unroll
+  for (int k = 0; k < kAccCopies; ++k) cnt += scratch->ep_acc[acc][k][URLG_MAX_TERMS];
+  if (live) {
+    const Seam seam = resolve_seam(c, b, pa);
     float* root = b.root_states + (size_t)e * 13;
+    // in pool mode the bound root_states row is current only for envs K2 reset; the others live in the pool frame
+    const float* src = (pa.enabled && !b.reset_buf[e]) ? seam.root + (size_t)e * 13 : root;
+    float v[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v[k] = src[7 + k];
     if (push) {
-      SlotRng rng;
-      rng.init(c.seed_lo, c.seed_hi, kStreamEnv, c.env_offset + e, step,
-               b.rng_override ? b.rng_override + (size_t)e * num_slots : nullptr);
-      const float m = c.max_push_vel;
-      root[7] = (m - (-m)) * rng.uniform(12 + A) + (-m);
-      root[8] = (m - (-m)) * rng.uniform(13 + A) + (-m);
+      v[0] = px; v[1] = py;
+      root[7] = px; root[8] = py;
     }
     float* lrv = b.last_root_vel + (size_t)e * 6;
-    for (int k = 0; k < 6; ++k) lrv[k] = root[7 + k];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) lrv[k] = v[k];
     if (cnt > 0.0f && c.send_timeouts) b.extras_time_outs[e] = b.time_out_buf[e];
   }
   if (blockIdx.x == 0 && threadIdx.x < URLG_MAX_TERMS + 1) {
     const int k = threadIdx.x;
-    if (cnt > 0.0f && k < c.num_sums) b.extras_episode[k] = scratch->ep_acc[acc][k] / cnt / c.max_episode_length_s;
-    if (k == 0 && b.reset_count) *b.reset_count = scratch->reset_cnt[acc];
+    if (cnt > 0.0f && k < c.num_sums) {
+      float s = 0.0f;
+#pragma unroll
+      for (int q = 0; q < kAccCopies; ++q) s += scratch->ep_acc[acc][q][k];
+      b.extras_episode[k] = s / cnt / c.max_episode_length_s;
+    }
+    if (k == 0) {
+      if (b.reset_count) *b.reset_count = scratch->reset_cnt[acc];
+      if (b.root_count) *b.root_count = scratch->root_cnt[acc];
+    }
     // clear the other parity for step+1 (its last reader was finalize of step-1)
-    scratch->ep_acc[acc ^ 1][k] = 0.0f;
-    if (k == 0) { scratch->push_flag[acc ^ 1] = 0; scratch->reset_cnt[acc ^ 1] = 0; }
+    for (int q = 0; q < kAccCopies; ++q) scratch->ep_acc[acc ^ 1][q][k] = 0.0f;
+    if (k == 0) { scratch->push_flag[acc ^ 1] = 0; scratch->reset_cnt[acc ^ 1] = 0; scratch->root_cnt[acc ^ 1] = 0; }
   }
 }
-
-}  // namespace urlg
-
-namespace urlg {
 
 // ---------------------------------------------------------------- reset_idx(env_ids) outside step()
 // base_task.py:82-86 -> legged_robot.py:723-768.  One thread per listed env, straight to global memory
@@ -698,7 +1009,7 @@ __global__ void __launch_bounds__(128) reset_idx_kernel(const __grid_constant__ 
   for (int k = 0; k < 6; ++k) groot[7 + k] = (0.5f - (-0.5f)) * rng.uniform(3 + A + k) + (-0.5f);
   float cmd[4];
   for (int k = 0; k < 4; ++k) cmd[k] = b.commands[(size_t)e * 4 + k];
-  resample_commands(c, rng, 9 + A, cmd);
+  resample_commands(c, rng.uniform(9 + A), rng.uniform(10 + A), rng.uniform(11 + A), cmd);
   for (int k = 0; k < 4; ++k) b.commands[(size_t)e * 4 + k] = cmd[k];
   for (int j = 0; j < A; ++j) {
     b.actions[(size_t)e * A + j] = 0.0f;
@@ -710,25 +1021,31 @@ __global__ void __launch_bounds__(128) reset_idx_kernel(const __grid_constant__ 
   b.reset_buf[e] = 1;
   for (int k = 0; k < c.num_sums; ++k) {
     float* s = b.episode_sums + (size_t)k * N + e;
-    atomicAdd(&scratch->ep_acc[2][k], *s);
+    atomicAdd(&scratch->ep_acc[2][0][k], *s);
     *s = 0.0f;
   }
-  atomicAdd(&scratch->ep_acc[2][URLG_MAX_TERMS], 1.0f);
+  atomicAdd(&scratch->ep_acc[2][0][URLG_MAX_TERMS], 1.0f);
+  if (b.reset_ids) b.reset_ids[i] = e;          // the explicit list is its own compaction (:569-572, 591-594)
+  if (b.root_ids) b.root_ids[i] = e;
 }
 
 __global__ void __launch_bounds__(256) finalize_reset_kernel(const __grid_constant__ urlg_env_desc c,
                                                              const __grid_constant__ urlg_env_buffers b,
-                                                             StepScratch* __restrict__ scratch) {
+                                                             StepScratch* __restrict__ scratch, int64_t n) {
   // single block: publish, then clear slot 2
-  const float cnt = scratch->ep_acc[2][URLG_MAX_TERMS];
+  const float cnt = scratch->ep_acc[2][0][URLG_MAX_TERMS];
   if (cnt > 0.0f) {
     if (c.send_timeouts)
       for (int e = threadIdx.x; e < c.num_envs; e += blockDim.x) b.extras_time_outs[e] = b.time_out_buf[e];
     if (threadIdx.x < c.num_sums)
-      b.extras_episode[threadIdx.x] = scratch->ep_acc[2][threadIdx.x] / cnt / c.max_episode_length_s;
+      b.extras_episode[threadIdx.x] = scratch->ep_acc[2][0][threadIdx.x] / cnt / c.max_episode_length_s;
+  }
+  if (threadIdx.x == 0) {
+    if (b.reset_count) *b.reset_count = (int32_t)n;
+    if (b.root_count) *b.root_count = (int32_t)n;
   }
   __syncthreads();
-  if (threadIdx.x < URLG_MAX_TERMS + 1) scratch->ep_acc[2][threadIdx.x] = 0.0f;
+  if (threadIdx.x < URLG_MAX_TERMS + 1) scratch->ep_acc[2][0][threadIdx.x] = 0.0f;
 }
 
 // ---------------------------------------------------------------- synthetic physics seam
@@ -753,6 +1070,20 @@ __global__ void __launch_bounds__(256) synth_refresh_kernel(float* __restrict__ 
   }
 }
 
+// rows[ids[i]] of dst <- rows[ids[i]] of src for i < *count: what set_*_state_tensor_indexed does inside a simulator
+// whose state lives apart from the exposed tensors (tests' stateful fake gym), with the count on the device.
+__global__ void __launch_bounds__(256) scatter_rows_kernel(float* __restrict__ dst, const float* __restrict__ src,
+                                                           const int32_t* __restrict__ ids,
+                                                           const int32_t* __restrict__ count, int row_floats, int max_n) {
+  const int n = min(*count, max_n);
+  const int64_t total = (int64_t)n * row_floats;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = ids[i / row_floats];
+    const int k = (int)(i % row_floats);
+    dst[(size_t)r * row_floats + k] = src[(size_t)r * row_floats + k];
+  }
+}
+
 __global__ void philox_uniform_kernel(float* out, int64_t n, int64_t num_slots, uint32_t seed_lo, uint32_t seed_hi,
                                       uint32_t stream_id, int64_t env_offset, int64_t step) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -772,6 +1103,20 @@ static int grid_for(int64_t work, int block, int max_waves = 8) {
   return (int)g;
 }
 
+using K2Fn = void (*)(const urlg_env_desc, const urlg_env_buffers, const TermTable, const PoolArgs, StepScratch*,
+                      const int64_t*, int64_t, int, int);
+static K2Fn k2_for(int num_dof, int family) {
+  if (num_dof == 12) {
+    if (family == URLG_FAMILY_BASE) return post_physics_kernel<12, URLG_FAMILY_BASE>;
+    if (family == URLG_FAMILY_H1) return post_physics_kernel<12, URLG_FAMILY_H1>;
+    if (family == URLG_FAMILY_HANDSTAND) return post_physics_kernel<12, URLG_FAMILY_HANDSTAND>;
+  } else if (num_dof == 10) {
+    if (family == URLG_FAMILY_BASE) return post_physics_kernel<10, URLG_FAMILY_BASE>;
+    if (family == URLG_FAMILY_H1) return post_physics_kernel<10, URLG_FAMILY_H1>;
+  }
+  return nullptr;
+}
+
 }  // namespace urlg
 
 // ================================================================= C ABI
@@ -787,15 +1132,28 @@ extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
     return fail(URLG_EINVAL, "urlg_env_create: num_envs=%d num_dof=%d out of range (max dof %d)", d->num_envs,
                 d->num_dof, URLG_MAX_DOF);
   if (d->num_obs > URLG_MAX_OBS || d->num_priv > URLG_MAX_OBS || d->num_terms > URLG_MAX_TERMS ||
-      d->num_sums > URLG_MAX_TERMS || d->num_feet > kMaxFeet || d->num_pen > URLG_MAX_IDX ||
+      d->num_sums > URLG_MAX_TERMS || d->num_feet > URLG_MAX_FEET || d->num_pen > URLG_MAX_IDX ||
       d->num_term_bodies > URLG_MAX_IDX || d->num_hip > URLG_MAX_IDX)
     return fail(URLG_EINVAL, "urlg_env_create: a table exceeds its ABI bound");
   if (d->control_type != 'P' && d->control_type != 'V' && d->control_type != 'T')
     return fail(URLG_EINVAL, "Unknown controller type: %c", (char)d->control_type);   // NameError at legged_robot.py:670
-  const int expect_obs = d->family == 0 ? 12 + 3 * d->num_dof : 9 + 3 * d->num_dof + 2;
-  if (d->num_obs != expect_obs || (d->family == 1 && d->num_priv != d->num_obs + 3) || (d->family == 0 && d->num_priv != 0))
+  if (d->family < URLG_FAMILY_BASE || d->family > URLG_FAMILY_HANDSTAND)
+    return fail(URLG_EINVAL, "urlg_env_create: unknown family %d", d->family);
+  if (!k2_for(d->num_dof, d->family))
+    return fail(URLG_EINVAL, "urlg_env_create: no fused step kernel for num_dof=%d family=%d (built: 12 x {base, h1, "
+                "handstand}, 10 x {base, h1})", d->num_dof, d->family);
+  const int A = d->num_dof;
+  const int expect_obs = d->family == URLG_FAMILY_BASE ? 12 + 3 * A : d->family == URLG_FAMILY_H1 ? 11 + 3 * A : 10 + 3 * A;
+  const bool priv_ok = d->family == URLG_FAMILY_BASE ? d->num_priv == 0
+                     : d->family == URLG_FAMILY_H1 ? d->num_priv == d->num_obs + 3
+                                                   : (d->num_priv == 0 || d->num_priv == d->num_obs);
+  if (d->num_obs != expect_obs || !priv_ok)
     return fail(URLG_EINVAL, "urlg_env_create: num_obs=%d num_priv=%d inconsistent with family %d, num_dof %d",
                 d->num_obs, d->num_priv, d->family, d->num_dof);
+  if (d->family == URLG_FAMILY_HANDSTAND && d->num_feet < 4)
+    return fail(URLG_EINVAL, "Expected at least 4 feet for Go2.");                    // go2_handstand_env.py:19
+  if (d->family == URLG_FAMILY_H1 && d->num_feet > 2)
+    return fail(URLG_EINVAL, "urlg_env_create: the H1-family terms read two feet (h1_env.py:98-123), got %d", d->num_feet);
   if (d->resample_steps <= 0 || d->push_interval <= 0)
     return fail(URLG_EINVAL, "urlg_env_create: resample_steps / push_interval must be positive");
   urlg_env* e = new (std::nothrow) urlg_env();
@@ -803,11 +1161,39 @@ extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
   e->desc = *d;
   e->bound = 0;
   e->scratch = nullptr;
+  e->pool.enabled = 0;
+  e->pool.calls_off = 0;
+  e->tt.mask = 0;
+  for (int i = 0; i < URLG_T_COUNT; ++i) { e->tt.scale[i] = 0.0f; e->tt.row[i] = 0; }
+  for (int t = 0; t < d->num_terms; ++t) {
+    const int id = d->term_ids[t];
+    const bool fam_ok = [&] {
+      switch (id) {
+        case URLG_T_ALIVE: case URLG_T_CONTACT: case URLG_T_CONTACT_NO_VEL: case URLG_T_FEET_SWING_HEIGHT: case URLG_T_HIP_POS:
+          return d->family == URLG_FAMILY_H1;
+        case URLG_T_BASE_HEIGHT_HS: case URLG_T_ENERGY: case URLG_T_FRONT_FEET_CONTACT: case URLG_T_FRONT_FEET_TOGETHER:
+        case URLG_T_FRONT_HIP_NEUTRAL: case URLG_T_HIND_FEET_NO_CONTACT: case URLG_T_LIN_VEL_XY: case URLG_T_ORIENTATION_HS:
+        case URLG_T_POSE: case URLG_T_STABILITY: case URLG_T_STAY_STILL:
+          return d->family == URLG_FAMILY_HANDSTAND;
+        default: return true;
+      }
+    }();
+    if (id < 0 || id >= URLG_T_COUNT || !fam_ok || d->term_sum_row[t] < 0 || d->term_sum_row[t] >= d->num_sums ||
+        (t > 0 && id <= d->term_ids[t - 1])) {
+      delete e;
+      return fail(URLG_EINVAL, "urlg_env_create: reward term #%d (id %d) is unknown, out of order, or not a term of "
+                  "env family %d", t, id, d->family);
+    }
+    e->tt.mask |= 1ull << id;
+    e->tt.scale[id] = d->term_scales[t];
+    e->tt.row[id] = d->term_sum_row[t];
+  }
   URLG_CUDA(cudaMalloc(&e->scratch, sizeof(StepScratch)));
   URLG_CUDA(cudaMemset(e->scratch, 0, sizeof(StepScratch)));
   e->smem_bytes = make_layout(e->desc).total * (int)sizeof(float);
-  if (e->smem_bytes > 48 * 1024)
-    URLG_CUDA(cudaFuncSetAttribute(post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes));
+  K2Fn fn = k2_for(d->num_dof, d->family);
+  URLG_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes > 48 * 1024 ? e->smem_bytes : 48 * 1024));
+  URLG_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   *out = e;
   return URLG_OK;
 }
@@ -821,19 +1207,41 @@ extern "C" int urlg_env_bind(urlg_env* env, const urlg_env_buffers* b) {
                         b->extras_episode, b->extras_time_outs};
   for (size_t i = 0; i < sizeof(need) / sizeof(need[0]); ++i)
     if (!need[i]) return fail(URLG_EINVAL, "urlg_env_bind: required buffer #%zu is NULL", i);
-  if (env->desc.family == 1 && (!b->rigid_body_states || !b->priv_obs_buf[0] || !b->priv_obs_buf[1] || !b->phase || !b->leg_phase))
+  const int fam = env->desc.family;
+  if (fam == URLG_FAMILY_H1 && (!b->rigid_body_states || !b->priv_obs_buf[0] || !b->priv_obs_buf[1] || !b->phase || !b->leg_phase))
     return fail(URLG_EINVAL, "urlg_env_bind: H1-family env needs rigid_body_states, priv_obs_buf, phase, leg_phase");
-  if (((uintptr_t)b->commands & 15) || ((uintptr_t)b->dof_state & 7))
-    return fail(URLG_EINVAL, "urlg_env_bind: commands must be 16-byte and dof_state 8-byte aligned");
-  env->bufs = *b;
+  if (fam == URLG_FAMILY_HANDSTAND && !b->rigid_body_states)
+    return fail(URLG_EINVAL, "urlg_env_bind: the handstand env needs rigid_body_states (feet positions)");
+  if (env->desc.num_priv && (!b->priv_obs_buf[0] || !b->priv_obs_buf[1]))
+    return fail(URLG_EINVAL, "urlg_env_bind: num_priv > 0 needs both priv_obs_buf slots");
   {
     const void* al[] = {b->root_states, b->dof_state, b->contact_forces, b->actions, b->last_actions, b->last_dof_vel,
-                        b->torques, b->obs_buf[0], b->obs_buf[1], b->priv_obs_buf[0], b->priv_obs_buf[1]};
+                        b->torques, b->obs_buf[0], b->obs_buf[1], b->priv_obs_buf[0], b->priv_obs_buf[1], b->commands,
+                        b->leg_phase};
     uintptr_t bits = 0;
     for (size_t i = 0; i < sizeof(al) / sizeof(al[0]); ++i) bits |= (uintptr_t)al[i];
-    env->vec_ok = (bits & 15) == 0;
+    if (bits & 15)
+      return fail(URLG_EINVAL, "urlg_env_bind: root_states, dof_state, contact_forces, actions, last_actions, last_dof_vel, "
+                  "torques, obs / privileged obs slots, commands and leg_phase must be 16-byte aligned");
   }
+  env->bufs = *b;
   env->bound = 1;
+  return URLG_OK;
+}
+
+extern "C" int urlg_env_bind_frame_pool(urlg_env* env, const urlg_frame_pool* pool) {
+  if (!env) return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: null env");
+  if (!pool) { env->pool.enabled = 0; return URLG_OK; }
+  if (!pool->root || !pool->dof || !pool->contact || !pool->calls_base || pool->num_frames <= 0 || pool->substeps <= 0 ||
+      pool->num_frames > 0x7fffffff || pool->substeps > 0x7fffffff)
+    return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: bad pool");
+  if (env->desc.family != URLG_FAMILY_BASE && !pool->rigid_body)
+    return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: this env family reads rigid_body_states");
+  const uintptr_t bits = (uintptr_t)pool->root | (uintptr_t)pool->dof | (uintptr_t)pool->contact;
+  if ((bits & 15) || (env->desc.num_envs & 3))
+    return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: pool tensors must be 16-byte aligned and num_envs a multiple of 4");
+  env->pool.pool = *pool;
+  env->pool.enabled = 1;
   return URLG_OK;
 }
 
@@ -844,40 +1252,61 @@ extern "C" void urlg_env_destroy(urlg_env* env) {
 }
 
 extern "C" int urlg_env_num_rng_slots(const urlg_env* env) {
-  return env ? 14 + env->desc.num_dof + env->desc.num_obs : 0;
+  if (!env) return 0;
+  return 14 + env->desc.num_dof + env->desc.num_obs + (env->desc.family == URLG_FAMILY_HANDSTAND ? 4 : 0);
 }
 
-extern "C" int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream) {
+static int pd_launch(urlg_env* env, const float* raw_actions, int64_t calls_off, void* stream) {
   if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_pd_torques: env not bound");
   const int64_t total = (int64_t)env->desc.num_envs * env->desc.num_dof;
   if (total >= 0x7fffffffll) return fail(URLG_EINVAL, "urlg_pd_torques: num_envs * num_dof must be < 2^31");
-  const urlg_env_buffers& eb = env->bufs;
-  const uintptr_t bits = (uintptr_t)raw_actions | (uintptr_t)eb.actions | (uintptr_t)eb.dof_state | (uintptr_t)eb.torques |
-                         (uintptr_t)eb.last_dof_vel;
-  if ((env->desc.num_dof & 3) == 0 && (bits & 15) == 0) {
+  PoolArgs pa = env->pool;
+  pa.calls_off = calls_off;
+  if (((uintptr_t)raw_actions & 15) == 0 && (env->desc.num_dof & 3) == 0) {
     const uint32_t total4 = (uint32_t)(total / 4);
-    pd_torques_vec4_kernel<<<(total4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions, total4);
+    pd_torques_vec4_kernel<<<(total4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, pa, raw_actions, total4);
   } else {
-    pd_torques_kernel<<<grid_for(total, 256, 64), 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, raw_actions);
+    pd_torques_kernel<<<grid_for(total, 256, 64), 256, 0, (cudaStream_t)stream>>>(env->desc, env->bufs, pa, raw_actions);
   }
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }
 
-extern "C" int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot,
-                                 void* stream) {
+extern "C" int urlg_pd_torques(urlg_env* env, const float* raw_actions, void* stream) {
+  if (env && env->pool.enabled) return fail(URLG_EINVAL, "urlg_pd_torques: a frame pool is bound; call urlg_pd_torques_at");
+  return pd_launch(env, raw_actions, 0, stream);
+}
+extern "C" int urlg_pd_torques_at(urlg_env* env, const float* raw_actions, int64_t calls_offset, void* stream) {
+  return pd_launch(env, raw_actions, calls_offset, stream);
+}
+
+static int post_launch(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot, int64_t calls_off,
+                       void* stream) {
   if (!env || !env->bound) return fail(URLG_EINVAL, "urlg_post_physics: env not bound");
   if (obs_slot != 0 && obs_slot != 1) return fail(URLG_EINVAL, "urlg_post_physics: obs_slot must be 0 or 1");
   const int N = env->desc.num_envs;
   const int slots = urlg_env_num_rng_slots(env);
   cudaStream_t st = (cudaStream_t)stream;
-  post_physics_kernel<<<(N + kEnvsPerBlock - 1) / kEnvsPerBlock, kK2Threads, env->smem_bytes, st>>>(
-      env->desc, env->bufs, env->scratch, step_base, step_offset, obs_slot, slots, env->vec_ok);
+  PoolArgs pa = env->pool;
+  pa.calls_off = calls_off;
+  K2Fn fn = k2_for(env->desc.num_dof, env->desc.family);
+  fn<<<(N + 31) / 32, 32, env->smem_bytes, st>>>(env->desc, env->bufs, env->tt, pa, env->scratch, step_base, step_offset,
+                                                 obs_slot, slots);
   URLG_LAUNCH_CHECK();
-  finalize_step_kernel<<<grid_for(N, 256), 256, 0, st>>>(env->desc, env->bufs, env->scratch, step_base, step_offset,
-                                                        slots);
-  URLG_LAUNCH_CHECK();
+  URLG_CUDA(launch_pdl(finalize_step_kernel, dim3((N + 127) / 128), dim3(128), 0, st, env->desc, env->bufs, pa,
+                       env->scratch, step_base, step_offset, slots));
+  ++urlg::g_launches;
   return URLG_OK;
+}
+
+extern "C" int urlg_post_physics(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot,
+                                 void* stream) {
+  if (env && env->pool.enabled) return fail(URLG_EINVAL, "urlg_post_physics: a frame pool is bound; call urlg_post_physics_at");
+  return post_launch(env, step_base, step_offset, obs_slot, 0, stream);
+}
+extern "C" int urlg_post_physics_at(urlg_env* env, const int64_t* step_base, int64_t step_offset, int obs_slot,
+                                    int64_t calls_offset, void* stream) {
+  return post_launch(env, step_base, step_offset, obs_slot, calls_offset, stream);
 }
 
 extern "C" int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t n, const int64_t* step_base,
@@ -889,7 +1318,7 @@ extern "C" int urlg_env_reset_idx(urlg_env* env, const int64_t* env_ids, int64_t
   reset_idx_kernel<<<(int)((n + 127) / 128), 128, 0, st>>>(env->desc, env->bufs, env->scratch, env_ids, n, step_base,
                                                           step_offset, urlg_env_num_rng_slots(env));
   URLG_LAUNCH_CHECK();
-  finalize_reset_kernel<<<1, 256, 0, st>>>(env->desc, env->bufs, env->scratch);
+  finalize_reset_kernel<<<1, 256, 0, st>>>(env->desc, env->bufs, env->scratch, n);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }
@@ -909,6 +1338,16 @@ extern "C" int urlg_synth_refresh(float* dst, const float* pool, int64_t elems, 
     return fail(URLG_EINVAL, "urlg_synth_refresh: bad argument");
   synth_refresh_kernel<<<grid_for((elems + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
       dst, pool, elems, num_frames, substeps, per_substep, calls_base, calls_offset);
+  URLG_LAUNCH_CHECK();
+  return URLG_OK;
+}
+
+extern "C" int urlg_scatter_rows(float* dst, const float* src, const int32_t* ids, const int32_t* count, int row_floats,
+                                 int max_rows, void* stream) {
+  if (!dst || !src || !ids || !count || row_floats <= 0 || max_rows <= 0)
+    return fail(URLG_EINVAL, "urlg_scatter_rows: bad argument");
+  scatter_rows_kernel<<<grid_for((int64_t)max_rows * row_floats, 256, 2), 256, 0, (cudaStream_t)stream>>>(
+      dst, src, ids, count, row_floats, max_rows);
   URLG_LAUNCH_CHECK();
   return URLG_OK;
 }

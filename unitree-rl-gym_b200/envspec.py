@@ -15,19 +15,44 @@ import torch
 
 from .legged_gym.utils.helpers import class_to_dict
 
-# Reward-term ids shared with csrc/env_kernels.cu (enum RewardTerm).  Alphabetical, like the
-# execution order; 'termination' is applied after the positive clamp and is not in this list.
-TERM_NAMES = [
-    "action_rate", "alive", "ang_vel_xy", "base_height", "collision", "contact", "contact_no_vel",
-    "dof_acc", "dof_pos_limits", "dof_vel", "dof_vel_limits", "feet_air_time", "feet_contact_forces",
-    "feet_swing_height", "hip_pos", "lin_vel_z", "orientation", "stand_still", "stumble",
-    "torque_limits", "torques", "tracking_ang_vel", "tracking_lin_vel",
+# Reward-term ids shared with include/urlg_b200.h (enum urlg_reward_term): alphabetical by reward NAME, like the
+# execution order.  'termination' is applied after the positive clamp and is not in this list.  A name whose formula
+# the handstand subclass overrides (go2_handstand_env.py:224-246) has a second id with the suffix '@hs'.
+TERM_KEYS = [
+    "action_rate", "alive", "ang_vel_xy", "base_height", "base_height@hs", "collision", "contact", "contact_no_vel",
+    "dof_acc", "dof_pos_limits", "dof_vel", "dof_vel_limits", "energy", "feet_air_time", "feet_contact_forces",
+    "feet_swing_height", "front_feet_contact", "front_feet_together", "front_hip_neutral", "hind_feet_no_contact",
+    "hip_pos", "lin_vel_xy", "lin_vel_z", "orientation", "orientation@hs", "pose", "stability", "stand_still",
+    "stay_still", "stumble", "torque_limits", "torques", "tracking_ang_vel", "tracking_lin_vel",
 ]
-TERM_ID = {n: i for i, n in enumerate(TERM_NAMES)}
+_TERM_KEY_ID = {n: i for i, n in enumerate(TERM_KEYS)}
 H1_FAMILY_TERMS = {"alive", "contact", "contact_no_vel", "feet_swing_height", "hip_pos"}
+HANDSTAND_TERMS = {"base_height", "orientation", "energy", "front_feet_contact", "front_feet_together",
+                   "front_hip_neutral", "hind_feet_no_contact", "lin_vel_xy", "pose", "stability", "stay_still"}
+TERM_NAMES = sorted({k.split("@")[0] for k in TERM_KEYS})      # every `_reward_<name>` the fused kernel implements
 
-FAMILY_BASE = 0   # LeggedRobot observation layout (legged_robot.py:800-807)
-FAMILY_H1 = 1     # H1/H1_2/G1 layout with gait phase + privileged obs (h1_env.py:68-95)
+FAMILY_BASE = 0        # LeggedRobot observation layout (legged_robot.py:800-807)
+FAMILY_H1 = 1          # H1/H1_2/G1 layout with gait phase + privileged obs (h1_env.py:68-95)
+FAMILY_HANDSTAND = 2   # GO2HandstandEnv: 6+3A+4 obs with contact flags (go2_handstand_env.py:140-176)
+
+
+def term_id(name, family):
+    """Kernel id of reward `name` for an env family; raises AttributeError where the reference's
+    getattr(self, '_reward_' + name) would (legged_robot.py:836)."""
+    if family == FAMILY_HANDSTAND and name + "@hs" in _TERM_KEY_ID:
+        return _TERM_KEY_ID[name + "@hs"]
+    if name not in _TERM_KEY_ID:
+        raise AttributeError(f"no reward term '_reward_{name}' in the fused step kernel "
+                             f"(the reference fails at legged_robot.py:836 for unknown names too)")
+    if name in H1_FAMILY_TERMS and family != FAMILY_H1:
+        raise AttributeError(f"'_reward_{name}' exists only on the H1-family env classes (h1_env.py:98-123)")
+    if name in HANDSTAND_TERMS and name not in ("base_height", "orientation") and family != FAMILY_HANDSTAND:
+        raise AttributeError(f"'_reward_{name}' exists only on GO2HandstandEnv (go2_handstand_env.py:224-383)")
+    return _TERM_KEY_ID[name]
+
+
+# kept for callers of the round-1 name: id of a base-class / H1-family term
+TERM_ID = {n: i for n, i in _TERM_KEY_ID.items() if "@" not in n}
 
 HIP_POS_IDX = {"h1": [0, 1, 5, 6], "h1_2": [0, 2, 6, 8], "g1": [1, 2, 7, 8]}   # h1_env.py:123 etc.
 
@@ -91,6 +116,14 @@ class EnvSpec:
     send_timeouts: bool = True
     dof_names: List[str] = field(default_factory=list)
     body_names: List[str] = field(default_factory=list)
+    # ---- variant tables: what a subclass of LeggedRobot changes by overriding methods (go2_handstand_env.py) ----
+    termination_mode: int = 0     # 0: roll/pitch rule (legged_robot.py:715-716); 1: projected-gravity band (:178-219)
+    callback_mode: int = 0        # 0: base callback (resample / heading, :488-517); 1: none (:84-96)
+    clip_torques: bool = True     # legged_robot.py:671; the handstand override has no clip (:349-350)
+    pd_target_lo: np.ndarray = None   # [A] P-control target clamp (+-inf = none); rear-leg clamp of :336-346
+    pd_target_hi: np.ndarray = None
+    pose_targets: np.ndarray = None   # [A] handstand pose (:22-24, 52-57)
+    num_front_dof: int = 0
 
     @property
     def num_feet(self):
@@ -98,7 +131,7 @@ class EnvSpec:
 
     @property
     def num_rng_slots(self):
-        return 14 + self.num_dof + self.num_obs
+        return 14 + self.num_dof + self.num_obs + (4 if self.family == FAMILY_HANDSTAND else 0)
 
     @property
     def sum_names(self):
@@ -128,7 +161,11 @@ def build_env_spec(task, cfg, robot, sim_dt, seed=1, env_offset=0, family=None) 
     A = robot.num_dof
     N = cfg.env.num_envs
     if family is None:
-        family = FAMILY_BASE if cfg.env.num_privileged_obs is None else FAMILY_H1
+        family = (FAMILY_HANDSTAND if hasattr(cfg, "handstand_pose") else
+                  FAMILY_BASE if cfg.env.num_privileged_obs is None else FAMILY_H1)
+    if cfg.commands.num_commands != 4:
+        raise ValueError("the fused step kernel reads commands as [N, 4] (legged_robot_config.py:92 num_commands = 4); "
+                         f"got num_commands = {cfg.commands.num_commands}")
     dt = cfg.control.decimation * sim_dt
     max_len_s = cfg.env.episode_length_s
     max_len = float(np.ceil(max_len_s / dt))
@@ -170,11 +207,7 @@ def build_env_spec(task, cfg, robot, sim_dt, seed=1, env_offset=0, family=None) 
         if key == "termination":
             term_scale = s * dt
             continue
-        if key not in TERM_ID:
-            raise AttributeError(f"no reward term '_reward_{key}' in the fused step kernel "
-                                 f"(reference would fail at legged_robot.py:836 for unknown names too)")
-        if key in H1_FAMILY_TERMS and family != FAMILY_H1:
-            raise AttributeError(f"'_reward_{key}' exists only on the H1-family env classes")
+        term_id(key, family)             # AttributeError for a name the env class has no _reward_ function for
         names.append(key)
         vals.append(s * dt)
 
@@ -187,11 +220,45 @@ def build_env_spec(task, cfg, robot, sim_dt, seed=1, env_offset=0, family=None) 
         nv[6:9] = ns.gravity * lvl
         nv[12:12 + A] = ns.dof_pos * lvl * os_.dof_pos
         nv[12 + A:12 + 2 * A] = ns.dof_vel * lvl * os_.dof_vel
-    else:
+    elif family == FAMILY_H1:
         nv[0:3] = ns.ang_vel * lvl * os_.ang_vel
         nv[3:6] = ns.gravity * lvl
         nv[9:9 + A] = ns.dof_pos * lvl * os_.dof_pos
         nv[9 + A:9 + 2 * A] = ns.dof_vel * lvl * os_.dof_vel
+    else:                                    # go2_handstand_env.py:386-422 (gyro, gravity, dof_pos, dof_vel; flags 0)
+        nv[0:3] = lvl * ns.gyro * os_.ang_vel
+        nv[3:6] = lvl * ns.gravity
+        nv[6:6 + A] = lvl * ns.dof_pos * os_.dof_pos
+        nv[6 + A:6 + 2 * A] = lvl * ns.dof_vel * os_.dof_vel
+
+    variant = {}
+    hip_idx = HIP_POS_IDX.get(robot.name, [])
+    if family == FAMILY_HANDSTAND:
+        # go2_handstand_env.py:17-42: pose targets from cfg.handstand_pose over the default angles; the six rear-leg
+        # joints' PD targets are clamped to pose +- 0.15 rad; front hips for _reward_front_hip_neutral (:352-358)
+        idx = {n: i for i, n in enumerate(robot.dof_names)}
+        pose = q0.copy()
+        for name, ang in cfg.handstand_pose.joint_angles.items():
+            if name in idx:
+                pose[idx[name]] = ang
+        lo = np.full(A, -np.inf, np.float32)
+        hi = np.full(A, np.inf, np.float32)
+        rear_limit = np.float32(0.15)
+        for n_ in ("RL_hip_joint", "RL_thigh_joint", "RL_calf_joint", "RR_hip_joint", "RR_thigh_joint", "RR_calf_joint"):
+            if n_ in idx:
+                lo[idx[n_]] = np.float32(pose[idx[n_]]) - rear_limit
+                hi[idx[n_]] = np.float32(pose[idx[n_]]) + rear_limit
+        front = [idx[l + j] for l in ("FL_", "FR_") for j in ("hip_joint", "thigh_joint", "calf_joint")]
+        if sorted(front) != list(range(len(front))):
+            raise ValueError("handstand pose term expects the front-leg DOFs first (go2.urdf order FL, FR, RL, RR)")
+        if len(feet) < 4:
+            raise AssertionError("Expected at least 4 feet for Go2.")          # go2_handstand_env.py:19
+        hip_idx = [idx["FL_hip_joint"], idx["FR_hip_joint"]]
+        variant = dict(termination_mode=1, callback_mode=1, clip_torques=False, pd_target_lo=lo, pd_target_hi=hi,
+                       pose_targets=pose.astype(np.float32), num_front_dof=len(front))
+    else:
+        variant = dict(pd_target_lo=np.full(A, -np.inf, np.float32), pd_target_hi=np.full(A, np.inf, np.float32),
+                       pose_targets=np.zeros(A, np.float32))
 
     ist = cfg.init_state
     rng = cfg.commands.ranges
@@ -205,7 +272,7 @@ def build_env_spec(task, cfg, robot, sim_dt, seed=1, env_offset=0, family=None) 
         control_type=cfg.control.control_type, p_gains=kp, d_gains=kd, default_dof_pos=q0,
         torque_limits=np.asarray(robot.dof_effort, np.float32),
         dof_vel_limits=np.asarray(robot.dof_velocity, np.float32), dof_pos_limits=lim.numpy().copy(),
-        feet_idx=feet, pen_idx=pen, term_idx=term, hip_idx=HIP_POS_IDX.get(robot.name, []),
+        feet_idx=feet, pen_idx=pen, term_idx=term, hip_idx=hip_idx,
         reward_names=names, reward_scales=vals, termination_scale=term_scale,
         only_positive=bool(cfg.rewards.only_positive_rewards), tracking_sigma=cfg.rewards.tracking_sigma,
         base_height_target=cfg.rewards.base_height_target, soft_dof_vel_limit=cfg.rewards.soft_dof_vel_limit,
@@ -216,4 +283,4 @@ def build_env_spec(task, cfg, robot, sim_dt, seed=1, env_offset=0, family=None) 
         cmd_yaw=list(rng.ang_vel_yaw), cmd_heading=list(rng.heading),
         base_init_state=np.asarray(ist.pos + ist.rot + ist.lin_vel + ist.ang_vel, np.float32),
         env_origins=env_origins_grid(N, cfg.env.env_spacing), seed=seed, env_offset=env_offset,
-        send_timeouts=bool(cfg.env.send_timeouts), dof_names=list(robot.dof_names), body_names=list(bodies))
+        send_timeouts=bool(cfg.env.send_timeouts), dof_names=list(robot.dof_names), body_names=list(bodies), **variant)

@@ -4,8 +4,11 @@ Public surface (constructor signature, VecEnv protocol, every public tensor name
 follows legged_gym/envs/base/legged_robot.py:24-49, 615-647 and base_task.py:31-86.  What differs
 by design: check_termination / compute_reward / compute_observations / _post_physics_step_callback /
 _push_robots / _resample_commands are not separate eager passes any more — they are stages of one
-kernel (csrc/env_kernels.cu) — so overriding them in a subclass is rejected at construction instead
-of being silently ignored.  Host syncs of the reference (`nonzero` x2, boolean-mask `len`) are gone.
+kernel (csrc/env_kernels.cu).  What the reference's own subclasses change by overriding them (H1Robot,
+GO2HandstandEnv) is a *variant* of that kernel selected by the class's `_family`; a subclass that overrides
+a fused stage (or defines a `_reward_<name>`) with Python code of its own is rejected at construction
+instead of being silently ignored.  Host syncs of the reference (`nonzero` x2, boolean-mask `len`) are gone;
+the indexed setters of the physics seam (:552-555, 569-572, 591-594) get device-resident id lists + counts.
 """
 import ctypes as C
 
@@ -15,7 +18,7 @@ import torch
 from .base_task import BaseTask
 from .legged_robot_config import LeggedRobotCfg
 from .... import _lib
-from ....envspec import build_env_spec, TERM_ID, FAMILY_BASE, FAMILY_H1
+from ....envspec import build_env_spec, term_id, FAMILY_BASE, FAMILY_H1
 from ....physics import SyntheticGym
 from ....robots import robot_for_asset
 
@@ -35,8 +38,14 @@ class LeggedRobot(BaseTask):
         for name in _FUSED_HOOKS:
             if getattr(type(self), name) is not getattr(LeggedRobot, name):
                 raise NotImplementedError(
-                    f"{type(self).__name__}.{name} overrides a stage that is fused into urlg_post_physics; "
-                    "add the behaviour as a kernel term (csrc/env_kernels.cu) instead")
+                    f"{type(self).__name__}.{name} overrides a stage that is fused into urlg_post_physics; Python code "
+                    "cannot run inside the kernel — add the behaviour as a kernel variant / reward term "
+                    "(csrc/env_kernels.cu, like GO2HandstandEnv's) instead")
+        for name in dir(type(self)):
+            if name.startswith("_reward_") and callable(getattr(type(self), name, None)):
+                raise NotImplementedError(
+                    f"{type(self).__name__}.{name} is a Python reward function; rewards are terms of the fused step "
+                    "kernel (urlg_reward_term in include/urlg_b200.h) — add it there")
         self._parse_cfg(self.cfg)
         super().__init__(self.cfg, sim_params, physics_engine, sim_device, headless)
         self._init_buffers()
@@ -97,10 +106,11 @@ class LeggedRobot(BaseTask):
         self.base_pos = self.root_states[:N, 0:3]
         self.contact_forces = g.acquire_net_contact_force_tensor(self.sim).view(N, -1, 3)
         self.rigid_body_states = None
-        if self._family == FAMILY_H1:
+        if self._family != FAMILY_BASE:
             self.rigid_body_states = g.acquire_rigid_body_state_tensor(self.sim)
             self.rigid_body_states_view = self.rigid_body_states.view(N, -1, 13)
             self.feet_num = len(s.feet_idx)
+        if self._family == FAMILY_H1:
             self.phase = torch.zeros(N, **f)
             self.leg_phase = torch.zeros(N, 2, **f)
         self.common_step_counter = 0
@@ -144,8 +154,11 @@ class LeggedRobot(BaseTask):
         self.episode_sums = {n: self._episode_sums_buf[i] for i, n in enumerate(names)}
         self._extras_episode = torch.zeros(len(names), dtype=torch.float, device=self.device)
         self._extras_time_outs = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
+        # compacted int32 id lists + device counts for the indexed setters of the physics seam (:552-555, 569-572, 591-594)
         self._reset_ids = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
         self._reset_count = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._root_ids = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
+        self._root_count = torch.zeros(1, dtype=torch.int32, device=self.device)
 
     # ------------------------------------------------------------------ C-ABI binding
     def _desc(self):
@@ -166,7 +179,7 @@ class LeggedRobot(BaseTask):
         d.termination_sum_row = names.index("termination") if s.termination_scale is not None else -1
         d.termination_scale = s.termination_scale or 0.0
         for i, (n, sc) in enumerate(zip(s.reward_names, s.reward_scales)):
-            d.term_ids[i], d.term_sum_row[i], d.term_scales[i] = TERM_ID[n], names.index(n), sc
+            d.term_ids[i], d.term_sum_row[i], d.term_scales[i] = term_id(n, s.family), names.index(n), sc
         for k in ("dt", "sim_dt", "max_episode_length", "max_episode_length_s", "action_scale", "clip_actions",
                   "tracking_sigma", "base_height_target", "soft_dof_vel_limit", "soft_torque_limit",
                   "max_contact_force", "obs_scale_lin_vel", "obs_scale_ang_vel", "obs_scale_dof_pos", "obs_scale_dof_vel"):
@@ -189,6 +202,10 @@ class LeggedRobot(BaseTask):
         for i, v in enumerate(s.base_init_state):
             d.base_init_state[i] = v
         d.seed_lo, d.seed_hi, d.env_offset = s.seed & 0xFFFFFFFF, (s.seed >> 32) & 0xFFFFFFFF, s.env_offset
+        d.termination_mode, d.callback_mode, d.clip_torques = s.termination_mode, s.callback_mode, int(s.clip_torques)
+        d.num_front_dof = s.num_front_dof
+        for j in range(s.num_dof):
+            d.pd_target_lo[j], d.pd_target_hi[j], d.pose_targets[j] = s.pd_target_lo[j], s.pd_target_hi[j], s.pose_targets[j]
         return d
 
     def _bind(self, rng_override=None):
@@ -217,9 +234,15 @@ class LeggedRobot(BaseTask):
         b.episode_sums, b.env_origins = p(self._episode_sums_buf), p(self.env_origins)
         b.extras_episode, b.extras_time_outs = p(self._extras_episode), p(self._extras_time_outs)
         b.reset_ids, b.reset_count = p(self._reset_ids), p(self._reset_count)
+        b.root_ids, b.root_count = p(self._root_ids), p(self._root_count)
         self._rng_override = rng_override
         b.rng_override = p(rng_override)
         _lib.check(L.urlg_env_bind(self._handle, C.byref(b)))
+        # pool-indexed physics seam (SyntheticGym(pool_seam=True)): the kernels read the current synthetic frame in place
+        self._pool = bool(getattr(self.gym, "pool_seam", False))
+        if self._pool:
+            self._pool_desc = self.gym.frame_pool_desc()
+            _lib.check(L.urlg_env_bind_frame_pool(self._handle, C.byref(self._pool_desc)))
 
     def __del__(self):
         h = getattr(self, "_handle", None)
@@ -238,7 +261,10 @@ class LeggedRobot(BaseTask):
         L, st, g = _lib.lib(), _lib.cur_stream(), self.gym
         raw = _lib.ptr(actions)
         for k in range(self.cfg.control.decimation):
-            _lib.check(L.urlg_pd_torques(self._handle, raw if k == 0 else None, st))
+            if self._pool:
+                _lib.check(L.urlg_pd_torques_at(self._handle, raw if k == 0 else None, g.sim_calls, st))
+            else:
+                _lib.check(L.urlg_pd_torques(self._handle, raw if k == 0 else None, st))
             g.set_dof_actuation_force_tensor(self.sim, self.torques)
             g.simulate(self.sim)
             g.refresh_dof_state_tensor(self.sim)
@@ -248,24 +274,40 @@ class LeggedRobot(BaseTask):
     def _compute_torques(self, actions):
         """K1 on its own (legged_robot.py:649-671); `actions` are clipped and stored like step() does."""
         actions = actions.to(device=self.device, dtype=torch.float).contiguous()
-        _lib.check(_lib.lib().urlg_pd_torques(self._handle, _lib.ptr(actions), _lib.cur_stream()))
+        if self._pool:
+            _lib.check(_lib.lib().urlg_pd_torques_at(self._handle, _lib.ptr(actions), self.gym.sim_calls, _lib.cur_stream()))
+        else:
+            _lib.check(_lib.lib().urlg_pd_torques(self._handle, _lib.ptr(actions), _lib.cur_stream()))
         return self.torques
 
     def post_physics_step(self):
-        """legged_robot.py:673-709 as one fused kernel + finalize (csrc/env_kernels.cu K2/K2b)."""
+        """legged_robot.py:673-709 as one fused kernel + finalize (csrc/env_kernels.cu K2/K2b), then the commits the
+        reference makes through the indexed setters: reset envs' DOF state (:569-572), reset + pushed envs' root state
+        (:591-594, 552-555) — as device-resident int32 id lists with device counts, so nothing syncs."""
         g = self.gym
         g.refresh_actor_root_state_tensor(self.sim)
         g.refresh_net_contact_force_tensor(self.sim)
-        if self._family == FAMILY_H1:
+        if self._family != FAMILY_BASE:
             g.refresh_rigid_body_state_tensor(self.sim)
         self.common_step_counter += 1
         self._obs_slot ^= 1
-        _lib.check(_lib.lib().urlg_post_physics(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
-                                                self._obs_slot, _lib.cur_stream()))
+        L = _lib.lib()
+        if self._pool:
+            _lib.check(L.urlg_post_physics_at(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
+                                              self._obs_slot, g.sim_calls, _lib.cur_stream()))
+        else:
+            _lib.check(L.urlg_post_physics(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
+                                           self._obs_slot, _lib.cur_stream()))
+        self._commit_indexed()
         self.obs_buf = self._obs_slots[self._obs_slot]
         if self._priv_slots:
             self.privileged_obs_buf = self._priv_slots[self._obs_slot]
         self._publish_extras()
+
+    def _commit_indexed(self):
+        g = self.gym
+        g.set_dof_state_tensor_indexed(self.sim, self.dof_state, self._reset_ids, self._reset_count)
+        g.set_actor_root_state_tensor_indexed(self.sim, self.root_states, self._root_ids, self._root_count)
 
     def _publish_extras(self):
         if "episode" not in self.extras:
@@ -282,6 +324,7 @@ class LeggedRobot(BaseTask):
         ids = torch.as_tensor(env_ids, device=self.device).to(torch.int64).contiguous()
         _lib.check(_lib.lib().urlg_env_reset_idx(self._handle, _lib.ptr(ids), ids.numel(), _lib.ptr(self._step_base),
                                                  self.common_step_counter, _lib.cur_stream()))
+        self._commit_indexed()
         self._publish_extras()
 
     # ------------------------------------------------------------------ graph support

@@ -1,5 +1,5 @@
-"""Per-robot env / PPO configs for the four BASELINE tasks (data only).  Values follow
-go2_config.py:3-53, h1_config.py:3-118, h1_2_config.py:4-130, g1_config.py:3-108."""
+"""Per-robot env / PPO configs for the five registered tasks (data only).  Values follow
+go2_config.py:3-53, h1_config.py:3-118, h1_2_config.py:4-130, g1_config.py:3-108, go2_handstand_config.py:4-219."""
 from .base.legged_robot_config import LeggedRobotCfg, LeggedRobotCfgPPO
 
 _ASSET = '{LEGGED_GYM_ROOT_DIR}/resources/robots/'
@@ -61,6 +61,64 @@ class GO2RoughCfgPPO(LeggedRobotCfgPPO):
 
     class runner(LeggedRobotCfgPPO.runner):
         run_name = ''; experiment_name = 'rough_go2'
+
+
+# ------------------------------------------------------------------ Go2 handstand (go2_handstand_config.py)
+def _leg_angles(hip, thigh, calf):
+    """{leg}_{joint}_joint table from per-leg (FL, FR, RL, RR) values."""
+    legs = ("FL", "FR", "RL", "RR")
+    return {f"{l}_{j}_joint": v[i] for j, v in (("hip", hip), ("thigh", thigh), ("calf", calf)) for i, l in enumerate(legs)}
+
+
+class GO2HandstandCfg(LeggedRobotCfg):
+    class env(LeggedRobotCfg.env):
+        num_observations = 46; num_privileged_obs = 46; num_actions = 12
+
+    class init_state(LeggedRobotCfg.init_state):
+        pos = [0.0, 0.0, 0.28]
+        default_joint_angles = _leg_angles((0.3, -0.3, 0.1, -0.1), (1.2, 1.2, 0.3, 0.3), (-2.0, -2.0, -1.4, -1.4))
+
+    class control(LeggedRobotCfg.control):
+        control_type = 'P'; stiffness = {'joint': 35.0}; damping = {'joint': 0.5}
+        action_scale = 0.3; decimation = 5
+
+    class asset(LeggedRobotCfg.asset):
+        file = _ASSET + 'go2/urdf/go2.urdf'; name = "go2"; foot_name = "foot"
+        penalize_contacts_on = ["thigh", "calf", "hip"]
+        terminate_after_contacts_on = ["base", "thigh", "calf", "hip", "Head_lower", "Head_upper"]
+        self_collisions = 1
+
+    class noise(LeggedRobotCfg.noise):
+        add_noise = True; noise_level = 1.0
+
+        class noise_scales(LeggedRobotCfg.noise.noise_scales):
+            gyro = 0.2; gravity = 0.05; dof_pos = 0.01; dof_vel = 1.5; lin_vel = 0.1; actions = 0.0
+
+    class rewards(LeggedRobotCfg.rewards):
+        only_positive_rewards = False; base_height_target = 0.65; soft_dof_pos_limit = 0.9
+
+        class scales(LeggedRobotCfg.rewards.scales):
+            orientation = 5.0; base_height = 2.0; front_feet_contact = 3.0; hind_feet_no_contact = 3.0
+            pose = 10.0; stability = 1.0; stay_still = 2.0; lin_vel_xy = -3
+            lin_vel_z = -0.001; ang_vel_xy = -0.005; torques = -2e-4; dof_vel = -1e-5; dof_acc = 0.0
+            action_rate = -0.006; dof_pos_limits = -1.0; dof_vel_limits = 0.0; torque_limits = 0.0
+            collision = -2.0; front_hip_neutral = 2.0; front_feet_together = 1.5; feet_contact_forces = 0.0
+            termination = -5.0; tracking_lin_vel = 0.0; tracking_ang_vel = 0.0; feet_air_time = 0.0
+            stumble = 0.0; energy = 0.0
+
+    class handstand_pose:
+        joint_angles = _leg_angles((0.0, 0.0, 0.0, 0.0), (-0.89, -0.89, 1.7, 1.7), (-1.5, -1.5, -1.853, -1.853))
+
+    class footstand_pose:
+        joint_angles = _leg_angles((0.0, 0.0, 0.0, 0.0), (0.82, 0.82, 1.82, 1.82), (-1.6, -1.68, -1.16, -1.16))
+
+
+class GO2HandstandCfgPPO(LeggedRobotCfgPPO):
+    class algorithm(LeggedRobotCfgPPO.algorithm):
+        entropy_coef = 0.01
+
+    class runner(LeggedRobotCfgPPO.runner):
+        run_name = ''; experiment_name = 'go2_handstand'
 
 
 # ------------------------------------------------------------------ H1

@@ -7,6 +7,12 @@ without Isaac Gym.  A real-PhysX binding would expose the same method names.
 
 Frame addressing is graph-safe: kernels read (device `calls_base` + host offset), and a captured
 graph ends with `advance_base()` so replays keep cycling through the pool.
+
+Two ways of serving a frame: `pool_seam=False` copies it into the acquired tensors on every refresh_* (one
+urlg_synth_refresh launch per tensor: the stand-in for PhysX filling its buffers); `pool_seam=True` hands the
+kernels the pool itself (urlg_env_bind_frame_pool) so refresh_* launches nothing and a timed region holds only the
+path.  Both give identical env outputs.  `StatefulGym` is the protocol a real simulator follows: its state lives
+apart from the exposed tensors and only the indexed setters write back into it.
 """
 import torch
 
@@ -14,7 +20,8 @@ from . import _lib
 
 
 class SyntheticGym:
-    def __init__(self, robot, num_envs, decimation, device, frames=None):
+    def __init__(self, robot, num_envs, decimation, device, frames=None, pool_seam=False):
+        self.pool_seam = bool(pool_seam)
         self.robot = robot
         self.num_envs = num_envs
         self.decimation = decimation
@@ -31,6 +38,8 @@ class SyntheticGym:
         self.frames = None
         self.last_torques = None
         self.indexed_calls = 0
+        self.last_dof_set = None      # (ids int32 [N], count int32 [1]) of the last set_dof_state_tensor_indexed
+        self.last_root_set = None
         if frames is not None:
             self.set_frames(frames)
 
@@ -68,8 +77,19 @@ class SyntheticGym:
     def fetch_results(self, *a):
         pass
 
+    def frame_pool_desc(self):
+        """urlg_frame_pool over the device-resident frames (pool_seam=True)."""
+        if self.frames is None:
+            raise RuntimeError("SyntheticGym(pool_seam=True) needs frames before the env binds")
+        d = _lib.FramePool()
+        d.root, d.dof, d.contact = _lib.ptr(self.frames["root"]), _lib.ptr(self.frames["dof"]), _lib.ptr(self.frames["contact"])
+        d.rigid_body = _lib.ptr(self.frames.get("rigid_body"))
+        d.num_frames, d.substeps = self.num_frames, self.decimation
+        d.calls_base = _lib.ptr(self.calls_base)
+        return d
+
     def _refresh(self, dst, key, per_substep):
-        if self.frames is None or self.frames.get(key) is None:
+        if self.pool_seam or self.frames is None or self.frames.get(key) is None:
             return
         pool = self.frames[key]
         elems = dst.numel()
@@ -92,11 +112,16 @@ class SyntheticGym:
     def set_dof_actuation_force_tensor(self, sim, torques):
         self.last_torques = torques
 
-    def set_dof_state_tensor_indexed(self, *a):
+    # Indexed setters (legged_robot.py:552-555, 569-572, 591-594).  The drop-in env passes (state tensor, int32 id
+    # tensor [N], int32 count tensor [1]) — ids and count stay on the device.  A pool of synthetic frames has no state
+    # to write back into, so these only record what they were given.
+    def set_dof_state_tensor_indexed(self, sim, state, ids, count):
         self.indexed_calls += 1
+        self.last_dof_set = (ids, count)
 
-    def set_actor_root_state_tensor_indexed(self, *a):
+    def set_actor_root_state_tensor_indexed(self, sim, state, ids, count):
         self.indexed_calls += 1
+        self.last_root_set = (ids, count)
 
     # ---- graph support ----
     def begin_relative(self):
@@ -107,3 +132,53 @@ class SyntheticGym:
     def advance_base(self):
         """Captured as the last node of a graph: base += calls made inside the graph."""
         self.calls_base += self.sim_calls
+
+
+class StatefulGym(SyntheticGym):
+    """A simulator whose state lives APART from the tensors it exposes — how PhysX behaves: `simulate` advances the
+    hidden state (here: a fixed drift per call), `refresh_*` copies hidden -> exposed, and ONLY the indexed setters
+    copy exposed rows back into the hidden state.  An env that rewrites reset / pushed rows in the exposed tensors
+    without committing them through the setters loses those writes at the next refresh (tests/test_env_cuda.py)."""
+
+    def __init__(self, robot, num_envs, decimation, device, seed=0):
+        super().__init__(robot, num_envs, decimation, device, frames=None, pool_seam=False)
+        g = torch.Generator().manual_seed(seed)
+        A, B = robot.num_dof, robot.num_bodies
+        dev = self.device
+        self.h_root = torch.zeros(num_envs, 13)
+        self.h_root[:, 2] = 0.4
+        self.h_root[:, 6] = 1.0
+        self.h_root[:, 7:13] = 0.1 * torch.randn(num_envs, 6, generator=g)
+        self.h_root = self.h_root.to(dev)
+        self.h_dof = (0.2 * torch.randn(num_envs * A, 2, generator=g)).to(dev)
+        self.h_contact = torch.zeros(num_envs * B, 3, device=dev)
+        self.drift = 1e-3
+
+    def simulate(self, sim=None):
+        self.sim_calls += 1
+        self.h_dof[:, 0] += self.drift
+        self.h_root[:, 0] += self.drift
+
+    def refresh_dof_state_tensor(self, sim=None):
+        self.dof_state.copy_(self.h_dof)
+
+    def refresh_actor_root_state_tensor(self, sim=None):
+        self.root_states.copy_(self.h_root)
+
+    def refresh_net_contact_force_tensor(self, sim=None):
+        self.net_contact_forces.copy_(self.h_contact)
+
+    def refresh_rigid_body_state_tensor(self, sim=None):
+        pass
+
+    def _scatter(self, dst, src, ids, count, row_floats):
+        _lib.check(_lib.lib().urlg_scatter_rows(_lib.ptr(dst), _lib.ptr(src), _lib.ptr(ids), _lib.ptr(count), row_floats,
+                                                self.num_envs, _lib.cur_stream()))
+
+    def set_dof_state_tensor_indexed(self, sim, state, ids, count):
+        super().set_dof_state_tensor_indexed(sim, state, ids, count)
+        self._scatter(self.h_dof, state, ids, count, 2 * self.robot.num_dof)
+
+    def set_actor_root_state_tensor_indexed(self, sim, state, ids, count):
+        super().set_actor_root_state_tensor_indexed(sim, state, ids, count)
+        self._scatter(self.h_root, state, ids, count, 13)

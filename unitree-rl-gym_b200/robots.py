@@ -104,6 +104,7 @@ def _h1_2():
 
 
 ROBOTS = {"go2": _go2(), "h1": _h1(), "g1": _g1(), "h1_2": _h1_2()}
+ROBOTS["go2_handstand"] = ROBOTS["go2"]      # task name -> table: the handstand task runs on the Go2 asset
 
 
 def robot_for_asset(asset_file: str) -> RobotTable:
