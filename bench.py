@@ -112,8 +112,7 @@ def make_frames(task, n, frames, seed=1):
     return spec, fr
 
 
-def make_env(task, n, frames, device, env_offset=0):
-    from unitree_rl_gym_b200.legged_gym.envs import LeggedRobot, H1Robot, H1_2Robot, G1Robot
+def make_env(task, n, frames, device, env_offset=0, pool_seam=False):
     from unitree_rl_gym_b200.legged_gym.utils.helpers import SimParams
     from unitree_rl_gym_b200.physics import SyntheticGym
     from unitree_rl_gym_b200.robots import ROBOTS
@@ -123,8 +122,8 @@ def make_env(task, n, frames, device, env_offset=0):
     cfg.env.env_offset = env_offset
     sp = SimParams()
     sp.dt = cfg.sim.dt
-    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames)
-    cls = {"go2": LeggedRobot, "h1": H1Robot, "h1_2": H1_2Robot, "g1": G1Robot}[task]
+    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames, pool_seam=pool_seam)
+    cls = H.env_class(task)
     return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device=device, headless=True), cfg
 
 
@@ -152,9 +151,30 @@ def config_dict(task, n, world, graph):
 
 DECIM = {"go2": 4, "h1": 4, "g1": 4, "h1_2": 8}
 # algorithmic bytes per env: K2 post-physics per env-step, K1 per substep
-K2_BYTES = {"go2": 1102, "g1": 1338, "h1_2": 1338, "h1": 1194}
-K1_BYTES = {"go2": 192, "g1": 192, "h1_2": 192, "h1": 160}
+K2_BYTES = {"go2": 1102, "g1": 1338, "h1_2": 1338, "h1": 1194, "go2_handstand": 1102 + 2 * 184 - 192 + 32}
+K1_BYTES = {"go2": 192, "g1": 192, "h1_2": 192, "h1": 160, "go2_handstand": 192}
 MLP_FLOP_PER_ENV_STEP = {"go2": 756992, "h1": 117952, "g1": 124224, "h1_2": 124224}
+
+
+def time_graph(fn, reps):
+    """us per call: `reps` back-to-back launches captured in one CUDA graph (no host launch cost in the bracket),
+    CUDA events on the replaying stream."""
+    import torch
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        for _ in range(reps):
+            fn()
+    gr.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    gr.replay()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / reps
 
 
 # ------------------------------------------------------------------ reference arm / cpu baseline (oracle port on host cores)
@@ -513,24 +533,7 @@ def own_arm(a):
                         "below the ridge point, so HBM is the roof"}
         iters = 200
 
-        def time_call(fn, reps):
-            """us per call: `reps` back-to-back launches captured in one CUDA graph (no host launch cost in the
-            bracket), CUDA events on the replaying stream."""
-            for _ in range(3):
-                fn()
-            torch.cuda.synchronize()
-            gr = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gr):
-                for _ in range(reps):
-                    fn()
-            gr.replay()
-            torch.cuda.synchronize()
-            e0, e1 = ev(), ev()
-            e0.record()
-            gr.replay()
-            e1.record()
-            e1.synchronize()
-            return e0.elapsed_time(e1) * 1e3 / reps
+        time_call = time_graph
 
         def post():
             env.common_step_counter += 1

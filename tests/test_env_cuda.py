@@ -145,7 +145,10 @@ def test_pool_seam_matches_copy_seam():
     for t, (a, b) in enumerate(zip(*out)):
         assert a.keys() == b.keys()
         for k in a:
-            assert np.array_equal(a[k], b[k]), f"step{t}/{k}"
+            if k.startswith("extras_episode/"):      # means over reset envs: float atomics, order not defined
+                np.testing.assert_allclose(a[k], b[k], rtol=1e-5, atol=1e-7, err_msg=f"step{t}/{k}")
+            else:
+                assert np.array_equal(a[k], b[k]), f"step{t}/{k}"
 
 
 def test_indexed_setter_lists_match_masks():

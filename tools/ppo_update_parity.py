@@ -23,7 +23,7 @@ for name, args in (("go2_mlp", (False, 48, None, 12, [512, 256, 128], N, 24)),
     out["cases"].append(rep)
     print(name, json.dumps({k: rep[k] for k in ("cuda_vs_oracle32", "oracle32_vs_oracle64", "cuda_vs_oracle64", "delta_scale", "lr_final")}),
           file=sys.stderr, flush=True)
-for kl in (0.0202, 0.00495):
+for kl in (0.0202, 0.00483):
     rep = T.one_update_report(False, 48, None, 12, [512, 256, 128], 1024, 24, kl_target=kl, with_fp64=False)
     rep["case"] = "go2_mlp_kl_%g" % kl
     out["cases"].append(rep)

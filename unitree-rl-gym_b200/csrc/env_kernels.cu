@@ -40,6 +40,9 @@ struct TermTable {
   unsigned long long mask;
   float scale[URLG_T_COUNT];
   int row[URLG_T_COUNT];
+  // sqrtf(s) > t  <=>  s > sq_thr(t): the largest float whose correctly-rounded root is still <= t (found on the host
+  // at create; sqrt is monotonic), so mask-deciding norm comparisons need no square root and stay bit-exact
+  float sq_thr_1p0, sq_thr_0p1;
 };
 
 struct PoolArgs {
@@ -136,6 +139,7 @@ static __device__ __noinline__ float py_remainder(float a, float b) {
 // One out-of-line copy of atan2f: K2 is latency-bound at 4096 envs and a cold instruction fetch costs more than a call.
 static __device__ __noinline__ float atan2_ni(float y, float x) { return atan2f(y, x); }
 __device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
+__device__ __forceinline__ float sq3(float x, float y, float z) { return x * x + y * y + z * z; }
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
 // [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw
@@ -284,8 +288,9 @@ __host__ __device__ inline Layout make_layout(const urlg_env_desc& c) {
   Layout L;
   int o = 0;
   L.oRoot = o; o += 32 * 13;
-  L.oCon = o; o += 32 * 3 * c.num_bodies;
-  L.oObs = o; o += 32 * obs_stride(c.num_obs);
+  // the observation image is assembled after the last read of the contact rows and overlays them
+  const int con = 32 * 3 * c.num_bodies, ob = 32 * obs_stride(c.num_obs);
+  L.oCon = o; L.oObs = o; o += con > ob ? con : ob;
   o = (o + 3) & ~3;
   L.oPriv = o; o += c.family == URLG_FAMILY_H1 ? 32 * c.num_priv : 0;
   o = (o + 3) & ~3;
@@ -320,7 +325,7 @@ __device__ __forceinline__ void resample_commands(const urlg_env_desc& c, float 
 //   0..2 callback resample | 3..3+A-1 _reset_dofs | 3+A..8+A root velocities | 9+A..11+A reset resample |
 //   12+A,13+A push | 14+A..14+A+O-1 observation noise | handstand: 14+A+O..+3 contact-flag flips
 template <int A, int FAM>
-__global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+__global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
                                                           const __grid_constant__ urlg_env_buffers b,
                                                           const __grid_constant__ TermTable tt,
                                                           const __grid_constant__ PoolArgs pa,
@@ -404,6 +409,11 @@ __global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant_
       }
     }
   }
+  // episode_sums rows of this env (read-modify-write at the end of the reward stage): in flight before the wait
+  constexpr int kSumsReg = 16;
+  float es[kSumsReg];
+#pragma unroll
+  for (int k = 0; k < kSumsReg; ++k) es[k] = k < c.num_sums ? b.episode_sums[(size_t)k * N + e] : 0.0f;
   const float* ovr = b.rng_override;
   const int64_t genv = c.env_offset + e;
 
@@ -466,7 +476,7 @@ __global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant_
   bool reset = false;
   _Pragma("unroll 1") for (int k = 0; k < c.num_term_bodies; ++k) {
     const float* f3 = con + 3 * c.term_idx[k];
-    reset |= norm3(f3[0], f3[1], f3[2]) > 1.0f;
+    reset |= sq3(f3[0], f3[1], f3[2]) > tt.sq_thr_1p0;          // ||F|| > 1.0
   }
   if (c.termination_mode == URLG_TERMINATION_RPY)
     reset |= (fabsf(pitch) > 1.0f) || (fabsf(roll) > 0.8f);
@@ -513,7 +523,7 @@ __global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant_
   TERM_BEGIN(URLG_T_COLLISION)
     _Pragma("unroll 1") for (int k = 0; k < c.num_pen; ++k) {
       const float* f3 = con + 3 * c.pen_idx[k];
-      r += norm3(f3[0], f3[1], f3[2]) > 0.1f ? 1.0f : 0.0f;
+      r += sq3(f3[0], f3[1], f3[2]) > tt.sq_thr_0p1 ? 1.0f : 0.0f;   // ||F|| > 0.1
     }
   TERM_END(URLG_T_COLLISION)
   if constexpr (FAM == URLG_FAMILY_H1) {
@@ -694,7 +704,15 @@ __global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant_
   {
     const bool pub = reset && live;
     float* accp = scratch->ep_acc[acc][blockIdx.x & (kAccCopies - 1)];
-    _Pragma("unroll 4") for (int k = 0; k < c.num_sums; ++k) {
+#pragma unroll
+    for (int k = 0; k < kSumsReg; ++k) {
+      if (k < c.num_sums) {
+        float v = es[k] + term[k * 32];
+        if (pub) { atomicAdd(accp + k, v); v = 0.0f; }
+        if (live) b.episode_sums[(size_t)k * N + e] = v;
+      }
+    }
+    _Pragma("unroll 1") for (int k = kSumsReg; k < c.num_sums; ++k) {
       float v = b.episode_sums[(size_t)k * N + e] + term[k * 32];
       if (pub) { atomicAdd(accp + k, v); v = 0.0f; }
       if (live) b.episode_sums[(size_t)k * N + e] = v;
@@ -796,55 +814,73 @@ __global__ void __launch_bounds__(32) post_physics_kernel(const __grid_constant_
     if constexpr (FAM == URLG_FAMILY_HANDSTAND) {
       // contact flags of the front (feet 0,1) and hind (feet 2,3) feet; with noise on, re-binarised and flipped with
       // probability 0.01 (:160-169) -- their noise scale is 0, so the flip can be applied here
+      float uf[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+      if (c.add_noise) {
+        constexpr int sf = 14 + A + O;
+        if (ovr) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) uf[k] = ovr[(size_t)e * num_slots + sf + k];
+        } else if constexpr ((sf & 3) == 0) {          // the four flip slots are one Philox block
+          const uint4 r = philox4x32_10(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
+                                                   (uint32_t)((uint64_t)step >> 32), (uint32_t)(sf >> 2)), c.seed_lo,
+                                        c.seed_hi ^ kStreamEnv);
+          uf[0] = u01(r.x); uf[1] = u01(r.y); uf[2] = u01(r.z); uf[3] = u01(r.w);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) uf[k] = slot_uniform(c, ovr, genv, step, sf + k, num_slots, e);
+        }
+      }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        bool flag = foot_fz[k] > 5.0f;
-        if (c.add_noise) flag = flag != (slot_uniform(c, ovr, genv, step, 14 + A + O + k, num_slots, e) < 0.01f);
+        const bool flag = (foot_fz[k] > 5.0f) != (uf[k] < 0.01f);
         obs[oq + 3 * A + k] = flag ? 1.0f : 0.0f;
+      }
+    }
+    // observation noise :811: obs += (2u - 1) * noise_scale_vec, one Philox block (4 uniforms) per 4 consecutive slots;
+    // unrolled so that columns and noise scales are compile-time indexed; blocks whose scales are all zero are skipped
+    if (c.add_noise) {
+      constexpr int s0 = 14 + A, b0 = s0 >> 2, b1 = (s0 + O - 1) >> 2;
+#pragma unroll
+      for (int blk = b0; blk <= b1; ++blk) {
+        const int i0 = 4 * blk - s0;               // obs column of this block's word 0 (may be < 0 / run past O)
+        float ns[4];
+        bool any = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k;
+          ns[k] = (i >= 0 && i < O) ? c.noise_scale_vec[i >= 0 && i < O ? i : 0] : 0.0f;
+          any |= ns[k] != 0.0f;
+        }
+        if (any) {
+          float u[4];
+          if (ovr) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int i = i0 + k;
+              u[k] = (i >= 0 && i < O) ? ovr[(size_t)e * num_slots + s0 + (i >= 0 && i < O ? i : 0)] : 0.0f;
+            }
+          } else {
+            const uint4 r = philox4x32_10_inl(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
+                                                         (uint32_t)((uint64_t)step >> 32), (uint32_t)blk), c.seed_lo,
+                                              c.seed_hi ^ kStreamEnv);
+            u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int i = i0 + k;
+            if (i >= 0 && i < O) { if (ns[k] != 0.0f) obs[i] = obs[i] + (2.0f * u[k] - 1.0f) * ns[k]; }
+          }
+        }
       }
     }
 #pragma unroll
     for (int i = 0; i < O; ++i) obs[i] = clampf(obs[i], -cl, cl);        // the clips of step() :643-646
+    __syncwarp();                                                        // every lane is done with the contact rows
     if constexpr (kPadObs) {
 #pragma unroll
       for (int i = 0; i < O; ++i) obs_s[i] = obs[i];
     } else {
       st_row<O>(obs_s, obs);
-    }
-  }
-  // ---- observation noise :811: obs += (2u - 1) * noise_scale_vec, one Philox block (4 uniforms) per iteration ----
-  if (c.add_noise) {
-    const float cl = c.clip_obs;
-    const int s0 = 14 + A, b0 = s0 >> 2, b1 = (s0 + O - 1) >> 2;
-    _Pragma("unroll 1") for (int blk = b0; blk <= b1; ++blk) {
-      const int i0 = 4 * blk - s0;                 // obs column of this block's word 0 (may be < 0 / run past O)
-      float ns[4];
-      bool any = false;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = i0 + k;
-        ns[k] = (i >= 0 && i < O) ? c.noise_scale_vec[i] : 0.0f;
-        any |= ns[k] != 0.0f;
-      }
-      if (!any) continue;
-      float u[4];
-      if (ovr) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int i = i0 + k;
-          u[k] = (i >= 0 && i < O) ? ovr[(size_t)e * num_slots + s0 + i] : 0.0f;
-        }
-      } else {
-        const uint4 r = philox4x32_10(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
-                                                 (uint32_t)((uint64_t)step >> 32), (uint32_t)blk), c.seed_lo,
-                                      c.seed_hi ^ kStreamEnv);
-        u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
-      }
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = i0 + k;
-        if (ns[k] != 0.0f) obs_s[i] = clampf(obs_s[i] + (2.0f * u[k] - 1.0f) * ns[k], -cl, cl);
-      }
     }
   }
 
@@ -928,18 +964,36 @@ __global__ void __launch_bounds__(128) finalize_step_kernel(const __grid_constan
                                                             StepScratch* __restrict__ scratch,
                                                             const int64_t* __restrict__ step_base, int64_t step_off,
                                                             int num_slots) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float rs[128 * 13];            // root rows of the block's 128 envs: coalesced in, thread-per-row use (stride 13)
+  __shared__ float lr[128 * 6];             // last_root_vel rows, coalesced out
+  const int tid = threadIdx.x;
+  const int env0 = blockIdx.x * 128;
+  const int e = env0 + tid;
   const int A = c.num_dof;
-  const bool live = e < c.num_envs;
+  const int nrows = min(128, c.num_envs - env0);
+  const bool live = tid < nrows;
   float px = 0.0f, py = 0.0f;
   const bool may_push = c.push_robots != 0;    // post_physics_step calls _push_robots itself (:700-701), not the callback
-  // ---- independent of K2: step counter (advanced by an earlier graph node), push draws ----
+  // ---- independent of K2: step counter (advanced by an earlier graph node), push draws (slots 12+A, 13+A) ----
   const int64_t step = eff_step(step_base, step_off);
   if (live && may_push) {
     const float m = c.max_push_vel;
     const float* ovr = b.rng_override;
-    px = (m - (-m)) * slot_uniform(c, ovr, c.env_offset + e, step, 12 + A, num_slots, e) + (-m);
-    py = (m - (-m)) * slot_uniform(c, ovr, c.env_offset + e, step, 13 + A, num_slots, e) + (-m);
+    float ux, uy;
+    const int s0 = 12 + A;
+    if (ovr || (s0 & 3) == 3) {
+      ux = slot_uniform(c, ovr, c.env_offset + e, step, s0, num_slots, e);
+      uy = slot_uniform(c, ovr, c.env_offset + e, step, s0 + 1, num_slots, e);
+    } else {                                   // both slots in one Philox block
+      const uint4 r = philox4x32_10(make_uint4((uint32_t)(c.env_offset + e), (uint32_t)(step & 0xffffffff),
+                                               (uint32_t)((uint64_t)step >> 32), (uint32_t)(s0 >> 2)), c.seed_lo,
+                                    c.seed_hi ^ kStreamEnv);
+      const int l = s0 & 3;
+      ux = u01(l == 0 ? r.x : l == 1 ? r.y : r.z);
+      uy = u01(l == 0 ? r.y : l == 1 ? r.z : r.w);
+    }
+    px = (m - (-m)) * ux + (-m);
+    py = (m - (-m)) * uy + (-m);
   }
   asm volatile("griddepcontrol.wait;" ::: "memory");       // K2 of this step has completed and flushed
   const int acc = (int)(step & 1);
@@ -947,30 +1001,32 @@ __global__ void __launch_bounds__(128) finalize_step_kernel(const __grid_constan
   float cnt = 0.0f;
 #pragma unroll
   for (int k = 0; k < kAccCopies; ++k) cnt += scratch->ep_acc[acc][k][URLG_MAX_TERMS];
+  const Seam seam = resolve_seam(c, b, pa);
+  for (int i = tid; i < nrows * 13; i += 128) rs[i] = seam.root[(size_t)env0 * 13 + i];
+  __syncthreads();
   if (live) {
-    const Seam seam = resolve_seam(c, b, pa);
-    float* root = b.root_states + (size_t)e * 13;
-    // in pool mode the bound root_states row is current only for envs K2 reset; the others live in the pool frame
-    const float* src = (pa.enabled && !b.reset_buf[e]) ? seam.root + (size_t)e * 13 : root;
-    float v[6];
+    float* row = rs + tid * 13;
+    // in pool mode the frame row is current except for envs K2 reset this step: their row lives in the bound tensor
+    if (pa.enabled && b.reset_buf[e]) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) v[k] = src[7 + k];
-    if (push) {
-      v[0] = px; v[1] = py;
-      root[7] = px; root[8] = py;
+      for (int k = 0; k < 13; ++k) row[k] = b.root_states[(size_t)e * 13 + k];
     }
-    float* lrv = b.last_root_vel + (size_t)e * 6;
+    if (push) { row[7] = px; row[8] = py; }
 #pragma unroll
-    for (int k = 0; k < 6; ++k) lrv[k] = v[k];
+    for (int k = 0; k < 6; ++k) lr[tid * 6 + k] = row[7 + k];
     if (cnt > 0.0f && c.send_timeouts) b.extras_time_outs[e] = b.time_out_buf[e];
   }
-  if (blockIdx.x == 0 && threadIdx.x < URLG_MAX_TERMS + 1) {
-    const int k = threadIdx.x;
+  __syncthreads();
+  for (int i = tid; i < nrows * 6; i += 128) b.last_root_vel[(size_t)env0 * 6 + i] = lr[i];
+  if (push)            // whole rows back, coalesced (the unpushed columns are rewritten with their own values)
+    for (int i = tid; i < nrows * 13; i += 128) b.root_states[(size_t)env0 * 13 + i] = rs[i];
+  if (blockIdx.x == 0 && tid < URLG_MAX_TERMS + 1) {
+    const int k = tid;
     if (cnt > 0.0f && k < c.num_sums) {
-      float s = 0.0f;
+      float sum = 0.0f;
 #pragma unroll
-      for (int q = 0; q < kAccCopies; ++q) s += scratch->ep_acc[acc][q][k];
-      b.extras_episode[k] = s / cnt / c.max_episode_length_s;
+      for (int q = 0; q < kAccCopies; ++q) sum += scratch->ep_acc[acc][q][k];
+      b.extras_episode[k] = sum / cnt / c.max_episode_length_s;
     }
     if (k == 0) {
       if (b.reset_count) *b.reset_count = scratch->reset_cnt[acc];
@@ -1188,6 +1244,14 @@ extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
     e->tt.scale[id] = d->term_scales[t];
     e->tt.row[id] = d->term_sum_row[t];
   }
+  auto sq_thr = [](float t) {       // largest s with sqrtf(s) <= t
+    float s2 = t * t;
+    while (std::sqrt(s2) > t) s2 = std::nextafter(s2, 0.0f);
+    while (std::sqrt(std::nextafter(s2, INFINITY)) <= t) s2 = std::nextafter(s2, INFINITY);
+    return s2;
+  };
+  e->tt.sq_thr_1p0 = sq_thr(1.0f);
+  e->tt.sq_thr_0p1 = sq_thr(0.1f);
   URLG_CUDA(cudaMalloc(&e->scratch, sizeof(StepScratch)));
   URLG_CUDA(cudaMemset(e->scratch, 0, sizeof(StepScratch)));
   e->smem_bytes = make_layout(e->desc).total * (int)sizeof(float);

@@ -77,6 +77,11 @@ inline void with_lo(const urlg_policy* p, urlg_gemm_desc& g) {
   if (g.out_bf16) g.out_bf16_lo = static_cast<bf16*>(g.out_bf16) + p->lo_off;
   if (g.dact_ref) g.dact_ref_lo = static_cast<const bf16*>(g.dact_ref) + p->lo_off;
 }
+// URLG_ONE_STREAM=1 keeps the critic chain on the caller's stream (debugging aid).
+inline cudaStream_t side_stream(const urlg_policy* p, cudaStream_t st) {
+  static const bool one = []() { const char* e = getenv("URLG_ONE_STREAM"); return e && e[0] == '1'; }();
+  return one ? st : p->side;
+}
 int sync_weights(urlg_policy* p, cudaStream_t st);
 int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max_ctas = 0);
 int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);

@@ -406,7 +406,7 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
     // fork: the critic's LSTM step + head on the side stream, the actor's on the caller's.  Each chain is a handful of
     // small launches (staging, gate GEMM, cell, 2 head GEMMs), so two concurrent chains beat pairing the heads after
     // a join (measured: 2.34 vs 2.52 ms per 24-step rollout); each GEMM is capped to half the SMs so both fit.
-    cudaStream_t sc = p->side;
+    cudaStream_t sc = side_stream(p, st);
     URLG_CUDA(cudaEventRecord(p->ev_fork, st));
     URLG_CUDA(cudaStreamWaitEvent(sc, p->ev_fork, 0));
     const int cap = N <= 8192 ? kNumSMs / 2 : 0;

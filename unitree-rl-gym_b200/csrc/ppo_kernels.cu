@@ -409,10 +409,10 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     // the two memories are independent chains of latency-bound kernels (staging, projection GEMM, one persistent
     // recurrence of ~100 us on a fraction of the SMs): the critic's runs on the side stream beside the actor's
     URLG_CUDA(cudaEventRecord(p->ev_fork, st));
-    URLG_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    URLG_CUDA(cudaStreamWaitEvent(side_stream(p, st), p->ev_fork, 0));
     const int rc_a = lstm_update_forward(p, 0, s, env_begin, env_count, st);
-    const int rc_c = lstm_update_forward(p, 1, s, env_begin, env_count, p->side);
-    URLG_CUDA(cudaEventRecord(p->ev_join, p->side));       // join always: a capture must not end with a forked stream
+    const int rc_c = lstm_update_forward(p, 1, s, env_begin, env_count, side_stream(p, st));
+    URLG_CUDA(cudaEventRecord(p->ev_join, side_stream(p, st)));       // join always: a capture must not end with a forked stream
     URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
     if (rc_a) return rc_a;
     if (rc_c) return rc_c;
@@ -429,10 +429,10 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
                                  d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
   if (d.recurrent) {
     URLG_CUDA(cudaEventRecord(p->ev_fork, st));
-    URLG_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    URLG_CUDA(cudaStreamWaitEvent(side_stream(p, st), p->ev_fork, 0));
     const int rc_a = lstm_update_backward(p, 0, s, env_begin, env_count, st);
-    const int rc_c = lstm_update_backward(p, 1, s, env_begin, env_count, p->side);
-    URLG_CUDA(cudaEventRecord(p->ev_join, p->side));
+    const int rc_c = lstm_update_backward(p, 1, s, env_begin, env_count, side_stream(p, st));
+    URLG_CUDA(cudaEventRecord(p->ev_join, side_stream(p, st)));
     URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
     if (rc_a) return rc_a;
     if (rc_c) return rc_c;
