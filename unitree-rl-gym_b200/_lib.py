@@ -9,7 +9,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "liburlg_b200.so")
+LIB_PATH = os.environ.get("URLG_LIB_PATH") or os.path.join(CSRC, "liburlg_b200.so")     # override: A/B builds
 
 MAX_DOF, MAX_IDX, MAX_TERMS, MAX_OBS, MAX_FEET = 16, 16, 32, 128, 4
 ABI_VERSION = 2

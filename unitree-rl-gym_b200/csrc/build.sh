@@ -6,8 +6,8 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 ARCH="-gencode arch=compute_100a,code=sm_100a"
 COMMON="-O3 -std=c++17 -lineinfo -Xcompiler -fPIC $ARCH"
 mkdir -p build
-# env kernels: no FMA contraction (expressions evaluate as written, like the reference's eager ops)
-$NVCC $COMMON -fmad=false -c env_kernels.cu -o build/env_kernels.o "$@"
+# env kernels: mask-deciding expressions are written with never-contracted __f*_rn intrinsics (see env_kernels.cu)
+$NVCC $COMMON -c env_kernels.cu -o build/env_kernels.o "$@"
 for f in tc_gemm storage_kernels policy_kernels ppo_kernels lstm_kernels; do
   if [ -f $f.cu ]; then $NVCC $COMMON -c $f.cu -o build/$f.o "$@"; fi
 done

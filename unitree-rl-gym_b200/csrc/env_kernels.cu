@@ -12,7 +12,10 @@
 // stride makes thread-per-row access bank-conflict-free; observations are assembled in registers, written to a shared
 // row image (noise is added there by a rolled loop over Philox blocks so the instruction footprint stays small) and
 // leave as one bulk-TMA store.  The rare reset path (2-3 % of envs) runs warp-cooperatively: one lane per random draw.
-// Compiled with -fmad=false: expressions evaluate as written (mask-deciding comparisons are bit-exact).
+// Floating point: every expression that DECIDES a mask (termination norms and angles, contact / stumble / command-norm
+// thresholds, the gait-phase comparison, the heading wrap) is written with __fmul_rn / __fadd_rn / __fsub_rn, which are
+// never contracted, so it evaluates exactly like the reference's separate eager ops and masks stay bit-exact; the
+// value-only arithmetic (reward sums, observation scaling) may contract to FMA (1e-7 relative, tolerance 1e-5).
 #include "common.cuh"
 #include "philox.cuh"
 #include <new>
@@ -43,6 +46,11 @@ struct TermTable {
   // sqrtf(s) > t  <=>  s > sq_thr(t): the largest float whose correctly-rounded root is still <= t (found on the host
   // at create; sqrt is monotonic), so mask-deciding norm comparisons need no square root and stay bit-exact
   float sq_thr_1p0, sq_thr_0p1;
+  // Philox round keys of the env stream (key + r * Weyl constant, r = 0..9): constant-bank operands of the inlined
+  // rounds instead of two integer adds per round; and which Philox blocks of the observation-noise slot range carry
+  // a non-zero noise scale (bit = block - first block)
+  uint32_t pk0[10], pk1[10];
+  uint32_t noise_blocks;
 };
 
 struct PoolArgs {
@@ -114,6 +122,13 @@ __device__ __forceinline__ bool divisible(int64_t len, int period) {
   return (len % period) == 0;
 }
 
+#define MUL __fmul_rn
+#define ADD __fadd_rn
+#define SUB __fsub_rn
+// x*x + y*y + z*z and x*x + y*y evaluated left to right without contraction (mask-deciding norms)
+__device__ __forceinline__ float sq3(float x, float y, float z) { return ADD(ADD(MUL(x, x), MUL(y, y)), MUL(z, z)); }
+__device__ __forceinline__ float sq2(float x, float y) { return ADD(MUL(x, x), MUL(y, y)); }
+
 // torch.remainder(a, b) for b > 0 (ATen: fmod, then += b if the sign differs).  fmod is exact; for |a| < 2b it is a or
 // a -+ b (exact by Sterbenz), for 0 <= a/b < 2^22 it is fma(-trunc(a/b), b, a) with a one-step correction (the exact
 // remainder is representable, so the fma is exact); anything else takes libm's fmodf.
@@ -122,35 +137,35 @@ static __device__ __noinline__ float py_remainder(float a, float b) {
   const float aa = fabsf(a);
   if (aa < b) {
     m = a;
-  } else if (aa < 2.0f * b) {
-    m = a < 0.0f ? a + b : a - b;
+  } else if (aa < MUL(2.0f, b)) {
+    m = a < 0.0f ? ADD(a, b) : SUB(a, b);
   } else if (a > 0.0f && a < b * 4194304.0f) {
     const float q = truncf(a / b);
     m = fmaf(-q, b, a);
-    if (m < 0.0f) m += b;
-    else if (m >= b) m -= b;
+    if (m < 0.0f) m = ADD(m, b);
+    else if (m >= b) m = SUB(m, b);
   } else {
     m = fmodf(a, b);
   }
-  if (m != 0.0f && m < 0.0f) m += b;
+  if (m != 0.0f && m < 0.0f) m = ADD(m, b);
   return m;
 }
 
 // One out-of-line copy of atan2f: K2 is latency-bound at 4096 envs and a cold instruction fetch costs more than a call.
 static __device__ __noinline__ float atan2_ni(float y, float x) { return atan2f(y, x); }
-__device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
-__device__ __forceinline__ float sq3(float x, float y, float z) { return x * x + y * y + z * z; }
+__device__ __forceinline__ float norm3(float x, float y, float z) { return sqrtf(sq3(x, y, z)); }
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
-// [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw
+// [UPSTREAM isaacgym.torch_utils.quat_rotate_inverse], q = xyzw: v*(2w^2-1) - 2w(u x v) + 2u(u.v), uncontracted (the
+// handstand termination compares projected gravity with a band; the velocities share the code)
 __device__ __forceinline__ void rot_inv(float qx, float qy, float qz, float qw, float vx, float vy, float vz,
                                         float& ox, float& oy, float& oz) {
-  const float s = 2.0f * (qw * qw) - 1.0f;
-  const float cx = qy * vz - qz * vy, cy = qz * vx - qx * vz, cz = qx * vy - qy * vx;
-  const float d = qx * vx + qy * vy + qz * vz;
-  ox = vx * s - cx * qw * 2.0f + qx * d * 2.0f;
-  oy = vy * s - cy * qw * 2.0f + qy * d * 2.0f;
-  oz = vz * s - cz * qw * 2.0f + qz * d * 2.0f;
+  const float s = SUB(MUL(2.0f, MUL(qw, qw)), 1.0f);
+  const float cx = SUB(MUL(qy, vz), MUL(qz, vy)), cy = SUB(MUL(qz, vx), MUL(qx, vz)), cz = SUB(MUL(qx, vy), MUL(qy, vx));
+  const float d = ADD(ADD(MUL(qx, vx), MUL(qy, vy)), MUL(qz, vz));
+  ox = ADD(SUB(MUL(vx, s), MUL(MUL(cx, qw), 2.0f)), MUL(MUL(qx, d), 2.0f));
+  oy = ADD(SUB(MUL(vy, s), MUL(MUL(cy, qw), 2.0f)), MUL(MUL(qy, d), 2.0f));
+  oz = ADD(SUB(MUL(vz, s), MUL(MUL(cz, qw), 2.0f)), MUL(MUL(qz, d), 2.0f));
 }
 
 // Uniform of (global env, step, slot): Philox word slot%4 of block slot/4, or the injected table.
@@ -309,13 +324,13 @@ struct ObsDims {
 
 // command resampling (E6, legged_robot.py:519-538) from three uniforms
 __device__ __forceinline__ void resample_commands(const urlg_env_desc& c, float ux, float uy, float uh, float (&cmd)[4]) {
-  cmd[0] = (c.cmd_x[1] - c.cmd_x[0]) * ux + c.cmd_x[0];
-  cmd[1] = (c.cmd_y[1] - c.cmd_y[0]) * uy + c.cmd_y[0];
+  cmd[0] = ADD(MUL(SUB(c.cmd_x[1], c.cmd_x[0]), ux), c.cmd_x[0]);
+  cmd[1] = ADD(MUL(SUB(c.cmd_y[1], c.cmd_y[0]), uy), c.cmd_y[0]);
   if (c.heading_command)
-    cmd[3] = (c.cmd_heading[1] - c.cmd_heading[0]) * uh + c.cmd_heading[0];
+    cmd[3] = ADD(MUL(SUB(c.cmd_heading[1], c.cmd_heading[0]), uh), c.cmd_heading[0]);
   else
-    cmd[2] = (c.cmd_yaw[1] - c.cmd_yaw[0]) * uh + c.cmd_yaw[0];
-  const float keep = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]) > 0.2f ? 1.0f : 0.0f;
+    cmd[2] = ADD(MUL(SUB(c.cmd_yaw[1], c.cmd_yaw[0]), uh), c.cmd_yaw[0]);
+  const float keep = sqrtf(sq2(cmd[0], cmd[1])) > 0.2f ? 1.0f : 0.0f;
   cmd[0] *= keep;
   cmd[1] *= keep;
 }
@@ -324,8 +339,13 @@ __device__ __forceinline__ void resample_commands(const urlg_env_desc& c, float 
 // RNG slot map per (env, step) (shared with oracle/refharness/run_reference.py):
 //   0..2 callback resample | 3..3+A-1 _reset_dofs | 3+A..8+A root velocities | 9+A..11+A reset resample |
 //   12+A,13+A push | 14+A..14+A+O-1 observation noise | handstand: 14+A+O..+3 contact-flag flips
-template <int A, int FAM>
-__global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
+#ifndef URLG_K2_MIN_BLOCKS
+#define URLG_K2_MIN_BLOCKS 16
+#endif
+// MASK: the active reward terms at compile time (0 = read tt.mask at run time).  The shipped task configs get their own
+// instantiation: the 34 per-term mask tests disappear and the reward stage becomes one schedulable block.
+template <int A, int FAM, unsigned long long MASK>
+__global__ void __launch_bounds__(32, URLG_K2_MIN_BLOCKS) post_physics_kernel(const __grid_constant__ urlg_env_desc c,
                                                           const __grid_constant__ urlg_env_buffers b,
                                                           const __grid_constant__ TermTable tt,
                                                           const __grid_constant__ PoolArgs pa,
@@ -348,7 +368,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
   const int acc = (int)(step & 1);
   const bool bulk = nrows == 32;
   const Seam seam = resolve_seam(c, b, pa);
-  const uint64_t mask = tt.mask;
+  const uint64_t mask = MASK ? MASK : tt.mask;
 #define HAS(ID) ((mask >> (ID)) & 1ull)
 
   // ---- stage the odd-width rows (root 13, contacts 3B floats per env) ----
@@ -385,8 +405,12 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
   uint8_t lastc[URLG_MAX_FEET];
 #pragma unroll
   for (int f = 0; f < URLG_MAX_FEET; ++f) {
-    air[f] = f < F ? b.feet_air_time[(size_t)e * F + f] : 0.0f;
-    lastc[f] = f < F ? b.last_contacts[(size_t)e * F + f] : (uint8_t)0;
+    air[f] = 0.0f;
+    lastc[f] = 0;
+    if (f < F) {
+      air[f] = b.feet_air_time[(size_t)e * F + f];
+      lastc[f] = b.last_contacts[(size_t)e * F + f];
+    }
   }
   // feet rows of rigid_body_states (h1_env.py:51-53; go2_handstand_env.py:73-76): only the columns the terms read
   float foot_z[2] = {0.0f, 0.0f}, foot_v[2][3] = {{0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}}, foot_xy[2][2] = {{0.0f, 0.0f}, {0.0f, 0.0f}};
@@ -412,8 +436,12 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
   // episode_sums rows of this env (read-modify-write at the end of the reward stage): in flight before the wait
   constexpr int kSumsReg = 16;
   float es[kSumsReg];
+  float* const esp = b.episode_sums + e;         // row k at esp[k * N]; num_sums * N < 2^31 (checked at create)
 #pragma unroll
-  for (int k = 0; k < kSumsReg; ++k) es[k] = k < c.num_sums ? b.episode_sums[(size_t)k * N + e] : 0.0f;
+  for (int k = 0; k < kSumsReg; ++k) {
+    es[k] = 0.0f;
+    if (k < c.num_sums) es[k] = esp[(uint32_t)k * (uint32_t)N];
+  }
   const float* ovr = b.rng_override;
   const int64_t genv = c.env_offset + e;
 
@@ -436,10 +464,11 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
 
   // ---- E4 frame transforms :685-690, isaacgym_utils.py:11-30 ----
   const float qx = root[3], qy = root[4], qz = root[5], qw = root[6];
-  const float roll = atan2_ni(2.0f * (qw * qx + qy * qz), qw * qw - qx * qx - qy * qy + qz * qz);
-  const float sinp = 2.0f * (qw * qy - qz * qx);
+  const float ww = MUL(qw, qw), xx = MUL(qx, qx), yy = MUL(qy, qy), zz = MUL(qz, qz);
+  const float roll = atan2_ni(MUL(2.0f, ADD(MUL(qw, qx), MUL(qy, qz))), ADD(SUB(SUB(ww, xx), yy), zz));
+  const float sinp = MUL(2.0f, SUB(MUL(qw, qy), MUL(qz, qx)));
   const float pitch = fabsf(sinp) >= 1.0f ? copysignf(kHalfPi, sinp) : asinf(sinp);
-  const float yaw = atan2_ni(2.0f * (qw * qz + qx * qy), qw * qw + qx * qx - qy * qy - qz * qz);
+  const float yaw = atan2_ni(MUL(2.0f, ADD(MUL(qw, qz), MUL(qx, qy))), SUB(SUB(ADD(ww, xx), yy), zz));
   float lvx, lvy, lvz, avx, avy, avz, gx, gy, gz;
   rot_inv(qx, qy, qz, qw, root[7], root[8], root[9], lvx, lvy, lvz);
   rot_inv(qx, qy, qz, qw, root[10], root[11], root[12], avx, avy, avz);
@@ -449,9 +478,9 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
   // ---- E5 callback: gait phase (h1_env.py:58-63), resample (:511-512), heading (:513-516) ----
   float phase = 0.0f, leg_phase[2] = {0.0f, 0.0f};
   if constexpr (FAM == URLG_FAMILY_H1) {
-    phase = py_remainder(flen * c.dt, 0.8f) / 0.8f;
+    phase = py_remainder(MUL(flen, c.dt), 0.8f) / 0.8f;
     leg_phase[0] = phase;
-    leg_phase[1] = py_remainder(phase + 0.5f, 1.0f);
+    leg_phase[1] = py_remainder(ADD(phase, 0.5f), 1.0f);
   }
   if (c.callback_mode == URLG_CALLBACK_BASE) {
     if (divisible(len, c.resample_steps)) {
@@ -462,12 +491,12 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
     }
     if (c.heading_command) {
       // forward = quat_apply(q, (1,0,0)): t = 2 (u x v) = (0, 2 qz, -2 qy)
-      const float ty = qz * 2.0f, tz = -qy * 2.0f;
-      const float fx = 1.0f + qw * 0.0f + (qy * tz - qz * ty);
-      const float fy = 0.0f + qw * ty + (qz * 0.0f - qx * tz);
+      const float ty = MUL(qz, 2.0f), tz = MUL(-qy, 2.0f);
+      const float fx = ADD(ADD(1.0f, MUL(qw, 0.0f)), SUB(MUL(qy, tz), MUL(qz, ty)));
+      const float fy = ADD(ADD(0.0f, MUL(qw, ty)), SUB(MUL(qz, 0.0f), MUL(qx, tz)));
       const float heading = atan2_ni(fy, fx);
-      float a = py_remainder(cmd[3] - heading, kTwoPi);
-      a -= kTwoPi * (a > kPi ? 1.0f : 0.0f);
+      float a = py_remainder(SUB(cmd[3], heading), kTwoPi);
+      a = SUB(a, MUL(kTwoPi, a > kPi ? 1.0f : 0.0f));
       cmd[2] = fminf(fmaxf(0.5f * a, -1.0f), 1.0f);
     }
   }
@@ -495,7 +524,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
       const float x = f3[0], y = f3[1], z = f3[2];
       foot_fz[f] = z;
       foot_fn[f] = norm3(x, y, z);
-      foot_fxy[f] = sqrtf(x * x + y * y);
+      foot_fxy[f] = sqrtf(sq2(x, y));
     }
   }
 
@@ -503,7 +532,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
   // tensor / python-scalar: ATen's CUDA kernel multiplies by the reciprocal (BinaryDivTrueKernel.cu, CPU-scalar divisor),
   // i.e. what the reference computes on its own device; the CPU fixtures (true division) agree to 1.2e-7 relative
   const float inv_dt = 1.0f / c.dt, inv_sigma = 1.0f / c.tracking_sigma;
-  const float cmd_xy = sqrtf(cmd[0] * cmd[0] + cmd[1] * cmd[1]);
+  const float cmd_xy = sqrtf(sq2(cmd[0], cmd[1]));
   float rew = 0.0f;
 #define TERM_END(ID) r *= tt.scale[ID]; rew += r; term[tt.row[ID] * 32] = r; }
 #define TERM_BEGIN(ID) if (HAS(ID)) { float r = 0.0f;
@@ -675,7 +704,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
     bool any = false;
 #pragma unroll
     for (int f = 0; f < URLG_MAX_FEET; ++f)
-      if (f < F) any |= foot_fxy[f] > 5.0f * fabsf(foot_fz[f]);
+      if (f < F) any |= foot_fxy[f] > MUL(5.0f, fabsf(foot_fz[f]));
     r = any ? 1.0f : 0.0f;
   TERM_END(URLG_T_STUMBLE)
   TERM_BEGIN(URLG_T_TORQUE_LIMITS)
@@ -709,7 +738,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
       if (k < c.num_sums) {
         float v = es[k] + term[k * 32];
         if (pub) { atomicAdd(accp + k, v); v = 0.0f; }
-        if (live) b.episode_sums[(size_t)k * N + e] = v;
+        if (live) esp[(uint32_t)k * (uint32_t)N] = v;
       }
     }
     _Pragma("unroll 1") for (int k = kSumsReg; k < c.num_sums; ++k) {
@@ -843,15 +872,7 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
 #pragma unroll
       for (int blk = b0; blk <= b1; ++blk) {
         const int i0 = 4 * blk - s0;               // obs column of this block's word 0 (may be < 0 / run past O)
-        float ns[4];
-        bool any = false;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int i = i0 + k;
-          ns[k] = (i >= 0 && i < O) ? c.noise_scale_vec[i >= 0 && i < O ? i : 0] : 0.0f;
-          any |= ns[k] != 0.0f;
-        }
-        if (any) {
+        if ((tt.noise_blocks >> (blk - b0)) & 1u) {
           float u[4];
           if (ovr) {
 #pragma unroll
@@ -860,15 +881,14 @@ __global__ void __launch_bounds__(32, 16) post_physics_kernel(const __grid_const
               u[k] = (i >= 0 && i < O) ? ovr[(size_t)e * num_slots + s0 + (i >= 0 && i < O ? i : 0)] : 0.0f;
             }
           } else {
-            const uint4 r = philox4x32_10_inl(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
-                                                         (uint32_t)((uint64_t)step >> 32), (uint32_t)blk), c.seed_lo,
-                                              c.seed_hi ^ kStreamEnv);
+            const uint4 r = philox4x32_10_keys(make_uint4((uint32_t)genv, (uint32_t)(step & 0xffffffff),
+                                                          (uint32_t)((uint64_t)step >> 32), (uint32_t)blk), tt.pk0, tt.pk1);
             u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const int i = i0 + k;
-            if (i >= 0 && i < O) { if (ns[k] != 0.0f) obs[i] = obs[i] + (2.0f * u[k] - 1.0f) * ns[k]; }
+            const int i = i0 + k;      // a zero scale adds (2u - 1) * 0 = +-0: the value is unchanged
+            if (i >= 0 && i < O) obs[i] = obs[i] + (2.0f * u[k] - 1.0f) * c.noise_scale_vec[i >= 0 && i < O ? i : 0];
           }
         }
       }
@@ -1161,14 +1181,32 @@ static int grid_for(int64_t work, int block, int max_waves = 8) {
 
 using K2Fn = void (*)(const urlg_env_desc, const urlg_env_buffers, const TermTable, const PoolArgs, StepScratch*,
                       const int64_t*, int64_t, int, int);
-static K2Fn k2_for(int num_dof, int family) {
+#define T_(x) (1ull << URLG_T_##x)
+// active terms of the five registered task configs (go2_handstand_config.py:62-133)
+constexpr unsigned long long kMaskGo2 = T_(ACTION_RATE) | T_(ANG_VEL_XY) | T_(COLLISION) | T_(DOF_ACC) | T_(DOF_POS_LIMITS) |
+                                        T_(FEET_AIR_TIME) | T_(LIN_VEL_Z) | T_(TORQUES) | T_(TRACKING_ANG_VEL) | T_(TRACKING_LIN_VEL);
+constexpr unsigned long long kMaskHumanoid = T_(ACTION_RATE) | T_(ALIVE) | T_(ANG_VEL_XY) | T_(BASE_HEIGHT) | T_(CONTACT) |
+                                             T_(CONTACT_NO_VEL) | T_(DOF_ACC) | T_(DOF_POS_LIMITS) | T_(FEET_SWING_HEIGHT) |
+                                             T_(HIP_POS) | T_(LIN_VEL_Z) | T_(ORIENTATION) | T_(TRACKING_ANG_VEL) | T_(TRACKING_LIN_VEL);
+constexpr unsigned long long kMaskH1 = kMaskHumanoid | T_(COLLISION);
+constexpr unsigned long long kMaskG1 = kMaskHumanoid | T_(DOF_VEL) | T_(TORQUES);          // g1 and h1_2
+constexpr unsigned long long kMaskHandstand = T_(ACTION_RATE) | T_(ANG_VEL_XY) | T_(BASE_HEIGHT_HS) | T_(COLLISION) |
+    T_(DOF_POS_LIMITS) | T_(DOF_VEL) | T_(FRONT_FEET_CONTACT) | T_(FRONT_FEET_TOGETHER) | T_(FRONT_HIP_NEUTRAL) |
+    T_(HIND_FEET_NO_CONTACT) | T_(LIN_VEL_XY) | T_(LIN_VEL_Z) | T_(ORIENTATION_HS) | T_(POSE) | T_(STABILITY) | T_(STAY_STILL) | T_(TORQUES);
+#undef T_
+static K2Fn k2_for(int num_dof, int family, unsigned long long mask = 0) {
   if (num_dof == 12) {
-    if (family == URLG_FAMILY_BASE) return post_physics_kernel<12, URLG_FAMILY_BASE>;
-    if (family == URLG_FAMILY_H1) return post_physics_kernel<12, URLG_FAMILY_H1>;
-    if (family == URLG_FAMILY_HANDSTAND) return post_physics_kernel<12, URLG_FAMILY_HANDSTAND>;
+    if (family == URLG_FAMILY_BASE)
+      return mask == kMaskGo2 ? post_physics_kernel<12, URLG_FAMILY_BASE, kMaskGo2> : post_physics_kernel<12, URLG_FAMILY_BASE, 0>;
+    if (family == URLG_FAMILY_H1)
+      return mask == kMaskG1 ? post_physics_kernel<12, URLG_FAMILY_H1, kMaskG1> : post_physics_kernel<12, URLG_FAMILY_H1, 0>;
+    if (family == URLG_FAMILY_HANDSTAND)
+      return mask == kMaskHandstand ? post_physics_kernel<12, URLG_FAMILY_HANDSTAND, kMaskHandstand>
+                                    : post_physics_kernel<12, URLG_FAMILY_HANDSTAND, 0>;
   } else if (num_dof == 10) {
-    if (family == URLG_FAMILY_BASE) return post_physics_kernel<10, URLG_FAMILY_BASE>;
-    if (family == URLG_FAMILY_H1) return post_physics_kernel<10, URLG_FAMILY_H1>;
+    if (family == URLG_FAMILY_BASE) return post_physics_kernel<10, URLG_FAMILY_BASE, 0>;
+    if (family == URLG_FAMILY_H1)
+      return mask == kMaskH1 ? post_physics_kernel<10, URLG_FAMILY_H1, kMaskH1> : post_physics_kernel<10, URLG_FAMILY_H1, 0>;
   }
   return nullptr;
 }
@@ -1210,6 +1248,8 @@ extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
     return fail(URLG_EINVAL, "Expected at least 4 feet for Go2.");                    // go2_handstand_env.py:19
   if (d->family == URLG_FAMILY_H1 && d->num_feet > 2)
     return fail(URLG_EINVAL, "urlg_env_create: the H1-family terms read two feet (h1_env.py:98-123), got %d", d->num_feet);
+  if ((int64_t)d->num_envs * URLG_MAX_TERMS >= 0x7fffffffll)
+    return fail(URLG_EINVAL, "urlg_env_create: num_envs too large for 32-bit episode-sum offsets");
   if (d->resample_steps <= 0 || d->push_interval <= 0)
     return fail(URLG_EINVAL, "urlg_env_create: resample_steps / push_interval must be positive");
   urlg_env* e = new (std::nothrow) urlg_env();
@@ -1250,12 +1290,22 @@ extern "C" int urlg_env_create(const urlg_env_desc* d, urlg_env** out) {
     while (std::sqrt(std::nextafter(s2, INFINITY)) <= t) s2 = std::nextafter(s2, INFINITY);
     return s2;
   };
+  for (int r = 0; r < 10; ++r) {
+    e->tt.pk0[r] = d->seed_lo + (uint32_t)r * kPhiloxW0;
+    e->tt.pk1[r] = (d->seed_hi ^ kStreamEnv) + (uint32_t)r * kPhiloxW1;
+  }
+  {
+    const int s0 = 14 + d->num_dof, b0 = s0 >> 2;
+    e->tt.noise_blocks = 0;
+    for (int i = 0; i < d->num_obs; ++i)
+      if (d->noise_scale_vec[i] != 0.0f) e->tt.noise_blocks |= 1u << (((s0 + i) >> 2) - b0);
+  }
   e->tt.sq_thr_1p0 = sq_thr(1.0f);
   e->tt.sq_thr_0p1 = sq_thr(0.1f);
   URLG_CUDA(cudaMalloc(&e->scratch, sizeof(StepScratch)));
   URLG_CUDA(cudaMemset(e->scratch, 0, sizeof(StepScratch)));
   e->smem_bytes = make_layout(e->desc).total * (int)sizeof(float);
-  K2Fn fn = k2_for(d->num_dof, d->family);
+  K2Fn fn = k2_for(d->num_dof, d->family, e->tt.mask);
   URLG_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes > 48 * 1024 ? e->smem_bytes : 48 * 1024));
   URLG_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   *out = e;
@@ -1353,7 +1403,7 @@ static int post_launch(urlg_env* env, const int64_t* step_base, int64_t step_off
   cudaStream_t st = (cudaStream_t)stream;
   PoolArgs pa = env->pool;
   pa.calls_off = calls_off;
-  K2Fn fn = k2_for(env->desc.num_dof, env->desc.family);
+  K2Fn fn = k2_for(env->desc.num_dof, env->desc.family, env->tt.mask);
   fn<<<(N + 31) / 32, 32, env->smem_bytes, st>>>(env->desc, env->bufs, env->tt, pa, env->scratch, step_base, step_offset,
                                                  obs_slot, slots);
   URLG_LAUNCH_CHECK();

@@ -36,6 +36,17 @@ __device__ __forceinline__ uint4 philox4x32_10_inl(uint4 c, uint32_t k0, uint32_
   return c;
 }
 
+// inlined form with the ten round keys precomputed (kernel-parameter / constant-bank operands)
+__device__ __forceinline__ uint4 philox4x32_10_keys(uint4 c, const uint32_t (&k0)[10], const uint32_t (&k1)[10]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(kPhiloxM0, c.x), lo0 = kPhiloxM0 * c.x;
+    uint32_t hi1 = __umulhi(kPhiloxM1, c.z), lo1 = kPhiloxM1 * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k0[r], lo1, hi0 ^ c.w ^ k1[r], lo0);
+  }
+  return c;
+}
+
 __device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 
 // Per-(env, step) slot reader with a one-block cache: slots are consumed mostly in order.
