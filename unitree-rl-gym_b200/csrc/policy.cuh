@@ -41,6 +41,8 @@ struct LstmWs {                      // one Memory (nn.LSTM, 1 layer)
 
 }  // namespace urlg
 
+namespace urlg { namespace fused { struct FusedArgs; } }
+
 struct urlg_policy {
   urlg_policy_desc desc;
   float *params, *grads, *m, *v, *stats;
@@ -55,6 +57,9 @@ struct urlg_policy {
   // stream forked from / joined to the caller's stream by events (capturable: the side stream joins the graph)
   cudaStream_t side;
   cudaEvent_t ev_fork, ev_join;
+  // fused multi-layer forward (mlp_fused.cuh): argument template with the weight / saved-activation tensor maps and the
+  // per-network schedules, built once at create; NULL when the layer widths are outside its limits or URLG_FUSED=0
+  urlg::fused::FusedArgs* fz;
 };
 
 namespace urlg {
@@ -87,5 +92,16 @@ int mlp_forward(urlg_policy* p, NetWs& n, int64_t rows, cudaStream_t st, int max
 int mlp_backward(urlg_policy* p, NetWs& n, int64_t rows, bf16* dx_out, cudaStream_t st);
 int mlp_forward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, cudaStream_t st);
 int mlp_backward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, bf16* dxa, bf16* dxc, cudaStream_t st);
+// mlp_fused.cu
+int fused_build(urlg_policy* p);
+void fused_free(urlg_policy* p);
+// rollout (PPO.act of a feed-forward policy): obs / critic obs rows -> actions, log-prob, values, transition slabs of step t
+int fused_act(urlg_policy* p, const float* obs, const float* cobs, const urlg_storage* s, int t, const float* noise,
+              float* actions_out, const int64_t* step_base, int64_t step_off, cudaStream_t st);
+// update forward: rows gathered by `indices` from the storage's observation tensors; saves x and the hidden activations
+// into the policy workspace (what the backward GEMMs read), outputs into net.out
+int fused_update_forward(urlg_policy* p, const urlg_storage* s, const int64_t* indices, int64_t rows, cudaStream_t st);
+// plain forward of one network on fp32 rows (act_inference / evaluate)
+int fused_forward_one(urlg_policy* p, int which, const float* x, int64_t rows, float* out, cudaStream_t st);
 int stage_obs(const float* src, int64_t rows, int cols, float* store, bf16* dst, int64_t lo_off, int kpad, int ld, cudaStream_t st);
 }

@@ -339,19 +339,21 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     delete p;
     return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
   }
-  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr;
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     urlg_policy_destroy(p);
     return fail(URLG_ECUDA, "urlg_policy_create: side stream / events: %s", cudaGetErrorString(cudaGetLastError()));
   }
+  if (int rc2 = fused_build(p)) { urlg_policy_destroy(p); return rc2; }
   *out = p;
   return URLG_OK;
 }
 
 extern "C" void urlg_policy_destroy(urlg_policy* p) {
   if (!p) return;
+  fused_free(p);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);
@@ -389,6 +391,11 @@ extern "C" int urlg_policy_act(urlg_policy* p, const float* obs, const float* cr
     if (!hidden) return fail(URLG_EINVAL, "urlg_policy_act: recurrent policy needs hidden state");
     if (!s->hid_a_h || !s->hid_a_c || !s->hid_c_h || !s->hid_c_c)
       return fail(URLG_EINVAL, "urlg_policy_act: recurrent storage lacks saved hidden states");
+  }
+  if (!d.recurrent && p->fz) {
+    // ONE launch: observation staging + slab copy, every layer of both networks, sampling / log-prob / transition store
+    if (d.num_actions > 16) return fail(URLG_EINVAL, "urlg_policy_act: more than 16 actions");
+    return fused_act(p, obs, cobs, s, t, noise, actions_out, step_base, step_offset, st);
   }
   if (!d.recurrent) {
     // both observation stagings, then one paired GEMM launch per layer on the caller's stream
@@ -438,6 +445,7 @@ extern "C" int urlg_policy_forward(urlg_policy* p, int which, const float* x, in
   const urlg_policy_desc& d = p->desc;
   NetWs& n = p->net[which];
   const int in = which == 0 ? d.num_actor_obs : d.num_critic_obs;
+  if (!d.recurrent && p->fz) return fused_forward_one(p, which, x, rows, out, st);
   if (!d.recurrent) {
     if (int rc = stage_obs(x, rows, in, nullptr, n.x, p->lo_off, n.kpad[0], n.kpad[0], st)) return rc;
   } else {

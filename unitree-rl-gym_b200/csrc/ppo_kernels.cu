@@ -393,7 +393,11 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   URLG_CUDA(cudaMemsetAsync(p->grads, 0, ((size_t)d.num_params + (sums_behind_grads ? 4 : 0)) * sizeof(float), st));
   if (!sums_behind_grads) zero_minibatch_stats_kernel<<<1, 32, 0, st>>>(p->stats);
   NetWs &na = p->net[0], &nc = p->net[1];
-  if (!d.recurrent) {
+  const bool fused_fwd = !d.recurrent && p->fz != nullptr;
+  if (fused_fwd) {
+    // gather + every forward layer of both networks in one launch; x and the hidden activations are saved for the backward
+    if (int rc = fused_update_forward(p, s, indices, rows, st)) return rc;
+  } else if (!d.recurrent) {
     const float* cobs = s->privileged_observations ? s->privileged_observations : s->observations;
     int blocks = (int)((rows * na.kpad[0] + 255) / 256);
     const bool shared = cobs == s->observations && na.kpad[0] == nc.kpad[0];   // no privileged obs: one gather feeds both nets
@@ -417,7 +421,8 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     if (rc_a) return rc_a;
     if (rc_c) return rc_c;
   }
-  if (int rc = mlp_forward_pair(p, na, nc, rows, st)) return rc;
+  if (!fused_fwd)
+    if (int rc = mlp_forward_pair(p, na, nc, rows, st)) return rc;
   if (d.num_actions < 2 || d.num_actions > kMaxA) return fail(URLG_EINVAL, "urlg_ppo_minibatch_grads: 2..%d actions", kMaxA);
   const int head_smem = (2 * kHeadRows * d.num_actions + 6 * kHeadRows + d.num_actions) * (int)sizeof(float);
   ppo_head_kernel<<<(int)((rows + kHeadRows - 1) / kHeadRows), kHeadRows * d.num_actions, head_smem, st>>>(
