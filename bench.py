@@ -78,11 +78,14 @@ def measured_peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
-def ncu_traffic_per_launch(path=os.path.join(REPO, "profiles", "r1_gemm_minibatch_ncu.csv")):
+def ncu_traffic_per_launch(path=None):
     """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch, averaged over the 22 launches of one update minibatch,
     from the committed `ncu --set full` capture (tools/ncu_summary.py output); None when the file is absent."""
     try:
         import csv
+        if path is None:
+            cands = [os.path.join(REPO, "profiles", f) for f in ("r2_tensor_minibatch_ncu.csv", "r1_gemm_minibatch_ncu.csv")]
+            path = next(c for c in cands if os.path.exists(c))
         rows = {r[0]: r for r in csv.reader(open(path))}
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         tot, n = 0.0, 0
@@ -130,30 +133,39 @@ def make_env(task, n, frames, device, env_offset=0, pool_seam=False):
 def train_cfg_dict(task, cuda_graph=False):
     from unitree_rl_gym_b200.legged_gym.envs import robot_configs as rc
     from unitree_rl_gym_b200.legged_gym.utils.helpers import class_to_dict
-    t = {"go2": rc.GO2RoughCfgPPO, "h1": rc.H1RoughCfgPPO, "g1": rc.G1RoughCfgPPO, "h1_2": rc.H1_2RoughCfgPPO}[task]()
+    t = {"go2": rc.GO2RoughCfgPPO, "h1": rc.H1RoughCfgPPO, "g1": rc.G1RoughCfgPPO, "h1_2": rc.H1_2RoughCfgPPO,
+         "go2_handstand": rc.GO2HandstandCfgPPO}[task]()
     d = class_to_dict(t)
     d["runner"]["cuda_graph"] = bool(cuda_graph)
     return d
 
 
-def config_dict(task, n, world, graph):
-    from unitree_rl_gym_b200.robots import ROBOTS
-    pol = "MLP actor/critic [512,256,128]" if task == "go2" else "ActorCriticRecurrent LSTM(64)+[32]"
+def config_dict(task, n, world):
+    """The workload (identical in both arms: the driver compares it key by key)."""
+    pol = "MLP actor/critic [512,256,128]" if task in ("go2", "go2_handstand") else "ActorCriticRecurrent LSTM(64)+[32]"
     return {"workload": f"{task} flat terrain, {n} envs/GPU, decimation {DECIM[task]}, {ROLLOUT}-step rollout, {pol}; "
                         "synthetic root/dof/contact state frames (PhysX is external to the path)",
             "task": task, "envs_per_gpu": n, "rollout_steps": ROLLOUT, "epochs": 5, "mini_batches": 4,
-            "parallelism": f"dp{world} (env shards, flat-gradient all-reduce)" if world > 1 else "single GPU",
-            "rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph; the 20 minibatch steps of "
-                              "the update as a second graph, N>1: with its per-minibatch NCCL all-reduce as graph nodes unless URLG_GRAPH_NCCL=0)" if graph else "eager",
+            "parallelism": f"dp{world} (env shards, flat-gradient all-reduce)" if world > 1 else "single GPU"}
+
+
+def run_dict(graph, pool_seam):
+    """How this arm ran the workload (not part of the workload itself)."""
+    return {"rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph; the 20 minibatch steps of "
+                              "the update as a second graph, N>1: with its per-minibatch NCCL all-reduce as graph nodes "
+                              "unless URLG_GRAPH_NCCL=0)" if graph else "eager",
+            "physics_seam": ("pool-indexed: kernels read the current synthetic frame in place (urlg_env_bind_frame_pool), no "
+                             "stand-in copies inside the timed region" if pool_seam else
+                             "copied: one urlg_synth_refresh launch per physics tensor per refresh inside the timed region"),
             "l2_policy": "working set per iteration (35 MB rollout storage + 8-frame physics pool) is cycled; every timed "
                          "iteration additionally starts after a 256 MiB L2 flush write outside the event bracket"}
 
 
-DECIM = {"go2": 4, "h1": 4, "g1": 4, "h1_2": 8}
+DECIM = {"go2": 4, "h1": 4, "g1": 4, "h1_2": 8, "go2_handstand": 5}
 # algorithmic bytes per env (SURVEY.md §8d): K2 post-physics per env-step, K1 per substep
 K2_BYTES = {"go2": 1102, "g1": 1338, "h1_2": 1338, "h1": 1194, "go2_handstand": 1102 + 2 * 184 - 192 + 32}
 K1_BYTES = {"go2": 192, "g1": 192, "h1_2": 192, "h1": 160, "go2_handstand": 192}
-MLP_FLOP_PER_ENV_STEP = {"go2": 756992, "h1": 117952, "g1": 124224, "h1_2": 124224}
+MLP_FLOP_PER_ENV_STEP = {"go2": 756992, "h1": 117952, "g1": 124224, "h1_2": 124224, "go2_handstand": 2 * (46 * 512 + 512 * 256 + 256 * 128) + 2 * 128 * 13}
 
 
 def time_graph(fn, reps):
@@ -179,10 +191,12 @@ def time_graph(fn, reps):
 
 # ------------------------------------------------------------------ reference arm / cpu baseline (oracle port on host cores)
 def cpu_run(task, n, iterations, warmup):
+    import contextlib
     import torch
     from oracle import cpu_bench
     spec, frames = make_frames(task, n, POOL_FRAMES)
-    out = cpu_bench.run(spec, frames, train_cfg_dict(task), iterations, warmup, threads=os.cpu_count())
+    with contextlib.redirect_stdout(sys.stderr):       # the port prints its module summary like rsl_rl does
+        out = cpu_bench.run(spec, frames, train_cfg_dict(task), iterations, warmup, threads=os.cpu_count())
     roll = sum(out["rollout_s"]) / len(out["rollout_s"])
     upd = sum(out["update_s"]) / len(out["update_s"])
     return {"env_steps_per_s": n * ROLLOUT / roll, "rollout_ms": roll * 1e3, "update_ms": upd * 1e3,
@@ -193,12 +207,18 @@ def reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if a.device != "cpu":            # context number only: the same eager torch code on the GPU
+        r = eager_gpu_run(a.task, a.envs, max(a.steps, 1), max(a.warmup, 1))
+        print(json.dumps({"impl": "reference", "device": a.device, "metric": METRIC, "value": r["value"], "unit": r["unit"],
+                          "n_gpus": 1, "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["ppo_iter_ms"],
+                          "higher_is_better": True, "config": config_dict(a.task, a.envs, 1), "eager_gpu": r}), flush=True)
+        return
     r = cpu_run(a.task, a.envs, max(a.steps, 1), a.warmup)
     line = {"impl": "reference", "metric": METRIC, "value": r["env_steps_per_s"], "unit": "env-steps/s",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["iter_ms"],
             "ppo_iter_ms": r["iter_ms"], "rollout_ms": r["rollout_ms"], "update_ms": r["update_ms"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(a.task, a.envs, 1, False),
+            "config": config_dict(a.task, a.envs, a.gpus),
             "cpu_baseline": {"value": r["env_steps_per_s"], "unit": "env-steps/s", "cores": r["threads"], "kind": "port",
                              "sample": f"{a.steps} full PPO iteration(s) ({a.envs} envs x {ROLLOUT} steps + 5x4 minibatch "
                                        f"update) after {a.warmup} warm-up, torch CPU with {r['threads']} threads of "
@@ -207,6 +227,90 @@ def reference_arm(a):
                                        "tests/golden stands in"},
             "e2e": {"value": r["env_steps_per_s"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def quick_config(task, n, steps, dev, world, rank, pool_seam=True):
+    """One of BASELINE.json's other configs (H1 / G1 at 4096 envs, H1_2 at 16384 envs per GPU) measured the same way as the
+    headline: rollout and update replayed as CUDA graphs, CUDA events per phase, max over ranks, L2 flush between
+    iterations.  Returns the sub-object stored under `configs` in the JSON line."""
+    import torch
+    import torch.distributed as dist
+    from unitree_rl_gym_b200.rsl_rl.runners import OnPolicyRunner
+    from unitree_rl_gym_b200.rsl_rl.runners.rollout_graph import RolloutGraph
+    spec, frames = make_frames(task, n, POOL_FRAMES, seed=1 + rank)
+    env, cfg = make_env(task, n, frames, dev, env_offset=rank * n, pool_seam=pool_seam)
+    runner = OnPolicyRunner(env, train_cfg_dict(task), log_dir=None, device=dev)
+    alg = runner.alg
+    env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
+    alg.cuda_graph_update = True
+    T = ROLLOUT
+
+    def eager():
+        obs = env.get_observations()
+        priv = env.get_privileged_observations()
+        cobs = priv if priv is not None else obs
+        with torch.inference_mode():
+            for _ in range(T):
+                act = alg.act(obs, cobs)
+                obs, priv, rew, dones, infos = env.step(act)
+                cobs = priv if priv is not None else obs
+                alg.process_env_step(rew, dones, infos)
+        return obs, cobs
+
+    def finish(cobs):
+        with torch.inference_mode():
+            alg.compute_returns(cobs)
+        return alg.update()
+    _, cobs = eager()
+    finish(cobs)
+    graph = RolloutGraph(runner).capture()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(3):
+        _, cobs = graph.replay()
+        finish(cobs)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    marks = []
+    for _ in range(steps):
+        flush.zero_()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        _, cobs = graph.replay()
+        e[1].record()
+        finish(cobs)
+        e[2].record()
+        marks.append(e)
+    torch.cuda.synchronize()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b, _ in marks) / steps, sum(b.elapsed_time(c) for _, b, c in marks) / steps],
+                     dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    roll_ms, upd_ms = t.tolist()
+    out = {"config": config_dict(task, n, world), "value": n * T * world / (roll_ms * 1e-3), "unit": "env-steps/s",
+           "rollout_ms": roll_ms, "update_ms": upd_ms, "ppo_iter_ms": roll_ms + upd_ms,
+           "train_env_steps_per_s": n * T * world / ((roll_ms + upd_ms) * 1e-3), "steps": steps, "n_gpus": world,
+           "update_tensor_frac": MLP_FLOP_PER_ENV_STEP[task] * 3 * n * T * 5 / (upd_ms * 1e-3) / 1e12 / measured_peaks()[2]}
+    if world > 1:
+        alg.release_graphs()
+    del graph, runner, env, alg
+    torch.cuda.empty_cache()
+    return out
+
+
+def eager_gpu_run(task, n, iterations=1, warmup=1):
+    """The oracle's eager torch code (what the reference runs: ~300 launches and 3 host syncs per env step) on the GPU --
+    the context number SURVEY.md 0.4 / BASELINE.md 4 name.  Not the comparison anchor (that is the CPU arm)."""
+    import contextlib
+    from oracle import cpu_bench
+    spec, frames = make_frames(task, n, POOL_FRAMES)
+    with contextlib.redirect_stdout(sys.stderr):
+        out = cpu_bench.run(spec, frames, train_cfg_dict(task), iterations, warmup, device="cuda")
+    roll = sum(out["rollout_s"]) / len(out["rollout_s"])
+    it = sum(out["iter_wall_s"]) / len(out["iter_wall_s"])
+    return {"value": n * ROLLOUT / roll, "unit": "env-steps/s", "rollout_ms": roll * 1e3, "ppo_iter_ms": it * 1e3,
+            "kind": "port", "device": "cuda", "sample": f"{iterations} PPO iteration(s) after {warmup} warm-up, eager torch "
+            "(oracle port of LeggedRobot.step + rsl_rl v1.0.2) on the same B200"}
 
 
 # ------------------------------------------------------------------ own arm
@@ -232,7 +336,7 @@ def own_arm(a):
     hbm, tf_burst, tf_sus, peak_src = measured_peaks()
 
     spec, frames = make_frames(task, n, POOL_FRAMES, seed=1 + rank)
-    env, cfg = make_env(task, n, frames, dev, env_offset=rank * n)
+    env, cfg = make_env(task, n, frames, dev, env_offset=rank * n, pool_seam=not a.copy_seam)
     runner = OnPolicyRunner(env, train_cfg_dict(task), log_dir=None, device=dev)
     alg = runner.alg
     env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
@@ -476,61 +580,65 @@ def own_arm(a):
                 e2e_mode = ("ONE CUDA graph per 24-step rollout (RolloutGraph with capture hooks): per-step H2D frame "
                             "uploads and reward/done read-backs are memcpy nodes on forked branches of the same graph")
 
-    # ---- roofline of the dominant kernel.  By the ncu launch list (profiles/) the tcgen05 GEMM is ~70% of the GPU time
-    #      of a step, so `roofline` is the GEMM against the tensor peak: CUDA events around every GEMM launch of one
-    #      eager iteration (library hook urlg_gemm_timing), achieved = sum(2*M*N*K) / sum(duration).  The fused env
-    #      kernels (K2 + K2b, K1) are timed alone under graph replay against the HBM peak: `roofline_env*`.
+    # ---- roofline of the dominant kernels (K3 / K7 are tensor-bound, 1.12 TFLOP per Go2 iteration).
+    #      Every tensor-core launch of ONE eager iteration (the fused multi-layer forward of the rollout and of the update,
+    #      the dgrad / wgrad GEMMs) is bracketed by CUDA events on its stream by the library hook urlg_gemm_timing (one
+    #      launch per bracket, in situ); achieved = sum of algorithmic flops (2*M*N*K once, although split-bf16 issues three
+    #      MMAs per product) / sum of durations, against the sustained bf16 peak.  The HBM view of the same launches and
+    #      the path's own algorithmic bytes stand beside it.  The fused env kernels (K2 + K2b, K1) are timed alone under
+    #      graph replay against the HBM peak: `roofline_env*`.
     roof = None
     extra = {}
     import ctypes as C
 
-    GEMM_REPEAT = 8                        # launches per event bracket: see include/urlg_b200.h (results are discarded)
-
     def gemm_timed(fn):
-        _lib.check(L.urlg_gemm_timing(GEMM_REPEAT))
+        _lib.check(L.urlg_gemm_timing(1))
         out = fn()
         torch.cuda.synchronize()
         ms, cnt, fl, by = C.c_double(), C.c_int64(), C.c_double(), C.c_double()
         _lib.check(L.urlg_gemm_timing_read(C.byref(ms), C.byref(cnt), C.byref(fl), C.byref(by)))
         _lib.check(L.urlg_gemm_timing(0))
         return out, ms.value, cnt.value, (fl.value, by.value)
-    # every rank runs this iteration (the update holds collectives); rank 0 reports its own GEMM times
+    # every rank runs this iteration (the update holds collectives); rank 0 reports its own times
     alg.cuda_graph_update = False          # the hook needs real launches, not graph replays
     (_, cobs), ms_r, n_r, fl_r = gemm_timed(eager_rollout)
     _, ms_u, n_u, fl_u = gemm_timed(lambda: finish(cobs))
     barrier()
     if rank == 0:
         (fl_r, by_r), (fl_u, by_u) = fl_r, fl_u
-        sec = (ms_r + ms_u) * 1e-3
+        sec = max((ms_r + ms_u) * 1e-3, 1e-12)
         tf, gbs = (fl_r + fl_u) / sec / 1e12, (by_r + by_u) / sec / 1e9
-        # which roof is lower for this mix of shapes: time at the HBM peak vs time at the tensor peak
-        t_hbm, t_tc = (by_r + by_u) / (hbm * 1e9), (fl_r + fl_u) / (tf_sus * 1e12)
-        mem_bound = t_hbm >= t_tc
-        roof = {"kernel": "tc::gemm_bf16_kernel (tcgen05/TMA GEMM: every Linear / LSTM-gate forward, dgrad, wgrad of the step)",
-                "bound": "hbm" if mem_bound else "tensor",
-                "achieved": gbs if mem_bound else tf, "peak": hbm if mem_bound else tf_sus,
-                "unit": "GB/s" if mem_bound else "TFLOP/s", "frac": (gbs / hbm) if mem_bound else (tf / tf_sus),
-                "traffic": ncu_traffic_per_launch(),
-                "traffic_scope": "ncu --set full capture of the 8 grouped GEMM launches of one update minibatch "
-                                 "(profiles/r1_gemm_minibatch_ncu.csv): DRAM read + write per launch; compare with "
-                                 "traffic_alg_bytes_per_launch = algorithmic bytes per update-phase launch",
-                "traffic_alg_bytes_per_launch": by_u / max(n_u, 1),
-                "launches_per_step": int(n_r + n_u),
-                "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
-                "alg_bytes_per_launch": (by_r + by_u) / max(n_r + n_u, 1), "alg_flops_per_launch": (fl_r + fl_u) / max(n_r + n_u, 1),
-                "tensor": {"achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus},
-                "hbm": {"achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm},
-                "arithmetic_intensity_flop_per_byte": (fl_r + fl_u) / (by_r + by_u),
+        obs_w, act_w = spec.num_obs, spec.num_dof
+        crit_w = spec.num_priv if spec.num_priv else spec.num_obs
+        # path-level algorithmic HBM bytes of an iteration's update: every minibatch row's gathered
+        # columns once per epoch + parameters, gradients and both Adam moments once per minibatch step
+        n_params = sum(p_.numel() for p_ in alg.actor_critic.parameters())
+        row_bytes = 4 * (obs_w + (crit_w if spec.num_priv else 0) + 3 * act_w + 4)
+        path_alg = 5 * n * T * row_bytes + 20 * n_params * 4 * 7
+        ncu_traffic = ncu_traffic_per_launch()
+        sub = lambda ms_, n_, fl_, by_: {"launches": int(n_), "ms": ms_, "tflops": fl_ / max(ms_ * 1e-3, 1e-12) / 1e12,
+                                         "gbs": by_ / max(ms_ * 1e-3, 1e-12) / 1e9}
+        roof = {"kernel": "tcgen05 kernels of the step: fused::mlp_fused_fwd_kernel (all four layers of actor + critic per "
+                          "128-row tile: rollout policy forward + update forward) and tc::gemm_bf16_kernel (dgrad / wgrad)",
+                "bound": "tensor", "achieved": tf, "peak": tf_sus, "unit": "TFLOP/s", "frac": tf / tf_sus,
+                "traffic": ncu_traffic,
+                "traffic_scope": "ncu --set full capture of the tensor-core launches of one update minibatch "
+                                 "(profiles/): DRAM read + write per launch",
+                "alg_flops_per_launch": (fl_r + fl_u) / max(n_r + n_u, 1),
+                "alg_bytes_per_launch": (by_r + by_u) / max(n_r + n_u, 1),
+                "launches_per_step": int(n_r + n_u), "us_per_launch": sec * 1e6 / max(n_r + n_u, 1),
+                "hbm_view": {"achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                             "note": "per-launch operand + output bytes of the same launches over the same time"},
+                "path_alg_bytes": path_alg,
+                "path_alg_bytes_note": "update phase per iteration: gathered minibatch rows (5 epochs) + parameters, "
+                                       "gradients, Adam moments per minibatch step; launch-level bytes above it are "
+                                       "activations saved by the forward and re-read by the backward",
+                "launch_bytes_over_path_bytes": by_u / max(path_alg, 1),
+                "arithmetic_intensity_flop_per_byte": (fl_r + fl_u) / max(by_r + by_u, 1),
                 "ridge_flop_per_byte": tf_sus * 1e12 / (hbm * 1e9), "peak_source": peak_src,
-                "rollout": {"launches": int(n_r), "ms": ms_r, "tflops": fl_r / (ms_r * 1e-3) / 1e12, "gbs": by_r / (ms_r * 1e-3) / 1e9},
-                "update": {"launches": int(n_u), "ms": ms_u, "tflops": fl_u / (ms_u * 1e-3) / 1e12, "gbs": by_u / (ms_u * 1e-3) / 1e9},
-                "launches_per_event_bracket": GEMM_REPEAT,
-                "note": "summed over every GEMM launch of one eager PPO iteration; each launch is issued 8 times back to back between "
-                        "two CUDA events on its stream and the bracket divided by 8 (one launch on an idle GPU would add event + "
-                        "launch latency to a 10-20 us kernel); algorithmic "
-                        "flops 2*M*N*K counted once (split-bf16 issues 3 MMAs per product), algorithmic bytes = every operand "
-                        "and output element once (bf16 hi+lo pairs, fp32 outputs); the shapes (K=48..512, N=1..512) sit far "
-                        "below the ridge point, so HBM is the roof"}
+                "rollout": sub(ms_r, n_r, fl_r, by_r), "update": sub(ms_u, n_u, fl_u, by_u),
+                "note": "one eager PPO iteration, one launch per event bracket; flops counted once (3 MMAs per product "
+                        "in split-bf16), so frac is the fraction of the bf16 peak an fp32-faithful result reaches"}
         iters = 200
 
         time_call = time_graph
@@ -538,11 +646,10 @@ def own_arm(a):
         def post():
             env.common_step_counter += 1
             env._obs_slot ^= 1
-            _lib.check(L.urlg_post_physics(env._handle, _lib.ptr(env._step_base), env.common_step_counter,
-                                           env._obs_slot, _lib.cur_stream()))
+            env._launch_post()
         raw_act = torch.randn(n, env.num_actions, device=dev)
         us_post = time_call(post, iters)
-        us_pd = time_call(lambda: _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(raw_act), _lib.cur_stream())), iters)
+        us_pd = time_call(lambda: env._launch_pd(raw_act), iters)
         b2 = K2_BYTES[task] * n
         extra["roofline_env"] = {
             "kernel": "post_physics_kernel (+finalize_step_kernel), K2 of SURVEY.md 8(a).7", "bound": "hbm",
@@ -574,10 +681,9 @@ def own_arm(a):
             def post_b():
                 env_b.common_step_counter += 1
                 env_b._obs_slot ^= 1
-                _lib.check(L.urlg_post_physics(env_b._handle, _lib.ptr(env_b._step_base), env_b.common_step_counter,
-                                               env_b._obs_slot, _lib.cur_stream()))
+                env_b._launch_post()
             us_b = time_call(post_b, 20)
-            us_pd_b = time_call(lambda: _lib.check(L.urlg_pd_torques(env_b._handle, _lib.ptr(act_b), _lib.cur_stream())), 20)
+            us_pd_b = time_call(lambda: env_b._launch_pd(act_b), 20)
             bb = K2_BYTES[task] * big
             extra["roofline_env_large"] = {"kernel": "post_physics_kernel (+finalize)", "envs": big, "bound": "hbm",
                                        "achieved": bb / us_b / 1e3, "peak": hbm, "unit": "GB/s",
@@ -588,6 +694,26 @@ def own_arm(a):
                                        "note": "working set >> 126 MB L2, back-to-back launches"}
             del env_b, frames_b, act_b
             torch.cuda.empty_cache()
+
+    # ---- BASELINE.json configs[2..4]: H1 and G1 at 4096 envs/GPU, H1_2 at 16384 envs/GPU (every rank takes part: the
+    #      update holds the gradient all-reduce), so the driver's single run records them at every N
+    configs = None
+    if not a.no_configs and task == TASK:
+        configs = {}
+        for name, tk, ne in (("h1_4096", "h1", 4096), ("g1_4096", "g1", 4096), ("h1_2_16384", "h1_2", 16384)):
+            try:
+                configs[name] = quick_config(tk, ne, max(3, min(a.steps, 5)), dev, world, rank, pool_seam=not a.copy_seam)
+            except Exception as ex:              # a sub-benchmark must not take the headline line down with it
+                configs[name] = {"error": repr(ex)[:300]}
+        barrier()
+
+    # ---- eager torch on the same GPU (context, rank 0 at N=1 only)
+    eager_gpu = None
+    if rank == 0 and world == 1 and not a.no_eager_gpu:
+        try:
+            eager_gpu = eager_gpu_run(task, n, 1, 1)
+        except Exception as ex:
+            eager_gpu = {"error": repr(ex)[:300]}
 
     # ---- CPU baseline (rank 0, N=1 only): the oracle port on the host cores, bounded sample
     cpu = None
@@ -605,7 +731,7 @@ def own_arm(a):
                 "update_ms": upd_ms, "wall_ms_per_step": wall_ms, "train_env_steps_per_s": n * T * world / (total_ms * 1e-3),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 env path; split-bf16 (hi+lo) tensor-core operands, fp32 accumulate, policy/PPO",
-                "data": "synthetic", "config": config_dict(task, n, world, graph is not None),
+                "data": "synthetic", "config": config_dict(task, n, world), "run": run_dict(graph is not None, not a.copy_seam),
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": n * T * world / (e2e_roll_ms * 1e-3), "unit": "env-steps/s",
                         "h2d_bytes_per_step": int(h2d * T), "d2h_bytes_per_step": int(d2h * T), "rollout_ms": e2e_roll_ms,
@@ -616,7 +742,7 @@ def own_arm(a):
                         "note": "public API with HOST physics frames: per env step the frame (root, dof x decimation, contact) "
                                 "is copied from pinned host memory and rewards + dones are read back to pinned host memory; "
                                 "bytes are per 24-step rollout (one bench step)"},
-                "roofline": roof, "cpu_baseline": cpu}
+                "roofline": roof, "cpu_baseline": cpu, "eager_gpu": eager_gpu, "configs": configs}
         line.update(extra)
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -636,6 +762,13 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="eager rollout instead of CUDA-graph replay")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-large", action="store_true", help="skip the large-N roofline point")
+    ap.add_argument("--no-configs", action="store_true", help="skip the H1 / G1 / H1_2 sub-benchmarks")
+    ap.add_argument("--no-eager-gpu", action="store_true", help="skip the eager-torch-on-GPU context number")
+    ap.add_argument("--copy-seam", action="store_true",
+                    help="serve synthetic frames by copying them into the physics tensors (urlg_synth_refresh launches "
+                         "inside the timed region) instead of the pool-indexed seam")
+    ap.add_argument("--device", default="cpu", help="--impl reference only: cpu (the arm the driver compares) or cuda "
+                                                    "(the same eager torch code on the GPU, context number)")
     ap.add_argument("--large-envs", type=int, default=1 << 18)
     a = ap.parse_args()
     if a.impl == "reference":

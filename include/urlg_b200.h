@@ -245,12 +245,10 @@ int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
  * other's wave tails.  All problems must use the same operand mode (hi+lo pairs or plain bf16); results are those of n
  * separate urlg_tc_gemm calls. */
 int urlg_tc_gemm_group(const urlg_gemm_desc* descs, int n, void* stream);
-/* Measurement hook (bench.py roofline): while enabled, every GEMM launch of this library is bracketed by CUDA events on
- * its stream (do not enable under graph capture); read returns the summed duration, launch count, 2*M*N*K flops and the
- * algorithmic HBM bytes (every operand and output element once).  enable = R > 1 issues every GEMM R times back to back
- * inside its bracket and divides the bracket by R: the per-launch duration of a busy stream instead of one launch on an
- * idle GPU (event + launch latency would otherwise be a third of a 10-20 us kernel); accumulating (atomic) outputs are
- * then R times too large, so the results of such a pass are for timing only. */
+/* Measurement hook (bench.py roofline): while enabled, every tensor-core launch of this library (GEMM or fused forward)
+ * is bracketed by CUDA events on its stream (do not enable under graph capture); read returns the summed duration, the
+ * launch count, the algorithmic flops (2*M*N*K, counted once) and the algorithmic HBM bytes (every operand and output
+ * element once).  One launch per bracket, outputs untouched: a timed pass computes exactly what an untimed one does. */
 int urlg_gemm_timing(int enable);
 int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double* flops, double* bytes);
 

@@ -21,8 +21,8 @@ class PortVecEnv:
     """VecEnv protocol (R1) over EnvPort with the synthetic physics seam (frame pool cycled like
     unitree_rl_gym_b200.physics.SyntheticGym: frame = (simulate calls - 1) // decimation % P)."""
 
-    def __init__(self, spec, frames):
-        self.port = env_port.EnvPort(spec)
+    def __init__(self, spec, frames, device="cpu"):
+        self.port = env_port.EnvPort(spec, device=device, fast_rng=True)   # torch.rand like the reference (timing only)
         self.spec = spec
         self.frames = frames
         self.num_frames = frames["root"].shape[0]
@@ -31,7 +31,7 @@ class PortVecEnv:
         self.num_privileged_obs = spec.num_priv if spec.num_priv else None
         self.num_actions = spec.num_dof
         self.max_episode_length = spec.max_episode_length
-        self.device = "cpu"
+        self.device = device
 
     def _physics(self, sub):
         if sub is not None:
@@ -65,22 +65,32 @@ class PortVecEnv:
         return self.port.step(actions, self._physics)
 
 
-def run(spec, frames, train_cfg, iterations, warmup, threads=None):
+def run(spec, frames, train_cfg, iterations, warmup, threads=None, device="cpu"):
     """Returns dict(rollout_s=[...], update_s=[...]) per timed iteration (one iteration = 24-step rollout +
-    compute_returns + 5x4 minibatch update), after `warmup` untimed iterations."""
+    compute_returns + 5x4 minibatch update), after `warmup` untimed iterations.  device="cuda" runs the same eager
+    torch code on the GPU (bench.py's `eager_gpu` context number: ~300 launches and 3 host syncs per env step)."""
     if threads:
         torch.set_num_threads(int(threads))
-    env = PortVecEnv(spec, frames)
-    torch.manual_seed(1)
-    runner = R.OnPolicyRunner(env, train_cfg, log_dir=None, device="cpu")
-    env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
-    out = {"rollout_s": [], "update_s": [], "threads": torch.get_num_threads()}
-    for it in range(warmup + iterations):
-        t0 = time.perf_counter()
-        runner.learn(1, init_at_random_ep_len=False)
-        st = runner.last_stats
-        if it >= warmup:
-            out["rollout_s"].append(st["collection_time"])
-            out["update_s"].append(st["learn_time"])
-        out["last_iter_wall_s"] = time.perf_counter() - t0
+    dev = torch.device(device)
+    if dev.type != "cpu":
+        frames = {k: (v.to(dev) if v is not None else None) for k, v in frames.items()}
+    out = {"rollout_s": [], "update_s": [], "iter_wall_s": [], "threads": torch.get_num_threads()}
+    with torch.device(dev):                  # the port's factory calls (torch.zeros(...)) follow the run's device
+        env = PortVecEnv(spec, frames, device=str(dev))
+        torch.manual_seed(1)
+        runner = R.OnPolicyRunner(env, train_cfg, log_dir=None, device=str(dev))
+        env.episode_length_buf = torch.randint_like(env.episode_length_buf, high=int(env.max_episode_length))
+        for it in range(warmup + iterations):
+            if dev.type != "cpu":
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            runner.learn(1, init_at_random_ep_len=False)
+            if dev.type != "cpu":
+                torch.cuda.synchronize()
+            st = runner.last_stats
+            if it >= warmup:
+                out["rollout_s"].append(st["collection_time"])
+                out["update_s"].append(st["learn_time"])
+                out["iter_wall_s"].append(time.perf_counter() - t0)
+            out["last_iter_wall_s"] = time.perf_counter() - t0
     return out

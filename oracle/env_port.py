@@ -61,7 +61,12 @@ class EnvPort:
     """State + step functions.  `spec` is duck-typed (unitree_rl_gym_b200.envspec.EnvSpec or
     the attributes scraped from a reference env by tests/golden/gen_golden.py)."""
 
-    def __init__(self, spec, threads=None):
+    def __init__(self, spec, threads=None, device="cpu", fast_rng=False):
+        """device / fast_rng serve the timed baselines only (bench.py): `device="cuda"` runs the same eager torch ops
+        on the GPU (the "eager GPU" context number), `fast_rng` draws the uniforms with torch.rand on that device --
+        what the reference itself does -- instead of building the shared Philox table in numpy (parity runs need the
+        table; timing runs must not pay for it)."""
+        self._device, self._fast_rng = torch.device(device), bool(fast_rng)
         s = self.spec = spec
         N, A, F = s.num_envs, s.num_dof, len(s.feet_idx)
         f = lambda *shape: torch.zeros(*shape, dtype=torch.float32)
@@ -103,6 +108,12 @@ class EnvPort:
         self.commands_scale = torch.tensor([s.obs_scale_lin_vel, s.obs_scale_lin_vel, s.obs_scale_ang_vel])
         self.env_ids_global = np.arange(N, dtype=np.int64) + s.env_offset
         self._ucache = (None, None)
+        if self._device.type != "cpu":
+            for k, v in list(vars(self).items()):
+                if torch.is_tensor(v):
+                    setattr(self, k, v.to(self._device))
+            self.episode_sums = {k: v.to(self._device) for k, v in self.episode_sums.items()}
+        self._gen = torch.Generator(device=self._device).manual_seed(int(s.seed)) if self._fast_rng else None
 
     # views, as :108-109
     @property
@@ -114,6 +125,11 @@ class EnvPort:
         return self.dof_state.view(self.spec.num_envs, self.spec.num_dof, 2)[..., 1]
 
     def uniforms(self, step):
+        if self._fast_rng:
+            if self._ucache[0] != step:
+                self._ucache = (step, torch.rand(self.spec.num_envs, self.spec.num_rng_slots, device=self._device,
+                                                 generator=self._gen))
+            return self._ucache[1]
         if self._ucache[0] != step:
             u = philox.uniform_table(self.spec.seed, philox.STREAM_ENV, self.env_ids_global, step,
                                      self.spec.num_rng_slots)

@@ -38,11 +38,10 @@ def main():
             def post():
                 env.common_step_counter += 1
                 env._obs_slot ^= 1
-                _lib.check(L.urlg_post_physics(env._handle, _lib.ptr(env._step_base), env.common_step_counter,
-                                               env._obs_slot, _lib.cur_stream()))
+                env._launch_post()
 
             def pd():
-                _lib.check(L.urlg_pd_torques(env._handle, _lib.ptr(act), _lib.cur_stream()))
+                env._launch_pd(act)
             if a.once:
                 for _ in range(3):
                     post()

@@ -10,6 +10,9 @@ namespace urlg {
 namespace tc {
 int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer,
                    CUtensorMapSwizzle swizzle);
+bool timing_on();
+int timing_begin(cudaStream_t st);
+int timing_end(cudaStream_t st, double flops, double bytes);
 }
 
 using namespace urlg::fused;
@@ -70,8 +73,24 @@ static int fused_launch(FusedArgs& A, int64_t rows, cudaStream_t st) {
   A.tiles_m = (int)((rows + 127) / 128);
   const int items = A.tiles_m * A.num_nets;
   const int grid = items < kNumSMs ? items : kNumSMs;
+  const bool timed = tc::timing_on();
+  if (timed) if (int rc = tc::timing_begin(st)) return rc;
   URLG_CUDA(launch_pdl(mlp_fused_fwd_kernel, dim3(grid), dim3(kThreads), (size_t)kSmemBytes, st, A));
   URLG_LAUNCH_CHECK();
+  if (timed) {
+    // algorithmic work of the launch: 2 M N K per layer; bytes = input rows + weights (hi+lo) + outputs (+ saved activations)
+    double fl = 0.0, by = 0.0;
+    for (int q = 0; q < A.num_nets; ++q) {
+      const NetArgs& n = A.net[q];
+      by += 4.0 * rows * n.x_cols * (n.x_store ? 2.0 : 1.0) + 4.0 * rows * n.dims[n.num_layers];
+      for (int l = 0; l < n.num_layers; ++l) {
+        fl += 2.0 * rows * n.dims[l] * n.dims[l + 1];
+        by += 4.0 * n.dims[l] * n.dims[l + 1];
+        if (A.save) by += 4.0 * rows * n.dims[l];
+      }
+    }
+    if (int rc = tc::timing_end(st, fl, by)) return rc;
+  }
   return URLG_OK;
 }
 

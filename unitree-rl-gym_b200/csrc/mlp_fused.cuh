@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fused_fwd_kernel(const __grid
         tma_prefetch_desc(&P.net[q].w_lo[l]);
       }
     for (int s = 0; s < kWStages; ++s) { mbar_init(wfull0 + 8 * s, 1); mbar_init(wempty0 + 8 * s, 1); }
-    for (int s = 0; s < kActSlots; ++s) { mbar_init(afull0 + 8 * s, kDrainWarps); mbar_init(aempty0 + 8 * s, P.save ? 2 : 1); }
+    for (int s = 0; s < kActSlots; ++s) { mbar_init(afull0 + 8 * s, 4); mbar_init(aempty0 + 8 * s, P.save ? 2 : 1); }
     mbar_init(xfull, kDrainWarps);
     mbar_init(xempty, P.save ? 2 : 1);
     for (int b = 0; b < kNumTfull; ++b) mbar_init(tfull0 + 8 * b, 1);
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fused_fwd_kernel(const __grid
     // ===== input staging + accumulator drains =====
     const int dw = warp - 2;
     const int lq = warp & 3;                 // TMEM lane quarter this warp may read (hardware rule: warp id % 4)
-    const int cg = dw >> 2;                  // 16-column group of a 64-column chunk
+    const int cg = dw >> 2;                  // warp group 0..3: one warp per lane quarter; chunks are dealt round-robin
     const int row_in_tile = lq * 32 + lane;  // accumulator row held by this thread
     uint32_t pc = 0, it = 0, tuse = 0;       // tuse: 4 bits per tfull barrier = uses so far (phase)
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -310,60 +310,86 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fused_fwd_kernel(const __grid
         __syncwarp();
         if (lane == 0) mbar_arrive(xfull);
       }
-      // ---- drains ----
+      // ---- drains: the four warp groups (one warp per TMEM lane quarter each) take the 64-column chunks round-robin, so up
+      //      to four chunks are in flight; a group waits for an accumulator the first time it reads from it ----
+      uint32_t cur_bar = 0, cur_par = 0;
+      bool waited = true;
       for (int i = 0; i < n.n_drains; ++i) {
         const DrainStep ds = n.drains[i];
         if (ds.flags & kDrainWait) {
           const uint32_t uses = (tuse >> (4 * ds.bar)) & 15u;
-          mbar_wait(tfull0 + 8 * ds.bar, uses & 1u);
+          cur_bar = tfull0 + 8 * ds.bar;
+          cur_par = uses & 1u;
+          waited = false;
           tuse += 1u << (4 * ds.bar);
           if (((tuse >> (4 * ds.bar)) & 15u) == 14u) tuse -= 14u << (4 * ds.bar);   // keep the nibble (parity preserved)
-          tc_fence_after();
         }
         const int N = n.dims[ds.layer + 1];
         const float* bias = n.bias[ds.layer];
         if (!(ds.flags & kDrainFinal)) {
-          const int col0 = ds.out_col + 16 * cg;                        // column of the layer output
-          float v[16];
-          tmem_ld16(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(ds.tmem_col + 16 * cg), v);
-          if (col0 < N) {                                                // N is a multiple of 16: whole group valid
-            if (((uintptr_t)(bias + col0) & 15) == 0) {
+          if ((int)(pc & 3u) == cg) {
+            if (!waited) { mbar_wait(cur_bar, cur_par); tc_fence_after(); waited = true; }
+            const uint32_t slot = pc % kActSlots;
+            const uint32_t sb = sAct + slot * kSlotBytes;
+            const uint32_t taddr = tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)ds.tmem_col;
+            bool slot_ready = false;
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
-                v[4 * j] += b4.x; v[4 * j + 1] += b4.y; v[4 * j + 2] += b4.z; v[4 * j + 3] += b4.w;
+            for (int h = 0; h < 2; ++h) {
+              uint32_t ra[16], rb[16];
+              tmem_ld16_issue(taddr + 32 * h, ra);
+              tmem_ld16_issue(taddr + 32 * h + 16, rb);
+              tmem_ld_wait_dep(ra);
+              tmem_ld_wait_dep(rb);
+#pragma unroll
+              for (int g2 = 0; g2 < 2; ++g2) {
+                const int cgi = 2 * h + g2;                              // 16-column group of the chunk
+                const int col0 = ds.out_col + 16 * cgi;                  // column of the layer output
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(g2 ? rb[j] : ra[j]);
+                if (col0 < N) {                                          // N is a multiple of 16: whole group valid
+                  if (((uintptr_t)(bias + col0) & 15) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                      const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
+                      v[4 * j] += b4.x; v[4 * j + 1] += b4.y; v[4 * j + 2] += b4.z; v[4 * j + 3] += b4.w;
+                    }
+                  } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] += __ldg(bias + col0 + j);
+                  }
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) v[j] = elu1(v[j]);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) v[j] = 0.0f;              // K padding of the next layer
+                }
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  hi[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                  lo[j] = pack_bf16x2(v[2 * j] - bf16lo(hi[j]), v[2 * j + 1] - bf16hi(hi[j]));
+                }
+                if (!slot_ready) {                                       // consumer MMAs (and saver) released the slot
+                  mbar_wait(aempty0 + 8 * slot, ((pc / kActSlots) & 1) ^ 1);
+                  slot_ready = true;
+                }
+                const uint32_t o0 = sw128_offset(row_in_tile, 2 * cgi), o1 = sw128_offset(row_in_tile, 2 * cgi + 1);
+                st_shared_v4(sb + o0, hi[0], hi[1], hi[2], hi[3]);
+                st_shared_v4(sb + o1, hi[4], hi[5], hi[6], hi[7]);
+                st_shared_v4(sb + kTileBytes + o0, lo[0], lo[1], lo[2], lo[3]);
+                st_shared_v4(sb + kTileBytes + o1, lo[4], lo[5], lo[6], lo[7]);
               }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] += __ldg(bias + col0 + j);
             }
-#pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = elu1(v[j]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = 0.0f;                    // K padding of the next layer
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(afull0 + 8 * slot);
           }
-          uint32_t hi[8], lo[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            hi[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-            lo[j] = pack_bf16x2(v[2 * j] - bf16lo(hi[j]), v[2 * j + 1] - bf16hi(hi[j]));
-          }
-          const uint32_t slot = pc % kActSlots;
-          mbar_wait(aempty0 + 8 * slot, ((pc / kActSlots) & 1) ^ 1);     // consumer MMAs (and saver) released the slot
-          const uint32_t sb = sAct + slot * kSlotBytes;
-          const uint32_t o0 = sw128_offset(row_in_tile, 2 * cg), o1 = sw128_offset(row_in_tile, 2 * cg + 1);
-          st_shared_v4(sb + o0, hi[0], hi[1], hi[2], hi[3]);
-          st_shared_v4(sb + o1, hi[4], hi[5], hi[6], hi[7]);
-          st_shared_v4(sb + kTileBytes + o0, lo[0], lo[1], lo[2], lo[3]);
-          st_shared_v4(sb + kTileBytes + o1, lo[4], lo[5], lo[6], lo[7]);
-          tc_fence_before();
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(afull0 + 8 * slot);
           ++pc;
         } else if (cg == 0) {
-          // ---- last layer: <= 16 outputs per row; thread = row ----
+          // ---- last layer: <= 16 outputs per row; thread = row (group 0) ----
+          if (!waited) { mbar_wait(cur_bar, cur_par); tc_fence_after(); waited = true; }
           float v[16];
           tmem_ld16(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)ds.tmem_col, v);
           const int row = m0 + row_in_tile;

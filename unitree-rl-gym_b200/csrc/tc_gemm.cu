@@ -45,18 +45,18 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
 }
 
 // Optional per-launch timing (bench.py's roofline leg): CUDA events recorded on the launching stream around every
-// GEMM launch while enabled (never under graph capture), summed on read.
+// tensor-core launch (GEMM or fused forward) while enabled -- never under graph capture -- summed on read.  One launch
+// per bracket, in situ: the stream stays busy (the host enqueues faster than these kernels run), so a bracket is the
+// kernel plus its inter-kernel gap with the caches in the state the real step leaves them.
 static bool g_timing = false;
-static int g_repeat = 1;        // launches per event bracket (urlg_gemm_timing(R)); the bracket's time is divided by R
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
 static double g_flops = 0.0, g_bytes = 0.0;
 static size_t g_used = 0;
 
 int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
 
-// n independent problems in one launch (n <= kMaxGroup); see GroupArgs in tc_gemm.cuh.
-int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
-  if (!g_timing) return launch_group_impl(ds, n, st);
+bool timing_on() { return g_timing; }
+int timing_begin(cudaStream_t st) {
   if (g_used == g_events.size()) {
     cudaEvent_t a, b;
     URLG_CUDA(cudaEventCreate(&a));
@@ -64,19 +64,32 @@ int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
     g_events.emplace_back(a, b);
   }
   URLG_CUDA(cudaEventRecord(g_events[g_used].first, st));
-  int rc = URLG_OK;
-  for (int r = 0; r < g_repeat && rc == URLG_OK; ++r) rc = launch_group_impl(ds, n, st);
+  return URLG_OK;
+}
+int timing_end(cudaStream_t st, double flops, double bytes) {
   URLG_CUDA(cudaEventRecord(g_events[g_used].second, st));
   ++g_used;
+  g_flops += flops;
+  g_bytes += bytes;
+  return URLG_OK;
+}
+
+// n independent problems in one launch (n <= kMaxGroup); see GroupArgs in tc_gemm.cuh.
+int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
+  if (!g_timing) return launch_group_impl(ds, n, st);
+  if (int rc = timing_begin(st)) return rc;
+  const int rc = launch_group_impl(ds, n, st);
+  double fl = 0.0, by = 0.0;
   for (int i = 0; ds && i < n; ++i) {
     const urlg_gemm_desc* d = ds[i];
     if (!d) continue;
-    g_flops += 2.0 * d->M * d->N * d->K;
-    // algorithmic HBM bytes: each operand element and each output element once (bf16, x2 when split into hi+lo)
+    fl += 2.0 * d->M * d->N * d->K;
+    // algorithmic HBM bytes of the launch: each operand element and each output element once (bf16, x2 when split into hi+lo)
     const double parts = (d->A_lo && d->B_lo) ? 2.0 : 1.0, mn = (double)d->M * d->N;
-    g_bytes += 2.0 * parts * ((double)d->M * d->K + (double)d->N * d->K) + (d->out_f32 ? 4.0 * mn : 0.0) +
-               (d->out_bf16 ? 2.0 * parts * mn : 0.0) + (d->dact_ref ? 2.0 * parts * mn : 0.0);
+    by += 2.0 * parts * ((double)d->M * d->K + (double)d->N * d->K) + (d->out_f32 ? 4.0 * mn : 0.0) +
+          (d->out_bf16 ? 2.0 * parts * mn : 0.0) + (d->dact_ref ? 2.0 * parts * mn : 0.0);
   }
+  if (int rc2 = timing_end(st, fl, by)) return rc2;
   return rc;
 }
 
@@ -171,7 +184,7 @@ static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, 
 
 template <int G>
 static int launch_group_g(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
-  static GroupArgs<G> P;                    // 1.2 KB of kernel parameters per problem, copied at launch
+  GroupArgs<G> P;                           // 1.2 KB of kernel parameters per problem, copied at launch (per call: thread-safe)
   P.num = n;
   int64_t tiles = 0;
   int bn_max = 0, max_ctas = 0;
@@ -221,7 +234,6 @@ int launch_group_impl(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
 extern "C" int urlg_gemm_timing(int enable) {
   using namespace urlg::tc;
   g_timing = enable != 0;
-  g_repeat = enable > 1 ? enable : 1;
   if (g_timing) { g_used = 0; g_flops = 0.0; g_bytes = 0.0; }
   return URLG_OK;
 }
@@ -233,7 +245,7 @@ extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double
     URLG_CUDA(cudaEventSynchronize(g_events[i].second));
     float t = 0.0f;
     URLG_CUDA(cudaEventElapsedTime(&t, g_events[i].first, g_events[i].second));
-    ms += t / g_repeat;
+    ms += t;
   }
   if (total_ms) *total_ms = ms;
   if (launches) *launches = (int64_t)g_used;

@@ -291,18 +291,30 @@ class LeggedRobot(BaseTask):
             g.refresh_rigid_body_state_tensor(self.sim)
         self.common_step_counter += 1
         self._obs_slot ^= 1
-        L = _lib.lib()
-        if self._pool:
-            _lib.check(L.urlg_post_physics_at(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
-                                              self._obs_slot, g.sim_calls, _lib.cur_stream()))
-        else:
-            _lib.check(L.urlg_post_physics(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
-                                           self._obs_slot, _lib.cur_stream()))
+        self._launch_post()
         self._commit_indexed()
         self.obs_buf = self._obs_slots[self._obs_slot]
         if self._priv_slots:
             self.privileged_obs_buf = self._priv_slots[self._obs_slot]
         self._publish_extras()
+
+    def _launch_post(self):
+        """K2 + K2b for the current step counter / obs slot (pool-indexed or bound physics tensors)."""
+        L = _lib.lib()
+        if self._pool:
+            _lib.check(L.urlg_post_physics_at(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
+                                              self._obs_slot, self.gym.sim_calls, _lib.cur_stream()))
+        else:
+            _lib.check(L.urlg_post_physics(self._handle, _lib.ptr(self._step_base), self.common_step_counter,
+                                           self._obs_slot, _lib.cur_stream()))
+
+    def _launch_pd(self, raw_actions=None):
+        """K1 for the current substep; raw_actions (device tensor) on the first substep of a step."""
+        L = _lib.lib()
+        if self._pool:
+            _lib.check(L.urlg_pd_torques_at(self._handle, _lib.ptr(raw_actions), self.gym.sim_calls, _lib.cur_stream()))
+        else:
+            _lib.check(L.urlg_pd_torques(self._handle, _lib.ptr(raw_actions), _lib.cur_stream()))
 
     def _commit_indexed(self):
         g = self.gym
