@@ -238,7 +238,15 @@ typedef struct urlg_gemm_desc {
   void* out_bf16_lo;              /* optional low part of out_bf16 */
   const void* dact_ref_lo;        /* optional low part of dact_ref */
   int32_t max_ctas;               /* 0 = one persistent CTA per SM; else cap the grid (two GEMMs side by side on two streams) */
+  /* Order-independent accumulation (with URLG_GEMM_ATOMIC): when out_fx / colsum_fx are set the values are added as
+   * 64-bit fixed point (value * 2^URLG_FX_SHIFT, rounded to nearest) with integer atomics instead of fp32 atomics into
+   * out_f32 / colsum: integer addition is associative, so split-K sums are bit-reproducible run to run.  Same shapes /
+   * leading dimension as out_f32 / colsum. */
+  int64_t* out_fx;
+  int64_t* colsum_fx;
 } urlg_gemm_desc;
+#define URLG_FX_SHIFT 40          /* gradient accumulators: resolution 2^-40 = 9.1e-13, range +-8.4e6 */
+#define URLG_FX_STAT_SHIFT 30     /* loss / KL sums: resolution 9.3e-10, range +-8.6e9 */
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
 /* n (1..4) independent problems in ONE launch: their tiles form one persistent tile space, so e.g. the same layer of the
  * actor and of the critic, or a layer's data and weight gradients, share a launch's fixed cost (~4 us) and fill each

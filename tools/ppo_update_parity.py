@@ -18,11 +18,13 @@ out = {"what": "one PPO.update (5 epochs x 4 minibatches), CUDA path vs oracle/r
        "threads": torch.get_num_threads(), "cases": []}
 for name, args in (("go2_mlp", (False, 48, None, 12, [512, 256, 128], N, 24)),
                    ("g1_lstm", (True, 47, 50, 12, [32], N, 24))):
-    rep = T.one_update_report(*args, with_fp64=True)
-    rep["case"] = name
-    out["cases"].append(rep)
-    print(name, json.dumps({k: rep[k] for k in ("cuda_vs_oracle32", "oracle32_vs_oracle64", "cuda_vs_oracle64", "delta_scale", "lr_final")}),
-          file=sys.stderr, flush=True)
+    for seed in range(5):              # every seed is recorded, also the ones with a clip-boundary row (see tests/test_ppo_cuda.py)
+        rep = T.one_update_report(*args, with_fp64=True, seed=seed)
+        rep["case"] = name
+        rep["seed"] = seed
+        out["cases"].append(rep)
+        print(name, seed, json.dumps({k: rep[k] for k in ("cuda_vs_oracle32", "oracle32_vs_oracle64", "delta_scale", "lr_final")}),
+              file=sys.stderr, flush=True)
 for kl in (0.0202, 0.00483):
     rep = T.one_update_report(False, 48, None, 12, [512, 256, 128], 1024, 24, kl_target=kl, with_fp64=False)
     rep["case"] = "go2_mlp_kl_%g" % kl

@@ -79,6 +79,7 @@ class GemmDesc(C.Structure):
         ("out_f32", _P), ("ld_f32", C.c_int32), ("out_bf16", _P), ("ld_bf16", C.c_int32),
         ("bias", _P), ("dact_ref", _P), ("ld_ref", C.c_int32), ("colsum", _P), ("flags", C.c_int32),
         ("A_lo", _P), ("B_lo", _P), ("out_bf16_lo", _P), ("dact_ref_lo", _P), ("max_ctas", C.c_int32),
+        ("out_fx", _P), ("colsum_fx", _P),
     ]
 
 

@@ -66,4 +66,14 @@ __device__ __forceinline__ int64_t eff_step(const int64_t* base, int64_t off) {
 
 constexpr int kNumSMs = 148;
 
+namespace tc {
+// value -> 64-bit fixed point and add: integer atomics commute, so a sum accumulated this way does not depend on the
+// arrival order of its contributions (bit-reproducible gradients; include/urlg_b200.h URLG_FX_SHIFT)
+__device__ __forceinline__ void fx_add(long long* p, float v, float scale) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(p), (unsigned long long)__float2ll_rn(v * scale));
+}
+constexpr float kFxScale = 1099511627776.0f;        // 2^URLG_FX_SHIFT
+constexpr float kFxStatScale = 1073741824.0f;       // 2^URLG_FX_STAT_SHIFT
+}  // namespace tc
+
 }  // namespace urlg

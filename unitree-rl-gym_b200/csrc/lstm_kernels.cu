@@ -97,7 +97,7 @@ lstm_cell_backward_kernel(const float* __restrict__ gates, int rows, int H, cons
                           const float* __restrict__ c_new, const bf16* __restrict__ dh_head, const float* __restrict__ dh_rec,
                           float* __restrict__ dc /* in: dL/dc_new from t+1, out: dL/dc_prev */,
                           const uint8_t* __restrict__ cut /* dones[t] of the slice: 1 = no gradient from t+1 */, int has_next,
-                          bf16* __restrict__ dgates, int64_t lo_off, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh) {
+                          bf16* __restrict__ dgates, int64_t lo_off, long long* __restrict__ g_b_ih, long long* __restrict__ g_b_hh) {
   extern __shared__ float acc[];   // [4H]
   for (int k = threadIdx.x; k < 4 * H; k += blockDim.x) acc[k] = 0.0f;
   __syncthreads();
@@ -124,7 +124,7 @@ lstm_cell_backward_kernel(const float* __restrict__ gates, int rows, int H, cons
   __syncthreads();
   for (int k = threadIdx.x; k < 4 * H; k += blockDim.x) {
     const float a = acc[k];
-    if (a != 0.0f) { atomicAdd(g_b_ih + k, a); atomicAdd(g_b_hh + k, a); }
+    if (a != 0.0f) { tc::fx_add(g_b_ih + k, a, tc::kFxScale); tc::fx_add(g_b_hh + k, a, tc::kFxScale); }
   }
 }
 
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(256)
 lstm_recur_bwd_kernel(const float* __restrict__ gates, int T, int E, int H, int N, int env_begin,
                       const uint8_t* __restrict__ dones, const float* __restrict__ c_prev, const float* __restrict__ c_new,
                       const bf16* __restrict__ dh_head, bf16* __restrict__ dgates, int64_t lo_off,
-                      const float* __restrict__ W_hh, float* __restrict__ g_b_ih, float* __restrict__ g_b_hh) {
+                      const float* __restrict__ W_hh, long long* __restrict__ g_b_ih, long long* __restrict__ g_b_hh) {
   extern __shared__ __align__(16) float lsm[];
   float* Wb = lsm;                                      // [4H][H] as stored by nn.LSTM
   float* dg = lsm + 4 * H * H;                          // [4H][rows_per_cta]
@@ -332,7 +332,7 @@ lstm_recur_bwd_kernel(const float* __restrict__ gates, int T, int E, int H, int 
   for (int q = threadIdx.x; q < 4 * H; q += blockDim.x) {
     float a = 0.0f;
     for (int rr = 0; rr < RG; ++rr) a += dg[q * RG + rr];
-    if (a != 0.0f) { atomicAdd(g_b_ih + q, a); atomicAdd(g_b_hh + q, a); }
+    if (a != 0.0f) { tc::fx_add(g_b_ih + q, a, tc::kFxScale); tc::fx_add(g_b_hh + q, a, tc::kFxScale); }
   }
 }
 
@@ -473,7 +473,7 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
 #define URLG_BWD(RPT)                                                                                                  \
     lstm_recur_bwd_kernel<RPT><<<grid, rpc * H, smem, st>>>(w.gates, T, E, H, s->N, env_begin, s->dones, c_prev, c_new, \
                                                            w.dx_head, w.dgates, p->lo_off, p->params + w.off[1],        \
-                                                           p->grads + w.off[2], p->grads + w.off[3])
+                                                           p->gacc + w.off[2], p->gacc + w.off[3])
     if (rpt == 4) URLG_BWD(4); else if (rpt == 2) URLG_BWD(2); else URLG_BWD(1);
 #undef URLG_BWD
     URLG_LAUNCH_CHECK();
@@ -482,8 +482,8 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
     const size_t ro = (size_t)t * E;
     lstm_cell_backward_kernel<<<(total + 255) / 256, 256, 4 * H * sizeof(float), st>>>(
         w.gates + ro * 4 * H, E, H, c_prev + ro * H, c_new + ro * H, w.dx_head + ro * H, w.dhrec, w.dc,
-        s->dones + (size_t)t * s->N + env_begin, t < T - 1 ? 1 : 0, w.dgates + ro * 4 * H, p->lo_off, p->grads + w.off[2],
-        p->grads + w.off[3]);
+        s->dones + (size_t)t * s->N + env_begin, t < T - 1 ? 1 : 0, w.dgates + ro * 4 * H, p->lo_off, p->gacc + w.off[2],
+        p->gacc + w.off[3]);
     URLG_LAUNCH_CHECK();
     if (t > 0) {   // dL/dh_{t-1} (recurrent part) = dgates_t * W_hh
       urlg_gemm_desc g = {};
@@ -508,6 +508,7 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
     g.M = 4 * H; g.N = part == 0 ? w.in : H; g.K = T * E;
     g.block_n = round_up(g.N, 64);
     g.out_f32 = p->grads + w.off[part]; g.ld_f32 = g.N;
+    g.out_fx = reinterpret_cast<int64_t*>(p->gacc + w.off[part]);
     g.flags = URLG_GEMM_ATOMIC;
     const int tiles = 2 * ((4 * H + 127) / 128);          // both parts share the wave
     int splits = kNumSMs / tiles;

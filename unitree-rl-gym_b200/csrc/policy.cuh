@@ -60,6 +60,10 @@ struct urlg_policy {
   // fused multi-layer forward (mlp_fused.cuh): argument template with the weight / saved-activation tensor maps and the
   // per-network schedules, built once at create; NULL when the layer widths are outside its limits or URLG_FUSED=0
   urlg::fused::FusedArgs* fz;
+  // order-independent gradient accumulation: [num_params + 4] 64-bit fixed-point accumulators (library-owned, zero
+  // between minibatches); every gradient / loss-sum contribution of a minibatch is an integer atomic add into it, and
+  // grads_finalize_kernel converts it into the flat fp32 gradient + the four per-minibatch sums and re-zeroes it
+  long long* gacc;
 };
 
 namespace urlg {

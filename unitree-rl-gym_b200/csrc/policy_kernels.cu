@@ -339,12 +339,17 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     delete p;
     return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
   }
-  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr;
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     urlg_policy_destroy(p);
     return fail(URLG_ECUDA, "urlg_policy_create: side stream / events: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  if (cudaMalloc(&p->gacc, ((size_t)desc->num_params + 4) * sizeof(long long)) != cudaSuccess ||
+      cudaMemset(p->gacc, 0, ((size_t)desc->num_params + 4) * sizeof(long long)) != cudaSuccess) {
+    urlg_policy_destroy(p);
+    return fail(URLG_ECUDA, "urlg_policy_create: gradient accumulators: %s", cudaGetErrorString(cudaGetLastError()));
   }
   if (int rc2 = fused_build(p)) { urlg_policy_destroy(p); return rc2; }
   *out = p;
@@ -354,6 +359,7 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
 extern "C" void urlg_policy_destroy(urlg_policy* p) {
   if (!p) return;
   fused_free(p);
+  if (p->gacc) cudaFree(p->gacc);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);

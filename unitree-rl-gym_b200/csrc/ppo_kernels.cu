@@ -85,8 +85,8 @@ ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_
                 const urlg_storage s, const int64_t* __restrict__ indices, int64_t rows, int env_begin, int env_count,
                 const urlg_ppo_hparams hp, bf16* __restrict__ dmu, int ld_dmu, bf16* __restrict__ dval, int ld_dval,
                 int64_t lo_off,
-                float* __restrict__ g_std, float* __restrict__ g_bias_mu, float* __restrict__ g_bias_val,
-                float* __restrict__ stats) {
+                long long* __restrict__ g_std, long long* __restrict__ g_bias_mu, long long* __restrict__ g_bias_val,
+                long long* __restrict__ sums /* [4] fixed point: KL, surrogate, value loss, entropy */) {
   extern __shared__ float sh[];
   const int A = s.num_actions;
   float* t_a = sh;                         // [rows][A]  log-prob terms, then d loss / d mu
@@ -179,18 +179,16 @@ ppo_head_kernel(const float* __restrict__ mu_new, const float* __restrict__ val_
   if (tid < A) {
     float sm = 0.0f, ss = 0.0f;
     for (int k = 0; k < kHeadRows; ++k) { sm += t_a[k * A + tid]; ss += t_b[k * A + tid]; }
-    atomicAdd(g_bias_mu + tid, sm);
+    tc::fx_add(g_bias_mu + tid, sm, tc::kFxScale);
     if (blockIdx.x == 0) ss += -hp.entropy_coef / std_param[tid];   // d(-c_ent * mean entropy)/d sigma_j
-    atomicAdd(g_std + tid, ss);
+    tc::fx_add(g_std + tid, ss, tc::kFxScale);
   } else if (tid >= 32 && tid < 37) {
     const int k5 = tid - 32;
     float a = 0.0f;
     for (int k = 0; k < kHeadRows; ++k) a += row_s[k * 5 + k5];
-    if (k5 == 0) atomicAdd(stats + URLG_STAT_KL_SUM, a);
-    else if (k5 == 1) atomicAdd(stats + URLG_STAT_SURR_SUM, a);
-    else if (k5 == 2) atomicAdd(stats + URLG_STAT_VLOSS_SUM, a);
-    else if (k5 == 3) atomicAdd(stats + URLG_STAT_ENT_SUM, a);
-    else atomicAdd(g_bias_val, a);
+    static_assert(URLG_STAT_KL_SUM == 0 && URLG_STAT_SURR_SUM == 1 && URLG_STAT_VLOSS_SUM == 2 && URLG_STAT_ENT_SUM == 3, "sum slots");
+    if (k5 < 4) tc::fx_add(sums + k5, a, tc::kFxStatScale);
+    else tc::fx_add(g_bias_val, a, tc::kFxScale);
   }
 }
 
@@ -214,6 +212,7 @@ static urlg_gemm_desc wgrad_desc(urlg_policy* p, NetWs& n, int l, int64_t rows) 
   g.ldb = l == 0 ? n.kpad[0] : nin; g.b_mn = 1;
   g.M = nout; g.N = nin; g.K = (int)rows;
   g.out_f32 = p->grads + n.d.w_off[l]; g.ld_f32 = nin;
+  g.out_fx = reinterpret_cast<int64_t*>(p->gacc + n.d.w_off[l]);
   g.flags = URLG_GEMM_ATOMIC;
   const int bn = nin > 256 ? 256 : round_up(nin, 64);
   g.block_n = bn;
@@ -247,6 +246,7 @@ static bool dgrad_desc(urlg_policy* p, NetWs& n, int l, int64_t rows, bf16* dx_o
     g.out_bf16 = n.dz[l]; g.ld_bf16 = nin;
     g.dact_ref = n.h[l]; g.ld_ref = nin;
     g.colsum = p->grads + n.d.b_off[l - 1];
+    g.colsum_fx = reinterpret_cast<int64_t*>(p->gacc + n.d.b_off[l - 1]);
   } else {
     g.out_bf16 = dx_out; g.ld_bf16 = nin;
   }
@@ -360,6 +360,19 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   }
 }
 
+// gacc (fixed point) -> flat fp32 gradient + the four per-minibatch sums; re-zeroes the accumulators for the next minibatch
+__global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restrict__ gacc, float* __restrict__ grads,
+                                                             float* __restrict__ stats, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    grads[i] = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
+    gacc[i] = 0;
+  } else if (i < n + 4) {
+    stats[i - n] = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
+    gacc[i] = 0;
+  }
+}
+
 __global__ void zero_minibatch_stats_kernel(float* stats) {
   const int i = threadIdx.x;
   if (i == URLG_STAT_KL_SUM || i == URLG_STAT_SURR_SUM || i == URLG_STAT_VLOSS_SUM || i == URLG_STAT_ENT_SUM ||
@@ -389,9 +402,8 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   // [grads | KL, surrogate, value, entropy sums]) the same memset clears the four sums; GNORM_SQ is overwritten by
   // urlg_ppo_apply before anything reads it
   static_assert(URLG_STAT_KL_SUM == 0 && URLG_STAT_ENT_SUM == 3, "the four per-minibatch sums lead the stats block");
-  const bool sums_behind_grads = p->stats == p->grads + d.num_params;
-  URLG_CUDA(cudaMemsetAsync(p->grads, 0, ((size_t)d.num_params + (sums_behind_grads ? 4 : 0)) * sizeof(float), st));
-  if (!sums_behind_grads) zero_minibatch_stats_kernel<<<1, 32, 0, st>>>(p->stats);
+  // every contribution of this minibatch goes into p->gacc (zero on entry: create / the previous finalize left it so);
+  // grads_finalize_kernel at the end writes the whole flat gradient and the four sums, so nothing is cleared here
   NetWs &na = p->net[0], &nc = p->net[1];
   const bool fused_fwd = !d.recurrent && p->fz != nullptr;
   if (fused_fwd) {
@@ -427,8 +439,8 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   const int head_smem = (2 * kHeadRows * d.num_actions + 6 * kHeadRows + d.num_actions) * (int)sizeof(float);
   ppo_head_kernel<<<(int)((rows + kHeadRows - 1) / kHeadRows), kHeadRows * d.num_actions, head_smem, st>>>(
       na.out, nc.out, p->params + d.std_off, *s, indices, rows, env_begin, env_count, *h, na.dout, na.opad, nc.dout,
-      nc.opad, p->lo_off, p->grads + d.std_off, p->grads + na.d.b_off[na.d.num_layers - 1],
-      p->grads + nc.d.b_off[nc.d.num_layers - 1], p->stats);
+      nc.opad, p->lo_off, p->gacc + d.std_off, p->gacc + na.d.b_off[na.d.num_layers - 1],
+      p->gacc + nc.d.b_off[nc.d.num_layers - 1], p->gacc + d.num_params);
   URLG_LAUNCH_CHECK();
   if (int rc = mlp_backward_pair(p, na, nc, rows, d.recurrent ? p->lstm[0].dx_head : nullptr,
                                  d.recurrent ? p->lstm[1].dx_head : nullptr, st)) return rc;
@@ -441,6 +453,11 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     URLG_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
     if (rc_a) return rc_a;
     if (rc_c) return rc_c;
+  }
+  {
+    const int64_t n = d.num_params + 4;
+    grads_finalize_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params);
+    URLG_LAUNCH_CHECK();
   }
   p->last_rows = rows;
   return URLG_OK;

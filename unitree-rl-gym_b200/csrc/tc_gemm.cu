@@ -126,6 +126,8 @@ static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, 
   g.bias = d->bias;
   g.dact_ref = reinterpret_cast<const __nv_bfloat16*>(d->dact_ref); g.ld_ref = d->ld_ref;
   g.colsum = d->colsum;
+  g.out_fx = reinterpret_cast<long long*>(d->out_fx);
+  g.colsum_fx = reinterpret_cast<long long*>(d->colsum_fx);
   g.flags = d->flags;
   g.split = (d->A_lo && d->B_lo) ? 1 : 0;
   if ((d->A_lo != nullptr) != (d->B_lo != nullptr)) return fail(URLG_EINVAL, "urlg_tc_gemm: A_lo and B_lo go together");

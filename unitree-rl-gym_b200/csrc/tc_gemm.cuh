@@ -7,6 +7,7 @@
 // copies of weights or activations are ever made.
 #pragma once
 #include <cuda.h>
+#include "common.cuh"
 #include "tc_ptx.cuh"
 
 namespace urlg {
@@ -35,7 +36,10 @@ struct GemmArgs {
   const __nv_bfloat16* dact_lo;   // split: low part of dact_ref
   int tma_ref;           // dact_ref chunks arrive by TMA tensor loads, one chunk ahead (tmR / tmRlo valid; needs tma_out)
   int tma_out;           // bf16 outputs leave through per-warp shared staging + TMA tensor stores (tmO / tmOlo valid)
+  long long* out_fx;     // fixed-point accumulation targets (see urlg_gemm_desc): replace the fp32 atomics when set
+  long long* colsum_fx;
 };
+
 
 __host__ __device__ inline int stage_bytes_a() { return kBlockM * kBlockK * 2; }
 __host__ __device__ inline int stage_bytes_b(int block_n) { return block_n * kBlockK * 2; }
@@ -377,7 +381,11 @@ gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
             bulk_commit();
           }
         }
-        if (row_ok) {
+        if (row_ok && g.out_fx) {
+          long long* o = g.out_fx + (size_t)row * g.ld_f32 + col0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) if (i < ncol) fx_add(o + i, v[i], kFxScale);
+        } else if (row_ok) {
           if (g.out_f32) {
             float* o = g.out_f32 + (size_t)row * g.ld_f32 + col0;
             const bool v4 = full && vec_f32 && ((uintptr_t)o & 15) == 0;
@@ -426,7 +434,7 @@ gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
             }
           }
         }
-        if (g.colsum) {
+        if (g.colsum || g.colsum_fx) {
           // 16 columns x 32 rows -> 16 sums with a transposing butterfly (16 shuffles): after the steps below lane l
           // (l even) holds the sum of column 8*b4 + 4*b3 + 2*b2 + b1 (bK = bit K of l).
           float w8[8], w4[4], w2[2], w1;
@@ -455,7 +463,10 @@ gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
           }
           w1 += __shfl_xor_sync(0xffffffffu, w1, 1);
           const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-          if ((lane & 1) == 0 && c < ncol) atomicAdd(g.colsum + col0 + c, w1);
+          if ((lane & 1) == 0 && c < ncol) {
+            if (g.colsum_fx) fx_add(g.colsum_fx + col0 + c, w1, kFxScale);
+            else atomicAdd(g.colsum + col0 + c, w1);
+          }
         }
       }
       tc_fence_before();
