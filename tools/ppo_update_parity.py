@@ -10,6 +10,7 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import contextlib  # noqa: E402
 import torch  # noqa: E402
 from tests import test_ppo_cuda as T  # noqa: E402
 
@@ -19,14 +20,16 @@ out = {"what": "one PPO.update (5 epochs x 4 minibatches), CUDA path vs oracle/r
 for name, args in (("go2_mlp", (False, 48, None, 12, [512, 256, 128], N, 24)),
                    ("g1_lstm", (True, 47, 50, 12, [32], N, 24))):
     for seed in range(5):              # every seed is recorded, also the ones with a clip-boundary row (see tests/test_ppo_cuda.py)
-        rep = T.one_update_report(*args, with_fp64=True, seed=seed)
+        with contextlib.redirect_stdout(sys.stderr):       # the modules print their layer summaries like rsl_rl does
+            rep = T.one_update_report(*args, with_fp64=True, seed=seed)
         rep["case"] = name
         rep["seed"] = seed
         out["cases"].append(rep)
         print(name, seed, json.dumps({k: rep[k] for k in ("cuda_vs_oracle32", "oracle32_vs_oracle64", "delta_scale", "lr_final")}),
               file=sys.stderr, flush=True)
 for kl in (0.0202, 0.00483):
-    rep = T.one_update_report(False, 48, None, 12, [512, 256, 128], 1024, 24, kl_target=kl, with_fp64=False)
+    with contextlib.redirect_stdout(sys.stderr):
+        rep = T.one_update_report(False, 48, None, 12, [512, 256, 128], 1024, 24, kl_target=kl, with_fp64=False)
     rep["case"] = "go2_mlp_kl_%g" % kl
     out["cases"].append(rep)
     print(rep["case"], rep["lr_trace_cuda"], file=sys.stderr, flush=True)
