@@ -198,3 +198,23 @@ def test_rollout_graph_with_host_traffic_hooks():
     assert torch.equal(ca, cb)
     assert torch.equal(rew_rows, ra.alg.storage.rewards.view(T, n).cpu())
     assert torch.equal(done_rows, ra.alg.storage.dones.view(T, n).cpu())
+
+
+def test_graph_captured_before_first_rollout_keeps_recurrent_state():
+    """Capture on a FRESH recurrent runner (nothing has run yet): buffers allocated on first use -- the (h, c) rollout state
+    -- must be created before the capture, or their zero-fill becomes a graph node and every replay restarts the LSTM
+    from zero.  Two iterations: the second replay continues from the first one's hidden state exactly like the eager loop."""
+    n = 128
+    ra, rb = make_runner("g1", n), make_runner("g1", n)
+    from unitree_rl_gym_b200.rsl_rl.runners.rollout_graph import RolloutGraph
+    g = RolloutGraph(rb).capture()
+    for _ in range(2):
+        ca = eager_rollout(ra)
+        cb = g.replay()[1]
+        torch.cuda.synchronize()
+        storage_equal(ra.alg.storage, rb.alg.storage)
+        assert torch.equal(ca, cb)
+        assert torch.equal(ra.alg.actor_critic._hidden, rb.alg.actor_critic._hidden)
+        finish(ra, ca)
+        finish(rb, cb)
+    assert torch.equal(ra.alg.engine.flat, rb.alg.engine.flat)

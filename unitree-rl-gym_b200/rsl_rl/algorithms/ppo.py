@@ -127,9 +127,7 @@ class PPO:
     # ---- learning rate lives on the device (adaptive schedule); the attribute stays readable / writable
     @property
     def learning_rate(self):
-        if self.engine is None:
-            return self._lr_host
-        return float(self.engine.stats[_lib.STAT_LR])
+        return self._lr_host          # host copy: set here and refreshed by update()'s one read-back (no device sync)
 
     @learning_rate.setter
     def learning_rate(self, v):

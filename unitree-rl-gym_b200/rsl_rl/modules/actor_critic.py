@@ -65,11 +65,14 @@ class ActorCritic(nn.Module):
             for k, v in kw.items():
                 self._engine_args[k] = max(v, self._engine_args[k]) if k in ("max_rows", "max_seq") else v
             old = self._engine
-            self._engine = PolicyEngine(self, **self._engine_args)
-            if old is not None and old.num_params == self._engine.num_params:
-                self._engine.exp_avg.copy_(old.exp_avg)
-                self._engine.exp_avg_sq.copy_(old.exp_avg_sq)
-                self._engine.stats.copy_(old.stats)
+            # normal (not inference) tensors even when the first call comes from inside torch.inference_mode() (the
+            # runner's rollout): the optimizer updates them in place later, outside inference mode
+            with torch.inference_mode(False):
+                self._engine = PolicyEngine(self, **self._engine_args)
+                if old is not None and old.num_params == self._engine.num_params:
+                    self._engine.exp_avg.copy_(old.exp_avg)
+                    self._engine.exp_avg_sq.copy_(old.exp_avg_sq)
+                    self._engine.stats.copy_(old.stats)
         return self._engine
 
     def load_state_dict(self, state_dict, strict=True):

@@ -2,9 +2,9 @@
 call sites legged_gym/utils/task_registry.py:118-126, scripts/train.py:14, scripts/play.py:34-39).
 
 Same constructor / learn / save / load / get_inference_policy.  Differences by design: per-step logging
-bookkeeping (reward / episode-length sums, finished-episode statistics) is accumulated on the device and
-read back once per iteration instead of a `.cpu()` per env step; TensorBoard is optional (used when
-importable and log_dir is given).
+bookkeeping (reward / episode-length sums, finished-episode statistics, infos["episode"]) is accumulated on the
+device and read back once per iteration instead of a `.cpu()` per env step (_EpisodeBook), which also lets the
+rollout CUDA graph stay on while logging; TensorBoard is optional (used when importable and log_dir is given).
 """
 import os
 import statistics
@@ -17,6 +17,61 @@ from ..algorithms import PPO  # noqa: F401  (resolved by name from the config, l
 from ..modules import ActorCritic, ActorCriticRecurrent  # noqa: F401
 
 _CLASSES = {"PPO": PPO, "ActorCritic": ActorCritic, "ActorCriticRecurrent": ActorCriticRecurrent}
+
+
+class _EpisodeBook:
+    """The logging bookkeeping of the reference's learn() loop ([UPSTREAM rsl_rl v1.0.2] on_policy_runner.py: ep_infos,
+    cur_reward_sum, cur_episode_length, rewbuffer / lenbuffer) as stream-ordered device work: `step` launches a handful
+    of elementwise kernels and reads nothing, so it can be recorded into the rollout CUDA graph; `read` is the one
+    device->host transfer of the iteration."""
+
+    def __init__(self, T, N, device):
+        self.T, self.N, self.device = T, N, device
+        self.cur_reward_sum = torch.zeros(N, dtype=torch.float, device=device)
+        self.cur_episode_length = torch.zeros(N, dtype=torch.float, device=device)
+        # (reward sum, length) of the episodes that finished at (step, env); NaN elsewhere
+        self.fin = torch.full((2, T, N), float("nan"), device=device)
+        self._nan = torch.full((), float("nan"), device=device)
+        self.keys = None            # names of the tensor-valued entries of infos["episode"]
+        self.consts = {}            # host-valued entries (e.g. max_command_x): logged as they are
+        self.ep = None              # [T, K]
+        self.present = [False] * T
+
+    def step(self, t, rewards, dones, infos):
+        ep = infos.get("episode") if isinstance(infos, dict) else None
+        if ep is not None:
+            if self.keys is None:
+                self.keys = [k for k, v in ep.items() if torch.is_tensor(v)]
+                self.ep = torch.zeros(self.T, max(len(self.keys), 1), device=self.device)
+            if self.keys:
+                vals = [ep[k] if ep[k].dim() == 0 else ep[k].float().mean() for k in self.keys]
+                torch.stack(vals, out=self.ep[t, :len(vals)])
+            self.consts = {k: float(v) for k, v in ep.items() if not torch.is_tensor(v)}
+            self.present[t] = True
+        self.cur_reward_sum += rewards
+        self.cur_episode_length += 1
+        d = dones > 0
+        torch.where(d, self.cur_reward_sum, self._nan, out=self.fin[0, t])
+        torch.where(d, self.cur_episode_length, self._nan, out=self.fin[1, t])
+        self.cur_reward_sum.masked_fill_(d, 0.0)
+        self.cur_episode_length.masked_fill_(d, 0.0)
+
+    def read(self):
+        """-> (finished reward sums, finished lengths, {episode key: mean over the iteration's steps})."""
+        n_fin = self.fin.numel()
+        parts = [self.fin.flatten()] + ([self.ep.flatten()] if self.ep is not None else [])
+        host = torch.cat(parts).cpu()                      # the iteration's single logging read-back
+        fin = host[:n_fin].view(2, -1)
+        keep = ~torch.isnan(fin[0])
+        means = {}
+        if self.ep is not None:
+            ep = host[n_fin:].view(self.T, -1).double()
+            rows = [t for t in range(self.T) if self.present[t]]
+            if rows:
+                m = ep[rows].mean(dim=0)
+                means = {k: float(m[i]) for i, k in enumerate(self.keys)}
+                means.update(self.consts)
+        return fin[0][keep].tolist(), fin[1][keep].tolist(), means
 
 
 class OnPolicyRunner:
@@ -65,23 +120,20 @@ class OnPolicyRunner:
         critic_obs = privileged_obs if privileged_obs is not None else obs
         obs, critic_obs = obs.to(self.device), critic_obs.to(self.device)
         alg.actor_critic.train()
-        ep_infos = []
         rewbuffer, lenbuffer = deque(maxlen=100), deque(maxlen=100)
         N, T = env.num_envs, self.num_steps_per_env
-        cur_reward_sum = torch.zeros(N, dtype=torch.float, device=self.device)
-        cur_episode_length = torch.zeros(N, dtype=torch.float, device=self.device)
-        # device-side log of finished episodes for this iteration: (reward sum, length) where done, else NaN
-        fin_rew = torch.empty(T, N, device=self.device)
-        fin_len = torch.empty(T, N, device=self.device)
-        nan = float("nan")
+        book = _EpisodeBook(T, N, self.device) if self.log_dir is not None else None
         tot_iter = self.current_learning_iteration + num_learning_iterations
-        # opt-in (runner cfg key `cuda_graph`): the whole rollout replayed as one CUDA graph (rollout_graph.py);
-        # per-step logging needs host-visible per-step values, so it is only used when log_dir is None
+        self._tot_iter = tot_iter
+        # opt-in (runner cfg key `cuda_graph`): the whole rollout replayed as one CUDA graph (rollout_graph.py).  The
+        # logging bookkeeping is stream-ordered device work (no host read per step), so it is recorded into the same
+        # graph through the post_step hook and the graph stays on when log_dir is set.
         graph = None
-        if self.cfg.get("cuda_graph", False) and self.log_dir is None:
+        if self.cfg.get("cuda_graph", False):
             from .rollout_graph import RolloutGraph
             if RolloutGraph.supported(self):
-                graph = self._rollout_graph = RolloutGraph(self).capture()
+                graph = self._rollout_graph = RolloutGraph(self)
+                graph.capture(post_step=None if book is None else (lambda t: book.step(t, *graph.last)))
         for it in range(self.current_learning_iteration, tot_iter):
             start = time.time()
             with torch.inference_mode():
@@ -94,27 +146,20 @@ class OnPolicyRunner:
                     obs, critic_obs, rewards, dones = (obs.to(self.device), critic_obs.to(self.device),
                                                        rewards.to(self.device), dones.to(self.device))
                     alg.process_env_step(rewards, dones, infos)
-                    if self.log_dir is not None:
-                        if "episode" in infos:
-                            ep_infos.append({k: (v.clone() if torch.is_tensor(v) else v)
-                                             for k, v in infos["episode"].items()})
-                        cur_reward_sum += rewards
-                        cur_episode_length += 1
-                        d = dones > 0
-                        fin_rew[i] = torch.where(d, cur_reward_sum, nan)
-                        fin_len[i] = torch.where(d, cur_episode_length, nan)
-                        cur_reward_sum.masked_fill_(d, 0.0)
-                        cur_episode_length.masked_fill_(d, 0.0)
+                    if book is not None:
+                        book.step(i, rewards, dones, infos)
+                if book is not None:
+                    torch.cuda.current_stream().synchronize()     # collection_time covers the rollout, like the reference
                 stop = time.time()
                 collection_time = stop - start
                 start = stop
                 alg.compute_returns(critic_obs)
             mean_value_loss, mean_surrogate_loss = alg.update()
-            if self.log_dir is not None:      # one read-back per iteration, in the reference's (step, env) order
-                fr, fl = fin_rew.flatten().cpu(), fin_len.flatten().cpu()
-                keep = ~torch.isnan(fr)
-                rewbuffer.extend(fr[keep].tolist())
-                lenbuffer.extend(fl[keep].tolist())
+            ep_means = {}
+            if book is not None:              # ONE read-back per iteration, in the reference's (step, env) order
+                fin_r, fin_l, ep_means = book.read()
+                rewbuffer.extend(fin_r)
+                lenbuffer.extend(fin_l)
             stop = time.time()
             learn_time = stop - start
             self.tot_timesteps += T * N
@@ -124,27 +169,25 @@ class OnPolicyRunner:
                 "fps": int(T * N / (collection_time + learn_time)),
                 "mean_value_loss": mean_value_loss, "mean_surrogate_loss": mean_surrogate_loss,
                 "learning_rate": alg.learning_rate,
-                "mean_noise_std": float(alg.actor_critic.std.mean()),
+                "mean_noise_std": float(alg.actor_critic.std.detach().mean()),
                 "mean_reward": statistics.mean(rewbuffer) if len(rewbuffer) > 0 else None,
                 "mean_episode_length": statistics.mean(lenbuffer) if len(lenbuffer) > 0 else None,
             }
             if self.log_dir is not None:
-                self.log(dict(self.last_stats), ep_infos)
+                self.log(dict(self.last_stats), ep_means)
                 if it % self.save_interval == 0:
                     self.save(os.path.join(self.log_dir, "model_{}.pt".format(it)))
-            ep_infos.clear()
         self.current_learning_iteration += num_learning_iterations
         if self.log_dir is not None:
             self.save(os.path.join(self.log_dir, "model_{}.pt".format(self.current_learning_iteration)))
+            if self.writer is not None:
+                self.writer.flush()
 
-    def log(self, st, ep_infos, width=80, pad=35):
-        """Same scalar names as the reference's TensorBoard output (SURVEY.md §5 metrics row)."""
+    def log(self, st, ep_means, width=80, pad=35):
+        """Same scalar names as the reference's TensorBoard output ([UPSTREAM rsl_rl v1.0.2]
+        runners/on_policy_runner.py log(); SURVEY.md §5 metrics row).  `ep_means`: {key: mean over the iteration's
+        steps of infos["episode"][key]}, already on the host."""
         w, it = self.writer, st["it"]
-        ep_means = {}
-        if ep_infos:
-            for key in ep_infos[0]:
-                vals = [float(e[key]) for e in ep_infos]
-                ep_means[key] = sum(vals) / len(vals)
         if w is not None:
             for key, v in ep_means.items():
                 w.add_scalar("Episode/" + key, v, it)
@@ -160,7 +203,8 @@ class OnPolicyRunner:
                 w.add_scalar("Train/mean_episode_length", st["mean_episode_length"], it)
                 w.add_scalar("Train/mean_reward/time", st["mean_reward"], self.tot_time)
                 w.add_scalar("Train/mean_episode_length/time", st["mean_episode_length"], self.tot_time)
-        head = f" \033[1m Learning iteration {it}/{self.current_learning_iteration + 0} \033[0m "
+        tot_iter = getattr(self, "_tot_iter", self.current_learning_iteration)
+        head = f" \033[1m Learning iteration {it}/{tot_iter} \033[0m "
         lines = [f"{'#' * width}", head.center(width, " "), "",
                  f"{'Computation:':>{pad}} {st['fps']:.0f} steps/s (collection: {st['collection_time']:.3f}s, "
                  f"learning {st['learn_time']:.3f}s)",
@@ -171,6 +215,12 @@ class OnPolicyRunner:
             lines += [f"{'Mean reward:':>{pad}} {st['mean_reward']:.2f}",
                       f"{'Mean episode length:':>{pad}} {st['mean_episode_length']:.2f}"]
         lines += [f"{'Mean episode ' + k + ':':>{pad}} {v:.4f}" for k, v in ep_means.items()]
+        iters_done = it + 1 - self.current_learning_iteration       # advanced only after the loop
+        lines += ["-" * width,
+                  f"{'Total timesteps:':>{pad}} {self.tot_timesteps}",
+                  f"{'Iteration time:':>{pad}} {st['collection_time'] + st['learn_time']:.2f}s",
+                  f"{'Total time:':>{pad}} {self.tot_time:.2f}s",
+                  f"{'ETA:':>{pad}} {self.tot_time / max(iters_done, 1) * (tot_iter - it - 1):.1f}s"]
         print("\n".join(lines))
 
     def save(self, path, infos=None):

@@ -15,6 +15,31 @@ first act() reads the buffer the previous replay wrote last).
 import torch
 
 
+def _baked_identity(runner):
+    """What a captured graph holds raw pointers into: the policy engine (weights, workspaces) and the storage slabs."""
+    alg = runner.alg
+    return (alg.engine, alg.storage, alg.storage.observations.data_ptr(), getattr(runner.env, "_handle", None))
+
+
+def _check_baked(runner, baked, who):
+    alg = runner.alg
+    now = (alg.engine, alg.storage, alg.storage.observations.data_ptr(), getattr(runner.env, "_handle", None))
+    if any(a is not b if not isinstance(a, int) else a != b for a, b in zip(now, baked)):
+        raise RuntimeError(who + ": the policy engine, rollout storage or env was rebuilt after capture (e.g. "
+                           "actor_critic.to(), a new init_storage); capture a new graph")
+
+
+def _materialize_lazy_state(runner):
+    """Everything the loop allocates on first use must exist BEFORE capture: an allocation made inside the capture
+    lands in the graph's private pool and its initialising kernel becomes a graph node, i.e. it would be re-run by
+    every replay (the recurrent policy's (h, c) buffer zeroed at the start of every rollout)."""
+    alg = runner.alg
+    alg._check_engine()
+    ac = alg.actor_critic
+    if ac.is_recurrent:
+        ac.hidden_buffer(alg.storage.num_envs)
+
+
 class RolloutGraph:
     def __init__(self, runner):
         self.runner = runner
@@ -36,6 +61,7 @@ class RolloutGraph:
             obs, privileged_obs, rewards, dones, infos = env.step(actions)
             critic_obs = privileged_obs if privileged_obs is not None else obs
             alg.process_env_step(rewards, dones, infos)
+            self.last = (rewards, dones, infos)      # what post_step hooks of this step may consume (device tensors)
             if post_step is not None:
                 post_step(t)
         return obs, critic_obs
@@ -56,6 +82,7 @@ class RolloutGraph:
         priv = env.get_privileged_observations()
         critic_obs = priv if priv is not None else obs
         slot0 = env._obs_slot
+        _materialize_lazy_state(r)
         torch.cuda.synchronize()
         env.begin_relative()
         alg.begin_relative()
@@ -74,10 +101,12 @@ class RolloutGraph:
         assert env._obs_slot == slot0
         self.graph = g
         self.obs_out, self.critic_out = obs_out, critic_out
+        self._baked = _baked_identity(r)
         return self
 
     def replay(self):
         """Run one rollout; returns (obs, critic_obs) after the last step (inputs of compute_returns)."""
+        _check_baked(self.runner, self._baked, "RolloutGraph")
         self.graph.replay()
         self.runner.alg.storage.step = self.runner.num_steps_per_env
         return self.obs_out, self.critic_out
@@ -103,6 +132,7 @@ class StepGraphs:
         if alg.storage.step != 0:
             raise RuntimeError("StepGraphs.capture: storage must be empty (call after update())")
         slot0 = env._obs_slot
+        _materialize_lazy_state(r)
         pool = torch.cuda.graph_pool_handle()
         self.outs = []
         n0 = _lib.lib().urlg_launch_count()
@@ -127,10 +157,12 @@ class StepGraphs:
         self.launches = (_lib.lib().urlg_launch_count() - n0) // max(len(self.graphs), 1)
         alg.storage.clear()
         assert env._obs_slot == slot0
+        self._baked = _baked_identity(r)
         return self
 
     def replay(self, t):
         """Run env step t of the rollout; returns (obs, critic_obs, rewards, dones) device tensors of that step."""
+        _check_baked(self.runner, self._baked, "StepGraphs")
         self.graphs[t].replay()
         self.runner.alg.storage.step = t + 1
         return self.outs[t]
