@@ -362,6 +362,20 @@ int urlg_process_env_step(const urlg_storage* s, int t, const float* rew, const 
 int urlg_gae(const urlg_storage* s, const float* last_values, float gamma, float lam, double* moments, int phase,
              void* stream);
 
+/* Allocation-free variant of urlg_gae (phase 3: scan + normalise) for callers that cannot call cudaMalloc or hand in
+ * scratch (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  It has NO counterpart
+ * in the reference.  The moments scratch (per-block partial sums
+ * + the folded moments) is a file-scope `static __device__` array of the library, 64.25 KB, held by every GPU that loads
+ * the library until exit; its device address is resolved with cudaGetSymbolAddress once per device on the first call
+ * made with that device current.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: s->N <= URLG_GAE_NOALLOC_MAX_ENVS, otherwise URLG_EINVAL with a message naming the limit.  Inputs and outputs
+ * are the caller's, as in urlg_gae; results equal urlg_gae's up to the order of the double-precision moment sums.
+ * All calls on a device share the one array (it keeps the last call's contents; every slot a call reads it has
+ * written first, so nothing needs clearing): calls that overlap on the GPU (different streams, no ordering) race --
+ * serialise them. */
+#define URLG_GAE_NOALLOC_MAX_ENVS 1048576
+int urlg_gae_noalloc(const urlg_storage* s, const float* last_values, float gamma, float lam, void* stream);
+
 /* One PPO minibatch: gather rows `indices` (flattened t*N+env, device int64 [rows]), forward, loss,
  * backward -> flat grads (+ KL / loss sums in stats).  Recurrent policies take an env slice instead:
  * envs [env_begin, env_begin+env_count), all T steps, hidden state re-seeded from the saved states at

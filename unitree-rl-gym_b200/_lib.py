@@ -158,6 +158,7 @@ SIGNATURES = {
     "urlg_policy_forward": (C.c_int, [C.c_void_p, C.c_int, _P, C.c_int64, _P, _P, _P, C.c_void_p]),
     "urlg_process_env_step": (C.c_int, [C.POINTER(Storage), C.c_int, _P, _P, _P, C.c_float, _P, C.c_void_p]),
     "urlg_gae": (C.c_int, [C.POINTER(Storage), _P, C.c_float, C.c_float, _P, C.c_int, C.c_void_p]),
+    "urlg_gae_noalloc": (C.c_int, [C.POINTER(Storage), _P, C.c_float, C.c_float, C.c_void_p]),
     "urlg_ppo_minibatch_grads": (C.c_int, [C.c_void_p, C.POINTER(Storage), _I64P, C.c_int64, C.c_int32, C.c_int32,
                                            C.POINTER(PpoHparams), C.c_void_p]),
     "urlg_ppo_apply": (C.c_int, [C.c_void_p, C.POINTER(PpoHparams), C.c_void_p]),
