@@ -13,6 +13,11 @@ namespace tc {
 int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st);
 int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st);
 }
+// lstm_tc.cu: the recurrence on tcgen05 (cluster size, or 0 when the Memory is outside its limits / URLG_LSTM_TC=0)
+int lstm_tc_clusters(const urlg_policy* p, const LstmWs& w);
+int lstm_tc_forward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int E, const float* saved_h,
+                    const float* saved_c, cudaStream_t st);
+int lstm_tc_backward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int E, cudaStream_t st);
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
@@ -417,6 +422,8 @@ int lstm_update_forward(urlg_policy* p, int k, const urlg_storage* s, int env_be
     lstm_stage_x_kernel<<<blocks_for((int64_t)T * E * w.in_pad), 256, 0, st>>>(obs, in, w.in_pad, w.kcat, T, s->N, env_begin, E,
                                                                              w.xcat, p->lo_off);
     URLG_LAUNCH_CHECK();
+    // tensor-core recurrence: input projection, recurrent product and cell update of all T steps in one cluster kernel
+    if (lstm_tc_clusters(p, w) > 0) return lstm_tc_forward(p, k, s, env_begin, E, sh, sc, st);
     urlg_gemm_desc g = {};
     g.A = w.xcat; g.lda = w.kcat;
     g.B = w.w; g.ldb = w.kcat;
@@ -464,7 +471,10 @@ int lstm_update_backward(urlg_policy* p, int k, const urlg_storage* s, int env_b
   float* c_new = w.c + (size_t)p->R * H;
   const int total = E * H;
   const int rpc = persistent_rows(H);
-  if (rpc > 0) {
+  const bool on_tc = rpc > 0 && lstm_tc_clusters(p, w) > 0;
+  if (on_tc) {
+    if (int rc = lstm_tc_backward(p, k, s, env_begin, E, st)) return rc;
+  } else if (rpc > 0) {
     const int rpt = rows_per_thread(E, rpc);
     const int rows_cta = rpc * rpt;
     const int smem = (4 * H * H + rows_cta * 4 * H) * (int)sizeof(float);
