@@ -227,6 +227,7 @@ def oracle_minibatch_grads(oppo, perm_or_none):
     (False, 48, None, 12, [512, 256, 128], 130, 7),
     (True, 47, 50, 12, [32], 256, 24),
     (True, 41, 44, 10, [32], 68, 9),
+    (True, 47, 50, 12, [32], 592, 24),     # env slice of 148: two 128-row tiles of the tensor-core recurrence, the second ragged
 ])
 def test_minibatch_gradients_match_oracle(recurrent, n_obs, n_priv, n_act, hidden, N, T):
     import ctypes as C

@@ -1,7 +1,7 @@
 // Host side of the tcgen05 LSTM recurrence (lstm_tc.cuh): tensor maps, cluster launches, the W_hh^T image of the
 // backward pass.  Called from lstm_kernels.cu (lstm_update_forward / lstm_update_backward) when the Memory fits the
 // kernel's limits: hidden size 64, input width <= 64, split-bf16 operands.  URLG_LSTM_TC = 0 keeps the CUDA-core
-// recurrence, 1 / 2 / 4 picks the cluster size (default 4).
+// recurrence (default: clusters of 4 CTAs).
 #include "common.cuh"
 #include "policy.cuh"
 #include "lstm_tc.cuh"
@@ -10,6 +10,8 @@ namespace urlg {
 namespace tc {
 int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer,
                    CUtensorMapSwizzle swizzle);
+int make_tmap_bf16_3d(CUtensorMap* out, const void* ptr, int64_t inner, int64_t rows, int64_t steps, int64_t ld, int box_inner,
+                      int box_rows);
 }
 
 using namespace urlg::lstmtc;
@@ -17,15 +19,14 @@ using namespace urlg::lstmtc;
 static int tc_mode() {
   static const int m = []() {
     const char* e = getenv("URLG_LSTM_TC");
-    if (!e || !e[0]) return 4;
-    const int v = atoi(e);
-    return (v == 0 || v == 1 || v == 2 || v == 4) ? v : 4;
+    return (e && e[0] == '0') ? 0 : 4;
   }();
   return m;
 }
 
+// Cluster size of the tensor-core recurrence for this Memory, or 0 when it is outside the kernel's limits.
 int lstm_tc_clusters(const urlg_policy* p, const LstmWs& w) {
-  if (!p->lo_off || w.H != kH || w.in_pad > 64 || (w.kcat & 7)) return 0;
+  if (!p->lo_off || w.H != kH || w.in_pad > 64 || (w.kcat & 7) || (int64_t)p->R * kH * 4 < 4 * kH * kH * 4) return 0;
   return tc_mode();
 }
 
@@ -51,53 +52,49 @@ int lstm_tc_forward(urlg_policy* p, int k, const urlg_storage* s, int env_begin,
                     const float* saved_c, cudaStream_t st) {
   LstmWs& w = p->lstm[k];
   NetWs& n = p->net[k];
-  const int NC = lstm_tc_clusters(p, w);
-  const int T = s->T, HU = kH / NC;
+  constexpr int NC = 4, HU = kH / NC;
+  const int T = s->T;
   FwdArgs a = {};
-  const int wbox = NC == 1 ? 256 : HU;
   int rc = tc::make_tmap_bf16(&a.x_hi, w.xcat, w.in_pad, (int64_t)T * E, w.kcat, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
   if (!rc) rc = tc::make_tmap_bf16(&a.x_lo, w.xcat + p->lo_off, w.in_pad, (int64_t)T * E, w.kcat, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
-  if (!rc) rc = tc::make_tmap_bf16(&a.wx_hi, w.w, w.in_pad, 4 * kH, w.kcat, 64, wbox, CU_TENSOR_MAP_SWIZZLE_128B);
-  if (!rc) rc = tc::make_tmap_bf16(&a.wx_lo, w.w + p->lo_off, w.in_pad, 4 * kH, w.kcat, 64, wbox, CU_TENSOR_MAP_SWIZZLE_128B);
-  if (!rc) rc = tc::make_tmap_bf16(&a.wh_hi, w.w + w.in_pad, kH, 4 * kH, w.kcat, 64, wbox, CU_TENSOR_MAP_SWIZZLE_128B);
-  if (!rc) rc = tc::make_tmap_bf16(&a.wh_lo, w.w + p->lo_off + w.in_pad, kH, 4 * kH, w.kcat, 64, wbox, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16(&a.wx_hi, w.w, w.in_pad, 4 * kH, w.kcat, 64, HU, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16(&a.wx_lo, w.w + p->lo_off, w.in_pad, 4 * kH, w.kcat, 64, HU, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16(&a.wh_hi, w.w + w.in_pad, kH, 4 * kH, w.kcat, 64, HU, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16(&a.wh_lo, w.w + p->lo_off + w.in_pad, kH, 4 * kH, w.kcat, 64, HU, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.xh_hi, w.xcat + w.in_pad, kH, E, T, w.kcat, 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.xh_lo, w.xcat + p->lo_off + w.in_pad, kH, E, T, w.kcat, 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.hx_hi, n.x, kH, E, T, n.kpad[0], 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.hx_lo, n.x + p->lo_off, kH, E, T, n.kpad[0], 8, 128);
   if (rc) return rc;
   a.bias = w.bias;
-  a.gates = w.gates; a.c_prev = w.c; a.c_new = w.c + (size_t)p->R * kH;
-  a.xcat = w.xcat; a.headx = n.x;
+  a.gates = w.gates; a.c_prev = w.c; a.tanh_c = w.c + (size_t)p->R * kH;
   a.dones = s->dones; a.saved_h = saved_h; a.saved_c = saved_c;
-  a.lo_off = p->lo_off;
-  a.T = T; a.E = E; a.N = s->N; a.env_begin = env_begin; a.kcat = w.kcat; a.in_pad = w.in_pad; a.ld_headx = n.kpad[0];
+  a.T = T; a.E = E; a.N = s->N; a.env_begin = env_begin;
   a.kx_steps = (w.in_pad + 15) / 16;
-  const int tiles = (E + 127) / 128;
-  if (NC == 1) return launch_cluster<1>(lstm_tc_fwd_kernel<1>, tiles, Cfg<1>::kFwdSmem, st, a);
-  if (NC == 2) return launch_cluster<2>(lstm_tc_fwd_kernel<2>, tiles, Cfg<2>::kFwdSmem, st, a);
-  return launch_cluster<4>(lstm_tc_fwd_kernel<4>, tiles, Cfg<4>::kFwdSmem, st, a);
+  return launch_cluster<NC>(lstm_tc_fwd_kernel<NC>, (E + 127) / 128, Cfg<NC>::kFwdSmem, st, a);
 }
 
 int lstm_tc_backward(urlg_policy* p, int k, const urlg_storage* s, int env_begin, int E, cudaStream_t st) {
   LstmWs& w = p->lstm[k];
-  const int NC = lstm_tc_clusters(p, w);
-  const int T = s->T, HU = kH / NC;
-  // W_hh^T image (hi, lo) in the [R, H] fp32 scratch of the per-step path (64 KB needed)
-  if ((int64_t)p->R * kH * (int64_t)sizeof(float) < 4 * kH * kH * 2 * (int64_t)sizeof(bf16))
-    return fail(URLG_EINVAL, "lstm update: max_rows too small for the W_hh^T image");
+  constexpr int NC = 4, HU = kH / NC;
+  const int T = s->T;
+  // W_hh^T image (hi, lo) in the [R, H] fp32 scratch of the per-step path (64 KB, checked by lstm_tc_clusters)
   bf16* img = reinterpret_cast<bf16*>(w.dhrec);
   lstm_tc_wt_image_kernel<<<(4 * kH * kH + 255) / 256, 256, 0, st>>>(p->params + w.off[1], HU, img);
   URLG_LAUNCH_CHECK();
   BwdArgs a = {};
   int rc = tc::make_tmap_bf16(&a.w_hi, img, 4 * kH, kH, 4 * kH, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
   if (!rc) rc = tc::make_tmap_bf16(&a.w_lo, img + 4 * kH * kH, 4 * kH, kH, 4 * kH, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.dh_hi, w.dx_head, kH, E, T, kH, 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.dh_lo, w.dx_head + p->lo_off, kH, E, T, kH, 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.dg_hi, w.dgates, 4 * kH, E, T, 4 * kH, 8, 128);
+  if (!rc) rc = tc::make_tmap_bf16_3d(&a.dg_lo, w.dgates + p->lo_off, 4 * kH, E, T, 4 * kH, 8, 128);
   if (rc) return rc;
-  a.gates = w.gates; a.c_prev = w.c; a.c_new = w.c + (size_t)p->R * kH;
-  a.dh_head = w.dx_head; a.dgates = w.dgates; a.dones = s->dones;
+  a.gates = w.gates; a.c_prev = w.c; a.tanh_c = w.c + (size_t)p->R * kH;
+  a.dones = s->dones;
   a.g_b_ih = p->gacc + w.off[2]; a.g_b_hh = p->gacc + w.off[3];
-  a.lo_off = p->lo_off;
   a.T = T; a.E = E; a.N = s->N; a.env_begin = env_begin;
-  const int tiles = (E + 127) / 128;
-  if (NC == 1) return launch_cluster<1>(lstm_tc_bwd_kernel<1>, tiles, Cfg<1>::kBwdSmem, st, a);
-  if (NC == 2) return launch_cluster<2>(lstm_tc_bwd_kernel<2>, tiles, Cfg<2>::kBwdSmem, st, a);
-  return launch_cluster<4>(lstm_tc_bwd_kernel<4>, tiles, Cfg<4>::kBwdSmem, st, a);
+  return launch_cluster<NC>(lstm_tc_bwd_kernel<NC>, (E + 127) / 128, Cfg<NC>::kBwdSmem, st, a);
 }
 
 }  // namespace urlg

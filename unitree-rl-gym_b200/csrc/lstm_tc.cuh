@@ -21,6 +21,13 @@
 // image; the h / dgates operand tiles are written by the drain warps.  The h tile uses the no-swizzle K-major core
 // matrix layout so a CTA's unit slice is one contiguous block (one bulk copy per peer).
 //
+// All bf16 images leave / enter through TMA: the operand tiles are columns of core matrices ([8-column chunk][128 rows]
+// [16 bytes]), which is exactly the shared-memory side of a {8 columns, 128 rows, 1 step} tensor box, so the h_prev part
+// of the [x | h] image, the h_t image of the MLP head and the dgates image are stored straight out of the tiles the MMAs
+// read, and dL/dh from the head is loaded the same way (3-D maps [step, env, column]: a ragged last tile is clipped per
+// step).  The fp32 state kept for the backward pass (activated gates, c_{t-1}, tanh c_t) uses a private layout
+// [4-column chunk][row][4] per (step, tile, CTA), so every warp access is 512 contiguous bytes.
+//
 // Warp roles (18 warps): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..17 = drains (4 per TMEM lane quarter).
 #pragma once
 #include <cuda.h>
@@ -45,13 +52,13 @@ struct Cfg {
   static constexpr int UT = HU / 4;                 // units per drain thread (4 drain warps per lane quarter)
   static constexpr int WB = NG * 128;               // bytes of one weight tile [NG rows, 64 k] (forward)
   static constexpr int kSliceBytes = HU * 256;      // a CTA's unit slice of a no-swizzle h tile (HU/8 chunks x 2 KB)
-  // forward shared memory: Wx(hi,lo) Wh(hi,lo) | X(hi,lo) | H[2](hi,lo) | bias | barriers
-  static constexpr int kFwdSmem = 4 * WB + 2 * kTileBytes + 4 * kTileBytes + NG * 4 + 128 + 1024;
+  // forward shared memory: Wx(hi,lo) Wh(hi,lo) | X(hi,lo) | H[2](hi,lo) | h_t slice [2](hi,lo) | bias | barriers
+  static constexpr int kFwdSmem = 4 * WB + 2 * kTileBytes + 4 * kTileBytes + 4 * kSliceBytes + NG * 4 + 128 + 1024;
   // backward shared memory: W(hi,lo) [64 units, NG k] | A(hi,lo) dgates tile [128, NG] | staging [2][NC][128][HU] f32 |
-  // reduce [2][NC][128][HU] f32 | barriers
+  // reduce [2][NC][128][HU] f32 | dL/dh_t slice from the head [2](hi,lo) | barriers
   static constexpr int kBlkBytes = 128 * HU * 4;    // one [128, HU] fp32 block of the reduce-scatter
   static constexpr int KB = NG / 64;                // 64-wide K blocks of the backward product (K = NG)
-  static constexpr int kBwdSmem = 2 * KB * 8192 + 2 * KB * kTileBytes + (NC > 1 ? 4 * NC * kBlkBytes : 0) + 128 + 1024;
+  static constexpr int kBwdSmem = 2 * KB * 8192 + 2 * KB * kTileBytes + 4 * NC * kBlkBytes + 4 * kSliceBytes + 128 + 1024;
 };
 
 struct FwdArgs {
@@ -59,23 +66,21 @@ struct FwdArgs {
   CUtensorMap wx_hi, wx_lo;      // W_ih image [256, in_pad] (row pitch kcat), box {64, HU or 256}
   CUtensorMap wh_hi, wh_lo;      // W_hh image [256, 64] (same rows, column offset in_pad), box {64, HU or 256}
   const float* bias;             // [256] b_ih + b_hh
-  float *gates, *c_prev, *c_new; // [T*E, 256], [T*E, 64] x2 (what the backward pass reads)
-  bf16* xcat;                    // [T*E, kcat] image; this kernel writes its h_prev part (columns in_pad..)
-  bf16* headx;                   // [T*E, ld_headx] h_t image = input of the MLP head
+  CUtensorMap xh_hi, xh_lo;      // h_prev part of the [x | h] image as [T, E, 64] (row pitch kcat), box {8, 128, 1}
+  CUtensorMap hx_hi, hx_lo;      // h_t image = input of the MLP head, [T, E, 64] (row pitch ld_headx), box {8, 128, 1}
+  float *gates, *c_prev, *tanh_c;// private layout (see top): activated gates, c_{t-1}, tanh c_t -- read by the backward kernel
   const uint8_t* dones;          // [T, N]
   const float *saved_h, *saved_c;// [T, N, 64] hidden states saved by the rollout
-  int64_t lo_off;
-  int T, E, N, env_begin, kcat, in_pad, ld_headx, kx_steps;
+  int T, E, N, env_begin, kx_steps;
 };
 
 struct BwdArgs {
   CUtensorMap w_hi, w_lo;        // permuted W_hh^T image [64 units, 256 k'], k' = r*NG + g*HU + j; box {64, 64}
-  const float *gates, *c_prev, *c_new;
-  const bf16* dh_head;           // [T*E, 64] image: dL/dh_t from the MLP head
-  bf16* dgates;                  // [T*E, 256] image (A operand of the weight-gradient GEMMs)
+  CUtensorMap dh_hi, dh_lo;      // dL/dh_t from the MLP head as [T, E, 64], box {8, 128, 1}
+  CUtensorMap dg_hi, dg_lo;      // dgates image (A operand of the weight-gradient GEMMs) as [T, E, 256], box {8, 128, 1}
+  const float *gates, *c_prev, *tanh_c;
   const uint8_t* dones;
   long long *g_b_ih, *g_b_hh;    // fixed-point bias gradient accumulators [256]
-  int64_t lo_off;
   int T, E, N, env_begin;
 };
 
@@ -134,7 +139,23 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 }
 __device__ __forceinline__ float lo16(uint32_t p) { return __uint_as_float(p << 16); }
 __device__ __forceinline__ float hi16(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
-__device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
+// ex2.approx / rcp.approx forms: relative error ~1e-6 (sigmoid), absolute error ~3e-7 (tanh) -- far inside the 1e-3
+// update tolerance; the exact expf / tanhf / IEEE-division forms are ~39 instructions each and were a third of the kernel
+__device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_(float x) { return __fdividef(2.0f, 1.0f + __expf(-2.0f * x)) - 1.0f; }
+// {8 columns, 128 rows, 1 step} box <-> 2 KB column of core matrices
+__device__ __forceinline__ void tma_store_3d(const void* tmap, uint32_t src_smem, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src_smem), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const void* tmap, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void tmem_wait_dep(uint32_t (&r)[N]) {
   if constexpr (N == 4) {
@@ -155,25 +176,26 @@ __device__ __forceinline__ void split_pack(const float* v, uint32_t* hi, uint32_
     lo[i] = pack2(v[2 * i] - lo16(hi[i]), v[2 * i + 1] - hi16(hi[i]));
   }
 }
-template <int UT>
-__device__ __forceinline__ void store_image(bf16* img, int64_t lo_off, size_t elem, const uint32_t* hi, const uint32_t* lo) {
-#pragma unroll
-  for (int i = 0; i < UT / 4; ++i) {
-    *reinterpret_cast<uint2*>(img + elem + 4 * i) = make_uint2(hi[2 * i], hi[2 * i + 1]);
-    *reinterpret_cast<uint2*>(img + elem + lo_off + 4 * i) = make_uint2(lo[2 * i], lo[2 * i + 1]);
-  }
+// fp32 state in the private layout: chunk q (4 columns) of a [rows_t, ncols] block -> float4 at ((q * rows_t) + row) * 4
+__device__ __forceinline__ float4* priv4(float* blk, int q, int rows_t, int row) {
+  return reinterpret_cast<float4*>(blk + ((size_t)q * rows_t + row) * 4);
+}
+__device__ __forceinline__ const float4* priv4(const float* blk, int q, int rows_t, int row) {
+  return reinterpret_cast<const float4*>(blk + ((size_t)q * rows_t + row) * 4);
 }
 
 // ================================================================ forward
 template <int NC>
 __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_constant__ FwdArgs P) {
   using C = Cfg<NC>;
-  constexpr int HU = C::HU, NG = C::NG, UT = C::UT, WB = C::WB;
+  constexpr int HU = C::HU, NG = C::NG, UT = C::UT, WB = C::WB, CH = HU / 8;
+  static_assert(UT % 4 == 0, "drain threads move float4 chunks");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t sWx = base, sWh = base + 2 * WB, sX = base + 4 * WB, sH = sX + 2 * kTileBytes;
-  const uint32_t sBias = sH + 4 * kTileBytes;
+  const uint32_t sM = sH + 4 * kTileBytes;                 // h_t slice (hi, lo) x 2 buffers: source of the head-input stores
+  const uint32_t sBias = sM + 4 * C::kSliceBytes;
   const uint32_t bars = sBias + NG * 4;
   const uint32_t wfull = bars, xfull = bars + 8, xempty = bars + 16, hready0 = bars + 24, gfull0 = bars + 40;
   const uint32_t tmem_slot = bars + 56;
@@ -184,12 +206,15 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_c
   const uint32_t r = NC > 1 ? cluster_ctarank() : 0u;
   const int e0 = (blockIdx.x / NC) * 128;
   const int T = P.T, E = P.E;
+  const int rows_t = min(128, E - e0);
   constexpr uint32_t kTmemCols = 2 * NG < 32 ? 32 : 2 * NG;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&P.x_hi); tma_prefetch_desc(&P.x_lo);
     tma_prefetch_desc(&P.wx_hi); tma_prefetch_desc(&P.wx_lo);
     tma_prefetch_desc(&P.wh_hi); tma_prefetch_desc(&P.wh_lo);
+    tma_prefetch_desc(&P.xh_hi); tma_prefetch_desc(&P.xh_lo);
+    tma_prefetch_desc(&P.hx_hi); tma_prefetch_desc(&P.hx_lo);
     mbar_init(wfull, 1); mbar_init(xfull, 1); mbar_init(xempty, 1);
     for (int b = 0; b < 2; ++b) { mbar_init(hready0 + 8 * b, 1); mbar_init(gfull0 + 8 * b, 1); }
     fence_mbar_init();
@@ -270,6 +295,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_c
     const int dw = warp - 2, lq = warp & 3, cg = dw >> 2;
     const int row = lq * 32 + lane, e = e0 + row;
     const bool valid = e < E;
+    const bool elected = dw == 0 && lane == 0;
     const int ul0 = cg * UT, u0 = (int)r * HU + ul0;
     for (int i = dw * 32 + lane; i < NG; i += kDrainThreads) bias_s[i] = P.bias[(i / HU) * kH + (int)r * HU + (i % HU)];
     float c[UT], h[UT];
@@ -283,45 +309,68 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_c
         c[4 * i] = b4.x; c[4 * i + 1] = b4.y; c[4 * i + 2] = b4.z; c[4 * i + 3] = b4.w;
       }
     };
-    // operand of step tn: (h, c) as they enter that step -> own h tile + xcat / c_prev rows, then hand the slice to the peers
-    auto publish = [&](int tn) {
-      const uint32_t nb = (uint32_t)tn & 1u;
+    // bf16 (hi, lo) of this thread's UT units into a column-of-core-matrices tile (unit index `u` within that tile)
+    auto put_tile = [&](uint32_t tile_hi, uint32_t tile_lo, int u, const float* v) {
       uint32_t hi[UT / 2], lo[UT / 2];
-      split_pack<UT>(h, hi, lo);
-      const uint32_t tile = sH + nb * 2 * kTileBytes, off = nosw_offset((uint32_t)row, (uint32_t)u0);
+      split_pack<UT>(v, hi, lo);
+      const uint32_t off = nosw_offset((uint32_t)row, (uint32_t)u);
       if constexpr (UT == 4) {
-        st_shared_v2(tile + off, hi[0], hi[1]);
-        st_shared_v2(tile + kTileBytes + off, lo[0], lo[1]);
+        st_shared_v2(tile_hi + off, hi[0], hi[1]);
+        st_shared_v2(tile_lo + off, lo[0], lo[1]);
       } else {
 #pragma unroll
         for (int q = 0; q < UT / 8; ++q) {
-          st_shared_v4(tile + off + q * 2048, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-          st_shared_v4(tile + kTileBytes + off + q * 2048, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+          st_shared_v4(tile_hi + off + q * 2048, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+          st_shared_v4(tile_lo + off + q * 2048, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
         }
       }
-      if (valid) {
-        const size_t rowg = (size_t)tn * E + e;
-        store_image<UT>(P.xcat, P.lo_off, rowg * P.kcat + P.in_pad + u0, hi, lo);
+    };
+    // End of step tn-1 (tn = 0: prologue; tn = T: epilogue).  (h, c) as they ENTER step tn go into the operand tile, the
+    // h_prev image and the c_prev state; h_{tn-1} (already in the slice tile) goes to the head-input image.
+    auto publish = [&](int tn) {
+      const uint32_t nb = (uint32_t)tn & 1u;
+      const uint32_t tile = sH + nb * 2 * kTileBytes;
+      if (tn < T) {
+        put_tile(tile, tile + kTileBytes, u0, h);
+        if (valid) {
+          float* cp = P.c_prev + ((size_t)tn * E + e0) * kH + (size_t)r * rows_t * HU;
 #pragma unroll
-        for (int i = 0; i < UT / 4; ++i)
-          *reinterpret_cast<float4*>(P.c_prev + rowg * kH + u0 + 4 * i) = make_float4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
+          for (int i = 0; i < UT / 4; ++i) *priv4(cp, cg * (UT / 4) + i, rows_t, row) = make_float4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
+        }
       }
       fence_proxy_async_smem();
+      if (elected) bulk_wait_read0();           // the previous step's tensor stores have finished reading their tiles
       drain_bar_sync();
-      if (dw == 0 && lane == 0) {
-        const uint32_t bar = hready0 + 8 * nb;
-        if constexpr (NC > 1) {
-          mbar_arrive_expect_tx(bar, (uint32_t)(NC - 1) * 2u * C::kSliceBytes);
+      if (elected) {
+        if (tn < T) {
+          const uint32_t bar = hready0 + 8 * nb;
           const uint32_t src = tile + r * C::kSliceBytes;
-          for (uint32_t d = 0; d < (uint32_t)NC; ++d) {
-            if (d == r) continue;
-            const uint32_t rbar = mapa_shared(bar, d);
-            dsmem_bulk_copy(mapa_shared(src, d), src, C::kSliceBytes, rbar);
-            dsmem_bulk_copy(mapa_shared(src + kTileBytes, d), src + kTileBytes, C::kSliceBytes, rbar);
+          if constexpr (NC > 1) {
+            mbar_arrive_expect_tx(bar, (uint32_t)(NC - 1) * 2u * C::kSliceBytes);
+            for (uint32_t d = 0; d < (uint32_t)NC; ++d) {
+              if (d == r) continue;
+              const uint32_t rbar = mapa_shared(bar, d);
+              dsmem_bulk_copy(mapa_shared(src, d), src, C::kSliceBytes, rbar);
+              dsmem_bulk_copy(mapa_shared(src + kTileBytes, d), src + kTileBytes, C::kSliceBytes, rbar);
+            }
+          } else {
+            mbar_arrive(bar);
           }
-        } else {
-          mbar_arrive(bar);
+#pragma unroll
+          for (int q = 0; q < CH; ++q) {            // h_prev part of the [x | h] image, rows of step tn
+            tma_store_3d(&P.xh_hi, src + q * 2048, (int)r * HU + 8 * q, e0, tn);
+            tma_store_3d(&P.xh_lo, src + kTileBytes + q * 2048, (int)r * HU + 8 * q, e0, tn);
+          }
         }
+        if (tn > 0) {
+          const uint32_t m = sM + (uint32_t)((tn - 1) & 1) * 2 * C::kSliceBytes;
+#pragma unroll
+          for (int q = 0; q < CH; ++q) {            // h_{tn-1}: input of the MLP head, rows of step tn-1
+            tma_store_3d(&P.hx_hi, m + q * 2048, (int)r * HU + 8 * q, e0, tn - 1);
+            tma_store_3d(&P.hx_lo, m + C::kSliceBytes + q * 2048, (int)r * HU + 8 * q, e0, tn - 1);
+          }
+        }
+        bulk_commit();
       }
     };
 #pragma unroll
@@ -330,6 +379,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_c
     publish(0);
     for (int t = 0; t < T; ++t) {
       const uint32_t b = (uint32_t)t & 1u;
+      // a done at t starts a new trajectory at t + 1 (fetched before the wait: the byte is off the critical path)
+      const bool reseed = valid && t + 1 < T && P.dones[(size_t)t * P.N + P.env_begin + e] != 0;
       mbar_wait(gfull0 + 8 * b, (t >> 1) & 1);
       tc_fence_after();
       uint32_t rg[4][UT];
@@ -339,37 +390,36 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_fwd_kernel(const __grid_c
 #pragma unroll
       for (int g = 0; g < 4; ++g) tmem_wait_dep<UT>(rg[g]);
       tc_fence_before();
-      float ga[4][UT];
+      float ga[4][UT], tch[UT];
 #pragma unroll
       for (int j = 0; j < UT; ++j) {
         const float ig = sigm(__uint_as_float(rg[0][j]) + bias_s[ul0 + j]);
         const float fg = sigm(__uint_as_float(rg[1][j]) + bias_s[HU + ul0 + j]);
-        const float gg = tanhf(__uint_as_float(rg[2][j]) + bias_s[2 * HU + ul0 + j]);
+        const float gg = tanh_(__uint_as_float(rg[2][j]) + bias_s[2 * HU + ul0 + j]);
         const float og = sigm(__uint_as_float(rg[3][j]) + bias_s[3 * HU + ul0 + j]);
         c[j] = fg * c[j] + ig * gg;
-        h[j] = og * tanhf(c[j]);
+        tch[j] = tanh_(c[j]);
+        h[j] = og * tch[j];
         ga[0][j] = ig; ga[1][j] = fg; ga[2][j] = gg; ga[3][j] = og;
       }
       if (valid) {
-        const size_t rowg = (size_t)t * E + e;
+        float* gb = P.gates + ((size_t)t * E + e0) * 4 * kH + (size_t)r * rows_t * NG;
+        float* tb = P.tanh_c + ((size_t)t * E + e0) * kH + (size_t)r * rows_t * HU;
 #pragma unroll
         for (int g = 0; g < 4; ++g)
 #pragma unroll
           for (int i = 0; i < UT / 4; ++i)
-            *reinterpret_cast<float4*>(P.gates + rowg * 4 * kH + g * kH + u0 + 4 * i) =
-                make_float4(ga[g][4 * i], ga[g][4 * i + 1], ga[g][4 * i + 2], ga[g][4 * i + 3]);
+            *priv4(gb, g * (HU / 4) + cg * (UT / 4) + i, rows_t, row) = make_float4(ga[g][4 * i], ga[g][4 * i + 1], ga[g][4 * i + 2], ga[g][4 * i + 3]);
 #pragma unroll
         for (int i = 0; i < UT / 4; ++i)
-          *reinterpret_cast<float4*>(P.c_new + rowg * kH + u0 + 4 * i) = make_float4(c[4 * i], c[4 * i + 1], c[4 * i + 2], c[4 * i + 3]);
-        uint32_t hi[UT / 2], lo[UT / 2];
-        split_pack<UT>(h, hi, lo);
-        store_image<UT>(P.headx, P.lo_off, rowg * P.ld_headx + u0, hi, lo);
+          *priv4(tb, cg * (UT / 4) + i, rows_t, row) = make_float4(tch[4 * i], tch[4 * i + 1], tch[4 * i + 2], tch[4 * i + 3]);
       }
-      if (t + 1 < T) {
-        if (valid && P.dones[(size_t)t * P.N + P.env_begin + e]) seed_from(t + 1);    // a new trajectory starts at t + 1
-        publish(t + 1);
-      }
+      const uint32_t m = sM + b * 2 * C::kSliceBytes;
+      put_tile(m, m + C::kSliceBytes, ul0, h);
+      if (reseed) seed_from(t + 1);
+      publish(t + 1);
     }
+    if (elected) bulk_wait_all0();
   }
   tc_fence_before();
   __syncthreads();
@@ -395,32 +445,38 @@ lstm_tc_wt_image_kernel(const float* __restrict__ W_hh, int HU, bf16* __restrict
 template <int NC>
 __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_constant__ BwdArgs P) {
   using C = Cfg<NC>;
-  constexpr int HU = C::HU, NG = C::NG, UT = C::UT, KB = C::KB;
+  constexpr int HU = C::HU, NG = C::NG, UT = C::UT, KB = C::KB, CH = HU / 8;
   constexpr uint32_t kBlk = C::kBlkBytes;
+  static_assert(NC > 1 && UT % 4 == 0, "the backward kernel exchanges partial sums across a cluster");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t sW = base, sA = sW + 2 * KB * 8192, sStage = sA + 2 * KB * kTileBytes;
-  const uint32_t sRed = sStage + (NC > 1 ? 2 * NC * kBlk : 0);
-  const uint32_t bars = sRed + (NC > 1 ? 2 * NC * kBlk : 0);
-  const uint32_t wfull = bars, aready = bars + 8, dfull = bars + 16, rready0 = bars + 24, tmem_slot = bars + 40;
+  const uint32_t sRed = sStage + 2 * NC * kBlk;
+  const uint32_t sDh = sRed + 2 * NC * kBlk;             // dL/dh_t slice from the head (hi, lo) x 2 buffers
+  const uint32_t bars = sDh + 4 * C::kSliceBytes;
+  const uint32_t wfull = bars, aready = bars + 8, dfull = bars + 16, rready0 = bars + 24, dhfull0 = bars + 40;
+  const uint32_t tmem_slot = bars + 56;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t r = NC > 1 ? cluster_ctarank() : 0u;
+  const uint32_t r = cluster_ctarank();
   const int e0 = (blockIdx.x / NC) * 128;
   const int T = P.T, E = P.E;
+  const int rows_t = min(128, E - e0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&P.w_hi); tma_prefetch_desc(&P.w_lo);
+    tma_prefetch_desc(&P.dh_hi); tma_prefetch_desc(&P.dh_lo);
+    tma_prefetch_desc(&P.dg_hi); tma_prefetch_desc(&P.dg_lo);
     mbar_init(wfull, 1); mbar_init(aready, 1); mbar_init(dfull, 1);
-    mbar_init(rready0, 1); mbar_init(rready0 + 8, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(rready0 + 8 * b, 1); mbar_init(dhfull0 + 8 * b, 1); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 64);
   tc_fence_before();
   __syncthreads();
-  if constexpr (NC > 1) cluster_sync_all();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -440,17 +496,14 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_c
         mbar_wait(aready, s & 1);
         tc_fence_after();
 #pragma unroll
-        for (int kb = 0; kb < KB; ++kb) {
-          const uint32_t ah = sA + kb * kTileBytes, al = sA + (KB + kb) * kTileBytes;
-          const uint32_t bh = sW + kb * 8192, bl = sW + (KB + kb) * 8192;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t ad = make_sdesc_sw128(ah + k * 32, 16, 1024), ald = make_sdesc_sw128(al + k * 32, 16, 1024);
-            const uint64_t bd = make_sdesc_sw128(bh + k * 32, 16, 1024), bld = make_sdesc_sw128(bl + k * 32, 16, 1024);
-            umma_bf16(tmem_base, ad, bd, idesc, (kb | k) ? 1u : 0u);
-            umma_bf16(tmem_base, ald, bd, idesc, 1u);
-            umma_bf16(tmem_base, ad, bld, idesc, 1u);
-          }
+        for (int k = 0; k < NG / 16; ++k) {            // A: columns of core matrices (2 KB per 8 k); W: SWIZZLE_128B blocks of 64 k
+          const uint32_t ah = sA + k * 4096, al = sA + KB * kTileBytes + k * 4096;
+          const uint32_t bh = sW + (k >> 2) * 8192 + (k & 3) * 32, bl = bh + KB * 8192;
+          const uint64_t ad = make_sdesc_nosw(ah, 2048, 128), ald = make_sdesc_nosw(al, 2048, 128);
+          const uint64_t bd = make_sdesc_sw128(bh, 16, 1024), bld = make_sdesc_sw128(bl, 16, 1024);
+          umma_bf16(tmem_base, ad, bd, idesc, k ? 1u : 0u);
+          umma_bf16(tmem_base, ald, bd, idesc, 1u);
+          umma_bf16(tmem_base, ad, bld, idesc, 1u);
         }
         umma_commit(dfull);
       }
@@ -459,38 +512,65 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_c
     const int dw = warp - 2, lq = warp & 3, cg = dw >> 2;
     const int row = lq * 32 + lane, e = e0 + row;
     const bool valid = e < E;
+    const bool elected = dw == 0 && lane == 0;
     const int ul0 = cg * UT, u0 = (int)r * HU + ul0;
     float dc[UT], dh_rec[UT], bsum[4][UT];
 #pragma unroll
     for (int j = 0; j < UT; ++j) { dc[j] = 0.0f; dh_rec[j] = 0.0f; bsum[0][j] = bsum[1][j] = bsum[2][j] = bsum[3][j] = 0.0f; }
-    // inputs of a step (prefetched one step ahead, while the previous step's product is in flight)
-    float ga[4][UT], cp[UT], cn[UT], dhh[UT];
+    // dL/dh_t from the head: this CTA's unit slice of step t, TMA -> columns of core matrices, two steps in flight
+    auto load_dh = [&](int t, uint32_t buf) {
+      const uint32_t bar = dhfull0 + 8 * buf, dst = sDh + buf * 2 * C::kSliceBytes;
+      mbar_arrive_expect_tx(bar, 2u * C::kSliceBytes);
+#pragma unroll
+      for (int q = 0; q < CH; ++q) {
+        tma_load_3d(dst + q * 2048, &P.dh_hi, bar, (int)r * HU + 8 * q, e0, t);
+        tma_load_3d(dst + C::kSliceBytes + q * 2048, &P.dh_lo, bar, (int)r * HU + 8 * q, e0, t);
+      }
+    };
+    if (elected) {
+      load_dh(T - 1, 0);
+      if (T > 1) load_dh(T - 2, 1);
+    }
+    // saved state of a step (private layout), prefetched one step ahead while the previous step's product is in flight
+    float ga[4][UT], cp[UT], tch[UT];
     bool carry = false;
     auto load_step = [&](int t) {
       carry = false;
       if (!valid) return;
-      const size_t rowg = (size_t)t * E + e;
+      const float* gb = P.gates + ((size_t)t * E + e0) * 4 * kH + (size_t)r * rows_t * NG;
+      const float* cb = P.c_prev + ((size_t)t * E + e0) * kH + (size_t)r * rows_t * HU;
+      const float* tb = P.tanh_c + ((size_t)t * E + e0) * kH + (size_t)r * rows_t * HU;
 #pragma unroll
       for (int i = 0; i < UT / 4; ++i) {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          const float4 v = *reinterpret_cast<const float4*>(P.gates + rowg * 4 * kH + g * kH + u0 + 4 * i);
+          const float4 v = *priv4(gb, g * (HU / 4) + cg * (UT / 4) + i, rows_t, row);
           ga[g][4 * i] = v.x; ga[g][4 * i + 1] = v.y; ga[g][4 * i + 2] = v.z; ga[g][4 * i + 3] = v.w;
         }
-        const float4 a = *reinterpret_cast<const float4*>(P.c_prev + rowg * kH + u0 + 4 * i);
-        const float4 b = *reinterpret_cast<const float4*>(P.c_new + rowg * kH + u0 + 4 * i);
+        const float4 a = *priv4(cb, cg * (UT / 4) + i, rows_t, row);
+        const float4 b = *priv4(tb, cg * (UT / 4) + i, rows_t, row);
         cp[4 * i] = a.x; cp[4 * i + 1] = a.y; cp[4 * i + 2] = a.z; cp[4 * i + 3] = a.w;
-        cn[4 * i] = b.x; cn[4 * i + 1] = b.y; cn[4 * i + 2] = b.z; cn[4 * i + 3] = b.w;
-        const uint2 hh = *reinterpret_cast<const uint2*>(P.dh_head + rowg * kH + u0 + 4 * i);
-        const uint2 hl = *reinterpret_cast<const uint2*>(P.dh_head + P.lo_off + rowg * kH + u0 + 4 * i);
-        dhh[4 * i] = lo16(hh.x) + lo16(hl.x); dhh[4 * i + 1] = hi16(hh.x) + hi16(hl.x);
-        dhh[4 * i + 2] = lo16(hh.y) + lo16(hl.y); dhh[4 * i + 3] = hi16(hh.y) + hi16(hl.y);
+        tch[4 * i] = b.x; tch[4 * i + 1] = b.y; tch[4 * i + 2] = b.z; tch[4 * i + 3] = b.w;
       }
       carry = t < T - 1 && P.dones[(size_t)t * P.N + P.env_begin + e] == 0;   // a done at t cuts the gradient from t+1
     };
     load_step(T - 1);
-    int s = 0;
-    for (int t = T - 1; t >= 0; --t) {
+    for (int t = T - 1, s = 0; t >= 0; --t, ++s) {
+      const uint32_t pb = (uint32_t)s & 1u;
+      // ---- dgates of step t ----
+      mbar_wait(dhfull0 + 8 * pb, (s >> 1) & 1);
+      float dhh[UT];
+      {
+        const uint32_t a = sDh + pb * 2 * C::kSliceBytes + nosw_offset((uint32_t)row, (uint32_t)ul0);
+#pragma unroll
+        for (int q = 0; q < UT / 4; ++q) {
+          uint2 hh, hl;
+          asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(hh.x), "=r"(hh.y) : "r"(a + 8 * q) : "memory");
+          asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(hl.x), "=r"(hl.y) : "r"(a + C::kSliceBytes + 8 * q) : "memory");
+          dhh[4 * q] = lo16(hh.x) + lo16(hl.x); dhh[4 * q + 1] = hi16(hh.x) + hi16(hl.x);
+          dhh[4 * q + 2] = lo16(hh.y) + lo16(hl.y); dhh[4 * q + 3] = hi16(hh.y) + hi16(hl.y);
+        }
+      }
       float pg[4][UT];
 #pragma unroll
       for (int j = 0; j < UT; ++j) {
@@ -499,9 +579,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_c
           const float dh = dhh[j] + (carry ? dh_rec[j] : 0.0f);
           const float dcn_in = carry ? dc[j] : 0.0f;
           const float ig = ga[0][j], fg = ga[1][j], gg = ga[2][j], og = ga[3][j];
-          const float tch = tanhf(cn[j]);
-          const float d_o = dh * tch;
-          const float dcn = dcn_in + dh * og * (1.0f - tch * tch);
+          const float th = tch[j];
+          const float d_o = dh * th;
+          const float dcn = dcn_in + dh * og * (1.0f - th * th);
           const float di = dcn * gg, dgg = dcn * ig, df = dcn * cp[j];
           dc[j] = dcn * fg;
           pi = di * ig * (1.0f - ig); pf = df * fg * (1.0f - fg); pgg = dgg * (1.0f - gg * gg); po = d_o * og * (1.0f - og);
@@ -509,84 +589,75 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_c
         pg[0][j] = pi; pg[1][j] = pf; pg[2][j] = pgg; pg[3][j] = po;
         bsum[0][j] += pi; bsum[1][j] += pf; bsum[2][j] += pgg; bsum[3][j] += po;
       }
-      uint32_t hi[4][UT / 2], lo[4][UT / 2];
-#pragma unroll
-      for (int g = 0; g < 4; ++g) split_pack<UT>(pg[g], hi[g], lo[g]);
-      if (valid) {
-        const size_t rowg = (size_t)t * E + e;
-#pragma unroll
-        for (int g = 0; g < 4; ++g) store_image<UT>(P.dgates, P.lo_off, rowg * 4 * kH + g * kH + u0, hi[g], lo[g]);
-      }
-      if (t == 0) break;
-      // ---- A tile: dgates of the CTA's columns, k = g*HU + local unit, SWIZZLE_128B K-major blocks of 64 ----
+      // ---- A tile (columns of core matrices, k = g*HU + local unit): MMA operand AND source of the dgates image ----
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        const int k = g * HU + ul0;
-        const uint32_t blk = (uint32_t)(k >> 6), kk = (uint32_t)(k & 63);
-        const uint32_t th = sA + blk * kTileBytes, tl = sA + (KB + blk) * kTileBytes;
+        uint32_t hi[UT / 2], lo[UT / 2];
+        split_pack<UT>(pg[g], hi, lo);
+        const uint32_t off = nosw_offset((uint32_t)row, (uint32_t)(g * HU + ul0));
         if constexpr (UT == 4) {
-          const uint32_t o = sw128_offset((uint32_t)row, kk >> 3) + (kk & 7u) * 2u;
-          st_shared_v2(th + o, hi[g][0], hi[g][1]);
-          st_shared_v2(tl + o, lo[g][0], lo[g][1]);
+          st_shared_v2(sA + off, hi[0], hi[1]);
+          st_shared_v2(sA + KB * kTileBytes + off, lo[0], lo[1]);
         } else {
 #pragma unroll
           for (int q = 0; q < UT / 8; ++q) {
-            const uint32_t o = sw128_offset((uint32_t)row, (kk >> 3) + q);
-            st_shared_v4(th + o, hi[g][4 * q], hi[g][4 * q + 1], hi[g][4 * q + 2], hi[g][4 * q + 3]);
-            st_shared_v4(tl + o, lo[g][4 * q], lo[g][4 * q + 1], lo[g][4 * q + 2], lo[g][4 * q + 3]);
+            st_shared_v4(sA + off + q * 2048, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+            st_shared_v4(sA + KB * kTileBytes + off + q * 2048, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
           }
         }
       }
       fence_proxy_async_smem();
       drain_bar_sync();
-      if (dw == 0 && lane == 0) mbar_arrive(aready);
+      if (elected) {
+        if (t > 0) mbar_arrive(aready);
+#pragma unroll
+        for (int ch = 0; ch < NG / 8; ++ch) {            // chunk ch = columns g*64 + r*HU + (8ch mod HU) of the dgates image
+          const int g = (8 * ch) / HU, ul = (8 * ch) % HU;
+          tma_store_3d(&P.dg_hi, sA + ch * 2048, g * kH + (int)r * HU + ul, e0, t);
+          tma_store_3d(&P.dg_lo, sA + KB * kTileBytes + ch * 2048, g * kH + (int)r * HU + ul, e0, t);
+        }
+        bulk_commit();
+        if (t >= 2) load_dh(t - 2, pb);                  // everyone has read buffer pb (barrier above)
+      }
+      if (t == 0) break;
       load_step(t - 1);                                  // overlaps the product
       mbar_wait(dfull, s & 1);
       tc_fence_after();
-      if constexpr (NC == 1) {
-        uint32_t rr[UT];
-        tmem_ldN<UT>(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)u0, rr);
-        tmem_wait_dep<UT>(rr);
-        tc_fence_before();
+      // partial dL/dh_{t-1}[row, 16cg .. 16cg+16) -> the block of the CTA that owns those units
+      uint32_t rr[16];
+      tmem_ld16_issue(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(16 * cg), rr);
+      tmem_ld_wait_dep(rr);
+      tc_fence_before();
+      const uint32_t dest = (uint32_t)(16 * cg) / HU, within = (uint32_t)(16 * cg) % HU;
+      const uint32_t sp = sStage + (pb * NC + dest) * kBlk + (uint32_t)row * (HU * 4) + within * 4;
 #pragma unroll
-        for (int j = 0; j < UT; ++j) dh_rec[j] = __uint_as_float(rr[j]);
-      } else {
-        // partial dL/dh_{t-1}[row, 16cg .. 16cg+16) -> the block of the CTA that owns those units
-        const uint32_t pb = (uint32_t)s & 1u;
-        uint32_t rr[16];
-        tmem_ld16_issue(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(16 * cg), rr);
-        tmem_ld_wait_dep(rr);
-        tc_fence_before();
-        const uint32_t dest = (uint32_t)(16 * cg) / HU, within = (uint32_t)(16 * cg) % HU;
-        const uint32_t sp = sStage + (pb * NC + dest) * kBlk + (uint32_t)row * (HU * 4) + within * 4;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) st_shared_v4(sp + 16 * q, rr[4 * q], rr[4 * q + 1], rr[4 * q + 2], rr[4 * q + 3]);
-        fence_proxy_async_smem();
-        drain_bar_sync();
-        const uint32_t bar = rready0 + 8 * pb;
-        if (dw == 0 && lane == 0) {
-          mbar_arrive_expect_tx(bar, (uint32_t)(NC - 1) * kBlk);
-          for (uint32_t d = 0; d < (uint32_t)NC; ++d) {
-            if (d == r) continue;
-            dsmem_bulk_copy(mapa_shared(sRed + (pb * NC + r) * kBlk, d), sStage + (pb * NC + d) * kBlk, kBlk, mapa_shared(bar, d));
-          }
-        }
-        mbar_wait(bar, (s >> 1) & 1);
-#pragma unroll
-        for (int j = 0; j < UT; ++j) dh_rec[j] = 0.0f;
-#pragma unroll
-        for (uint32_t src = 0; src < (uint32_t)NC; ++src) {     // fixed order: the sum does not depend on arrival order
-          const uint32_t blk = (src == r ? sStage : sRed) + (pb * NC + src) * kBlk + (uint32_t)row * (HU * 4) + (uint32_t)ul0 * 4;
-#pragma unroll
-          for (int q = 0; q < UT / 4; ++q) {
-            const uint4 v = ld_shared_v4(blk + 16 * q);
-            dh_rec[4 * q] += __uint_as_float(v.x); dh_rec[4 * q + 1] += __uint_as_float(v.y);
-            dh_rec[4 * q + 2] += __uint_as_float(v.z); dh_rec[4 * q + 3] += __uint_as_float(v.w);
-          }
+      for (int q = 0; q < 4; ++q) st_shared_v4(sp + 16 * q, rr[4 * q], rr[4 * q + 1], rr[4 * q + 2], rr[4 * q + 3]);
+      fence_proxy_async_smem();
+      if (elected) bulk_wait_read0();                    // the dgates stores have finished reading the A tile
+      drain_bar_sync();
+      const uint32_t bar = rready0 + 8 * pb;
+      if (elected) {
+        mbar_arrive_expect_tx(bar, (uint32_t)(NC - 1) * kBlk);
+        for (uint32_t d = 0; d < (uint32_t)NC; ++d) {
+          if (d == r) continue;
+          dsmem_bulk_copy(mapa_shared(sRed + (pb * NC + r) * kBlk, d), sStage + (pb * NC + d) * kBlk, kBlk, mapa_shared(bar, d));
         }
       }
-      ++s;
+      mbar_wait(bar, (s >> 1) & 1);
+#pragma unroll
+      for (int j = 0; j < UT; ++j) dh_rec[j] = 0.0f;
+#pragma unroll
+      for (uint32_t src = 0; src < (uint32_t)NC; ++src) {     // fixed order: the sum does not depend on arrival order
+        const uint32_t blk = (src == r ? sStage : sRed) + (pb * NC + src) * kBlk + (uint32_t)row * (HU * 4) + (uint32_t)ul0 * 4;
+#pragma unroll
+        for (int q = 0; q < UT / 4; ++q) {
+          const uint4 v = ld_shared_v4(blk + 16 * q);
+          dh_rec[4 * q] += __uint_as_float(v.x); dh_rec[4 * q + 1] += __uint_as_float(v.y);
+          dh_rec[4 * q + 2] += __uint_as_float(v.z); dh_rec[4 * q + 3] += __uint_as_float(v.w);
+        }
+      }
     }
+    if (elected) bulk_wait_all0();
     // bias gradients: sum over the warp's 32 rows, one fixed-point atomic per (warp, gate unit)
 #pragma unroll
     for (int g = 0; g < 4; ++g)
@@ -602,7 +673,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_tc_bwd_kernel(const __grid_c
   }
   tc_fence_before();
   __syncthreads();
-  if constexpr (NC > 1) cluster_sync_all();
+  cluster_sync_all();
   if (warp == 1) tmem_dealloc(tmem_base, 64);
 }
 

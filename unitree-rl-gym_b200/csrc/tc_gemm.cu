@@ -44,6 +44,26 @@ int make_tmap_bf16(CUtensorMap* out, const void* ptr, int64_t inner, int64_t out
   return URLG_OK;
 }
 
+// bf16 tensor [steps, rows, inner] (row pitch ld elements, step pitch rows*ld): box {box_inner, box_rows, 1}, no swizzle.
+// The LSTM recurrence moves per-step [128 rows, 8 columns] core-matrix columns with it; rows past `rows` are clipped
+// (stores) / zero-filled (loads) per step, so a ragged last tile never touches the next step's rows.
+int make_tmap_bf16_3d(CUtensorMap* out, const void* ptr, int64_t inner, int64_t rows, int64_t steps, int64_t ld, int box_inner,
+                      int box_rows) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  if (((uintptr_t)ptr & 15) || ((ld * 2) & 15))
+    return fail(URLG_EINVAL, "tensor map: base must be 16-byte aligned and row pitch a multiple of 16 bytes (ld=%lld)", (long long)ld);
+  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)steps};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows * (cuuint64_t)ld * 2};
+  cuuint32_t box[3] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(URLG_ECUDA, "cuTensorMapEncodeTiled (3-D) failed with CUresult %d", (int)r);
+  return URLG_OK;
+}
+
 // Optional per-launch timing (bench.py's roofline leg): CUDA events recorded on the launching stream around every
 // tensor-core launch (GEMM or fused forward) while enabled -- never under graph capture -- summed on read.  One launch
 // per bracket, in situ: the stream stays busy (the host enqueues faster than these kernels run), so a bracket is the
