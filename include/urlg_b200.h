@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define URLG_ABI_VERSION 2
+#define URLG_ABI_VERSION 3
 #define URLG_MAX_DOF 16
 #define URLG_MAX_IDX 16
 #define URLG_MAX_TERMS 32
@@ -244,10 +244,17 @@ typedef struct urlg_gemm_desc {
    * leading dimension as out_f32 / colsum. */
   int64_t* out_fx;
   int64_t* colsum_fx;
+  /* Split-K without atomics: when out_part is set, split z of the K range stores its fp32 partial tile into
+   * out_part[z][M][ld_f32] (plain stores; k_splits > 1 allowed without URLG_GEMM_ATOMIC) and the caller sums the
+   * urlg_tc_gemm_splits(K, k_splits) slabs in split order -- bit-reproducible like out_fx, without the 64-bit atomics.
+   * Takes precedence over out_f32 / out_fx. */
+  float* out_part;
 } urlg_gemm_desc;
 #define URLG_FX_SHIFT 40          /* gradient accumulators: resolution 2^-40 = 9.1e-13, range +-8.4e6 */
 #define URLG_FX_STAT_SHIFT 30     /* loss / KL sums: resolution 9.3e-10, range +-8.6e9 */
 int urlg_tc_gemm(const urlg_gemm_desc* desc, void* stream);
+/* The number of K splits a launch with this K and requested k_splits really uses (splits cover whole 64-wide k-blocks). */
+int urlg_tc_gemm_splits(int K, int k_splits);
 /* n (1..4) independent problems in ONE launch: their tiles form one persistent tile space, so e.g. the same layer of the
  * actor and of the critic, or a layer's data and weight gradients, share a launch's fixed cost (~4 us) and fill each
  * other's wave tails.  All problems must use the same operand mode (hi+lo pairs or plain bf16); results are those of n

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(L, s), f"{s} declared in include/urlg_b200.h but not exported"
         assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in _lib.py"
-    assert L.urlg_version() == 2
+    assert L.urlg_version() == _lib.ABI_VERSION == 3
 
 
 def test_struct_sizes_match_header():

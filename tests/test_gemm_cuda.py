@@ -152,3 +152,25 @@ def test_group_rejects_bad_counts_and_mixed_modes():
     two[1].A_lo, two[1].B_lo = None, None                           # plain bf16 next to a hi+lo problem
     assert L.urlg_tc_gemm_group(two, 2, _lib.cur_stream()) != 0
     assert b"operand mode" in L.urlg_last_error()
+
+
+def test_split_k_partial_slabs_sum_to_the_product_and_are_reproducible():
+    """out_part mode: every K split stores its fp32 partial tile into slab z of out_part[splits][M][ld] (no atomics, no
+    flag needed); the slabs summed in split order equal the fp64 product, and two launches give bit-identical slabs."""
+    from unitree_rl_gym_b200 import _lib
+    L = _lib.lib()
+    for (M, N, K, ks) in ((256, 48, 3000, 7), (12, 128, 1000, 96), (130, 200, 640, 3)):
+        p = Problem("wgrad", M, N, K, 31)
+        eff = L.urlg_tc_gemm_splits(K, ks)
+        assert 1 <= eff <= ks
+        part = torch.full((eff, M, N), float("nan"), device="cuda")
+        p.d.flags, p.d.k_splits, p.d.out_f32, p.d.out_part = 0, ks, None, part.data_ptr()
+        _lib.check(L.urlg_tc_gemm(C.byref(p.d), _lib.cur_stream()))
+        torch.cuda.synchronize()
+        first = part.clone()
+        assert not torch.isnan(first).any(), "every slab element must be written"
+        check(p, first.double().sum(0))
+        part.fill_(float("nan"))
+        _lib.check(L.urlg_tc_gemm(C.byref(p.d), _lib.cur_stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(part, first)

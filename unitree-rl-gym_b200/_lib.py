@@ -12,7 +12,7 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("URLG_LIB_PATH") or os.path.join(CSRC, "liburlg_b200.so")     # override: A/B builds
 
 MAX_DOF, MAX_IDX, MAX_TERMS, MAX_OBS, MAX_FEET = 16, 16, 32, 128, 4
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class EnvDesc(C.Structure):
@@ -79,7 +79,7 @@ class GemmDesc(C.Structure):
         ("out_f32", _P), ("ld_f32", C.c_int32), ("out_bf16", _P), ("ld_bf16", C.c_int32),
         ("bias", _P), ("dact_ref", _P), ("ld_ref", C.c_int32), ("colsum", _P), ("flags", C.c_int32),
         ("A_lo", _P), ("B_lo", _P), ("out_bf16_lo", _P), ("dact_ref_lo", _P), ("max_ctas", C.c_int32),
-        ("out_fx", _P), ("colsum_fx", _P),
+        ("out_fx", _P), ("colsum_fx", _P), ("out_part", _P),
     ]
 
 
@@ -146,6 +146,7 @@ SIGNATURES = {
                                      C.c_int64, C.c_void_p]),
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
     "urlg_tc_gemm_group": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_void_p]),
+    "urlg_tc_gemm_splits": (C.c_int, [C.c_int, C.c_int]),
     "urlg_gemm_timing": (C.c_int, [C.c_int]),
     "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                        C.POINTER(C.c_double)]),

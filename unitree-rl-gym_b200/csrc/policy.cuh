@@ -64,6 +64,15 @@ struct urlg_policy {
   // between minibatches); every gradient / loss-sum contribution of a minibatch is an integer atomic add into it, and
   // grads_finalize_kernel converts it into the flat fp32 gradient + the four per-minibatch sums and re-zeroes it
   long long* gacc;
+  // split-K weight gradients of the MLPs: every split stores its fp32 partial tile into its own slab of wpart
+  // (library-owned) and grads_finalize_kernel sums the slabs in split order -- as reproducible as the integer atomics,
+  // without their cost (ncu: 30 % of the backward launches' stall samples sat on the 64-bit REDs).  wpart_off[net][l] =
+  // float offset of layer l's slabs (sized for the largest split count at create), wpart_splits = splits of the
+  // pending minibatch (0 = this layer accumulated into gacc instead)
+  float* wpart;
+  int64_t wpart_off[2][URLG_MAX_LAYERS];
+  int wpart_cap[2][URLG_MAX_LAYERS];
+  int wpart_splits[2][URLG_MAX_LAYERS];
 };
 
 namespace urlg {

@@ -339,7 +339,7 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     delete p;
     return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
   }
-  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr;
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr; p->wpart = nullptr;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {
@@ -351,6 +351,29 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     urlg_policy_destroy(p);
     return fail(URLG_ECUDA, "urlg_policy_create: gradient accumulators: %s", cudaGetErrorString(cudaGetLastError()));
   }
+  {
+    // slabs for the split-K weight-gradient partials: a wgrad is split so that tiles x splits fills one wave of the
+    // persistent grid (ppo_kernels.cu wgrad_desc), i.e. at most kNumSMs / tiles splits of [out, in] floats per layer
+    int64_t total_f = 0;
+    for (int q = 0; q < 2; ++q) {
+      const urlg_mlp_desc& m = p->net[q].d;
+      for (int l = 0; l < URLG_MAX_LAYERS; ++l) { p->wpart_off[q][l] = 0; p->wpart_cap[q][l] = 0; p->wpart_splits[q][l] = 0; }
+      for (int l = 0; l < m.num_layers; ++l) {
+        const int nout = m.dims[l + 1], nin = m.dims[l];
+        const int bn = nin > 128 ? 128 : round_up(nin, 64);
+        const int tiles = ((nout + 127) / 128) * ((nin + bn - 1) / bn);
+        const int cap = tiles >= kNumSMs ? 1 : kNumSMs / tiles;
+        p->wpart_off[q][l] = total_f;
+        p->wpart_cap[q][l] = cap;
+        total_f += ((int64_t)cap * nout * nin + 3) / 4 * 4;
+      }
+    }
+    if (total_f > 0 && cudaMalloc(&p->wpart, (size_t)total_f * sizeof(float)) != cudaSuccess) {
+      urlg_policy_destroy(p);
+      return fail(URLG_ECUDA, "urlg_policy_create: weight-gradient partial slabs (%lld MB): %s",
+                  (long long)(total_f * 4 >> 20), cudaGetErrorString(cudaGetLastError()));
+    }
+  }
   if (int rc2 = fused_build(p)) { urlg_policy_destroy(p); return rc2; }
   *out = p;
   return URLG_OK;
@@ -360,6 +383,7 @@ extern "C" void urlg_policy_destroy(urlg_policy* p) {
   if (!p) return;
   fused_free(p);
   if (p->gacc) cudaFree(p->gacc);
+  if (p->wpart) cudaFree(p->wpart);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);

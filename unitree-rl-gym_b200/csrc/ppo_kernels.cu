@@ -5,8 +5,9 @@
 //   ppo_head_kernel     Gaussian log-prob / entropy / KL / clipped surrogate / clipped value loss and their
 //                       gradients wrt mu, value and std; last-layer bias gradients; loss sums
 //   backward            dgrad + wgrad on the tcgen05 GEMM (MN-major operands, ELU' and bias-gradient
-//                       column sums fused in the dgrad epilogue, split-K fp32 atomics for wgrad)
-//   apply               grad-norm, device-side adaptive-KL learning rate, clip, Adam, bf16 weight images
+//                       column sums fused in the dgrad epilogue, split-K partial slabs for wgrad summed in split
+//                       order by grads_finalize_kernel: bit-reproducible without atomics)
+//   apply               grad-norm, device-side adaptive-KL learning rate, clip, Adam + bf16 weight images
 #include "policy.cuh"
 
 namespace urlg {
@@ -217,15 +218,28 @@ static urlg_gemm_desc wgrad_desc(urlg_policy* p, NetWs& n, int l, int64_t rows) 
   const int bn = nin > 256 ? 256 : round_up(nin, 64);
   g.block_n = bn;
   // split K so that tiles x splits fills ONE wave of the persistent grid (split-bf16 tiles are at most 128 wide):
-  // measured on B200, one wave beats two (wgrad1 23.0 vs 25.8 us, wgrad0 12.1 vs 13.6): half the fp32 atomics
+  // measured on B200, one wave beats two (wgrad1 23.0 vs 25.8 us, wgrad0 12.1 vs 13.6): half the partial tiles
   // and twice the k-blocks per tile to pipeline
   const int bn_eff = bn > 128 ? 128 : bn;
   const int tiles = ((nout + 127) / 128) * ((nin + bn_eff - 1) / bn_eff);
-  int splits = kNumSMs / tiles;
+  // the wgrads of BOTH networks of a level share the wave (mlp_backward_pair): tiles x splits x 2 ~ one wave.  Measured
+  // (Go2 minibatch): same launch times as per-problem one-wave splits, half the partial-slab volume for the finalize
+  static const int share = []() { const char* e = getenv("URLG_WGRAD_SHARE"); return e ? atoi(e) : 2; }();
+  int splits = kNumSMs / (tiles * (share > 0 ? share : 1));
   const int kblocks = (int)((rows + 63) / 64);
   if (splits > kblocks / 4) splits = kblocks / 4;
   if (splits < 1) splits = 1;
   g.k_splits = splits;
+  // partial slabs instead of atomics (policy.cuh wpart): grads_finalize_kernel sums them in split order
+  const int q = &n == &p->net[0] ? 0 : &n == &p->net[1] ? 1 : -1;
+  if (q >= 0 && p->wpart) {
+    const int eff = urlg_tc_gemm_splits((int)rows, splits);
+    if (eff <= p->wpart_cap[q][l]) {
+      g.out_part = p->wpart + p->wpart_off[q][l];
+      g.out_fx = nullptr;
+      p->wpart_splits[q][l] = eff;
+    }
+  }
   with_lo(p, g);
   return g;
 }
@@ -360,16 +374,95 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   }
 }
 
+// Adam + the bf16 (hi, lo) operand images of the weights it has just updated, in one pass (feed-forward policies): the
+// thread that owns parameter i also owns its image element (the K-padding columns of an image are zero from the full
+// sync at create / load and never change), so the separate weight_images launch after every optimiser step is gone.
+struct WImgSeg { long long off; int n, cols, ld; bf16* dst; };
+struct WImgTable { WImgSeg s[2 * URLG_MAX_LAYERS]; int num; };
+__global__ void __launch_bounds__(256)
+adam_images_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
+                   const float* __restrict__ stats, const urlg_ppo_hparams hp, const __grid_constant__ WImgTable wt,
+                   int64_t lo_off) {
+  const float lr = stats[URLG_STAT_LR];
+  const float gs = hp.grad_scale * stats[URLG_STAT_CLIP_COEF];
+  const float step_size = lr / stats[URLG_STAT_BC1];
+  const float bc2_sqrt = sqrtf(stats[URLG_STAT_BC2]);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gs;
+    const float mi = m[i] + (gi - m[i]) * (1.0f - hp.beta1);
+    const float vi = v[i] * hp.beta2 + (1.0f - hp.beta2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + hp.eps;
+    const float pn = p[i] - step_size * (mi / denom);
+    p[i] = pn;
+#pragma unroll 1
+    for (int k = 0; k < wt.num; ++k) {
+      const long long j = i - wt.s[k].off;
+      if (j >= 0 && j < wt.s[k].n) {
+        const int r = (int)j / wt.s[k].cols, c = (int)j - r * wt.s[k].cols;
+        store_split(wt.s[k].dst, lo_off, (size_t)r * wt.s[k].ld + c, pn);
+        break;
+      }
+    }
+  }
+}
+
 // gacc (fixed point) -> flat fp32 gradient + the four per-minibatch sums; re-zeroes the accumulators for the next minibatch
+// Weight matrices whose split-K partials were stored as slabs (PartTable) are summed from them in split order instead:
+// blocks >= blocks_b walk the flat parameter index (fixed-point accumulators; slab-backed elements are skipped),
+// blocks [0, blocks_b) sum the slabs: four consecutive elements of a slab-backed matrix per thread.
+struct PartSeg { long long off; int n, splits; const float* ws; int item_end; };
+struct PartTable { PartSeg s[2 * URLG_MAX_LAYERS]; int num; };
 __global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restrict__ gacc, float* __restrict__ grads,
-                                                             float* __restrict__ stats, int64_t n) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) {
-    grads[i] = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
-    gacc[i] = 0;
-  } else if (i < n + 4) {
-    stats[i - n] = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
-    gacc[i] = 0;
+                                                             float* __restrict__ stats, int64_t n,
+                                                             const __grid_constant__ PartTable pt, int blocks_b) {
+  // the slab sums (blocks [0, blocks_b)) are the long blocks: they are dispatched first
+  if ((int)blockIdx.x >= blocks_b) {
+    const int64_t i = (int64_t)((int)blockIdx.x - blocks_b) * blockDim.x + threadIdx.x;
+    if (i < n) {
+#pragma unroll 1
+      for (int s = 0; s < pt.num; ++s)
+        if (i >= pt.s[s].off && i < pt.s[s].off + pt.s[s].n) return;
+      grads[i] = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
+      gacc[i] = 0;
+    } else if (i < n + 4) {
+      stats[i - n] = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
+      gacc[i] = 0;
+    }
+    return;
+  }
+  // one thread per four consecutive elements; the slabs are read sixteen at a time (independent, predicated 16-byte loads:
+  // the kernel is a handful of L2 round trips) and added in split order in double precision
+  const int item = (int)blockIdx.x * (int)blockDim.x + (int)threadIdx.x;
+  int k = 0;
+  while (k < pt.num && item >= pt.s[k].item_end) ++k;
+  if (k >= pt.num) return;
+  const PartSeg& sg = pt.s[k];
+  const int e0 = 4 * (item - (k ? pt.s[k - 1].item_end : 0));
+  const int sn = sg.n, splits = sg.splits;
+  const float* w = sg.ws + e0;
+  float* out = grads + sg.off + e0;
+  if ((sn & 3) == 0) {
+    // fp32 adds in split order (a fixed order: still bit-reproducible; <= 148 terms, relative error ~1e-6); the
+    // float -> double conversions of a double-precision sum ran on the 16-lane XU pipe and dominated this kernel
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+    for (int z = 0; z < splits; z += 16) {
+      float4 tv[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        tv[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (z + j < splits) tv[j] = __ldcg(reinterpret_cast<const float4*>(w + (size_t)(z + j) * sn));
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) { a0 += tv[j].x; a1 += tv[j].y; a2 += tv[j].z; a3 += tv[j].w; }
+    }
+    out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+  } else {
+    for (int j = 0; j < 4 && e0 + j < sn; ++j) {
+      float a = 0.0f;
+      for (int z = 0; z < splits; ++z) a += __ldcg(w + j + (size_t)z * sn);
+      out[j] = a;
+    }
   }
 }
 
@@ -405,6 +498,8 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   // every contribution of this minibatch goes into p->gacc (zero on entry: create / the previous finalize left it so);
   // grads_finalize_kernel at the end writes the whole flat gradient and the four sums, so nothing is cleared here
   NetWs &na = p->net[0], &nc = p->net[1];
+  for (int q = 0; q < 2; ++q)
+    for (int l = 0; l < URLG_MAX_LAYERS; ++l) p->wpart_splits[q][l] = 0;
   const bool fused_fwd = !d.recurrent && p->fz != nullptr;
   if (fused_fwd) {
     // gather + every forward layer of both networks in one launch; x and the hidden activations are saved for the backward
@@ -456,7 +551,22 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
   }
   {
     const int64_t n = d.num_params + 4;
-    grads_finalize_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params);
+    PartTable pt;
+    pt.num = 0;
+    int items = 0;
+    for (int q = 0; q < 2; ++q) {
+      const urlg_mlp_desc& m = p->net[q].d;
+      for (int l = 0; l < m.num_layers; ++l)
+        if (p->wpart_splits[q][l] > 0) {
+          PartSeg& sg = pt.s[pt.num++];
+          sg.off = m.w_off[l]; sg.n = m.dims[l + 1] * m.dims[l]; sg.splits = p->wpart_splits[q][l];
+          sg.ws = p->wpart + p->wpart_off[q][l];
+          items += (sg.n + 3) / 4;
+          sg.item_end = items;
+        }
+    }
+    const int blocks_a = (int)((n + 255) / 256), blocks_b = (items + 255) / 256;
+    grads_finalize_kernel<<<blocks_a + blocks_b, 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params, pt, blocks_b);
     URLG_LAUNCH_CHECK();
   }
   p->last_rows = rows;
@@ -475,6 +585,22 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
                                                    reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
                                                    (float)p->last_rows * h->kl_count_scale);
   URLG_LAUNCH_CHECK();
+  static const bool fuse_img = []() { const char* e = getenv("URLG_ADAM_IMAGES"); return !(e && e[0] == '0'); }();
+  if (fuse_img && !p->desc.recurrent) {
+    WImgTable wt;
+    wt.num = 0;
+    for (int q = 0; q < 2; ++q) {
+      const NetWs& nw = p->net[q];
+      for (int l = 0; l < nw.d.num_layers; ++l) {
+        WImgSeg& sg = wt.s[wt.num++];
+        sg.off = nw.d.w_off[l]; sg.n = nw.d.dims[l + 1] * nw.d.dims[l]; sg.cols = nw.d.dims[l]; sg.ld = nw.kpad[l];
+        sg.dst = nw.w[l];
+      }
+    }
+    adam_images_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h, wt, p->lo_off);
+    URLG_LAUNCH_CHECK();
+    return URLG_OK;
+  }
   adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
   URLG_LAUNCH_CHECK();
   return sync_weights(p, st);

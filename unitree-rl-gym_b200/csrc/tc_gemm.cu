@@ -115,6 +115,14 @@ int launch_gemm_group(const urlg_gemm_desc* const* ds, int n, cudaStream_t st) {
 
 int launch_gemm(const urlg_gemm_desc* d, cudaStream_t st) { return launch_gemm_group(&d, 1, st); }
 
+// K splits cover whole k-blocks: the count actually used for a requested k_splits (and the K range of one split).
+int effective_splits(int K, int k_splits, int* k_per_split) {
+  int splits = k_splits > 0 ? k_splits : 1;
+  const int kps = ((K + splits - 1) / splits + kBlockK - 1) / kBlockK * kBlockK;
+  if (k_per_split) *k_per_split = kps;
+  return (K + kps - 1) / kps;
+}
+
 // Fills one problem's kernel arguments and its 8 tensor maps.
 static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, int group_n) {
   if (!d || !d->A || !d->B || d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(URLG_EINVAL, "urlg_tc_gemm: bad argument");
@@ -136,11 +144,11 @@ static int build_problem(const urlg_gemm_desc* d, GemmArgs& g, CUtensorMap* tm, 
   if (bn > 256) bn = 256;
   if ((bn & 15) || (g.b_mn && (bn & 63))) return fail(URLG_EINVAL, "urlg_tc_gemm: block_n=%d invalid", bn);
   g.block_n = bn;
-  int splits = d->k_splits > 0 ? d->k_splits : 1;
-  int kps = ((d->K + splits - 1) / splits + kBlockK - 1) / kBlockK * kBlockK;
-  splits = (d->K + kps - 1) / kps;
+  int kps = 0;
+  const int splits = effective_splits(d->K, d->k_splits, &kps);
   g.k_per_split = kps;
-  if (splits > 1 && !(d->flags & kFlagAtomic)) return fail(URLG_EINVAL, "urlg_tc_gemm: k_splits > 1 needs the atomic flag");
+  g.out_part = d->out_part;
+  if (splits > 1 && !(d->flags & kFlagAtomic) && !d->out_part) return fail(URLG_EINVAL, "urlg_tc_gemm: k_splits > 1 needs the atomic flag");
   g.out_f32 = d->out_f32; g.ld_f32 = d->ld_f32;
   g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(d->out_bf16); g.ld_bf16 = d->ld_bf16;
   g.bias = d->bias;
@@ -274,6 +282,11 @@ extern "C" int urlg_gemm_timing_read(double* total_ms, int64_t* launches, double
   if (flops) *flops = g_flops;
   if (bytes) *bytes = g_bytes;
   return URLG_OK;
+}
+
+extern "C" int urlg_tc_gemm_splits(int K, int k_splits) {
+  if (K <= 0) return urlg::fail(URLG_EINVAL, "urlg_tc_gemm_splits: K must be positive");
+  return urlg::tc::effective_splits(K, k_splits, nullptr);
 }
 
 extern "C" int urlg_tc_gemm(const urlg_gemm_desc* d, void* stream) {

@@ -38,6 +38,7 @@ struct GemmArgs {
   int tma_out;           // bf16 outputs leave through per-warp shared staging + TMA tensor stores (tmO / tmOlo valid)
   long long* out_fx;     // fixed-point accumulation targets (see urlg_gemm_desc): replace the fp32 atomics when set
   long long* colsum_fx;
+  float* out_part;       // split-K partial slabs [splits][M][ld_f32] (plain stores; replaces out_f32 / out_fx when set)
 };
 
 
@@ -381,7 +382,16 @@ gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
             bulk_commit();
           }
         }
-        if (row_ok && g.out_fx) {
+        if (row_ok && g.out_part) {
+          float* o = g.out_part + ((size_t)tw.tz * g.M + row) * g.ld_f32 + col0;
+          if (full && vec_f32 && ((uintptr_t)o & 15) == 0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) if (i < ncol) o[i] = v[i];
+          }
+        } else if (row_ok && g.out_fx) {
           long long* o = g.out_fx + (size_t)row * g.ld_f32 + col0;
 #pragma unroll
           for (int i = 0; i < 16; ++i) if (i < ncol) fx_add(o + i, v[i], kFxScale);
