@@ -152,8 +152,9 @@ def config_dict(task, n, world):
 def run_dict(graph, pool_seam):
     """How this arm ran the workload (not part of the workload itself)."""
     return {"rollout_launch": "CUDA graph replay (24 env steps incl. policy forward per graph; the 20 minibatch steps of "
-                              "the update as a second graph, N>1: with its per-minibatch NCCL all-reduce as graph nodes "
-                              "unless URLG_GRAPH_NCCL=0)" if graph else "eager",
+                              "the update as a second graph, N>1: with its per-minibatch gradient exchange -- the one-shot "
+                              "peer-memory all-reduce urlg_peer_allreduce, or NCCL when URLG_PEER_XCHG=0 -- as graph nodes)"
+                              if graph else "eager",
             "physics_seam": ("pool-indexed: kernels read the current synthetic frame in place (urlg_env_bind_frame_pool), no "
                              "stand-in copies inside the timed region" if pool_seam else
                              "copied: one urlg_synth_refresh launch per physics tensor per refresh inside the timed region"),
@@ -731,7 +732,7 @@ def own_arm(a):
                 "update_ms": upd_ms, "wall_ms_per_step": wall_ms, "train_env_steps_per_s": n * T * world / (total_ms * 1e-3),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 env path; split-bf16 (hi+lo) tensor-core operands, fp32 accumulate, policy/PPO",
-                "data": "synthetic", "config": config_dict(task, n, world), "run": run_dict(graph is not None, not a.copy_seam),
+                "data": "synthetic", "config": config_dict(task, n, world), "run": dict(run_dict(graph is not None, not a.copy_seam), gradient_exchange=alg.exchange),
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": n * T * world / (e2e_roll_ms * 1e-3), "unit": "env-steps/s",
                         "h2d_bytes_per_step": int(h2d * T), "d2h_bytes_per_step": int(d2h * T), "rollout_ms": e2e_roll_ms,

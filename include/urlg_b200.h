@@ -260,6 +260,26 @@ int urlg_tc_gemm_splits(int K, int k_splits);
  * other's wave tails.  All problems must use the same operand mode (hi+lo pairs or plain bf16); results are those of n
  * separate urlg_tc_gemm calls. */
 int urlg_tc_gemm_group(const urlg_gemm_desc* descs, int n, void* stream);
+/* ---- data-parallel gradient exchange over peer memory (NVLink 5 / NVSwitch) ----
+ * No counterpart in the reference (it is single-GPU); this is the path's one real exchange step when it is sharded over
+ * GPUs: per minibatch the flat gradient + the four loss / KL sums become their sum over ranks before clip_grad_norm_ / Adam
+ * ([UPSTREAM rsl_rl v1.0.2] algorithms/ppo.py update).  One-shot all-reduce: every rank owns an exchange
+ * buffer that all peers have mapped (symmetric memory); a call publishes `data` into it, signals the peers' flag rows, waits
+ * for theirs and replaces data[i] by the sum over ranks in rank order (bit-identical on every rank, reproducible).
+ * Two launches on `stream`, no host synchronisation, capturable in a CUDA graph.  Every rank must make the same sequence
+ * of calls.  Layout of one rank's symmetric allocation, in floats: [2 * count exchange halves | URLG_PEER_MAX_WORLD flag
+ * words], zero-filled before the first call (and a barrier between the fill and the first call). */
+#define URLG_PEER_MAX_WORLD 16
+typedef struct urlg_peer_exchange {
+  int32_t world, rank;
+  float* const* bufs;        /* DEVICE array [world]: peer-mapped pointer to rank r's exchange halves */
+  uint32_t* const* flags;    /* DEVICE array [world]: peer-mapped pointer to rank r's flag row */
+  int64_t count;             /* floats per half (multiple of 4, >= n) */
+  uint32_t* epoch;           /* local device word, zero at start: exchanges completed */
+  uint32_t* ticket;          /* local device words [2], zero at start */
+} urlg_peer_exchange;
+int urlg_peer_allreduce(const urlg_peer_exchange* x, float* data, int64_t n, void* stream);
+
 /* Measurement hook (bench.py roofline): while enabled, every tensor-core launch of this library (GEMM or fused forward)
  * is bracketed by CUDA events on its stream (do not enable under graph capture); read returns the summed duration, the
  * launch count, the algorithmic flops (2*M*N*K, counted once) and the algorithmic HBM bytes (every operand and output

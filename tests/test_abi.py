@@ -66,7 +66,7 @@ def test_policy_side_struct_sizes_match_header():
     """The ctypes mirrors of the policy / storage / PPO structs have the size gcc gives the header's."""
     from unitree_rl_gym_b200 import _lib
     names = [("urlg_gemm_desc", _lib.GemmDesc), ("urlg_mlp_desc", _lib.MlpDesc), ("urlg_policy_desc", _lib.PolicyDesc),
-             ("urlg_storage", _lib.Storage), ("urlg_ppo_hparams", _lib.PpoHparams)]
+             ("urlg_storage", _lib.Storage), ("urlg_ppo_hparams", _lib.PpoHparams), ("urlg_peer_exchange", _lib.PeerExchange)]
     body = 'printf("' + " ".join("%zu" for _ in names) + '\\n",' + ",".join(f"sizeof({n})" for n, _ in names) + ");"
     sizes = list(map(int, _probe(body)))
     for (n, cls), sz in zip(names, sizes):

@@ -27,7 +27,8 @@ def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
-    n_loc, steps, n_obs, n_act, hidden = 128, 24, 48, 12, [512, 256, 128]
+    n_loc = int(os.environ.get("URLG_PARITY_NLOC", "128"))          # 4096 = the BASELINE per-GPU size (oracle over the union: ~1 min on CPU)
+    steps, n_obs, n_act, hidden = 24, 48, 12, [512, 256, 128]
     n_glob = n_loc * world
 
     # ---- the oracle over the union (every rank builds it: cheap, deterministic, avoids shipping tensors around)
@@ -121,7 +122,7 @@ def main():
            "update_param_rel_l2_worst": worst_rel, "update_param_max_abs": worst_abs, "update_frac_within_1e-3": n_in / n_tot,
            "oracle_param_moved_max": moved, "lr": [oppo.learning_rate, pppo.learning_rate],
            "losses": [ov, pv, osur, psur], "ranks_bit_identical": bool(flags.item()),
-           "update_graph_with_nccl": graph_rounds, "update_graph_launches": pppo.update_graph_launches}
+           "gradient_exchange": pppo.exchange, "n_loc": n_loc, "update_graph_with_nccl": graph_rounds, "update_graph_launches": pppo.update_graph_launches}
     graph_ok = all(g["graph"] and g["update_param_rel_l2_worst"] < 1e-3 and g["update_frac_within_1e-3"] >= 0.9999 and
                    g["update_param_max_abs"] <= 3e-3 for g in graph_rounds) or not pppo._graph_nccl
     ok = (graph_ok and adv_err < 1e-4 and ret_err < 1e-4 and worst_rel < 1e-3 and n_in / n_tot >= 0.9999 and worst_abs <= 3e-3 and

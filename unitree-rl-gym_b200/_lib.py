@@ -84,6 +84,12 @@ class GemmDesc(C.Structure):
 
 
 GEMM_ELU, GEMM_ATOMIC = 1, 2
+PEER_MAX_WORLD = 16
+
+
+class PeerExchange(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("bufs", _P), ("flags", _P), ("count", C.c_int64),
+                ("epoch", _P), ("ticket", _P)]
 MAX_LAYERS = 8
 
 
@@ -147,6 +153,7 @@ SIGNATURES = {
     "urlg_tc_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_void_p]),
     "urlg_tc_gemm_group": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_void_p]),
     "urlg_tc_gemm_splits": (C.c_int, [C.c_int, C.c_int]),
+    "urlg_peer_allreduce": (C.c_int, [C.POINTER(PeerExchange), C.c_void_p, C.c_int64, C.c_void_p]),
     "urlg_gemm_timing": (C.c_int, [C.c_int]),
     "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                        C.POINTER(C.c_double)]),

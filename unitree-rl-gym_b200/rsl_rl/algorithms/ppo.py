@@ -123,6 +123,11 @@ class PPO:
         self.rank = dist.get_rank() if self.world > 1 else 0
         self._graph_nccl = os.environ.get("URLG_GRAPH_NCCL", "1") != "0" and (
             self.world > 1 and dist.get_backend() == "nccl")
+        # gradient exchange: one-shot all-reduce over peer memory (urlg_peer_allreduce) when the ranks can map each other's
+        # memory; URLG_PEER_XCHG=0 or a failed symmetric-memory rendezvous keeps the NCCL all-reduce
+        self._peer = None
+        self.exchange = "none" if self.world == 1 else "nccl"
+
 
     # ---- learning rate lives on the device (adaptive schedule); the attribute stays readable / writable
     @property
@@ -152,10 +157,26 @@ class PPO:
         if self.world > 1:       # identical initial parameters on every rank
             dist.broadcast(self.engine.flat, 0)
             self.engine.sync_weights()
+            self._setup_peer_exchange()
         dev = self.engine.device
         self._actions = torch.zeros(N, action_shape[0], device=dev)
         self._act_base = torch.zeros(1, dtype=torch.int64, device=dev)
         self._last_values = torch.zeros(N, 1, device=dev)
+
+    def _setup_peer_exchange(self):
+        self._peer, self.exchange = None, "nccl"
+        if os.environ.get("URLG_PEER_XCHG", "1") == "0" or dist.get_backend() != "nccl" or self.world > _lib.PEER_MAX_WORLD:
+            return
+        ok = torch.ones(1, device=self.engine.device)
+        try:
+            from ..peer_exchange import PeerExchange
+            peer = PeerExchange(self.engine.grads_and_sums.numel(), self.engine.device)
+        except Exception as ex:            # no peer access / symmetric memory on this box: every rank must agree
+            peer, ok[0] = None, 0.0
+            self._peer_error = repr(ex)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok) > 0:
+            self._peer, self.exchange = peer, "peer-memory one-shot (urlg_peer_allreduce)"
 
     def _check_engine(self):
         if self.engine is None:
@@ -267,8 +288,10 @@ class PPO:
             for ind, rows, e0, ec in batches:
                 _lib.check(L.urlg_ppo_minibatch_grads(eng.handle, C.byref(sd), _lib.ptr(ind), rows, e0, ec,
                                                       C.byref(h), st))
-                if self.world > 1:
-                    dist.all_reduce(eng.grads_and_sums)     # flat gradients + (KL, surrogate, value, entropy) sums
+                if self._peer is not None:
+                    self._peer.all_reduce(eng.grads_and_sums, st)      # flat gradients + (KL, surrogate, value, entropy) sums
+                elif self.world > 1:
+                    dist.all_reduce(eng.grads_and_sums)
                 _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), st))
                 if self.lr_trace is not None:
                     v = eng.stats.tolist()
