@@ -279,6 +279,13 @@ typedef struct urlg_peer_exchange {
   uint32_t* ticket;          /* local device words [2], zero at start */
 } urlg_peer_exchange;
 int urlg_peer_allreduce(const urlg_peer_exchange* x, float* data, int64_t n, void* stream);
+/* The same exchange fused into the update: with an exchange bound to the policy (halves of >= num_params + 4 floats; the
+ * stats block must lie directly behind the flat gradients), urlg_ppo_minibatch_grads publishes [gradient | KL, surrogate,
+ * value, entropy sums] from the kernel that finalises the gradient, and urlg_ppo_apply sums the ranks' halves inside its
+ * gradient-norm kernel: the all-reduce adds NO launch to a minibatch step.  Call urlg_ppo_minibatch_grads and urlg_ppo_apply
+ * strictly alternately on every rank while bound.  NULL unbinds. */
+struct urlg_policy;
+int urlg_policy_bind_peer_exchange(struct urlg_policy* policy, const urlg_peer_exchange* x);
 
 /* Measurement hook (bench.py roofline): while enabled, every tensor-core launch of this library (GEMM or fused forward)
  * is bracketed by CUDA events on its stream (do not enable under graph capture); read returns the summed duration, the

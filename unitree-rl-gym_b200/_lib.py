@@ -154,6 +154,7 @@ SIGNATURES = {
     "urlg_tc_gemm_group": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_void_p]),
     "urlg_tc_gemm_splits": (C.c_int, [C.c_int, C.c_int]),
     "urlg_peer_allreduce": (C.c_int, [C.POINTER(PeerExchange), C.c_void_p, C.c_int64, C.c_void_p]),
+    "urlg_policy_bind_peer_exchange": (C.c_int, [C.c_void_p, C.POINTER(PeerExchange)]),
     "urlg_gemm_timing": (C.c_int, [C.c_int]),
     "urlg_gemm_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                        C.POINTER(C.c_double)]),

@@ -16,27 +16,9 @@
 // e + 1, which is stream-ordered behind that peer's reduce (= last read) of exchange e.  Epoch and flags live in device
 // memory and only ever grow, so the pair of launches is capturable in a CUDA graph and replayable.
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace urlg {
-
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ float4 ld_relaxed_sys_v4(const float* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float ld_relaxed_sys(const float* p) {
-  float v;
-  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-  return v;
-}
 
 __global__ void __launch_bounds__(256) peer_publish_kernel(const urlg_peer_exchange x, const float* __restrict__ data, int64_t n) {
   const uint32_t epoch = *x.epoch;
@@ -46,24 +28,17 @@ __global__ void __launch_bounds__(256) peer_publish_kernel(const urlg_peer_excha
     reinterpret_cast<float4*>(mine)[i] = reinterpret_cast<const float4*>(data)[i];
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) mine[(n4 << 2) + threadIdx.x] = data[(n4 << 2) + threadIdx.x];
   __shared__ bool last;
-  __threadfence();
+  __threadfence_system();          // the half is read by other GPUs: every block orders its own stores at system scope
   __syncthreads();
   if (threadIdx.x == 0) last = atomicInc(x.ticket, gridDim.x - 1) == gridDim.x - 1;      // wraps to 0 on the last draw
   __syncthreads();
   if (!last) return;
-  __threadfence_system();                       // every block's stores are ordered before the flags below
-  if ((int)threadIdx.x < x.world) st_release_sys(x.flags[threadIdx.x] + x.rank, epoch + 1u);
+  peer_signal(x, epoch + 1u);                   // every block's stores are ordered before the flags
 }
 
 __global__ void __launch_bounds__(256) peer_reduce_kernel(const urlg_peer_exchange x, float* __restrict__ data, int64_t n) {
   const uint32_t epoch = *x.epoch;
-  if ((int)threadIdx.x < x.world) {
-    const uint32_t* f = x.flags[x.rank] + threadIdx.x;
-    const long long t0 = clock64();
-    for (uint32_t spins = 1; (int32_t)(ld_acquire_sys(f) - (epoch + 1u)) < 0; ++spins)
-      if ((spins & 0x3ffu) == 0 && clock64() - t0 > 20000000000LL) __trap();       // ~10 s: a peer died; fail instead of hanging
-  }
-  __syncthreads();
+  peer_wait_flags(x, epoch + 1u);
   const size_t half = (size_t)(epoch & 1u) * x.count;
   const int64_t n4 = n >> 2;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {

@@ -73,6 +73,10 @@ struct urlg_policy {
   int64_t wpart_off[2][URLG_MAX_LAYERS];
   int wpart_cap[2][URLG_MAX_LAYERS];
   int wpart_splits[2][URLG_MAX_LAYERS];
+  // data-parallel gradient exchange over peer memory (urlg_policy_bind_peer_exchange): when bound, grads_finalize_kernel
+  // publishes [grads | 4 sums] into this rank's exchange half and urlg_ppo_apply's norm kernel sums the ranks' halves
+  urlg_peer_exchange peer;
+  int peer_bound;
 };
 
 namespace urlg {

@@ -339,7 +339,7 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     delete p;
     return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
   }
-  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr; p->wpart = nullptr;
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr; p->wpart = nullptr; p->peer_bound = 0;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {

@@ -9,6 +9,7 @@
 //                       order by grads_finalize_kernel: bit-reproducible without atomics)
 //   apply               grad-norm, device-side adaptive-KL learning rate, clip, Adam + bf16 weight images
 #include "policy.cuh"
+#include "peer.cuh"
 
 namespace urlg {
 namespace tc {
@@ -306,15 +307,11 @@ int mlp_backward_pair(urlg_policy* p, NetWs& a, NetWs& c, int64_t rows, bf16* dx
 // the block that draws the last ticket sums the (<= 256) partials in block order (fixed-shape tree: the norm, hence the
 // clip coefficient and the whole Adam step, is bit-reproducible, so data-parallel ranks stay bit-identical) and then
 // runs the LR rule / Adam bias corrections / loss accumulators as one thread -- no .item(), no KL branch sync.
-__global__ void __launch_bounds__(256)
-grad_norm_scalars_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ partials,
-                         unsigned int* __restrict__ ticket, float* __restrict__ stats, const urlg_ppo_hparams hp,
-                         float rows_total) {
-  float acc = 0.0f;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float x = g[i] * scale;
-    acc += x * x;
-  }
+// Tail shared by the two gradient-norm kernels: block partial -> ticket -> the last block sums the partials in block order
+// and runs the scalar logic as one thread.  `epoch` (peer exchange) is advanced by that block when given.
+__device__ __forceinline__ void norm_tail(float acc, float* __restrict__ partials, unsigned int* __restrict__ ticket,
+                                          float* __restrict__ stats, const urlg_ppo_hparams& hp, float rows_total,
+                                          uint32_t* epoch) {
   acc = warp_sum(acc);
   __shared__ float sh[256];
   __shared__ bool last;
@@ -337,6 +334,7 @@ grad_norm_scalars_kernel(const float* __restrict__ g, int64_t n, float scale, fl
     __syncthreads();
   }
   if (threadIdx.x != 0) return;
+  if (epoch) *epoch = *epoch + 1u;          // every block read the old epoch before it drew its ticket
   stats[URLG_STAT_GNORM_SQ] = sh[0];
   float lr = stats[URLG_STAT_LR];
   const float kl_mean = stats[URLG_STAT_KL_SUM] / rows_total;
@@ -355,6 +353,56 @@ grad_norm_scalars_kernel(const float* __restrict__ g, int64_t n, float scale, fl
   stats[URLG_STAT_ACC_VLOSS] += stats[URLG_STAT_VLOSS_SUM] / rows_total;
   stats[URLG_STAT_ACC_SURR] += stats[URLG_STAT_SURR_SUM] / rows_total;
   stats[URLG_STAT_ACC_N] += 1.0f;
+}
+
+__global__ void __launch_bounds__(256)
+grad_norm_scalars_kernel(const float* __restrict__ g, int64_t n, float scale, float* __restrict__ partials,
+                         unsigned int* __restrict__ ticket, float* __restrict__ stats, const urlg_ppo_hparams hp,
+                         float rows_total) {
+  float acc = 0.0f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float x = g[i] * scale;
+    acc += x * x;
+  }
+  norm_tail(acc, partials, ticket, stats, hp, rows_total, nullptr);
+}
+
+// Data-parallel variant (a peer exchange is bound, include/urlg_b200.h urlg_policy_bind_peer_exchange): the all-reduce IS
+// this kernel's load phase.  Every rank's grads_finalize_kernel has published [gradient | 4 loss sums] into its exchange
+// half and flagged the peers; here every block waits for the flags, sums the `world` halves in rank order over NVLink
+// (bit-identical on every rank) into the local [grads | sums] block and accumulates the norm of the scaled sum on the fly.
+__global__ void __launch_bounds__(256)
+peer_reduce_norm_scalars_kernel(const urlg_peer_exchange x, float* __restrict__ g, int64_t n, int64_t n_total, float scale,
+                                float* __restrict__ partials, unsigned int* __restrict__ ticket, float* __restrict__ stats,
+                                const urlg_ppo_hparams hp, float rows_total) {
+  const uint32_t epoch = *x.epoch;
+  peer_wait_flags(x, epoch + 1u);
+  const size_t half = (size_t)(epoch & 1u) * x.count;
+  float acc = 0.0f;
+  const int64_t n4 = (n_total + 3) >> 2;          // the halves are padded to a multiple of 4 floats (zero beyond n_total)
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 a = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 1
+    for (int r0 = 0; r0 < x.world; r0 += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (r0 + j < x.world) v[j] = ld_relaxed_sys_v4(x.bufs[r0 + j] + half + 4 * i);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (r0 + j < x.world) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+    }
+    const float e[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t k = 4 * i + j;
+      if (k < n_total) g[k] = e[j];              // [grads (n) | KL, surrogate, value, entropy sums]: stats follow the gradients
+      if (k < n) { const float y = e[j] * scale; acc += y * y; }
+    }
+  }
+  norm_tail(acc, partials, ticket, stats, hp, rows_total, x.epoch);
 }
 
 __global__ void __launch_bounds__(256)
@@ -413,9 +461,9 @@ adam_images_kernel(float* __restrict__ p, const float* __restrict__ g, float* __
 // blocks [0, blocks_b) sum the slabs: four consecutive elements of a slab-backed matrix per thread.
 struct PartSeg { long long off; int n, splits; const float* ws; int item_end; };
 struct PartTable { PartSeg s[2 * URLG_MAX_LAYERS]; int num; };
-__global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restrict__ gacc, float* __restrict__ grads,
-                                                             float* __restrict__ stats, int64_t n,
-                                                             const __grid_constant__ PartTable pt, int blocks_b) {
+__device__ __forceinline__ void grads_finalize_body(long long* __restrict__ gacc, float* __restrict__ grads,
+                                                    float* __restrict__ stats, int64_t n, const PartTable& pt, int blocks_b,
+                                                    float* __restrict__ xb) {
   // the slab sums (blocks [0, blocks_b)) are the long blocks: they are dispatched first
   if ((int)blockIdx.x >= blocks_b) {
     const int64_t i = (int64_t)((int)blockIdx.x - blocks_b) * blockDim.x + threadIdx.x;
@@ -423,10 +471,14 @@ __global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restri
 #pragma unroll 1
       for (int s = 0; s < pt.num; ++s)
         if (i >= pt.s[s].off && i < pt.s[s].off + pt.s[s].n) return;
-      grads[i] = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
+      const float gv = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
+      grads[i] = gv;
+      if (xb) xb[i] = gv;
       gacc[i] = 0;
     } else if (i < n + 4) {
-      stats[i - n] = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
+      const float sv = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
+      stats[i - n] = sv;
+      if (xb) xb[i] = sv;
       gacc[i] = 0;
     }
     return;
@@ -457,13 +509,37 @@ __global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restri
       for (int j = 0; j < 16; ++j) { a0 += tv[j].x; a1 += tv[j].y; a2 += tv[j].z; a3 += tv[j].w; }
     }
     out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+    if (xb) { float* xo = xb + sg.off + e0; xo[0] = a0; xo[1] = a1; xo[2] = a2; xo[3] = a3; }
   } else {
     for (int j = 0; j < 4 && e0 + j < sn; ++j) {
       float a = 0.0f;
       for (int z = 0; z < splits; ++z) a += __ldcg(w + j + (size_t)z * sn);
       out[j] = a;
+      if (xb) xb[sg.off + e0 + j] = a;
     }
   }
+}
+
+// `pub` (data-parallel, a peer exchange is bound): every value is also written into this rank's exchange half and the
+// block that draws the last ticket flags the peers -- the publish step of the gradient all-reduce costs no launch.
+__global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restrict__ gacc, float* __restrict__ grads,
+                                                             float* __restrict__ stats, int64_t n,
+                                                             const __grid_constant__ PartTable pt, int blocks_b,
+                                                             const urlg_peer_exchange pub) {
+  uint32_t epoch = 0;
+  float* xb = nullptr;
+  if (pub.world > 0) {
+    epoch = *pub.epoch;
+    xb = pub.bufs[pub.rank] + (size_t)(epoch & 1u) * pub.count;
+  }
+  grads_finalize_body(gacc, grads, stats, n, pt, blocks_b, xb);
+  if (pub.world == 0) return;
+  __shared__ bool last;
+  __threadfence_system();          // the exchange half is read by other GPUs: every block orders its own stores at system scope
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicInc(pub.ticket, gridDim.x - 1) == gridDim.x - 1;
+  __syncthreads();
+  if (last) peer_signal(pub, epoch + 1u);
 }
 
 __global__ void zero_minibatch_stats_kernel(float* stats) {
@@ -566,7 +642,9 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
         }
     }
     const int blocks_a = (int)((n + 255) / 256), blocks_b = (items + 255) / 256;
-    grads_finalize_kernel<<<blocks_a + blocks_b, 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params, pt, blocks_b);
+    urlg_peer_exchange pub = {};
+    if (p->peer_bound) pub = p->peer;
+    grads_finalize_kernel<<<blocks_a + blocks_b, 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params, pt, blocks_b, pub);
     URLG_LAUNCH_CHECK();
   }
   p->last_rows = rows;
@@ -581,9 +659,14 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   int blocks = (int)((n + 255) / 256);
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
   const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
-  grad_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red,
-                                                   reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
-                                                   (float)p->last_rows * h->kl_count_scale);
+  if (p->peer_bound)
+    peer_reduce_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
+                                                            reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                            (float)p->last_rows * h->kl_count_scale);
+  else
+    grad_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red,
+                                                     reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                     (float)p->last_rows * h->kl_count_scale);
   URLG_LAUNCH_CHECK();
   static const bool fuse_img = []() { const char* e = getenv("URLG_ADAM_IMAGES"); return !(e && e[0] == '0'); }();
   if (fuse_img && !p->desc.recurrent) {
@@ -604,4 +687,22 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   adam_kernel<<<blocks, 256, 0, st>>>(p->params, p->grads, p->m, p->v, n, p->stats, *h);
   URLG_LAUNCH_CHECK();
   return sync_weights(p, st);
+}
+
+extern "C" int urlg_policy_bind_peer_exchange(urlg_policy* p, const urlg_peer_exchange* x) {
+  if (!p) return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: null policy");
+  if (!x) { p->peer_bound = 0; return URLG_OK; }
+  if (!x->bufs || !x->flags || !x->epoch || !x->ticket || x->world < 1 || x->world > URLG_PEER_MAX_WORLD || x->rank < 0 ||
+      x->rank >= x->world)
+    return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: bad exchange (rank %d of %d, at most %d ranks)", x->rank, x->world,
+                URLG_PEER_MAX_WORLD);
+  if (x->count < p->desc.num_params + 4 || (x->count & 3))
+    return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: exchange halves of %lld floats, need >= %lld (multiple of 4)",
+                (long long)x->count, (long long)p->desc.num_params + 4);
+  if (p->stats != p->grads + p->desc.num_params)
+    return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: the stats block must follow the flat gradients directly "
+                             "([grads | KL, surrogate, value, entropy sums ...] is what the ranks exchange)");
+  p->peer = *x;
+  p->peer_bound = 1;
+  return URLG_OK;
 }

@@ -246,13 +246,12 @@ gemm_bf16_kernel(const __grid_constant__ GroupArgs<G> P) {
     int it = 0;
     // dact_ref prefetch cursor: walks this warp's valid chunks (of the problems that read a reference) in processing
     // order, one chunk ahead of the consumer
-    int ptile = blockIdx.x, pc = -1, pw_tile = -1;
-    TileRef pw = {0, 0, 0, 0};
+    int ptile = blockIdx.x, pc = -1;
     uint32_t ref_phase = 0;
     auto prefetch_ref = [&]() {
       for (;;) {
         if (ptile >= num_tiles) return;
-        if (pw_tile != ptile) { pw = locate(P, ptile); pw_tile = ptile; }     // the tile walk costs two divisions: once per tile
+        const TileRef pw = locate(P, ptile);
         const GemmArgs& q = P.g[pw.p];
         pc = pc < 0 ? 16 * cg : pc + 64;
         if (q.tma_ref && pc < q.block_n && pw.ty * q.block_n + pc < q.N) {

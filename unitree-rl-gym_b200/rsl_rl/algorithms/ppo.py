@@ -125,7 +125,7 @@ class PPO:
             self.world > 1 and dist.get_backend() == "nccl")
         # gradient exchange: one-shot all-reduce over peer memory (urlg_peer_allreduce) when the ranks can map each other's
         # memory; URLG_PEER_XCHG=0 or a failed symmetric-memory rendezvous keeps the NCCL all-reduce
-        self._peer = None
+        self._peer, self._peer_fused = None, False
         self.exchange = "none" if self.world == 1 else "nccl"
 
 
@@ -176,7 +176,18 @@ class PPO:
             self._peer_error = repr(ex)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if float(ok) > 0:
-            self._peer, self.exchange = peer, "peer-memory one-shot (urlg_peer_allreduce)"
+            self._peer = peer
+            self._bind_peer()
+
+    def _bind_peer(self):
+        """Fused form: the gradient-finalising kernel publishes, the gradient-norm kernel reduces (no extra launch per
+        minibatch step); URLG_PEER_FUSED=0 keeps the exchange as the two stand-alone launches of urlg_peer_allreduce."""
+        self._peer_fused = False
+        self.exchange = "peer-memory one-shot (urlg_peer_allreduce)"
+        if os.environ.get("URLG_PEER_FUSED", "1") != "0":
+            _lib.check(_lib.lib().urlg_policy_bind_peer_exchange(self.engine.handle, C.byref(self._peer.x)))
+            self._peer_fused = True
+            self.exchange = "peer-memory one-shot, fused into the gradient finalize / norm kernels (urlg_policy_bind_peer_exchange)"
 
     def _check_engine(self):
         if self.engine is None:
@@ -184,6 +195,8 @@ class PPO:
         if not self.engine.owns(self.actor_critic):
             self.engine = self.actor_critic.engine()
             self.engine.stats[_lib.STAT_LR] = self._lr_host
+            if self._peer is not None:
+                self._bind_peer()
         return self.engine
 
     # ---- CUDA-graph support: the Philox step of act() is (device base + host offset), like the env's counters
@@ -289,7 +302,8 @@ class PPO:
                 _lib.check(L.urlg_ppo_minibatch_grads(eng.handle, C.byref(sd), _lib.ptr(ind), rows, e0, ec,
                                                       C.byref(h), st))
                 if self._peer is not None:
-                    self._peer.all_reduce(eng.grads_and_sums, st)      # flat gradients + (KL, surrogate, value, entropy) sums
+                    if not self._peer_fused:                           # fused: minibatch_grads published, apply reduces
+                        self._peer.all_reduce(eng.grads_and_sums, st)  # flat gradients + (KL, surrogate, value, entropy) sums
                 elif self.world > 1:
                     dist.all_reduce(eng.grads_and_sums)
                 _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), st))
