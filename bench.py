@@ -125,7 +125,11 @@ def make_env(task, n, frames, device, env_offset=0, pool_seam=False):
     cfg.env.env_offset = env_offset
     sp = SimParams()
     sp.dt = cfg.sim.dt
-    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames, pool_seam=pool_seam)
+    # pool seam: frames are packed ([P, frame] rows holding root | dof x decimation | contact (| rigid body)), so the
+    # e2e legs upload a frame with ONE contiguous copy from pinned host memory
+    if pool_seam and task in ("go2",):          # the base family never reads rigid_body_states: keep it out of the frame rows
+        frames = {k: (None if k == "rigid_body" else v) for k, v in frames.items()}
+    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames, pool_seam=pool_seam, packed=pool_seam)
     cls = H.env_class(task)
     return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device=device, headless=True), cfg
 
@@ -416,8 +420,12 @@ def own_arm(a):
 
     # ---- e2e: the same rollout through the public API (eager), physics frames arriving from pinned HOST memory
     #      every env step (H2D inside the timed region) and rewards / dones read back to the host every step
-    pin = {k: v.pin_memory() for k, v in frames.items() if v is not None and (k != "rigid_body" or spec.family == 1)}
-    pool = env.gym.frames
+    if env.gym.packed:          # one pinned host row per frame, one copy per upload
+        pin = {"frame": env.gym.frame_buf.cpu().pin_memory()}
+        pool = {"frame": env.gym.frame_buf}
+    else:
+        pin = {k: v.pin_memory() for k, v in frames.items() if v is not None and (k != "rigid_body" or spec.family == 1)}
+        pool = env.gym.frames
     D = spec.decimation
     rew_h = torch.empty(n, dtype=torch.float, pin_memory=True)
     done_h = torch.empty(n, dtype=torch.bool, pin_memory=True)

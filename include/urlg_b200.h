@@ -179,6 +179,10 @@ typedef struct urlg_frame_pool {
   const float* rigid_body;    /* [P, N*B, 13] or NULL */
   int64_t num_frames, substeps;
   const int64_t* calls_base;  /* device int64 [1] */
+  /* 0: every tensor is its own dense [P, ...] array (above).  > 0: PACKED frames -- frame f of every tensor starts
+   * frame_stride floats after frame f - 1 (root / dof / contact / rigid_body then point at frame 0's sections of one
+   * [P, frame_stride] buffer), so a host-side physics engine uploads a whole frame with ONE contiguous copy. */
+  int64_t frame_stride;
 } urlg_frame_pool;
 int urlg_env_bind_frame_pool(urlg_env* env, const urlg_frame_pool* pool /* NULL: unbind */);
 int urlg_pd_torques_at(urlg_env* env, const float* raw_actions, int64_t calls_offset, void* stream);

@@ -9,7 +9,7 @@ from tests import helpers as H
 pytestmark = pytest.mark.gpu
 
 
-def make_env(case, fx=None, frames=None, seed=1, pool_seam=False):
+def make_env(case, fx=None, frames=None, seed=1, pool_seam=False, packed=False):
     from unitree_rl_gym_b200.legged_gym.utils.helpers import SimParams
     from unitree_rl_gym_b200.physics import SyntheticGym
     from unitree_rl_gym_b200.robots import ROBOTS
@@ -19,7 +19,7 @@ def make_env(case, fx=None, frames=None, seed=1, pool_seam=False):
     sp = SimParams()
     sp.dt = cfg.sim.dt
     gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, "cuda:0",
-                       frames=frames if frames is not None else H.frames_of(fx), pool_seam=pool_seam)
+                       frames=frames if frames is not None else H.frames_of(fx), pool_seam=pool_seam, packed=packed)
     cls = H.env_class(task)
     return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device="cuda:0", headless=True)
 
@@ -59,7 +59,7 @@ def test_env_matches_reference_fixture(case):
             cmp(k, snap[k], fx[f"step{t}/{k}"], f"step{t}/")
 
 
-def _oracle_pair(task, n, frames_n=3, seed=5, tweak=None, pool_seam=False):
+def _oracle_pair(task, n, frames_n=3, seed=5, tweak=None, pool_seam=False, packed=False):
     """(cuda env, oracle port, spec, frames, physics callback) on the same seeded synthetic frames."""
     from unitree_rl_gym_b200 import synthetic
     from unitree_rl_gym_b200.robots import ROBOTS
@@ -72,7 +72,7 @@ def _oracle_pair(task, n, frames_n=3, seed=5, tweak=None, pool_seam=False):
         frames = synthetic.make_frames(ROBOTS[task], None, n, frames_n, spec.decimation, seed=seed, feet_idx=spec.feet_idx,
                                        pen_idx=spec.pen_idx, term_idx=spec.term_idx, init_z=float(spec.base_init_state[2]),
                                        default_dof_pos=torch.from_numpy(spec.default_dof_pos))
-        env = make_env(case, frames=frames, pool_seam=pool_seam)
+        env = make_env(case, frames=frames, pool_seam=pool_seam, packed=packed)
     finally:
         del H.ENV_CASES[case]
         H.TWEAKS.pop(case, None)
@@ -127,10 +127,12 @@ def test_env_matches_oracle_port_larger(task, n):
 
 def test_pool_seam_matches_copy_seam():
     """urlg_env_bind_frame_pool: reading the synthetic frames in place gives bit-identical env outputs to copying them
-    into the acquired tensors first (the pool seam only removes the stand-in copies from a timed region)."""
+    into the acquired tensors first (the pool seam only removes the stand-in copies from a timed region) -- with one dense
+    array per tensor and with packed frames (urlg_frame_pool.frame_stride: root | dof x decimation | contact | rigid body of a
+    frame in one row, what a host-side engine uploads with a single copy)."""
     out = []
-    for pool in (False, True):
-        env, port, spec, frames, physics = _oracle_pair("g1", 2048, pool_seam=pool)
+    for pool, packed in ((False, False), (True, False), (True, True)):
+        env, port, spec, frames, physics = _oracle_pair("g1", 2048, pool_seam=pool, packed=packed)
         env.reset()
         g = torch.Generator().manual_seed(3)
         env.episode_length_buf = torch.randint(0, 1001, (2048,), generator=g).cuda()
@@ -142,13 +144,14 @@ def test_pool_seam_matches_copy_seam():
                 snap.pop(k)
             snaps.append(snap)
         out.append(snaps)
-    for t, (a, b) in enumerate(zip(*out)):
-        assert a.keys() == b.keys()
-        for k in a:
-            if k.startswith("extras_episode/"):      # means over reset envs: float atomics, order not defined
-                np.testing.assert_allclose(a[k], b[k], rtol=1e-5, atol=1e-7, err_msg=f"step{t}/{k}")
-            else:
-                assert np.array_equal(a[k], b[k]), f"step{t}/{k}"
+    for other in out[1:]:
+        for t, (a, b) in enumerate(zip(out[0], other)):
+            assert a.keys() == b.keys()
+            for k in a:
+                if k.startswith("extras_episode/"):      # means over reset envs: float atomics, order not defined
+                    np.testing.assert_allclose(a[k], b[k], rtol=1e-5, atol=1e-7, err_msg=f"step{t}/{k}")
+                else:
+                    assert np.array_equal(a[k], b[k]), f"step{t}/{k}"
 
 
 def test_indexed_setter_lists_match_masks():

@@ -68,7 +68,7 @@ class EnvBuffers(C.Structure):
 
 class FramePool(C.Structure):
     _fields_ = [("root", _P), ("dof", _P), ("contact", _P), ("rigid_body", _P),
-                ("num_frames", C.c_int64), ("substeps", C.c_int64), ("calls_base", _P)]
+                ("num_frames", C.c_int64), ("substeps", C.c_int64), ("calls_base", _P), ("frame_stride", C.c_int64)]
 
 
 class GemmDesc(C.Structure):

@@ -97,11 +97,12 @@ __device__ __forceinline__ Seam resolve_seam(const urlg_env_desc& c, const urlg_
         frame = (cidx / D) % P;
         sub = cidx % D;
       }
-      const size_t N = (size_t)c.num_envs;
-      s.root = pa.pool.root + frame * N * 13;
-      s.dof = pa.pool.dof + (frame * D + sub) * N * (size_t)c.num_dof * 2;
-      s.contact = pa.pool.contact + frame * N * (size_t)c.num_bodies * 3;
-      if (pa.pool.rigid_body) s.rigid = pa.pool.rigid_body + frame * N * (size_t)c.num_bodies * 13;
+      const size_t N = (size_t)c.num_envs, fs = (size_t)pa.pool.frame_stride;
+      const size_t dof_sub = N * (size_t)c.num_dof * 2;
+      s.root = pa.pool.root + frame * (fs ? fs : N * 13);
+      s.dof = pa.pool.dof + frame * (fs ? fs : D * dof_sub) + sub * dof_sub;
+      s.contact = pa.pool.contact + frame * (fs ? fs : N * (size_t)c.num_bodies * 3);
+      if (pa.pool.rigid_body) s.rigid = pa.pool.rigid_body + frame * (fs ? fs : N * (size_t)c.num_bodies * 13);
     }
   }
   return s;
@@ -1352,6 +1353,8 @@ extern "C" int urlg_env_bind_frame_pool(urlg_env* env, const urlg_frame_pool* po
   if (env->desc.family != URLG_FAMILY_BASE && !pool->rigid_body)
     return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: this env family reads rigid_body_states");
   const uintptr_t bits = (uintptr_t)pool->root | (uintptr_t)pool->dof | (uintptr_t)pool->contact;
+  if (pool->frame_stride < 0 || (pool->frame_stride & 3))
+    return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: frame_stride must be 0 or a positive multiple of 4 floats");
   if ((bits & 15) || (env->desc.num_envs & 3))
     return fail(URLG_EINVAL, "urlg_env_bind_frame_pool: pool tensors must be 16-byte aligned and num_envs a multiple of 4");
   env->pool.pool = *pool;

@@ -20,8 +20,15 @@ from . import _lib
 
 
 class SyntheticGym:
-    def __init__(self, robot, num_envs, decimation, device, frames=None, pool_seam=False):
+    def __init__(self, robot, num_envs, decimation, device, frames=None, pool_seam=False, packed=False):
         self.pool_seam = bool(pool_seam)
+        # packed: frame f of root / dof (all substeps) / contact (/ rigid body) are consecutive sections of ONE row of
+        # `frame_buf` [P, frame_floats], so a host-side engine uploads a frame with a single contiguous copy
+        # (urlg_frame_pool.frame_stride); the per-tensor `frames[k]` stay available as views of it.  Pool seam only.
+        self.packed = bool(packed)
+        self.frame_buf = None
+        if self.packed and not self.pool_seam:
+            raise ValueError("SyntheticGym(packed=True) needs pool_seam=True")
         self.robot = robot
         self.num_envs = num_envs
         self.decimation = decimation
@@ -45,6 +52,21 @@ class SyntheticGym:
 
     def set_frames(self, frames):
         """frames: dict from synthetic.make_frames (CPU or CUDA tensors)."""
+        if self.packed:
+            keys = [k for k in ("root", "dof", "contact", "rigid_body") if frames.get(k) is not None]
+            P = frames["root"].shape[0]
+            sizes = [frames[k][0].numel() for k in keys]
+            if any(n % 4 for n in sizes):
+                raise ValueError("packed frames: every section must be a multiple of 4 floats")
+            self.frame_buf = torch.empty(P, sum(sizes), device=self.device)
+            self.frames, off = {k: None for k in frames}, 0
+            for k, n in zip(keys, sizes):
+                view = self.frame_buf[:, off:off + n].view((P,) + tuple(frames[k].shape[1:]))
+                view.copy_(frames[k])
+                self.frames[k] = view
+                off += n
+            self.num_frames = P
+            return
         self.frames = {k: (v.to(self.device).contiguous() if v is not None else None) for k, v in frames.items()}
         self.num_frames = self.frames["root"].shape[0]
 
@@ -86,6 +108,7 @@ class SyntheticGym:
         d.rigid_body = _lib.ptr(self.frames.get("rigid_body"))
         d.num_frames, d.substeps = self.num_frames, self.decimation
         d.calls_base = _lib.ptr(self.calls_base)
+        d.frame_stride = self.frame_buf.shape[1] if self.packed else 0
         return d
 
     def _refresh(self, dst, key, per_substep):
