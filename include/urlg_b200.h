@@ -272,7 +272,7 @@ int urlg_tc_gemm_group(const urlg_gemm_desc* descs, int n, void* stream);
  * for theirs and replaces data[i] by the sum over ranks in rank order (bit-identical on every rank, reproducible).
  * Two launches on `stream`, no host synchronisation, capturable in a CUDA graph.  Every rank must make the same sequence
  * of calls.  Layout of one rank's symmetric allocation, in floats: [2 * count exchange halves | URLG_PEER_MAX_WORLD flag
- * words], zero-filled before the first call (and a barrier between the fill and the first call). */
+ * words] (mode 1: see below), zero-filled before the first call (and a barrier between the fill and the first call). */
 #define URLG_PEER_MAX_WORLD 16
 typedef struct urlg_peer_exchange {
   int32_t world, rank;
@@ -281,6 +281,13 @@ typedef struct urlg_peer_exchange {
   int64_t count;             /* floats per half (multiple of 4, >= n) */
   uint32_t* epoch;           /* local device word, zero at start: exchanges completed */
   uint32_t* ticket;          /* local device words [2], zero at start */
+  /* 0: one-shot (every rank reads all halves: world x n floats in, best at 2 ranks).  1: two-shot, fused form only
+   * (urlg_policy_bind_peer_exchange): rank r sums slice r of the halves and stores it into every rank's result area, then
+   * every rank reads its own result area -- 2 (world - 1) / world x n floats per rank, what 4 and 8 ranks need.  Needs the
+   * larger allocation: [2 * count halves | count result area | 2 * URLG_PEER_MAX_WORLD flag words]; `flags[r]` points at
+   * the first flag word either way. */
+  int32_t mode;
+  int32_t reserved;
 } urlg_peer_exchange;
 int urlg_peer_allreduce(const urlg_peer_exchange* x, float* data, int64_t n, void* stream);
 /* The same exchange fused into the update: with an exchange bound to the policy (halves of >= num_params + 4 floats; the

@@ -78,8 +78,11 @@ def _one_step(alg, idx, h, phase):
         _lib.check(L.urlg_ppo_apply(eng.handle, C.byref(h), _lib.cur_stream()))
 
 
-def test_fused_exchange_equals_separate_allreduce_and_keeps_ranks_identical():
-    """Two logical ranks on one GPU, three minibatch steps.  Fused: urlg_policy_bind_peer_exchange (finalize publishes, the
+@pytest.mark.parametrize("mode", [0, 1])
+def test_fused_exchange_equals_separate_allreduce_and_keeps_ranks_identical(mode):
+    """Two logical ranks on one GPU, three minibatch steps, one-shot (mode 0) and two-shot (mode 1: every rank reduces its
+    slice, stores it into both result areas and waits for the other's -- the two apply kernels run on separate streams so
+    that each can see the other's slice arrive).  Fused: urlg_policy_bind_peer_exchange (finalize publishes, the
     norm kernel reduces).  Reference: the same gradients summed in rank order between urlg_ppo_minibatch_grads and
     urlg_ppo_apply.  The ranks of the fused run stay bit-identical to each other and agree with the reference to rounding
     (the two norm kernels add the squares in a different association)."""
@@ -90,7 +93,8 @@ def test_fused_exchange_equals_separate_allreduce_and_keeps_ranks_identical():
     fused = [_filled_ppo(11 + r, state) for r in range(2)]
     ref = [_filled_ppo(11 + r, state) for r in range(2)]
     n = fused[0].engine.grads_and_sums.numel()
-    grp = LocalPeerGroup(2, n, torch.device("cuda", 0))
+    grp = LocalPeerGroup(2, n, torch.device("cuda", 0), mode=mode)
+    streams = [torch.cuda.Stream() for _ in range(2)]
     for r in range(2):
         _lib.check(_lib.lib().urlg_policy_bind_peer_exchange(fused[r].engine.handle, C.byref(grp.ranks[r].x)))
     N, T = 256, 8
@@ -105,8 +109,11 @@ def test_fused_exchange_equals_separate_allreduce_and_keeps_ranks_identical():
             hs.append(h)
         for r in range(2):
             _one_step(fused[r], idx, hs[r], "grads")           # publishes into rank r's half, flags both rows
+        torch.cuda.synchronize()
         for r in range(2):
-            _one_step(fused[r], idx, hs[r], "apply")           # sums both halves in rank order inside the norm kernel
+            with torch.cuda.stream(streams[r]):
+                _one_step(fused[r], idx, hs[r], "apply")       # sums the halves in rank order inside the norm kernel
+        torch.cuda.synchronize()
         for r in range(2):
             _one_step(ref[r], idx, hs[2 + r], "grads")
         torch.cuda.synchronize()

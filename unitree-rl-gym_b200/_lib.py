@@ -89,7 +89,7 @@ PEER_MAX_WORLD = 16
 
 class PeerExchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("bufs", _P), ("flags", _P), ("count", C.c_int64),
-                ("epoch", _P), ("ticket", _P)]
+                ("epoch", _P), ("ticket", _P), ("mode", C.c_int32), ("reserved", C.c_int32)]
 MAX_LAYERS = 8
 
 

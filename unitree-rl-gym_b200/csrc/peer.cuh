@@ -24,11 +24,12 @@ __device__ __forceinline__ float ld_relaxed_sys(const float* p) {
   return v;
 }
 
+// Flag rows of a rank: row 0 = "rank r has published exchange e", row 1 (two-shot) = "rank r has stored its reduced slice".
 // Spin until every word of this rank's flag row has reached `want` (threads 0 .. world-1 poll one word each); traps after
 // ~10 s instead of hanging the GPU when a peer has died.  Call from all threads of the block.
-__device__ __forceinline__ void peer_wait_flags(const urlg_peer_exchange& x, uint32_t want) {
+__device__ __forceinline__ void peer_wait_flags(const urlg_peer_exchange& x, uint32_t want, int row = 0) {
   if ((int)threadIdx.x < x.world) {
-    const uint32_t* f = x.flags[x.rank] + threadIdx.x;
+    const uint32_t* f = x.flags[x.rank] + row * URLG_PEER_MAX_WORLD + threadIdx.x;
     const long long t0 = clock64();
     for (uint32_t spins = 1; (int32_t)(ld_acquire_sys(f) - want) < 0; ++spins)
       if ((spins & 0x3ffu) == 0 && clock64() - t0 > 20000000000LL) __trap();
@@ -36,9 +37,9 @@ __device__ __forceinline__ void peer_wait_flags(const urlg_peer_exchange& x, uin
   __syncthreads();
 }
 // The last block of a publishing grid: order every block's stores before the flags, then flag all peers.
-__device__ __forceinline__ void peer_signal(const urlg_peer_exchange& x, uint32_t value) {
+__device__ __forceinline__ void peer_signal(const urlg_peer_exchange& x, uint32_t value, int row = 0) {
   __threadfence_system();
-  if ((int)threadIdx.x < x.world) st_release_sys(x.flags[threadIdx.x] + x.rank, value);
+  if ((int)threadIdx.x < x.world) st_release_sys(x.flags[threadIdx.x] + row * URLG_PEER_MAX_WORLD + x.rank, value);
 }
 
 }  // namespace urlg

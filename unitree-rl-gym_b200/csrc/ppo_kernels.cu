@@ -405,6 +405,61 @@ peer_reduce_norm_scalars_kernel(const urlg_peer_exchange x, float* __restrict__ 
   norm_tail(acc, partials, ticket, stats, hp, rows_total, x.epoch);
 }
 
+// Two-shot form of the same kernel (urlg_peer_exchange.mode 1; 4 and 8 ranks): rank r sums only slice r of the published
+// halves (world - 1 remote reads of n / world floats) and stores the reduced slice into every rank's result area (world - 1
+// remote writes); the block that finishes the slice last flags the peers' second flag row; then every block waits until
+// all `world` slices have arrived in its OWN result area and reads it locally.  Per rank 2 (world - 1) / world x n floats
+// cross NVLink instead of (world - 1) x n.  The grid (<= 256 blocks) is co-resident, so the blocks that spin in the
+// second wait cannot starve the ones still reducing.  Each element is reduced by exactly one rank in rank order and
+// broadcast: bit-identical on every rank.
+__global__ void __launch_bounds__(256)
+peer_reduce2_norm_scalars_kernel(const urlg_peer_exchange x, float* __restrict__ g, int64_t n, int64_t n_total, float scale,
+                                 float* __restrict__ partials, unsigned int* __restrict__ ticket, float* __restrict__ stats,
+                                 const urlg_ppo_hparams hp, float rows_total) {
+  const uint32_t epoch = *x.epoch;
+  peer_wait_flags(x, epoch + 1u, 0);
+  const size_t half = (size_t)(epoch & 1u) * x.count, res = 2 * (size_t)x.count;
+  const int64_t n4 = (n_total + 3) >> 2;
+  const int64_t s4 = (n4 + x.world - 1) / x.world, lo = (int64_t)x.rank * s4, hi = lo + s4 < n4 ? lo + s4 : n4;
+  for (int64_t i = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 a = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 1
+    for (int r0 = 0; r0 < x.world; r0 += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (r0 + j < x.world) v[j] = ld_relaxed_sys_v4(x.bufs[r0 + j] + half + 4 * i);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (r0 + j < x.world) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+    }
+#pragma unroll 1
+    for (int q = 0; q < x.world; ++q) reinterpret_cast<float4*>(x.bufs[q] + res)[i] = a;
+  }
+  __shared__ bool slice_last;
+  __threadfence_system();                          // this block's slice stores are ordered at system scope
+  __syncthreads();
+  if (threadIdx.x == 0) slice_last = atomicInc(x.ticket + 1, gridDim.x - 1) == gridDim.x - 1;
+  __syncthreads();
+  if (slice_last) peer_signal(x, epoch + 1u, 1);
+  peer_wait_flags(x, epoch + 1u, 1);
+  const float* mine = x.bufs[x.rank] + res;
+  float acc = 0.0f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = ld_relaxed_sys_v4(mine + 4 * i);
+    const float e[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t k = 4 * i + j;
+      if (k < n_total) g[k] = e[j];
+      if (k < n) { const float y = e[j] * scale; acc += y * y; }
+    }
+  }
+  norm_tail(acc, partials, ticket, stats, hp, rows_total, x.epoch);
+}
+
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
             const float* __restrict__ stats, const urlg_ppo_hparams hp) {
@@ -659,7 +714,11 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   int blocks = (int)((n + 255) / 256);
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
   const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
-  if (p->peer_bound)
+  if (p->peer_bound && p->peer.mode == 1)
+    peer_reduce2_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
+                                                             reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                             (float)p->last_rows * h->kl_count_scale);
+  else if (p->peer_bound)
     peer_reduce_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
                                                             reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
                                                             (float)p->last_rows * h->kl_count_scale);
@@ -696,6 +755,7 @@ extern "C" int urlg_policy_bind_peer_exchange(urlg_policy* p, const urlg_peer_ex
       x->rank >= x->world)
     return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: bad exchange (rank %d of %d, at most %d ranks)", x->rank, x->world,
                 URLG_PEER_MAX_WORLD);
+  if (x->mode != 0 && x->mode != 1) return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: mode %d (0 one-shot, 1 two-shot)", x->mode);
   if (x->count < p->desc.num_params + 4 || (x->count & 3))
     return fail(URLG_EINVAL, "urlg_policy_bind_peer_exchange: exchange halves of %lld floats, need >= %lld (multiple of 4)",
                 (long long)x->count, (long long)p->desc.num_params + 4);

@@ -165,7 +165,11 @@ class PPO:
 
     def _setup_peer_exchange(self):
         self._peer, self.exchange = None, "nccl"
-        if os.environ.get("URLG_PEER_XCHG", "1") == "0" or dist.get_backend() != "nccl" or self.world > _lib.PEER_MAX_WORLD:
+        # measured on B200 (bench.py, Go2 4096 envs/GPU, update as one graph): 2 ranks 7.30 ms fused peer exchange vs 7.60 ms
+        # NCCL; 8 ranks 8.28 ms (one- and two-shot alike: flag + remote-read round trips, not bytes) vs 8.00 ms NCCL.  So the
+        # default is the peer exchange for 2 ranks and NCCL beyond; URLG_PEER_XCHG=1 forces it at any world size, 0 disables it
+        want = os.environ.get("URLG_PEER_XCHG", "auto")
+        if want == "0" or (want == "auto" and self.world > 2) or dist.get_backend() != "nccl" or self.world > _lib.PEER_MAX_WORLD:
             return
         ok = torch.ones(1, device=self.engine.device)
         try:

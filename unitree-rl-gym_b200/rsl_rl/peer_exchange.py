@@ -23,15 +23,22 @@ def _round4(n):
 class _Exchange:
     """Common part: the C struct, its device-resident pointer tables and counters."""
 
-    def _fill(self, world, rank, buf_ptrs, count, device):
+    @staticmethod
+    def floats_needed(count):
+        """[2 halves | result area (two-shot) | publish flags + slice flags]"""
+        return 3 * count + 2 * _lib.PEER_MAX_WORLD
+
+    def _fill(self, world, rank, buf_ptrs, count, device, mode=None):
         if world > _lib.PEER_MAX_WORLD:
             raise ValueError("peer exchange supports at most %d ranks, got %d" % (_lib.PEER_MAX_WORLD, world))
         self.world, self.rank, self.count = world, rank, count
-        flag_ptrs = [p + 2 * count * 4 for p in buf_ptrs]
+        flag_ptrs = [p + 3 * count * 4 for p in buf_ptrs]
+        # one-shot reads world x n floats per rank (fine at 2 ranks); two-shot moves 2 (world - 1) / world x n
+        self.mode = (1 if world > 2 else 0) if mode is None else int(mode)
         self._tables = torch.tensor([buf_ptrs, flag_ptrs], dtype=torch.int64, device=device)
         self._counters = torch.zeros(4, dtype=torch.int32, device=device)      # epoch, ticket[2], pad
         x = self.x = _lib.PeerExchange()
-        x.world, x.rank, x.count = world, rank, count
+        x.world, x.rank, x.count, x.mode = world, rank, count, self.mode
         x.bufs = self._tables[0].data_ptr()
         x.flags = self._tables[1].data_ptr()
         x.epoch = self._counters.data_ptr()
@@ -53,12 +60,14 @@ class PeerExchange(_Exchange):
         import torch.distributed._symmetric_memory as symm_mem
         group = group if group is not None else dist.group.WORLD
         count = _round4(n)
-        total = 2 * count + _lib.PEER_MAX_WORLD
+        total = self.floats_needed(count)
         self.buf = symm_mem.empty(total, dtype=torch.float32, device=device)
         self.buf.zero_()
         self.handle = symm_mem.rendezvous(self.buf, group.group_name)
         ptrs = [int(p) for p in self.handle.buffer_ptrs]
-        self._fill(dist.get_world_size(group), dist.get_rank(group), ptrs, count, device)
+        import os
+        mode = os.environ.get("URLG_PEER_MODE")
+        self._fill(dist.get_world_size(group), dist.get_rank(group), ptrs, count, device, None if mode is None else int(mode))
         torch.cuda.synchronize(device)
         dist.barrier(group)            # every rank's buffer and flag row are zero before anyone publishes
 
@@ -66,13 +75,13 @@ class PeerExchange(_Exchange):
 class LocalPeerGroup:
     """`world` logical ranks on one device (tests): rank r's exchange is .ranks[r]."""
 
-    def __init__(self, world, n, device):
+    def __init__(self, world, n, device, mode=None):
         count = _round4(n)
-        total = 2 * count + _lib.PEER_MAX_WORLD
+        total = _Exchange.floats_needed(count)
         self.bufs = [torch.zeros(total, dtype=torch.float32, device=device) for _ in range(world)]
         ptrs = [b.data_ptr() for b in self.bufs]
         self.ranks = []
         for r in range(world):
             e = _Exchange()
-            e._fill(world, r, ptrs, count, device)
+            e._fill(world, r, ptrs, count, device, mode)
             self.ranks.append(e)
