@@ -77,6 +77,11 @@ struct urlg_policy {
   // publishes [grads | 4 sums] into this rank's exchange half and urlg_ppo_apply's norm kernel sums the ranks' halves
   urlg_peer_exchange peer;
   int peer_bound;
+  // single-rank updates: grads_finalize_kernel also produces the gradient norm + scalars (ppo_kernels.cu NormArgs);
+  // one partial per block of that kernel (library-owned), norm_done = the pending minibatch's apply may skip its norm launch
+  float* norm_partials;
+  int norm_partials_cap;
+  int norm_done;
 };
 
 namespace urlg {

@@ -339,7 +339,7 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
     delete p;
     return fail(URLG_ECUDA, "urlg_policy_create: workspace memset: %s", cudaGetErrorString(cudaGetLastError()));
   }
-  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr; p->wpart = nullptr; p->peer_bound = 0;
+  p->side = nullptr; p->ev_fork = nullptr; p->ev_join = nullptr; p->fz = nullptr; p->gacc = nullptr; p->wpart = nullptr; p->peer_bound = 0; p->norm_partials = nullptr; p->norm_partials_cap = 0; p->norm_done = 0;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) {
@@ -374,6 +374,11 @@ extern "C" int urlg_policy_create(const urlg_policy_desc* desc, float* params, f
                   (long long)(total_f * 4 >> 20), cudaGetErrorString(cudaGetLastError()));
     }
   }
+  p->norm_partials_cap = (int)((desc->num_params + 4 + 255) / 256 + (desc->num_params / 4 + 255) / 256 + 2 * URLG_MAX_LAYERS + 8);
+  if (cudaMalloc(&p->norm_partials, (size_t)p->norm_partials_cap * sizeof(float)) != cudaSuccess) {
+    urlg_policy_destroy(p);
+    return fail(URLG_ECUDA, "urlg_policy_create: norm partials: %s", cudaGetErrorString(cudaGetLastError()));
+  }
   if (int rc2 = fused_build(p)) { urlg_policy_destroy(p); return rc2; }
   *out = p;
   return URLG_OK;
@@ -384,6 +389,7 @@ extern "C" void urlg_policy_destroy(urlg_policy* p) {
   fused_free(p);
   if (p->gacc) cudaFree(p->gacc);
   if (p->wpart) cudaFree(p->wpart);
+  if (p->norm_partials) cudaFree(p->norm_partials);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);

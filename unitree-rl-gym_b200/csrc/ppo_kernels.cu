@@ -327,7 +327,11 @@ __device__ __forceinline__ void norm_tail(float acc, float* __restrict__ partial
   __syncthreads();
   if (!last) return;
   __threadfence();
-  sh[threadIdx.x] = threadIdx.x < gridDim.x ? __ldcg(partials + threadIdx.x) : 0.0f;
+  {
+    float a = 0.0f;                                 // thread t adds partials t, t + 256, ... in that order (<= 256 blocks: one term)
+    for (unsigned k = threadIdx.x; k < gridDim.x; k += 256) a += __ldcg(partials + k);
+    sh[threadIdx.x] = a;
+  }
   __syncthreads();
   for (int w = 128; w > 0; w >>= 1) {
     if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
@@ -516,7 +520,7 @@ adam_images_kernel(float* __restrict__ p, const float* __restrict__ g, float* __
 // blocks [0, blocks_b) sum the slabs: four consecutive elements of a slab-backed matrix per thread.
 struct PartSeg { long long off; int n, splits; const float* ws; int item_end; };
 struct PartTable { PartSeg s[2 * URLG_MAX_LAYERS]; int num; };
-__device__ __forceinline__ void grads_finalize_body(long long* __restrict__ gacc, float* __restrict__ grads,
+__device__ __forceinline__ float grads_finalize_body(long long* __restrict__ gacc, float* __restrict__ grads,
                                                     float* __restrict__ stats, int64_t n, const PartTable& pt, int blocks_b,
                                                     float* __restrict__ xb) {
   // the slab sums (blocks [0, blocks_b)) are the long blocks: they are dispatched first
@@ -525,25 +529,26 @@ __device__ __forceinline__ void grads_finalize_body(long long* __restrict__ gacc
     if (i < n) {
 #pragma unroll 1
       for (int s = 0; s < pt.num; ++s)
-        if (i >= pt.s[s].off && i < pt.s[s].off + pt.s[s].n) return;
+        if (i >= pt.s[s].off && i < pt.s[s].off + pt.s[s].n) return 0.0f;
       const float gv = (float)((double)gacc[i] * (1.0 / 1099511627776.0));
       grads[i] = gv;
       if (xb) xb[i] = gv;
       gacc[i] = 0;
+      return gv * gv;
     } else if (i < n + 4) {
       const float sv = (float)((double)gacc[i] * (1.0 / 1073741824.0));      // URLG_STAT_KL_SUM .. URLG_STAT_ENT_SUM
       stats[i - n] = sv;
       if (xb) xb[i] = sv;
       gacc[i] = 0;
     }
-    return;
+    return 0.0f;
   }
   // one thread per four consecutive elements; the slabs are read sixteen at a time (independent, predicated 16-byte loads:
   // the kernel is a handful of L2 round trips) and added in split order in double precision
   const int item = (int)blockIdx.x * (int)blockDim.x + (int)threadIdx.x;
   int k = 0;
   while (k < pt.num && item >= pt.s[k].item_end) ++k;
-  if (k >= pt.num) return;
+  if (k >= pt.num) return 0.0f;
   const PartSeg& sg = pt.s[k];
   const int e0 = 4 * (item - (k ? pt.s[k - 1].item_end : 0));
   const int sn = sg.n, splits = sg.splits;
@@ -565,29 +570,41 @@ __device__ __forceinline__ void grads_finalize_body(long long* __restrict__ gacc
     }
     out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
     if (xb) { float* xo = xb + sg.off + e0; xo[0] = a0; xo[1] = a1; xo[2] = a2; xo[3] = a3; }
+    return a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
   } else {
+    float sq = 0.0f;
     for (int j = 0; j < 4 && e0 + j < sn; ++j) {
       float a = 0.0f;
       for (int z = 0; z < splits; ++z) a += __ldcg(w + j + (size_t)z * sn);
       out[j] = a;
       if (xb) xb[sg.off + e0 + j] = a;
+      sq += a * a;
     }
+    return sq;
   }
 }
 
 // `pub` (data-parallel, a peer exchange is bound): every value is also written into this rank's exchange half and the
 // block that draws the last ticket flags the peers -- the publish step of the gradient all-reduce costs no launch.
+// `nrm` (single rank: nothing happens to the gradient between this kernel and the optimiser step): the squared gradient
+// norm is accumulated from the values as they are written and the last block runs the scalar logic of urlg_ppo_apply
+// (norm, LR rule, clip coefficient, Adam bias corrections), so apply is the Adam launch alone.
+struct NormArgs { int enabled; float* partials; unsigned int* ticket; urlg_ppo_hparams hp; float rows_total; };
 __global__ void __launch_bounds__(256) grads_finalize_kernel(long long* __restrict__ gacc, float* __restrict__ grads,
                                                              float* __restrict__ stats, int64_t n,
                                                              const __grid_constant__ PartTable pt, int blocks_b,
-                                                             const urlg_peer_exchange pub) {
+                                                             const urlg_peer_exchange pub, const __grid_constant__ NormArgs nrm) {
   uint32_t epoch = 0;
   float* xb = nullptr;
   if (pub.world > 0) {
     epoch = *pub.epoch;
     xb = pub.bufs[pub.rank] + (size_t)(epoch & 1u) * pub.count;
   }
-  grads_finalize_body(gacc, grads, stats, n, pt, blocks_b, xb);
+  const float sq = grads_finalize_body(gacc, grads, stats, n, pt, blocks_b, xb);
+  if (nrm.enabled) {
+    norm_tail(sq, nrm.partials, nrm.ticket, stats, nrm.hp, nrm.rows_total, nullptr);
+    return;
+  }
   if (pub.world == 0) return;
   __shared__ bool last;
   __threadfence_system();          // the exchange half is read by other GPUs: every block orders its own stores at system scope
@@ -699,7 +716,17 @@ extern "C" int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, c
     const int blocks_a = (int)((n + 255) / 256), blocks_b = (items + 255) / 256;
     urlg_peer_exchange pub = {};
     if (p->peer_bound) pub = p->peer;
-    grads_finalize_kernel<<<blocks_a + blocks_b, 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params, pt, blocks_b, pub);
+    // single rank: the gradient norm and the scalar logic of urlg_ppo_apply ride on this kernel (see NormArgs)
+    static const bool fuse_norm = []() { const char* e = getenv("URLG_FUSED_NORM"); return !(e && e[0] == '0'); }();
+    NormArgs nrm = {};
+    p->norm_done = 0;
+    if (fuse_norm && !p->peer_bound && h->grad_scale == 1.0f && h->kl_count_scale == 1.0f && p->norm_partials &&
+        blocks_a + blocks_b <= p->norm_partials_cap) {
+      nrm.enabled = 1; nrm.partials = p->norm_partials; nrm.ticket = reinterpret_cast<unsigned int*>(p->red + 257);
+      nrm.hp = *h; nrm.rows_total = (float)rows;
+      p->norm_done = 1;
+    }
+    grads_finalize_kernel<<<blocks_a + blocks_b, 256, 0, st>>>(p->gacc, p->grads, p->stats, d.num_params, pt, blocks_b, pub, nrm);
     URLG_LAUNCH_CHECK();
   }
   p->last_rows = rows;
@@ -714,19 +741,26 @@ extern "C" int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* s
   int blocks = (int)((n + 255) / 256);
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
   const int nparts = blocks < 256 ? blocks : 256;      // p->red holds 256 floats
-  if (p->peer_bound && p->peer.mode == 1)
-    peer_reduce2_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
-                                                             reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
-                                                             (float)p->last_rows * h->kl_count_scale);
-  else if (p->peer_bound)
-    peer_reduce_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
-                                                            reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
-                                                            (float)p->last_rows * h->kl_count_scale);
-  else
-    grad_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red,
-                                                     reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
-                                                     (float)p->last_rows * h->kl_count_scale);
-  URLG_LAUNCH_CHECK();
+  if (p->norm_done) {
+    // grads_finalize_kernel has already produced the norm and the scalars for exactly these hyper-parameters
+    if (p->peer_bound || h->grad_scale != 1.0f || h->kl_count_scale != 1.0f)
+      return fail(URLG_EINVAL, "urlg_ppo_apply: grad_scale / kl_count_scale / peer binding changed since urlg_ppo_minibatch_grads");
+    p->norm_done = 0;
+  } else {
+    if (p->peer_bound && p->peer.mode == 1)
+      peer_reduce2_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
+                                                               reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                               (float)p->last_rows * h->kl_count_scale);
+    else if (p->peer_bound)
+      peer_reduce_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->peer, p->grads, n, n + 4, h->grad_scale, p->red,
+                                                              reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                              (float)p->last_rows * h->kl_count_scale);
+    else
+      grad_norm_scalars_kernel<<<nparts, 256, 0, st>>>(p->grads, n, h->grad_scale, p->red,
+                                                       reinterpret_cast<unsigned int*>(p->red + 256), p->stats, *h,
+                                                       (float)p->last_rows * h->kl_count_scale);
+    URLG_LAUNCH_CHECK();
+  }
   static const bool fuse_img = []() { const char* e = getenv("URLG_ADAM_IMAGES"); return !(e && e[0] == '0'); }();
   if (fuse_img && !p->desc.recurrent) {
     WImgTable wt;
