@@ -427,7 +427,12 @@ int urlg_gae_noalloc(const urlg_storage* s, const float* last_values, float gamm
  * trajectory starts (equivalent to split_and_pad_trajectories + masks). */
 int urlg_ppo_minibatch_grads(urlg_policy* p, const urlg_storage* s, const int64_t* indices, int64_t rows,
                              int32_t env_begin, int32_t env_count, const urlg_ppo_hparams* h, void* stream);
-/* Adaptive-KL learning-rate rule, clip_grad_norm_, Adam, refresh of the bf16 weight images. */
+/* Adaptive-KL learning-rate rule, clip_grad_norm_, Adam, refresh of the bf16 weight images ([UPSTREAM rsl_rl v1.0.2]
+ * algorithms/ppo.py update: the schedule block, nn.utils.clip_grad_norm_, optimizer.step()).  Call once after every
+ * urlg_ppo_minibatch_grads with the same hparams.  Single rank (grad_scale == kl_count_scale == 1, no peer exchange
+ * bound): the norm and the scalar logic (STAT_LR, STAT_STEP, STAT_CLIP_COEF, STAT_BC1/2, loss accumulators) are already
+ * produced by the last kernel of urlg_ppo_minibatch_grads, and this call is the Adam launch alone; data-parallel callers
+ * reduce the [grads | sums] block in between (or let this call do it: urlg_policy_bind_peer_exchange). */
 int urlg_ppo_apply(urlg_policy* p, const urlg_ppo_hparams* h, void* stream);
 
 #ifdef __cplusplus
