@@ -125,11 +125,9 @@ def make_env(task, n, frames, device, env_offset=0, pool_seam=False):
     cfg.env.env_offset = env_offset
     sp = SimParams()
     sp.dt = cfg.sim.dt
-    # pool seam: frames are packed ([P, frame] rows holding root | dof x decimation | contact (| rigid body)), so the
-    # e2e legs upload a frame with ONE contiguous copy from pinned host memory
-    if pool_seam and task in ("go2",):          # the base family never reads rigid_body_states: keep it out of the frame rows
-        frames = {k: (None if k == "rigid_body" else v) for k, v in frames.items()}
-    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames, pool_seam=pool_seam, packed=pool_seam)
+    # (SyntheticGym(packed=True) would hold a frame's tensors in one row for single-copy uploads; measured on B200 it does not
+    # shorten the one-graph e2e rollout and the eager e2e loop got slower, so the bench keeps one dense array per tensor)
+    gym = SyntheticGym(ROBOTS[task], n, cfg.control.decimation, device, frames=frames, pool_seam=pool_seam)
     cls = H.env_class(task)
     return cls(cfg=cfg, sim_params=sp, physics_engine=gym, sim_device=device, headless=True), cfg
 
