@@ -84,3 +84,18 @@ def test_stat_slots_match_header_and_lead_with_the_minibatch_sums():
     for n, v in zip(names, vals):
         assert getattr(_lib, "STAT_" + n) == v, n
     assert [_lib.STAT_KL_SUM, _lib.STAT_SURR_SUM, _lib.STAT_VLOSS_SUM, _lib.STAT_ENT_SUM] == [0, 1, 2, 3]
+
+
+def test_peer_exchange_constants_and_layout_match_header():
+    """The Python mirror of the peer-exchange constants and the buffer layout rsl_rl/peer_exchange.py allocates
+    ([2 halves | result area | publish flags + slice flags]) agree with include/urlg_b200.h; header compiles as plain C."""
+    from unitree_rl_gym_b200 import _lib
+    from unitree_rl_gym_b200.rsl_rl.peer_exchange import _Exchange, _round4
+    w, ver = map(int, _probe('printf("%d %d\\n", URLG_PEER_MAX_WORLD, URLG_ABI_VERSION);'))
+    assert w == _lib.PEER_MAX_WORLD and ver == _lib.ABI_VERSION
+    for n in (1, 4, 380_000, 380_005):
+        c = _round4(n)
+        assert c >= n and c % 4 == 0 and c - n < 4
+        assert _Exchange.floats_needed(c) == 3 * c + 2 * w
+    offs = dict(_lib.PeerExchange._fields_)
+    assert list(offs) == ["world", "rank", "bufs", "flags", "count", "epoch", "ticket", "mode", "reserved"]
